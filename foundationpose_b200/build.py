@@ -1,0 +1,81 @@
+"""In-tree nvcc build of libfpb200.so (sm_100a only).
+
+`python -m foundationpose_b200.build` or `build()`; the .so is git-ignored but travels to the GPU box.
+Geometry translation units are compiled with -fmad=false so their fp32 arithmetic is bit-identical to the
+CPU oracle; the network kernels use the default (fused) arithmetic.
+"""
+import hashlib
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, 'csrc')
+OUT = os.path.join(HERE, 'libfpb200.so')
+OBJ = os.path.join(HERE, 'build')
+
+ARCH = ['-gencode', 'arch=compute_100a,code=sm_100a']
+COMMON = ['-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC,-fvisibility=hidden', '--expt-relaxed-constexpr']
+UNITS = [
+  ('api.cu', []),
+  ('depth.cu', ['-fmad=false']),
+  ('hypo.cu', ['-fmad=false']),
+  ('render.cu', ['-fmad=false']),
+  ('net_ref.cu', []),
+  ('net_tc.cu', []),
+  ('net.cu', []),
+]
+
+
+def _nvcc():
+  for p in (os.environ.get('NVCC'), '/usr/local/cuda/bin/nvcc', 'nvcc'):
+    if p and (os.path.isabs(p) and os.path.exists(p) or not os.path.isabs(p)):
+      return p
+  raise RuntimeError('nvcc not found')
+
+
+def _digest(paths, extra):
+  h = hashlib.sha256(repr(extra).encode())
+  for p in sorted(paths):
+    with open(p, 'rb') as f:
+      h.update(f.read())
+  return h.hexdigest()
+
+
+def build(force=False, verbose=False):
+  os.makedirs(OBJ, exist_ok=True)
+  nvcc = _nvcc()
+  headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(('.cuh', '.h'))]
+  headers.append(os.path.join(HERE, '..', 'include', 'fpb200.h'))
+  objs = []
+  rebuilt = False
+  env = dict(os.environ)
+  env.pop('CC', None); env.pop('CXX', None)
+  for name, flags in UNITS:
+    src = os.path.join(CSRC, name)
+    if not os.path.exists(src):
+      continue
+    obj = os.path.join(OBJ, name.replace('.cu', '.o'))
+    stamp = obj + '.sha'
+    dig = _digest([src] + headers, flags + COMMON + ARCH)
+    if force or not os.path.exists(obj) or not os.path.exists(stamp) or open(stamp).read() != dig:
+      cmd = [nvcc] + ARCH + COMMON + flags + ['-ccbin', '/usr/bin/g++', '-c', src, '-o', obj]
+      if verbose:
+        print(' '.join(cmd), flush=True)
+      r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+      if r.returncode != 0:
+        raise RuntimeError(f'nvcc failed for {name}:\n{r.stdout}\n{r.stderr}')
+      with open(stamp, 'w') as f:
+        f.write(dig)
+      rebuilt = True
+    objs.append(obj)
+  if rebuilt or force or not os.path.exists(OUT):
+    cmd = [nvcc] + ARCH + ['-shared', '-ccbin', '/usr/bin/g++', '-o', OUT] + objs + ['-cudart', 'static']
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    if r.returncode != 0:
+      raise RuntimeError(f'link failed:\n{r.stdout}\n{r.stderr}')
+  return OUT
+
+
+if __name__ == '__main__':
+  print(build(force='--force' in sys.argv, verbose=True))

@@ -1,0 +1,166 @@
+// Hypothesis-side small kernels: cluster_poses, crop windows, pose update.
+// Compiled with -fmad=false (see depth.cu).
+//   cluster_poses                     mycpp/src/app/pybind_api.cpp:24-68, mycpp/src/Utils.cpp:21-26
+//   compute_crop_window_tf_batch      src/Utils.py:577-621
+//   bbox2d_ori / render zoom / mtx    predict_pose_refine.py:44-45, src/Utils.py:159-181
+//   pose update                       predict_pose_refine.py:195-231, src/Utils.py:848-855
+#include "common.cuh"
+
+namespace {
+
+struct K9 { float k[9]; };
+struct P16 { float p[16]; };
+
+// Greedy, order-dependent de-duplication: one CTA; pose i is tested against all kept poses in
+// parallel, the append is serial, so the kept set is identical to the sequential C++ loop.
+__global__ void __launch_bounds__(256) cluster_kernel(const float* __restrict__ poses, int N, const float* __restrict__ sym,
+                                                      int S, float radian_thres, float dist_diff,
+                                                      int32_t* __restrict__ keep, int32_t* __restrict__ n_keep)
+{
+  __shared__ int s_nk;
+  if (threadIdx.x == 0) { s_nk = 1; keep[0] = 0; }
+  __syncthreads();
+  for (int i = 1; i < N; i++) {
+    const float* cur = poses + (size_t)i * 16;
+    const int nk = s_nk;
+    int dup = 0;
+    for (int c = threadIdx.x; c < nk && !dup; c += blockDim.x) {
+      const float* cl = poses + (size_t)keep[c] * 16;
+      float dx = cl[3] - cur[3], dy = cl[7] - cur[7], dz = cl[11] - cur[11];
+      float nrm = sqrtf((dx * dx + dy * dy) + dz * dz);
+      if (nrm >= dist_diff) continue;
+      for (int s = 0; s < S; s++) {
+        const float* tf = sym + (size_t)s * 16;
+        float tr = 0.0f;
+        for (int r = 0; r < 3; r++) {
+          float R1[3];
+          for (int cc = 0; cc < 3; cc++)
+            R1[cc] = ((cur[r * 4 + 0] * tf[0 * 4 + cc] + cur[r * 4 + 1] * tf[1 * 4 + cc]) + cur[r * 4 + 2] * tf[2 * 4 + cc]) +
+                     cur[r * 4 + 3] * tf[3 * 4 + cc];
+          tr += (R1[0] * cl[r * 4 + 0] + R1[1] * cl[r * 4 + 1]) + R1[2] * cl[r * 4 + 2];
+        }
+        float cosv = (float)(((double)tr - 1.0) / 2.0);
+        cosv = fmaxf(fminf(cosv, 1.0f), -1.0f);
+        if (acosf(cosv) < radian_thres) { dup = 1; break; }
+      }
+    }
+    int any = __syncthreads_or(dup);
+    if (threadIdx.x == 0 && !any) { keep[nk] = i; s_nk = nk + 1; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) n_keep[0] = s_nk;
+}
+
+__global__ void crop_params_kernel(const float* __restrict__ poses, int N, K9 K, float radius, int S, int H, int W, P16 P,
+                                   float* __restrict__ params)
+{
+  int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const float* T = poses + (size_t)n * 16;
+  float* o = params + (size_t)n * FPB_CROP_STRIDE;
+  const float tx = T[3], ty = T[7], tz = T[11];
+  float u0 = 0.f, v0 = 0.f, rad = 0.0f;
+  for (int k = 0; k < 5; k++) {
+    float ox = (k == 1) ? radius : (k == 2 ? -radius : 0.0f);
+    float oy = (k == 3) ? radius : (k == 4 ? -radius : 0.0f);
+    float X = tx + ox, Y = ty + oy, Z = tz + 0.0f;
+    float px = (K.k[0] * X + K.k[1] * Y) + K.k[2] * Z;
+    float py = (K.k[3] * X + K.k[4] * Y) + K.k[5] * Z;
+    float pz = (K.k[6] * X + K.k[7] * Y) + K.k[8] * Z;
+    float u = px / pz, v = py / pz;
+    if (k == 0) { u0 = u; v0 = v; }
+    float du = fabsf(u - u0), dv = fabsf(v - v0);
+    if (du > rad) rad = du;
+    if (dv > rad) rad = dv;
+  }
+  float left = rintf(u0 - rad), right = rintf(u0 + rad), top = rintf(v0 - rad), bottom = rintf(v0 + rad);
+  float sx = (float)S / (right - left), sy = (float)S / (bottom - top);
+  float ttx = sx * (-left), tty = sy * (-top);
+  o[0] = sx; o[1] = 0; o[2] = ttx; o[3] = 0; o[4] = sy; o[5] = tty; o[6] = 0; o[7] = 0; o[8] = 1;
+  float i00 = 1.0f / sx, i02 = -(ttx / sx), i11 = 1.0f / sy, i12 = -(tty / sy);
+  float umin = i02, vmin = i12, umax = i00 * (float)(S - 1) + i02, vmax = i11 * (float)(S - 1) + i12;
+  o[9] = umin; o[10] = vmin; o[11] = umax; o[12] = vmax;
+  float l = umin, t = (float)H - vmin, r = umax, b = (float)H - vmax;
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) {
+      float g0 = T[j], g1 = -T[4 + j], g2 = -T[8 + j], g3 = T[12 + j];
+      o[13 + i * 4 + j] = ((P.p[i * 4 + 0] * g0 + P.p[i * 4 + 1] * g1) + P.p[i * 4 + 2] * g2) + P.p[i * 4 + 3] * g3;
+    }
+  o[29] = (float)W / (r - l);
+  o[30] = (float)H / (t - b);
+  o[31] = (((float)W - r) - l) / (r - l);
+  o[32] = (((float)H - t) - b) / (t - b);
+  o[33] = i00; o[34] = i02; o[35] = i11; o[36] = i12;
+  o[37] = 0; o[38] = 0; o[39] = 0;
+}
+
+struct F3 { float v[3]; };
+
+__global__ void pose_update_kernel(const float* __restrict__ poses, const float* __restrict__ trans,
+                                   const float* __restrict__ rot, int N, float radius, float rot_normalizer, F3 tn,
+                                   int normalize_xyz, float* __restrict__ out)
+{
+  int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const float* T = poses + (size_t)n * 16;
+  float td[3], r[3];
+  for (int k = 0; k < 3; k++) {
+    float t = trans[n * 3 + k];
+    td[k] = normalize_xyz ? t * radius : tanhf(t) * tn.v[k];
+    r[k] = tanhf(rot[n * 3 + k]) * rot_normalizer;
+  }
+  // so3_exp_map (pytorch3d, eps 1e-4), then transposed as in predict_pose_refine.py:222
+  float nrm = (r[0] * r[0] + r[1] * r[1]) + r[2] * r[2];
+  float theta = sqrtf(fmaxf(nrm, 1e-4f));
+  float f1 = sinf(theta) / theta;
+  float f2 = (1.0f - cosf(theta)) / (theta * theta);
+  float Km[9] = {0.f, -r[2], r[1], r[2], 0.f, -r[0], -r[1], r[0], 0.f};
+  float K2[9];
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) K2[i * 3 + j] = (Km[i * 3] * Km[j] + Km[i * 3 + 1] * Km[3 + j]) + Km[i * 3 + 2] * Km[6 + j];
+  float R[9];
+  for (int i = 0; i < 9; i++) R[i] = (f1 * Km[i] + f2 * K2[i]) + ((i % 4 == 0) ? 1.0f : 0.0f);
+  float* o = out + (size_t)n * 16;
+  // rot_delta = R^T ; B[:3,:3] = rot_delta @ A[:3,:3]
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) o[i * 4 + j] = (R[0 * 3 + i] * T[0 * 4 + j] + R[1 * 3 + i] * T[1 * 4 + j]) + R[2 * 3 + i] * T[2 * 4 + j];
+  o[3] = T[3] + td[0]; o[7] = T[7] + td[1]; o[11] = T[11] + td[2];
+  o[12] = 0.f; o[13] = 0.f; o[14] = 0.f; o[15] = 1.f;
+}
+
+}  // namespace
+
+FPB_EXPORT int fpb_cluster_poses_f32(const float* poses, int N, const float* sym, int S, float angle_deg, float dist,
+                                     int32_t* out_keep_idx, int32_t* out_n_keep, void* stream)
+{
+  FPB_CHECK_ARG(poses && sym && out_keep_idx && out_n_keep && N > 0 && S > 0);
+  const float radian_thres = (float)((double)angle_deg / 180.0 * 3.14159265358979323846);
+  cluster_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(poses, N, sym, S, radian_thres, dist, out_keep_idx, out_n_keep);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_crop_params(const float* poses, int N, const float* K9_h, float radius, int S, int H, int W,
+                               const float* P16_h, float* params, void* stream)
+{
+  FPB_CHECK_ARG(poses && K9_h && P16_h && params && N > 0 && S > 1 && H > 1 && W > 1);
+  K9 K; P16 P;
+  for (int i = 0; i < 9; i++) K.k[i] = K9_h[i];
+  for (int i = 0; i < 16; i++) P.p[i] = P16_h[i];
+  crop_params_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(poses, N, K, radius, S, H, W, P, params);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_pose_update(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
+                               float rot_normalizer, const float* tn3_h, int normalize_xyz, float* out_poses, void* stream)
+{
+  FPB_CHECK_ARG(poses && trans && rot && out_poses && N > 0);
+  FPB_CHECK_ARG(normalize_xyz || tn3_h);
+  F3 tn = {{0.f, 0.f, 0.f}};
+  if (tn3_h) for (int i = 0; i < 3; i++) tn.v[i] = tn3_h[i];
+  pose_update_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(poses, trans, rot, N, mesh_diameter / 2.0f,
+                                                                       rot_normalizer, tn, normalize_xyz, out_poses);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}

@@ -1,0 +1,62 @@
+// Launch-level interface between net.cu (orchestration) and the kernel translation units
+// net_ref.cu (SIMT fp32 parity kernels + small ops) and net_tc.cu (tcgen05 bf16 implicit GEMM).
+#pragma once
+#include "common.cuh"
+#include <string.h>
+
+// One implicit-GEMM problem:  C[m][n] = epi( sum_k A(m,k) * W[n][k] )
+//   A(m,k): m -> (img, oy, ox) over Ho x Wo outputs; k -> (ky, kx, c) with c fastest;
+//           element = in[((img*Hin + oy*stride-pad+ky)*Win + ox*stride-pad+kx)*pix_pitch + c]  (0 outside)
+//   plain GEMM: Hin=Win=Ho=Wo=1, KH=KW=1, Cin=K, pix_pitch = lda.
+//   W: [Ncols][K] row-major (K contiguous).
+// Batched: blockIdx.z = b;  X_off = (b / b_inner) * X_outer + (b % b_inner) * X_inner   (elements)
+// Epilogue: v = acc*alpha; v = v*scale[n]+shift[n] (scale may be null -> v += shift[n], shift may be null);
+//           v += residual[m*ldr + n]; relu; v += pe[(m % pe_rows)*pe_ld + n];
+//           out[(m % m_split) * ldc + (m / m_split) * split_col_off + n]
+struct GemmProblem {
+  const void* A;      // fp32 (ref) or bf16 (tc)
+  const void* W;      // fp32 (ref) or bf16 (tc)
+  void* C;            // fp32 or bf16 (out_bf16)
+  int M, N, K;
+  int Hin, Win, Cin, Ho, Wo, KH, KW, stride, pad, pix_pitch;
+  int ldw;            // row pitch of W in elements (>= K)
+  int batch, b_inner;
+  long long A_outer, A_inner, W_outer, W_inner, C_outer, C_inner;
+  float alpha;
+  const float* scale;
+  const float* shift;
+  const void* residual;  // same dtype as A-side activations (fp32 ref / bf16 tc)
+  int ldr;
+  int relu;
+  const float* pe;
+  int pe_rows, pe_ld;
+  int ldc, m_split, split_col_off;
+  int out_bf16;
+  int n_valid;        // columns >= n_valid are not stored (N padding)
+};
+
+static inline GemmProblem gemm_problem_default()
+{
+  GemmProblem p;
+  memset(&p, 0, sizeof(p));
+  p.Hin = p.Win = p.Ho = p.Wo = p.KH = p.KW = p.stride = 1;
+  p.batch = 1; p.b_inner = 1;
+  p.alpha = 1.0f;
+  p.m_split = 0x7fffffff;
+  return p;
+}
+
+int ref_gemm(const GemmProblem& p, cudaStream_t st);   // fp32 SIMT
+int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 accumulate
+
+// small ops (fp32 math; io dtype flags)
+int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int cols, int ld_in, int ld_out,
+                 cudaStream_t st);                                     // pad columns [cols, ld_out) written as 0
+int layernorm_rows(const void* x, int x_bf16, const float* gamma, const float* beta, void* out, int out_bf16,
+                   long long rows, int cols, float eps, cudaStream_t st);
+int token_mean(const void* x, int x_bf16, float* out, int groups, int tokens, int cols, cudaStream_t st);
+int small_linear(const float* x, const float* W, const float* b, float* out, int rows, int K, int N,
+                 cudaStream_t st);                                     // out[r][n] = x[r].W[n] + b[n]
+int transpose_v(const void* qkv, void* vt, int is_bf16, int groups, int tokens, int heads, int dh, int ld_qkv, int v_off,
+                int ld_vt, cudaStream_t st);                           // vt[(g*heads+h)][d][t]
+int f32_to_bf16(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st);

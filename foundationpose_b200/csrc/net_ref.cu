@@ -1,0 +1,272 @@
+// SIMT fp32 kernels: the parity-mode implicit GEMM (conv / linear / batched attention products) and the
+// small row-wise ops used by both precision modes (softmax, LayerNorm, token mean, tiny linear, V transpose).
+//   ConvBNReLU / ResnetBasicBlock   learning/models/network_modules.py:37-50, 73-111
+//   TransformerEncoderLayer / MHA   learning/models/refine_network.py:56-70, score_network.py:53-54
+#include "net_kernels.cuh"
+
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16;
+
+// 256 threads, 64x64 tile, 4x4 outputs per thread, fp32 FMA.
+__global__ void __launch_bounds__(256) ref_gemm_kernel(GemmProblem p)
+{
+  __shared__ float As[BK][BM + 4];
+  __shared__ float Bs[BK][BN + 4];
+  const int b = blockIdx.z;
+  const float* A = (const float*)p.A + (long long)(b / p.b_inner) * p.A_outer + (long long)(b % p.b_inner) * p.A_inner;
+  const float* W = (const float*)p.W + (long long)(b / p.b_inner) * p.W_outer + (long long)(b % p.b_inner) * p.W_inner;
+  const long long c_off = (long long)(b / p.b_inner) * p.C_outer + (long long)(b % p.b_inner) * p.C_inner;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int tid = threadIdx.x;
+  const int lr = tid >> 2, lk = (tid & 3) * 4;   // loader: row 0..63, k offset 0,4,8,12
+  // decode the A row handled by this loader thread
+  const int m = m0 + lr;
+  int img = 0, oy = 0, ox = 0;
+  const bool mrow_ok = m < p.M;
+  if (mrow_ok) {
+    const int hw = p.Ho * p.Wo;
+    img = m / hw;
+    const int r = m - img * hw;
+    oy = r / p.Wo; ox = r - oy * p.Wo;
+  }
+  const int wn = n0 + lr;
+  const bool wrow_ok = wn < p.N;
+  const int ty = tid >> 4, tx = tid & 15;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j] = 0.0f;
+
+  for (int k0 = 0; k0 < p.K; k0 += BK) {
+    const int k = k0 + lk;
+    float4 av = make_float4(0.f, 0.f, 0.f, 0.f), wv = av;
+    if (mrow_ok && k < p.K) {
+      const int tap = k / p.Cin, c = k - tap * p.Cin;
+      const int ky = tap / p.KW, kx = tap - ky * p.KW;
+      const int iy = oy * p.stride - p.pad + ky, ix = ox * p.stride - p.pad + kx;
+      if (iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win)
+        av = *reinterpret_cast<const float4*>(A + ((long long)(img * p.Hin + iy) * p.Win + ix) * p.pix_pitch + c);
+    }
+    if (wrow_ok && k < p.K) wv = *reinterpret_cast<const float4*>(W + (long long)wn * p.ldw + k);
+    As[lk + 0][lr] = av.x; As[lk + 1][lr] = av.y; As[lk + 2][lr] = av.z; As[lk + 3][lr] = av.w;
+    Bs[lk + 0][lr] = wv.x; Bs[lk + 1][lr] = wv.y; Bs[lk + 2][lr] = wv.z; Bs[lk + 3][lr] = wv.w;
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; kk++) {
+      float a[4], w[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) { a[i] = As[kk][ty * 4 + i]; w[i] = Bs[kk][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  const int nst = p.n_valid > 0 ? p.n_valid : p.N;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int mm = m0 + ty * 4 + i;
+    if (mm >= p.M) continue;
+    const long long orow = (long long)(mm % p.m_split) * p.ldc + (long long)(mm / p.m_split) * p.split_col_off + c_off;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int nn = n0 + tx * 4 + j;
+      if (nn >= nst) continue;
+      float v = acc[i][j] * p.alpha;
+      if (p.scale) v = v * p.scale[nn] + (p.shift ? p.shift[nn] : 0.0f);
+      else if (p.shift) v += p.shift[nn];
+      if (p.residual) v += ((const float*)p.residual)[(long long)mm * p.ldr + nn];
+      if (p.relu) v = fmaxf(v, 0.0f);
+      if (p.pe) v += p.pe[(long long)(mm % p.pe_rows) * p.pe_ld + nn];
+      if (p.out_bf16) ((__nv_bfloat16*)p.C)[orow + nn] = __float2bfloat16(v);
+      else ((float*)p.C)[orow + nn] = v;
+    }
+  }
+}
+
+__device__ __forceinline__ float warp_sum(float v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// one warp per row
+__global__ void __launch_bounds__(256) softmax_kernel(const float* __restrict__ in, void* __restrict__ out, int out_bf16,
+                                                      long long rows, int cols, int ld_in, int ld_out)
+{
+  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float* x = in + row * ld_in;
+  float mx = -INFINITY;
+  for (int c = lane; c < cols; c += 32) mx = fmaxf(mx, x[c]);
+  mx = warp_max(mx);
+  float s = 0.0f;
+  for (int c = lane; c < cols; c += 32) s += __expf(x[c] - mx);
+  s = warp_sum(s);
+  const float inv = 1.0f / s;
+  for (int c = lane; c < ld_out; c += 32) {
+    float v = c < cols ? __expf(x[c] - mx) * inv : 0.0f;
+    if (out_bf16) ((__nv_bfloat16*)out)[row * ld_out + c] = __float2bfloat16(v);
+    else ((float*)out)[row * ld_out + c] = v;
+  }
+}
+
+template <bool XBF>
+__global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__ x_, const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, void* __restrict__ out,
+                                                        int out_bf16, long long rows, int cols, float eps)
+{
+  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  auto ld = [&](int c) -> float {
+    if (XBF) return __bfloat162float(((const __nv_bfloat16*)x_)[row * cols + c]);
+    return ((const float*)x_)[row * cols + c];
+  };
+  float s = 0.0f;
+  for (int c = lane; c < cols; c += 32) s += ld(c);
+  const float mean = warp_sum(s) / (float)cols;
+  float v = 0.0f;
+  for (int c = lane; c < cols; c += 32) { float d = ld(c) - mean; v += d * d; }
+  const float rstd = rsqrtf(warp_sum(v) / (float)cols + eps);
+  for (int c = lane; c < cols; c += 32) {
+    float y = (ld(c) - mean) * rstd * gamma[c] + beta[c];
+    if (out_bf16) ((__nv_bfloat16*)out)[row * cols + c] = __float2bfloat16(y);
+    else ((float*)out)[row * cols + c] = y;
+  }
+}
+
+// out[g][c] = mean_t x[g][t][c]; one block per (g, 64-column slab), 256 threads = 4 token lanes x 64 cols
+template <bool XBF>
+__global__ void __launch_bounds__(256) token_mean_kernel(const void* __restrict__ x_, float* __restrict__ out, int tokens,
+                                                         int cols)
+{
+  __shared__ float part[4][64];
+  const int g = blockIdx.x, c = blockIdx.y * 64 + (threadIdx.x & 63), tl = threadIdx.x >> 6;
+  float s = 0.0f;
+  if (c < cols)
+    for (int t = tl; t < tokens; t += 4) {
+      const long long i = ((long long)g * tokens + t) * cols + c;
+      s += XBF ? __bfloat162float(((const __nv_bfloat16*)x_)[i]) : ((const float*)x_)[i];
+    }
+  part[tl][threadIdx.x & 63] = s;
+  __syncthreads();
+  if (tl == 0 && c < cols)
+    out[(long long)g * cols + c] = (((part[0][threadIdx.x] + part[1][threadIdx.x]) + part[2][threadIdx.x]) + part[3][threadIdx.x]) / (float)tokens;
+}
+
+// one warp per output element
+__global__ void __launch_bounds__(256) small_linear_kernel(const float* __restrict__ x, const float* __restrict__ W,
+                                                           const float* __restrict__ b, float* __restrict__ out, int rows,
+                                                           int K, int N)
+{
+  const long long o = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (o >= (long long)rows * N) return;
+  const int r = (int)(o / N), n = (int)(o % N);
+  float s = 0.0f;
+  for (int k = lane; k < K; k += 32) s = fmaf(x[(long long)r * K + k], W[(long long)n * K + k], s);
+  s = warp_sum(s);
+  if (lane == 0) out[o] = s + (b ? b[n] : 0.0f);
+}
+
+// vt[(g*heads+h)][d][t] = qkv[(g*tokens+t)][v_off + h*dh + d]; pad columns [tokens, ld_vt) are zeroed
+template <typename T>
+__global__ void __launch_bounds__(256) transpose_v_kernel(const T* __restrict__ qkv, T* __restrict__ vt, int tokens,
+                                                          int heads, int dh, int ld_qkv, int v_off, int ld_vt)
+{
+  __shared__ T tile[32][33];
+  const int gh = blockIdx.z, g = gh / heads, h = gh % heads;
+  const int t0 = blockIdx.x * 32, d0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  for (int i = ty; i < 32; i += 8) {
+    const int t = t0 + i, d = d0 + tx;
+    tile[i][tx] = (t < tokens && d < dh) ? qkv[((long long)g * tokens + t) * ld_qkv + v_off + h * dh + d]
+                                          : T(0.0f);
+  }
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) {
+    const int d = d0 + i, t = t0 + tx;
+    if (d < dh && t < ld_vt) vt[((long long)gh * dh + d) * ld_vt + t] = tile[tx][i];
+  }
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n)
+{
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = __float2bfloat16(in[i]);
+}
+
+}  // namespace
+
+int ref_gemm(const GemmProblem& p, cudaStream_t st)
+{
+  FPB_CHECK_ARG(p.A && p.W && p.C && p.M > 0 && p.N > 0 && p.K > 0 && p.K % 4 == 0 && p.Cin % 4 == 0);
+  dim3 grid(fpb_cdiv(p.M, BM), fpb_cdiv(p.N, BN), p.batch);
+  ref_gemm_kernel<<<grid, 256, 0, st>>>(p);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int cols, int ld_in, int ld_out, cudaStream_t st)
+{
+  softmax_kernel<<<fpb_cdiv(rows, 8), 256, 0, st>>>(in, out, out_bf16, rows, cols, ld_in, ld_out);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+int layernorm_rows(const void* x, int x_bf16, const float* gamma, const float* beta, void* out, int out_bf16,
+                   long long rows, int cols, float eps, cudaStream_t st)
+{
+  if (x_bf16) layernorm_kernel<true><<<fpb_cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, out, out_bf16, rows, cols, eps);
+  else layernorm_kernel<false><<<fpb_cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, out, out_bf16, rows, cols, eps);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+int token_mean(const void* x, int x_bf16, float* out, int groups, int tokens, int cols, cudaStream_t st)
+{
+  dim3 grid(groups, fpb_cdiv(cols, 64));
+  if (x_bf16) token_mean_kernel<true><<<grid, 256, 0, st>>>(x, out, tokens, cols);
+  else token_mean_kernel<false><<<grid, 256, 0, st>>>(x, out, tokens, cols);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+int small_linear(const float* x, const float* W, const float* b, float* out, int rows, int K, int N, cudaStream_t st)
+{
+  small_linear_kernel<<<fpb_cdiv((long long)rows * N, 8), 256, 0, st>>>(x, W, b, out, rows, K, N);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+int transpose_v(const void* qkv, void* vt, int is_bf16, int groups, int tokens, int heads, int dh, int ld_qkv, int v_off,
+                int ld_vt, cudaStream_t st)
+{
+  dim3 grid(fpb_cdiv(ld_vt, 32), fpb_cdiv(dh, 32), groups * heads);
+  if (is_bf16)
+    transpose_v_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)qkv, (__nv_bfloat16*)vt, tokens, heads,
+                                                             dh, ld_qkv, v_off, ld_vt);
+  else
+    transpose_v_kernel<float><<<grid, 256, 0, st>>>((const float*)qkv, (float*)vt, tokens, heads, dh, ld_qkv, v_off, ld_vt);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+int f32_to_bf16(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st)
+{
+  f32_to_bf16_kernel<<<fpb_cdiv(n, 256), 256, 0, st>>>(in, out, n);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}

@@ -1,0 +1,494 @@
+// Batched mesh rasteriser with fused shading (network input A) and the fused
+// crop / perspective-warp of the observed frame (network input B).
+// Compiled with -fmad=false: arithmetic is bit-identical to oracle/fp_oracle.c.
+//   nvdiffrast_render                 src/Utils.py:133-219 (+ :752-802 projection)
+//   make_crop_data_batch (refiner)    learning/training/predict_pose_refine.py:26-89
+//   make_crop_data_batch (scorer)     learning/training/predict_score.py:57-114
+//   transform_batch                   learning/datasets/h5_dataset.py:79-127, 137-179
+//
+// Design: all N hypotheses in one launch per stage.
+//   1. vertex kernel   (N x V threads)  clip-space xyzw + camera xyz + diffuse term  -> L2-resident scratch
+//   2. raster kernel   (N x F threads)  1/16-px snapped integer coverage; 64-bit (z/w | face) atomicMin
+//                                       z-buffer; big triangles are re-distributed over the warp
+//   3. shade kernel    (N x S x S)      barycentrics -> xyz / colour|texture / lighting -> normalised
+//                                       8-channel NHWC pixel, one 128-bit store (bf16) per pixel
+#include "common.cuh"
+
+struct fpb_mesh {
+  int V, F, Vt, Ht, Wt;
+  float* pos;       // [V,3]
+  float* vnormals;  // [V,3]
+  int32_t* faces;   // [F,3]
+  float* vcolor;    // [V,3] or null
+  float* uv;        // [Vt,2] or null
+  int32_t* uv_idx;  // [F,3] or null
+  float* tex;       // [Ht,Wt,3] or null
+};
+
+namespace {
+
+__device__ __forceinline__ uint32_t f2ord(float f)
+{
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__device__ __forceinline__ void bary_zw(const float4 c0, const float4 c1, const float4 c2, float fx, float fy, float& b0,
+                                        float& b1, float& zw)
+{
+  float p0x = c0.x - fx * c0.w, p0y = c0.y - fy * c0.w;
+  float p1x = c1.x - fx * c1.w, p1y = c1.y - fy * c1.w;
+  float p2x = c2.x - fx * c2.w, p2y = c2.y - fy * c2.w;
+  float a0 = p1x * p2y - p1y * p2x;
+  float a1 = p2x * p0y - p2y * p0x;
+  float a2 = p0x * p1y - p0y * p1x;
+  float iw = 1.0f / ((a0 + a1) + a2);
+  float z = (c0.z * a0 + c1.z * a1) + c2.z * a2;
+  float w = (c0.w * a0 + c1.w * a1) + c2.w * a2;
+  b0 = fminf(fmaxf(a0 * iw, 0.0f), 1.0f);
+  b1 = fminf(fmaxf(a1 * iw, 0.0f), 1.0f);
+  zw = fminf(fmaxf(z / w, -1.0f), 1.0f);
+}
+
+__global__ void __launch_bounds__(256) vertex_kernel(const float* __restrict__ pos, const float* __restrict__ vnormals, int V,
+                                                     const float* __restrict__ poses, const float* __restrict__ params,
+                                                     float4* __restrict__ clip, float4* __restrict__ camd)
+{
+  const int n = blockIdx.y;
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float sT[16], sM[16], sR[4];
+  if (threadIdx.x < 16) {
+    sT[threadIdx.x] = poses[(size_t)n * 16 + threadIdx.x];
+    sM[threadIdx.x] = params[(size_t)n * FPB_CROP_STRIDE + 13 + threadIdx.x];
+  }
+  if (threadIdx.x < 4) sR[threadIdx.x] = params[(size_t)n * FPB_CROP_STRIDE + 29 + threadIdx.x];
+  __syncthreads();
+  if (v >= V) return;
+  const float x = pos[v * 3], y = pos[v * 3 + 1], z = pos[v * 3 + 2];
+  float c[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) c[j] = ((sM[j * 4] * x + sM[j * 4 + 1] * y) + sM[j * 4 + 2] * z) + sM[j * 4 + 3];
+  float4 cl;
+  cl.x = c[0] * sR[0] + c[3] * sR[2];
+  cl.y = c[1] * sR[1] + c[3] * sR[3];
+  cl.z = c[2];
+  cl.w = c[3];
+  float cam[3], cn[3];
+  const float nx = vnormals[v * 3], ny = vnormals[v * 3 + 1], nz = vnormals[v * 3 + 2];
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    cam[j] = ((sT[j * 4] * x + sT[j * 4 + 1] * y) + sT[j * 4 + 2] * z) + sT[j * 4 + 3];
+    cn[j] = (sT[j * 4] * nx + sT[j * 4 + 1] * ny) + sT[j * 4 + 2] * nz;
+  }
+  float nrm = sqrtf((cn[0] * cn[0] + cn[1] * cn[1]) + cn[2] * cn[2]);
+  float d = -(cn[2] / fmaxf(nrm, 1e-12f));
+  d = fminf(fmaxf(d, 0.0f), 1.0f);
+  clip[(size_t)n * V + v] = cl;
+  camd[(size_t)n * V + v] = make_float4(cam[0], cam[1], cam[2], d);
+}
+
+struct TriSetup {
+  long long X[3], Y[3];
+  int px0, px1, py0, py1;
+  int ok;
+};
+
+__device__ __forceinline__ long long floordiv16(long long a) { return a >> 4; }
+__device__ __forceinline__ long long ceildiv16(long long a) { return -((-a) >> 4); }
+
+__device__ __forceinline__ void tri_setup(const float4 c0, const float4 c1, const float4 c2, int S, TriSetup& t)
+{
+  t.ok = 0;
+  if (!(c0.w > 0.0f && c1.w > 0.0f && c2.w > 0.0f)) return;
+  const float sub = (float)(8 * S);
+  const float4 cc[3] = {c0, c1, c2};
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    float sx = (cc[k].x / cc[k].w) * sub + sub;
+    float sy = (cc[k].y / cc[k].w) * sub + sub;
+    if (!(fabsf(sx) < 1073741824.0f) || !(fabsf(sy) < 1073741824.0f)) return;
+    t.X[k] = (long long)rintf(sx);
+    t.Y[k] = (long long)rintf(sy);
+  }
+  long long area = (t.X[1] - t.X[0]) * (t.Y[2] - t.Y[0]) - (t.Y[1] - t.Y[0]) * (t.X[2] - t.X[0]);
+  if (area == 0) return;
+  if (area < 0) {  // orient for the coverage test only
+    long long tx = t.X[1], ty = t.Y[1];
+    t.X[1] = t.X[2]; t.Y[1] = t.Y[2]; t.X[2] = tx; t.Y[2] = ty;
+  }
+  long long xmin = min(t.X[0], min(t.X[1], t.X[2])), xmax = max(t.X[0], max(t.X[1], t.X[2]));
+  long long ymin = min(t.Y[0], min(t.Y[1], t.Y[2])), ymax = max(t.Y[0], max(t.Y[1], t.Y[2]));
+  long long px0 = max(0LL, ceildiv16(xmin - 8)), px1 = min((long long)(S - 1), floordiv16(xmax - 8));
+  long long py0 = max(0LL, ceildiv16(ymin - 8)), py1 = min((long long)(S - 1), floordiv16(ymax - 8));
+  if (px0 > px1 || py0 > py1) return;
+  t.px0 = (int)px0; t.px1 = (int)px1; t.py0 = (int)py0; t.py1 = (int)py1;
+  t.ok = 1;
+}
+
+__device__ __forceinline__ bool covers(const TriSetup& t, int px, int py)
+{
+  const long long cx = 16LL * px + 8, cy = 16LL * py + 8;
+#pragma unroll
+  for (int e = 0; e < 3; e++) {
+    const int a = e, b = (e + 1) % 3;
+    long long dx = t.X[b] - t.X[a], dy = t.Y[b] - t.Y[a];
+    long long E = dx * (cy - t.Y[a]) - dy * (cx - t.X[a]);
+    if (E < 0) return false;
+    if (E == 0 && !(dy > 0 || (dy == 0 && dx < 0))) return false;
+  }
+  return true;
+}
+
+__device__ __forceinline__ void raster_pixel(const TriSetup& t, const float4 c0, const float4 c1, const float4 c2, int px,
+                                             int py, int S, uint32_t face, unsigned long long* zb)
+{
+  if (!covers(t, px, py)) return;
+  const float xs = 2.0f / (float)S, xo = 1.0f / (float)S - 1.0f;
+  float fx = (float)px * xs + xo, fy = (float)py * xs + xo;
+  float b0, b1, zw;
+  bary_zw(c0, c1, c2, fx, fy, b0, b1, zw);
+  if (zw != zw) return;
+  unsigned long long key = ((unsigned long long)f2ord(zw) << 32) | face;
+  atomicMin(zb + (size_t)py * S + px, key);
+}
+
+constexpr int SMALL_TRI_PIXELS = 16;
+
+__global__ void __launch_bounds__(256) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
+                                                     const float4* __restrict__ clip, int S,
+                                                     unsigned long long* __restrict__ zbuf)
+{
+  const int n = blockIdx.y;
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  unsigned long long* zb = zbuf + (size_t)n * S * S;
+  const float4* cl = clip + (size_t)n * V;
+  TriSetup t;
+  t.ok = 0;
+  float4 c0 = make_float4(0, 0, 0, 0), c1 = c0, c2 = c0;
+  if (f < F) {
+    c0 = cl[faces[f * 3]]; c1 = cl[faces[f * 3 + 1]]; c2 = cl[faces[f * 3 + 2]];
+    tri_setup(c0, c1, c2, S, t);
+  }
+  int big = 0;
+  if (t.ok) {
+    int npx = (t.px1 - t.px0 + 1) * (t.py1 - t.py0 + 1);
+    if (npx <= SMALL_TRI_PIXELS) {
+      for (int py = t.py0; py <= t.py1; py++)
+        for (int px = t.px0; px <= t.px1; px++) raster_pixel(t, c0, c1, c2, px, py, S, (uint32_t)f, zb);
+    } else {
+      big = 1;
+    }
+  }
+  // triangles with a large footprint: the whole warp sweeps the bounding box together
+  unsigned m = __ballot_sync(0xffffffffu, big);
+  while (m) {
+    const int src = __ffs(m) - 1;
+    m &= m - 1;
+    TriSetup s;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      s.X[k] = __shfl_sync(0xffffffffu, t.X[k], src);
+      s.Y[k] = __shfl_sync(0xffffffffu, t.Y[k], src);
+    }
+    s.px0 = __shfl_sync(0xffffffffu, t.px0, src); s.px1 = __shfl_sync(0xffffffffu, t.px1, src);
+    s.py0 = __shfl_sync(0xffffffffu, t.py0, src); s.py1 = __shfl_sync(0xffffffffu, t.py1, src);
+    float4 d0, d1, d2;
+    d0.x = __shfl_sync(0xffffffffu, c0.x, src); d0.y = __shfl_sync(0xffffffffu, c0.y, src);
+    d0.z = __shfl_sync(0xffffffffu, c0.z, src); d0.w = __shfl_sync(0xffffffffu, c0.w, src);
+    d1.x = __shfl_sync(0xffffffffu, c1.x, src); d1.y = __shfl_sync(0xffffffffu, c1.y, src);
+    d1.z = __shfl_sync(0xffffffffu, c1.z, src); d1.w = __shfl_sync(0xffffffffu, c1.w, src);
+    d2.x = __shfl_sync(0xffffffffu, c2.x, src); d2.y = __shfl_sync(0xffffffffu, c2.y, src);
+    d2.z = __shfl_sync(0xffffffffu, c2.z, src); d2.w = __shfl_sync(0xffffffffu, c2.w, src);
+    const uint32_t face = (uint32_t)(f - lane + src);
+    const int bw = s.px1 - s.px0 + 1, tot = bw * (s.py1 - s.py0 + 1);
+    for (int i = lane; i < tot; i += 32) {
+      int py = s.py0 + i / bw, px = s.px0 + i % bw;
+      raster_pixel(s, d0, d1, d2, px, py, S, face, zb);
+    }
+  }
+}
+
+__device__ __forceinline__ void xyz_norm(const float xyz[3], const float* T, float inv_radius, float zthr, float o[3])
+{
+  const bool inv = xyz[2] < zthr;
+  const float t[3] = {T[3], T[7], T[11]};
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    float x = (xyz[k] - t[k]) * inv_radius;
+    o[k] = (inv || fabsf(x) >= 2.0f) ? 0.0f : x;
+  }
+}
+
+template <bool BF16>
+__device__ __forceinline__ void store_px8(void* base, size_t pix, const float v[6])
+{
+  if (BF16) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]),
+                   c = __floats2bfloat162_rn(v[4], v[5]);
+    uint4 q;
+    q.x = *reinterpret_cast<uint32_t*>(&a); q.y = *reinterpret_cast<uint32_t*>(&b);
+    q.z = *reinterpret_cast<uint32_t*>(&c); q.w = 0u;
+    reinterpret_cast<uint4*>(base)[pix] = q;
+  } else {
+    float4* p = reinterpret_cast<float4*>(base) + pix * 2;
+    p[0] = make_float4(v[0], v[1], v[2], v[3]);
+    p[1] = make_float4(v[4], v[5], 0.0f, 0.0f);
+  }
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4* __restrict__ clip,
+                                                    const float4* __restrict__ camd,
+                                                    const unsigned long long* __restrict__ zbuf,
+                                                    const float* __restrict__ poses, int N, int S, float inv_radius,
+                                                    float zthr, void* __restrict__ outA, float* __restrict__ out_color,
+                                                    float* __restrict__ out_xyz, int32_t* __restrict__ out_tri)
+{
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t total = (size_t)N * S * S;
+  if (idx >= total) return;
+  const int n = (int)(idx / ((size_t)S * S));
+  const int rem = (int)(idx - (size_t)n * S * S);
+  const int i = rem / S, j = rem - i * S;
+  const int py = S - 1 - i, px = j;  // row flip (src/Utils.py:197,216-218)
+  const unsigned long long key = zbuf[(size_t)n * S * S + (size_t)py * S + px];
+  float col[3] = {0.f, 0.f, 0.f}, xyz[3] = {0.f, 0.f, 0.f};
+  int tri = 0;
+  if (key != ~0ull) {
+    const int f = (int)(uint32_t)(key & 0xffffffffu);
+    const int i0 = mesh.faces[f * 3], i1 = mesh.faces[f * 3 + 1], i2 = mesh.faces[f * 3 + 2];
+    const float4* cl = clip + (size_t)n * mesh.V;
+    const float4* cd = camd + (size_t)n * mesh.V;
+    const float xs = 2.0f / (float)S, xo = 1.0f / (float)S - 1.0f;
+    float fx = (float)px * xs + xo, fy = (float)py * xs + xo;
+    float b0, b1, zw;
+    bary_zw(cl[i0], cl[i1], cl[i2], fx, fy, b0, b1, zw);
+    const float b2 = (1.0f - b0) - b1;
+    const float4 q0 = cd[i0], q1 = cd[i1], q2 = cd[i2];
+    xyz[0] = (b0 * q0.x + b1 * q1.x) + b2 * q2.x;
+    xyz[1] = (b0 * q0.y + b1 * q1.y) + b2 * q2.y;
+    xyz[2] = (b0 * q0.z + b1 * q1.z) + b2 * q2.z;
+    const float dm = (b0 * q0.w + b1 * q1.w) + b2 * q2.w;
+    float c[3];
+    if (mesh.tex) {
+      const int t0 = mesh.uv_idx[f * 3], t1 = mesh.uv_idx[f * 3 + 1], t2 = mesh.uv_idx[f * 3 + 2];
+      float tu = (b0 * mesh.uv[t0 * 2] + b1 * mesh.uv[t1 * 2]) + b2 * mesh.uv[t2 * 2];
+      float tv = (b0 * mesh.uv[t0 * 2 + 1] + b1 * mesh.uv[t1 * 2 + 1]) + b2 * mesh.uv[t2 * 2 + 1];
+      float u = tu * (float)mesh.Wt - 0.5f, v = tv * (float)mesh.Ht - 0.5f;
+      float uf = floorf(u), vf = floorf(v);
+      float du = u - uf, dv = v - vf;
+      int iu0 = (int)uf, iv0 = (int)vf, iu1 = iu0 + 1, iv1 = iv0 + 1;
+      const int Wt = mesh.Wt, Ht = mesh.Ht;
+      iu0 = ((iu0 % Wt) + Wt) % Wt; iu1 = ((iu1 % Wt) + Wt) % Wt;
+      iv0 = ((iv0 % Ht) + Ht) % Ht; iv1 = ((iv1 % Ht) + Ht) % Ht;
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        float a00 = mesh.tex[(iv0 * Wt + iu0) * 3 + k], a10 = mesh.tex[(iv0 * Wt + iu1) * 3 + k];
+        float a01 = mesh.tex[(iv1 * Wt + iu0) * 3 + k], a11 = mesh.tex[(iv1 * Wt + iu1) * 3 + k];
+        float top = a00 + du * (a10 - a00), bot = a01 + du * (a11 - a01);
+        c[k] = top + dv * (bot - top);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 3; k++)
+        c[k] = (b0 * mesh.vcolor[i0 * 3 + k] + b1 * mesh.vcolor[i1 * 3 + k]) + b2 * mesh.vcolor[i2 * 3 + k];
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      float cv = c[k] * 0.8f + (dm * c[k]) * 0.5f;
+      col[k] = fminf(fmaxf(cv, 0.0f), 1.0f);
+    }
+    tri = f + 1;
+  }
+  if (out_color) { out_color[idx * 3] = col[0]; out_color[idx * 3 + 1] = col[1]; out_color[idx * 3 + 2] = col[2]; }
+  if (out_xyz) { out_xyz[idx * 3] = xyz[0]; out_xyz[idx * 3 + 1] = xyz[1]; out_xyz[idx * 3 + 2] = xyz[2]; }
+  if (out_tri) out_tri[idx] = tri;
+  float v6[6];
+#pragma unroll
+  for (int k = 0; k < 3; k++) v6[k] = (col[k] * 255.0f) / 255.0f;
+  xyz_norm(xyz, poses + (size_t)n * 16, inv_radius, zthr, v6 + 3);
+  store_px8<BF16>(outA, idx, v6);
+}
+
+__device__ __forceinline__ int nearest_src(float p, float scale, int size)
+{
+  float r = nearbyintf(p * scale - 0.5f);
+  if (!(r >= 0.0f && r <= (float)(size - 1))) return -1;
+  return (int)r;
+}
+
+struct K9f { float k[9]; };
+
+template <bool BF16, bool U8>
+__global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_, const float* __restrict__ xyz_map,
+                                                   const float* __restrict__ depth, int H, int W,
+                                                   const float* __restrict__ poses, const float* __restrict__ params, K9f K,
+                                                   int N, int S, float inv_radius, int mode, void* __restrict__ outB)
+{
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t total = (size_t)N * S * S;
+  if (idx >= total) return;
+  const int n = (int)(idx / ((size_t)S * S));
+  const int rem = (int)(idx - (size_t)n * S * S);
+  const int i = rem / S, j = rem - i * S;
+  const float* pr = params + (size_t)n * FPB_CROP_STRIDE;
+  const float i00 = pr[33], i02 = pr[34], i11 = pr[35], i12 = pr[36];
+  const float wsc = (float)W / (float)(W - 1), hsc = (float)H / (float)(H - 1), ssc = (float)S / (float)(S - 1);
+  const float zthr = mode ? 0.1f : 0.001f;
+  const float px = (float)j * i00 + i02, py = (float)i * i11 + i12;
+  float v6[6];
+  {
+    const float ix = px * wsc - 0.5f, iy = py * hsc - 0.5f;
+    const float x0 = floorf(ix), y0 = floorf(iy), x1 = x0 + 1.0f, y1 = y0 + 1.0f;
+    const float wnw = (x1 - ix) * (y1 - iy), wne = (ix - x0) * (y1 - iy);
+    const float wsw = (x1 - ix) * (iy - y0), wse = (ix - x0) * (iy - y0);
+    const bool inx0 = x0 >= 0.0f && x0 <= (float)(W - 1), inx1 = x1 >= 0.0f && x1 <= (float)(W - 1);
+    const bool iny0 = y0 >= 0.0f && y0 <= (float)(H - 1), iny1 = y1 >= 0.0f && y1 <= (float)(H - 1);
+    auto tap = [&](float yy, float xx, int k) -> float {
+      size_t o = ((size_t)(int)yy * W + (int)xx) * 3 + k;
+      if (U8) return (float)reinterpret_cast<const uint8_t*>(rgb_)[o];
+      return reinterpret_cast<const float*>(rgb_)[o];
+    };
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      float acc = 0.0f;
+      if (inx0 && iny0) acc += tap(y0, x0, k) * wnw;
+      if (inx1 && iny0) acc += tap(y0, x1, k) * wne;
+      if (inx0 && iny1) acc += tap(y1, x0, k) * wsw;
+      if (inx1 && iny1) acc += tap(y1, x1, k) * wse;
+      v6[k] = acc / 255.0f;
+    }
+  }
+  float xyz[3] = {0.f, 0.f, 0.f};
+  const int u = nearest_src(px, wsc, W), v = nearest_src(py, hsc, H);
+  if (u >= 0 && v >= 0) {
+    if (mode == 0) {
+      const float* s = xyz_map + ((size_t)v * W + u) * 3;
+      xyz[0] = s[0]; xyz[1] = s[1]; xyz[2] = s[2];
+    } else {
+      const float qx = pr[0] * (float)u + pr[2], qy = pr[4] * (float)v + pr[5];
+      const int j2 = nearest_src(qx, ssc, S), i2 = nearest_src(qy, ssc, S);
+      if (j2 >= 0 && i2 >= 0) {
+        const float px1 = (float)j2 * i00 + i02, py1 = (float)i2 * i11 + i12;
+        const int u1 = nearest_src(px1, wsc, W), v1 = nearest_src(py1, hsc, H);
+        if (u1 >= 0 && v1 >= 0) {
+          const float z = depth[(size_t)v1 * W + u1];
+          if (!(z < 0.001f)) {
+            xyz[0] = ((float)u - K.k[2]) * z / K.k[0];
+            xyz[1] = ((float)v - K.k[5]) * z / K.k[4];
+            xyz[2] = z;
+          }
+        }
+      }
+    }
+  }
+  xyz_norm(xyz, poses + (size_t)n * 16, inv_radius, zthr, v6 + 3);
+  store_px8<BF16>(outB, idx, v6);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+static int dev_copy(T** dst, const T* src, size_t count, cudaStream_t st)
+{
+  *dst = nullptr;
+  if (!src || count == 0) return FPB_OK;
+  FPB_CUDA(cudaMalloc((void**)dst, count * sizeof(T)));
+  FPB_CUDA(cudaMemcpyAsync(*dst, src, count * sizeof(T), cudaMemcpyDeviceToDevice, st));
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_mesh_create(fpb_mesh** out, const float* pos, const float* vnormals, int V, const int32_t* faces, int F,
+                               const float* vcolor, const float* uv, int Vt, const int32_t* uv_idx, const float* tex,
+                               int Ht, int Wt, void* stream)
+{
+  FPB_CHECK_ARG(out && pos && vnormals && faces && V > 0 && F > 0);
+  FPB_CHECK_ARG((vcolor != nullptr) != (tex != nullptr));
+  FPB_CHECK_ARG(!tex || (uv && uv_idx && Vt > 0 && Ht > 0 && Wt > 0));
+  cudaStream_t st = (cudaStream_t)stream;
+  fpb_mesh* m = new fpb_mesh();
+  m->V = V; m->F = F; m->Vt = Vt; m->Ht = Ht; m->Wt = Wt;
+  int rc = FPB_OK;
+  if ((rc = dev_copy(&m->pos, pos, (size_t)V * 3, st))) goto fail;
+  if ((rc = dev_copy(&m->vnormals, vnormals, (size_t)V * 3, st))) goto fail;
+  if ((rc = dev_copy(&m->faces, faces, (size_t)F * 3, st))) goto fail;
+  if ((rc = dev_copy(&m->vcolor, vcolor, (size_t)V * 3, st))) goto fail;
+  if ((rc = dev_copy(&m->uv, uv, tex ? (size_t)Vt * 2 : 0, st))) goto fail;
+  if ((rc = dev_copy(&m->uv_idx, uv_idx, tex ? (size_t)F * 3 : 0, st))) goto fail;
+  if ((rc = dev_copy(&m->tex, tex, tex ? (size_t)Ht * Wt * 3 : 0, st))) goto fail;
+  FPB_CUDA(cudaStreamSynchronize(st));
+  *out = m;
+  return FPB_OK;
+fail:
+  fpb_mesh_destroy(m);
+  return rc;
+}
+
+FPB_EXPORT int fpb_mesh_destroy(fpb_mesh* m)
+{
+  if (!m) return FPB_OK;
+  cudaFree(m->pos); cudaFree(m->vnormals); cudaFree(m->faces); cudaFree(m->vcolor);
+  cudaFree(m->uv); cudaFree(m->uv_idx); cudaFree(m->tex);
+  delete m;
+  return FPB_OK;
+}
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+FPB_EXPORT size_t fpb_render_ws_bytes(int N, int V, int S)
+{
+  return 2 * align256((size_t)N * V * sizeof(float4)) + align256((size_t)N * S * S * sizeof(unsigned long long));
+}
+
+FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
+                                float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, float* out_color,
+                                float* out_xyz, int32_t* out_tri, void* stream)
+{
+  FPB_CHECK_ARG(mesh && poses && params && ws && out_A && N > 0 && S > 1 && S <= 4096 && N <= 65535);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int V = mesh->V, F = mesh->F;
+  char* w = (char*)ws;
+  float4* clip = (float4*)w; w += align256((size_t)N * V * sizeof(float4));
+  float4* camd = (float4*)w; w += align256((size_t)N * V * sizeof(float4));
+  unsigned long long* zbuf = (unsigned long long*)w;
+  FPB_CUDA(cudaMemsetAsync(zbuf, 0xff, (size_t)N * S * S * sizeof(unsigned long long), st));
+  vertex_kernel<<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, clip, camd);
+  FPB_LAUNCH_CHECK();
+  raster_kernel<<<dim3(fpb_cdiv(F, 256), N), 256, 0, st>>>(mesh->faces, F, V, clip, S, zbuf);
+  FPB_LAUNCH_CHECK();
+  const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
+  const int blocks = fpb_cdiv((long long)N * S * S, 256);
+  if (a_is_bf16)
+    shade_kernel<true><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_color,
+                                               out_xyz, out_tri);
+  else
+    shade_kernel<false><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_color,
+                                                out_xyz, out_tri);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_hw3, const float* depth_hw, int H, int W,
+                              const float* poses, const float* params, const float* K9_h, int N, int S,
+                              float mesh_diameter, int mode, void* out_B, int b_is_bf16, void* stream)
+{
+  FPB_CHECK_ARG(rgb && poses && params && K9_h && out_B && N > 0 && S > 1 && H > 1 && W > 1);
+  FPB_CHECK_ARG(mode == 0 ? xyz_hw3 != nullptr : depth_hw != nullptr);
+  cudaStream_t st = (cudaStream_t)stream;
+  K9f K;
+  for (int i = 0; i < 9; i++) K.k[i] = K9_h[i];
+  const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
+  const int blocks = fpb_cdiv((long long)N * S * S, 256);
+#define LAUNCH_WARP(BF, U8)                                                                                         \
+  warp_kernel<BF, U8><<<blocks, 256, 0, st>>>(rgb, xyz_hw3, depth_hw, H, W, poses, params, K, N, S, inv_radius, mode, \
+                                              out_B)
+  if (b_is_bf16) { if (rgb_is_u8) LAUNCH_WARP(true, true); else LAUNCH_WARP(true, false); }
+  else           { if (rgb_is_u8) LAUNCH_WARP(false, true); else LAUNCH_WARP(false, false); }
+#undef LAUNCH_WARP
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}

@@ -1,0 +1,435 @@
+"""Host-side mirror of the hot-path functions of the reference's `src/Utils.py`, backed by libfpb200.so.
+
+Same names, argument meaning and numpy-in => numpy-out / torch-in => torch-out behaviour as the reference
+(file:line cited per function).  There is no CPU fallback: every compute function needs a CUDA device.
+"""
+import logging
+import math
+import random
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check, ptr, hptr, stream, f32_host
+
+glcam_in_cvcam = np.array([[1, 0, 0, 0], [0, -1, 0, 0], [0, 0, -1, 0], [0, 0, 0, 1]]).astype(float)
+CROP_STRIDE = 40
+
+
+def set_seed(random_seed):
+  """reference: src/Utils.py:222-229"""
+  np.random.seed(random_seed)
+  random.seed(random_seed)
+  torch.manual_seed(random_seed)
+  if torch.cuda.is_available():
+    torch.cuda.manual_seed_all(random_seed)
+  torch.backends.cudnn.deterministic = True
+  torch.backends.cudnn.benchmark = False
+
+
+def _as_cuda_f32(x, device='cuda'):
+  return torch.as_tensor(x, dtype=torch.float, device=device).contiguous()
+
+
+# ------------------------------------------------------------------------------------------------
+# depth pre-processing
+# ------------------------------------------------------------------------------------------------
+def erode_depth(depth, radius=2, depth_diff_thres=0.001, ratio_thres=0.8, zfar=100, device='cuda'):
+  """reference: src/Utils.py:387-395 (kernel :359-384)"""
+  _lib.require_cuda()
+  d = _as_cuda_f32(depth, device)
+  out = torch.empty_like(d)
+  check(lib().fpb_erode_depth_f32(ptr(d), ptr(out), d.shape[0], d.shape[1], radius, depth_diff_thres, ratio_thres,
+                                  zfar, stream()))
+  if isinstance(depth, np.ndarray):
+    return out.data.cpu().numpy()
+  return out
+
+
+def bilateral_filter_depth(depth, radius=2, zfar=100, sigmaD=2, sigmaR=100000, device='cuda'):
+  """reference: src/Utils.py:345-356 (kernel :304-343)"""
+  _lib.require_cuda()
+  d = _as_cuda_f32(depth, device)
+  out = torch.empty_like(d)
+  check(lib().fpb_bilateral_depth_f32(ptr(d), ptr(out), d.shape[0], d.shape[1], radius, zfar, sigmaD, sigmaR,
+                                      stream()))
+  if isinstance(depth, np.ndarray):
+    return out.data.cpu().numpy()
+  return out
+
+
+def depth2xyzmap_cuda(depth_t, K, math_f64=True, zfar=np.inf):
+  """Device-resident depth -> xyz map ([H,W] fp32 -> [H,W,3] fp32)."""
+  K9 = np.ascontiguousarray(np.asarray(K, dtype=np.float64).reshape(9))
+  out = torch.empty(depth_t.shape + (3,), dtype=torch.float, device=depth_t.device)
+  zf = float(min(zfar, 3.0e38))
+  check(lib().fpb_depth_to_xyz(ptr(depth_t), hptr(K9), zf, ptr(out), depth_t.shape[0], depth_t.shape[1],
+                               1 if math_f64 else 0, stream()))
+  return out
+
+
+def depth2xyzmap(depth, K, uvs=None):
+  """reference: src/Utils.py:399-417 -- float64 math evaluated on the GPU, float32 numpy result."""
+  _lib.require_cuda()
+  d = _as_cuda_f32(depth)
+  xyz = depth2xyzmap_cuda(d, K, math_f64=True).data.cpu().numpy()
+  if uvs is not None:
+    uvs = np.asarray(uvs).round().astype(int)
+    keep = np.zeros(xyz.shape[:2], dtype=bool)
+    keep[uvs[:, 1], uvs[:, 0]] = True
+    xyz[~keep] = 0
+  return xyz
+
+
+def depth2xyzmap_batch(depths, Ks, zfar):
+  """reference: src/Utils.py:420-438 -- fp32 math; depths (B,H,W), Ks (B,3,3) torch tensors."""
+  _lib.require_cuda()
+  depths = _as_cuda_f32(depths)
+  Ks_h = torch.as_tensor(Ks).detach().cpu().double().numpy().reshape(-1, 3, 3)
+  outs = []
+  for b in range(depths.shape[0]):
+    Kb = Ks_h[b if len(Ks_h) > 1 else 0].astype(np.float32).astype(np.float64)
+    outs.append(depth2xyzmap_cuda(depths[b].contiguous(), Kb, math_f64=False, zfar=zfar))
+  return torch.stack(outs, dim=0)
+
+
+def mask_depth_stats(depth_t, mask_t):
+  """Device statistics behind guess_translation (src/estimater.py:137-156).
+  Returns (umin, umax, vmin, vmax, n_mask, n_valid, mid_lo, mid_hi)."""
+  oi = torch.empty(6, dtype=torch.int32, device=depth_t.device)
+  of = torch.empty(2, dtype=torch.float, device=depth_t.device)
+  check(lib().fpb_mask_depth_stats(ptr(depth_t), ptr(mask_t), depth_t.shape[0], depth_t.shape[1], ptr(oi), ptr(of),
+                                   stream()))
+  oi = oi.cpu().numpy(); of = of.cpu().numpy()
+  return int(oi[0]), int(oi[1]), int(oi[2]), int(oi[3]), int(oi[4]), int(oi[5]), of[0], of[1]
+
+
+# ------------------------------------------------------------------------------------------------
+# hypothesis generation helpers (host, float64 -- init-time only in the reference too)
+# ------------------------------------------------------------------------------------------------
+_ICO_T = (1.0 + math.sqrt(5.0)) / 2.0
+_ICO_V = [(-1, _ICO_T, 0), (1, _ICO_T, 0), (-1, -_ICO_T, 0), (1, -_ICO_T, 0), (0, -1, _ICO_T), (0, 1, _ICO_T),
+          (0, -1, -_ICO_T), (0, 1, -_ICO_T), (_ICO_T, 0, -1), (_ICO_T, 0, 1), (-_ICO_T, 0, -1), (-_ICO_T, 0, 1)]
+_ICO_F = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4), (11, 10, 2), (10, 7, 6),
+          (7, 1, 8), (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9), (4, 9, 5), (2, 4, 11), (6, 2, 10),
+          (8, 6, 7), (9, 8, 1)]
+
+
+def icosphere(subdivisions=1, radius=1.0):
+  """trimesh 4.2.2 `creation.icosphere` vertex/face order (requirements.txt:43; used at src/Utils.py:485-489):
+  every level appends the unique edge mid-points, ordered by the (lo, hi) edge key with hi most significant,
+  then re-projects all vertices onto the sphere."""
+  verts = np.asarray(_ICO_V, dtype=np.float64) / np.sqrt(2.0 + _ICO_T)
+  faces = np.asarray(_ICO_F, dtype=np.int64)
+  for _ in range(int(subdivisions)):
+    nv = len(verts)
+    e = np.stack([faces[:, [0, 1]], faces[:, [1, 2]], faces[:, [2, 0]]], axis=1).reshape(-1, 2)
+    e.sort(axis=1)
+    code = e[:, 0] ^ (e[:, 1] << 32)
+    _, first, inv = np.unique(code, return_index=True, return_inverse=True)
+    mids = verts[e[first]].mean(axis=1)
+    m = inv.reshape(-1, 3) + nv
+    a, b, c = faces[:, 0], faces[:, 1], faces[:, 2]
+    faces = np.stack([a, m[:, 0], m[:, 2], m[:, 0], b, m[:, 1], m[:, 2], m[:, 1], c, m[:, 0], m[:, 1], m[:, 2]],
+                     axis=1).reshape(-1, 3)
+    verts = np.vstack((verts, mids))
+    norm = np.sqrt(np.dot(verts ** 2, [1, 1, 1]))
+    verts = verts + (verts / norm.reshape(-1, 1)) * (radius - norm).reshape(-1, 1)
+  return verts, faces
+
+
+def sample_views_icosphere(n_views, subdivisions=None, radius=1):
+  """reference: src/Utils.py:483-507 -> cam_in_obs float64 [n,4,4]"""
+  if subdivisions is not None:
+    verts, _ = icosphere(subdivisions, radius)
+  else:
+    level = 1
+    while True:
+      verts, _ = icosphere(level, radius)
+      if verts.shape[0] >= n_views:
+        break
+      level += 1
+  n = len(verts)
+  cam_in_obs = np.tile(np.eye(4)[None], (n, 1, 1))
+  cam_in_obs[:, :3, 3] = verts
+  up = np.array([0, 0, 1])
+  z_axis = -cam_in_obs[:, :3, 3]
+  z_axis /= np.linalg.norm(z_axis, axis=-1).reshape(-1, 1)
+  x_axis = np.cross(up.reshape(1, 3), z_axis)
+  degenerate = (x_axis == 0).all(axis=-1)
+  x_axis[degenerate] = [1, 0, 0]
+  x_axis /= np.linalg.norm(x_axis, axis=-1).reshape(-1, 1)
+  y_axis = np.cross(z_axis, x_axis)
+  y_axis /= np.linalg.norm(y_axis, axis=-1).reshape(-1, 1)
+  cam_in_obs[:, :3, 0] = x_axis
+  cam_in_obs[:, :3, 1] = y_axis
+  cam_in_obs[:, :3, 2] = z_axis
+  return cam_in_obs
+
+
+def euler_matrix(ai, aj, ak):
+  """`transformations.euler_matrix` (2024.6.1), static 'sxyz' axes only (src/estimater.py:113)."""
+  si, sj, sk = math.sin(ai), math.sin(aj), math.sin(ak)
+  ci, cj, ck = math.cos(ai), math.cos(aj), math.cos(ak)
+  cc, cs = ci * ck, ci * sk
+  sc, ss = si * ck, si * sk
+  M = np.identity(4)
+  M[0, 0] = cj * ck; M[0, 1] = sj * sc - cs; M[0, 2] = sj * cc + ss
+  M[1, 0] = cj * sk; M[1, 1] = sj * ss + cc; M[1, 2] = sj * cs - sc
+  M[2, 0] = -sj; M[2, 1] = cj * si; M[2, 2] = cj * ci
+  return M
+
+
+def projection_matrix_from_intrinsics(K, height, width, znear, zfar, window_coords='y_down'):
+  """reference: src/Utils.py:752-802 (float64)"""
+  w, h = width, height
+  depth = float(zfar - znear)
+  q = -(zfar + znear) / depth
+  qn = -2 * (zfar * znear) / depth
+  if window_coords == 'y_up':
+    row1 = [0, -2 * K[1, 1] / h, (-2 * K[1, 2] + h) / h, 0]
+  elif window_coords == 'y_down':
+    row1 = [0, 2 * K[1, 1] / h, (2 * K[1, 2] - h) / h, 0]
+  else:
+    raise NotImplementedError
+  return np.array([[2 * K[0, 0] / w, -2 * K[0, 1] / w, (-2 * K[0, 2] + w) / w, 0], row1, [0, 0, q, qn], [0, 0, -1, 0]])
+
+
+def compute_mesh_diameter(model_pts=None, mesh=None, n_sample=1000):
+  """reference: src/Utils.py:559-574 (host numpy; the mesh= branch of the reference is broken and unused)."""
+  if mesh is not None:
+    model_pts = np.asarray(mesh.vertices)
+  model_pts = np.asarray(model_pts)
+  if n_sample is None:
+    pts = model_pts
+  else:
+    ids = np.random.choice(len(model_pts), size=min(n_sample, len(model_pts)), replace=False)
+    pts = model_pts[ids]
+  best = 0.0
+  for b in range(0, len(pts), 512):   # blocked pairwise distances (bounded memory)
+    d = np.linalg.norm(pts[None, b:b + 512] - pts[:, None], axis=-1)
+    best = max(best, float(d.max()))
+  return best
+
+
+# ------------------------------------------------------------------------------------------------
+# crop windows
+# ------------------------------------------------------------------------------------------------
+def crop_params(poses, K, mesh_diameter, crop_ratio, S, H, W):
+  """All per-hypothesis window quantities in one launch -> cuda float tensor [N, 40]
+  (layout: include/fpb200.h FPB_CROP_STRIDE)."""
+  _lib.require_cuda()
+  poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
+  N = len(poses)
+  K64 = np.asarray(torch.as_tensor(K).detach().cpu().numpy() if torch.is_tensor(K) else K, dtype=np.float64)
+  K9 = f32_host(K64, 9)
+  P16 = f32_host(projection_matrix_from_intrinsics(K64, height=H, width=W, znear=0.001, zfar=100), 16)
+  radius = float(np.float32(mesh_diameter * crop_ratio / 2))
+  params = torch.empty((N, CROP_STRIDE), dtype=torch.float, device=poses.device)
+  check(lib().fpb_crop_params(ptr(poses), N, hptr(K9), radius, S, H, W, hptr(P16), ptr(params), stream()))
+  return params
+
+
+def compute_crop_window_tf_batch(pts=None, H=None, W=None, poses=None, K=None, crop_ratio=1.2, out_size=None, rgb=None,
+                                 uvs=None, method='min_box', mesh_diameter=None):
+  """reference: src/Utils.py:577-626 -> tf_to_crops (B,3,3) cuda float.  Only method='box_3d' exists upstream."""
+  if method != 'box_3d':
+    raise RuntimeError
+  assert out_size[0] == out_size[1], 'square crops only'
+  params = crop_params(poses, K, mesh_diameter, crop_ratio, int(out_size[0]), H, W)
+  return params[:, :9].reshape(-1, 3, 3).contiguous()
+
+
+# ------------------------------------------------------------------------------------------------
+# mesh
+# ------------------------------------------------------------------------------------------------
+class MeshHandle:
+  """Owns an fpb_mesh (device copies of the mesh arrays)."""
+
+  def __init__(self, mesh_tensors):
+    import ctypes
+    _lib.require_cuda()
+    mt = mesh_tensors
+    pos = _as_cuda_f32(mt['pos']); vn = _as_cuda_f32(mt['vnormals'])
+    faces = torch.as_tensor(mt['faces'], dtype=torch.int32, device='cuda').contiguous()
+    vc = uv = uvi = tex = None
+    Vt = Ht = Wt = 0
+    if 'tex' in mt:
+      tex = _as_cuda_f32(mt['tex']).reshape(mt['tex'].shape[-3], mt['tex'].shape[-2], 3).contiguous()
+      Ht, Wt = tex.shape[:2]
+      uv = _as_cuda_f32(mt['uv']); Vt = len(uv)
+      uvi = torch.as_tensor(mt['uv_idx'], dtype=torch.int32, device='cuda').contiguous()
+    else:
+      vc = _as_cuda_f32(mt['vertex_color'])
+    self.V, self.F = len(pos), len(faces)
+    h = ctypes.c_void_p()
+    check(lib().fpb_mesh_create(ctypes.byref(h), ptr(pos), ptr(vn), self.V, ptr(faces), self.F, ptr(vc), ptr(uv), Vt,
+                                ptr(uvi), ptr(tex), Ht, Wt, stream()))
+    self.handle = h
+
+  def __del__(self):
+    try:
+      if getattr(self, 'handle', None):
+        lib().fpb_mesh_destroy(self.handle)
+        self.handle = None
+    except Exception:
+      pass
+
+
+def make_mesh_tensors(mesh, device='cuda', max_tex_size=None):
+  """reference: src/Utils.py:104-130.  `mesh` is trimesh-like (duck-typed: .vertices, .faces, .vertex_normals and
+  either .visual.uv + .visual.material.image, or .visual.vertex_colors)."""
+  mesh_tensors = {}
+  visual = getattr(mesh, 'visual', None)
+  uv = getattr(visual, 'uv', None) if visual is not None else None
+  if uv is not None and getattr(visual, 'material', None) is not None:
+    img = visual.material.image
+    img = np.array(img.convert('RGB')) if hasattr(img, 'convert') else np.asarray(img)
+    img = img[..., :3]
+    if max_tex_size is not None and max(img.shape[0], img.shape[1]) > max_tex_size:
+      import cv2
+      scale = 1 / max(img.shape[0], img.shape[1]) * max_tex_size
+      img = cv2.resize(img, fx=scale, fy=scale, dsize=None)
+    mesh_tensors['tex'] = torch.as_tensor(np.ascontiguousarray(img), device=device, dtype=torch.float)[None] / 255.0
+    mesh_tensors['uv_idx'] = torch.as_tensor(np.asarray(mesh.faces), device=device, dtype=torch.int)
+    uv_t = torch.as_tensor(np.asarray(uv), device=device, dtype=torch.float).clone()
+    uv_t[:, 1] = 1 - uv_t[:, 1]
+    mesh_tensors['uv'] = uv_t
+  else:
+    vcol = getattr(visual, 'vertex_colors', None) if visual is not None else None
+    if vcol is None:
+      logging.info("WARN: mesh doesn't have vertex_colors, assigning a pure color")
+      vcol = np.tile(np.array([128, 128, 128]).reshape(1, 3), (len(mesh.vertices), 1))
+    mesh_tensors['vertex_color'] = torch.as_tensor(np.asarray(vcol)[..., :3], device=device, dtype=torch.float) / 255.0
+  mesh_tensors.update({
+    'pos': torch.tensor(np.asarray(mesh.vertices), device=device, dtype=torch.float),
+    'faces': torch.tensor(np.asarray(mesh.faces), device=device, dtype=torch.int),
+    'vnormals': torch.tensor(np.asarray(mesh.vertex_normals), device=device, dtype=torch.float),
+  })
+  return mesh_tensors
+
+
+def mesh_handle_of(mesh_tensors):
+  """Cache the device mesh handle inside the mesh_tensors dict (the dict is the drop-in's mesh interface)."""
+  h = mesh_tensors.get('_fpb_handle')
+  if h is None:
+    h = MeshHandle(mesh_tensors)
+    mesh_tensors['_fpb_handle'] = h
+  return h
+
+
+# ------------------------------------------------------------------------------------------------
+# render / warp / pose update
+# ------------------------------------------------------------------------------------------------
+def render_crops(mesh_tensors, poses, params, S, mesh_diameter, zthr, out_A=None, bf16=True, debug=False):
+  """Render all N hypotheses at crop resolution and write network input A ([N,S,S,8]).
+  Returns (A, extras) where extras holds fp32 color/xyz/tri when debug=True."""
+  mh = mesh_handle_of(mesh_tensors)
+  poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
+  N = len(poses)
+  if out_A is None:
+    out_A = torch.empty((N, S, S, 8), dtype=torch.bfloat16 if bf16 else torch.float, device='cuda')
+  ws = torch.empty(lib().fpb_render_ws_bytes(N, mh.V, S), dtype=torch.uint8, device='cuda')
+  extras = {}
+  c = x = t = None
+  if debug:
+    c = torch.empty((N, S, S, 3), dtype=torch.float, device='cuda')
+    x = torch.empty((N, S, S, 3), dtype=torch.float, device='cuda')
+    t = torch.empty((N, S, S), dtype=torch.int32, device='cuda')
+    extras = dict(color=c, xyz=x, tri=t)
+  check(lib().fpb_render_crops(mh.handle, ptr(poses), ptr(params), N, S, float(mesh_diameter), float(zthr), ptr(ws),
+                               ptr(out_A), 1 if out_A.dtype == torch.bfloat16 else 0, ptr(c), ptr(x), ptr(t), stream()))
+  return out_A, extras
+
+
+def warp_crops(rgb_t, xyz_map_t, depth_t, poses, params, K, S, mesh_diameter, mode, out_B=None, bf16=True):
+  """Observed-side crops -> network input B ([N,S,S,8]).  rgb_t: cuda uint8 or float [H,W,3] (0..255)."""
+  poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
+  N = len(poses)
+  H, W = rgb_t.shape[:2]
+  if out_B is None:
+    out_B = torch.empty((N, S, S, 8), dtype=torch.bfloat16 if bf16 else torch.float, device='cuda')
+  K9 = f32_host(torch.as_tensor(K).detach().cpu().numpy() if torch.is_tensor(K) else K, 9)
+  is_u8 = rgb_t.dtype == torch.uint8
+  if not is_u8:
+    rgb_t = rgb_t.float().contiguous()
+  check(lib().fpb_warp_crops(ptr(rgb_t), 1 if is_u8 else 0, ptr(xyz_map_t), ptr(depth_t), H, W, ptr(poses), ptr(params),
+                             hptr(K9), N, S, float(mesh_diameter), mode, ptr(out_B),
+                             1 if out_B.dtype == torch.bfloat16 else 0, stream()))
+  return out_B
+
+
+def pose_update(poses, trans, rot, mesh_diameter, rot_normalizer, trans_normalizer=None, normalize_xyz=True):
+  """predict_pose_refine.py:195-231 + egocentric_delta_pose_to_pose (src/Utils.py:848-855) in one kernel."""
+  poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
+  out = torch.empty_like(poses)
+  tn = f32_host(trans_normalizer, 3) if trans_normalizer is not None else None
+  check(lib().fpb_pose_update(ptr(poses), ptr(trans.contiguous()), ptr(rot.contiguous()), len(poses),
+                              float(mesh_diameter), float(rot_normalizer), hptr(tn), 1 if normalize_xyz else 0,
+                              ptr(out), stream()))
+  return out
+
+
+def nvdiffrast_render(K=None, H=None, W=None, ob_in_cams=None, glctx=None, context='cuda', get_normal=False,
+                      mesh_tensors=None, mesh=None, projection_mat=None, bbox2d=None, output_size=None, use_light=False,
+                      light_color=None, light_dir=np.array([0, 0, 1]), light_pos=np.array([0, 0, 0]), w_ambient=0.8,
+                      w_diffuse=0.5, extra={}):
+  """reference: src/Utils.py:133-219, for the configuration the hot path uses (use_light=True, default light,
+  square crop given by bbox2d + output_size).  glctx/context are accepted and ignored.
+  Returns (color [n,S,S,3], depth [n,S,S], None); extra['xyz_map'] = camera-frame xyz [n,S,S,3]."""
+  if not use_light or light_color is not None or get_normal or projection_mat is not None or bbox2d is None:
+    raise NotImplementedError('only the render configuration used by make_crop_data_batch is implemented')
+  if mesh_tensors is None:
+    mesh_tensors = make_mesh_tensors(mesh)
+  S = int(output_size[0])
+  assert int(output_size[1]) == S
+  poses = _as_cuda_f32(ob_in_cams).reshape(-1, 4, 4)
+  N = len(poses)
+  K64 = np.asarray(K, dtype=np.float64)
+  # rebuild the parameter block from the caller's bbox2d (umin,vmin,umax,vmax)
+  params = torch.zeros((N, CROP_STRIDE), dtype=torch.float, device='cuda')
+  P = torch.as_tensor(projection_matrix_from_intrinsics(K64, height=H, width=W, znear=0.001, zfar=100),
+                      dtype=torch.float, device='cuda')
+  G = torch.as_tensor(glcam_in_cvcam, dtype=torch.float, device='cuda')
+  params[:, 13:29] = (P[None] @ (G[None] @ poses)).reshape(N, 16)
+  bb = _as_cuda_f32(bbox2d).reshape(N, 4)
+  l, t, r, b = bb[:, 0], H - bb[:, 1], bb[:, 2], H - bb[:, 3]
+  params[:, 29] = W / (r - l); params[:, 30] = H / (t - b)
+  params[:, 31] = (W - r - l) / (r - l); params[:, 32] = (H - t - b) / (t - b)
+  _, ex = render_crops(mesh_tensors, poses, params, S, 1.0, 0.0, bf16=False, debug=True)
+  extra['xyz_map'] = ex['xyz']
+  return ex['color'], ex['xyz'][..., 2].contiguous(), None
+
+
+# ------------------------------------------------------------------------------------------------
+# small torch helpers kept for API compatibility (src/Utils.py:520-546, 836-855)
+# ------------------------------------------------------------------------------------------------
+def to_homo_torch(pts):
+  ones = torch.ones((*pts.shape[:-1], 1), dtype=torch.float, device=pts.device)
+  return torch.cat((pts, ones), dim=-1)
+
+
+def transform_pts(pts, tf):
+  if len(tf.shape) >= 3 and tf.shape[-3] != pts.shape[-2]:
+    tf = tf[..., None, :, :]
+  return (tf[..., :-1, :-1] @ pts[..., None] + tf[..., :-1, -1:])[..., 0]
+
+
+def transform_dirs(dirs, tf):
+  if len(tf.shape) >= 3 and tf.shape[-3] != dirs.shape[-2]:
+    tf = tf[..., None, :, :]
+  return (tf[..., :3, :3] @ dirs[..., None])[..., 0]
+
+
+def pose_to_egocentric_delta_pose(A_in_cam, B_in_cam):
+  trans_delta = B_in_cam[:, :3, 3] - A_in_cam[:, :3, 3]
+  rot_mat_delta = B_in_cam[:, :3, :3] @ A_in_cam[:, :3, :3].permute(0, 2, 1)
+  return trans_delta, rot_mat_delta
+
+
+def egocentric_delta_pose_to_pose(A_in_cam, trans_delta, rot_mat_delta):
+  B_in_cam = torch.eye(4, dtype=torch.float, device=A_in_cam.device)[None].expand(len(A_in_cam), -1, -1).contiguous()
+  B_in_cam[:, :3, 3] = A_in_cam[:, :3, 3] + trans_delta
+  B_in_cam[:, :3, :3] = rot_mat_delta @ A_in_cam[:, :3, :3]
+  return B_in_cam

@@ -1,0 +1,120 @@
+/*
+ * fpb200.h -- C ABI of libfpb200.so: the B200-native (sm_100a) kernels behind
+ * FoundationPose's render-and-compare hypothesis path.
+ *
+ * Conventions:
+ *   - every pointer is a DEVICE pointer unless its name ends in _h (host);
+ *   - the caller owns every buffer, including workspaces; handles own only their
+ *     packed weights;  no allocation, no implicit sync inside compute calls;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it;
+ *   - return 0 on success, <0 on error; text via fpb_last_error() (thread-local);
+ *   - layouts: images [H,W] / [H,W,3] row-major; poses [N,4,4] row-major fp32;
+ *     network inputs NHWC with 8 channels (r,g,b,x,y,z,0,0).
+ * Each entry point cites the reference interface it replaces (paths relative to the
+ * reference repository root).
+ */
+#ifndef FPB200_H
+#define FPB200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FPB_OK 0
+#define FPB_ERR_ARG (-1)
+#define FPB_ERR_CUDA (-2)
+#define FPB_ERR_UNSUPPORTED (-3)
+
+/* precision modes of the network path */
+#define FPB_PREC_FP32 0   /* SIMT fp32 parity mode */
+#define FPB_PREC_BF16 1   /* tcgen05 bf16 operands, fp32 accumulation */
+
+const char* fpb_last_error(void);
+int fpb_version(void);
+
+/* ---- depth pre-processing: src/Utils.py:359-395 (erode_depth), :304-356
+ *      (bilateral_filter_depth), :399-417 (depth2xyzmap, math_f64=1),
+ *      :420-438 (depth2xyzmap_batch, math_f64=0) ------------------------- */
+int fpb_erode_depth_f32(const float* in, float* out, int H, int W, int radius, float diff_thres,
+                        float ratio_thres, float zfar, void* stream);
+int fpb_bilateral_depth_f32(const float* in, float* out, int H, int W, int radius, float zfar,
+                            float sigmaD, float sigmaR, void* stream);
+int fpb_depth_to_xyz(const float* depth, const double* K9_h, float zfar, float* xyz_hw3, int H, int W,
+                     int math_f64, void* stream);
+
+/* ---- guess_translation statistics: src/estimater.py:137-156.
+ *      out_i32[6] = umin, umax, vmin, vmax, n_mask, n_valid;
+ *      out_f32[2] = the two middle order statistics of depth[mask & depth>=0.001]
+ *      (equal when n_valid is odd).  mask is uint8 [H,W] (non-zero = set). ---- */
+int fpb_mask_depth_stats(const float* depth, const uint8_t* mask, int H, int W, int32_t* out_i32,
+                         float* out_f32, void* stream);
+
+/* ---- cluster_poses: mycpp/src/app/pybind_api.cpp:24-68.
+ *      out_keep_idx[N] receives kept input indices, out_n_keep[1] their count. ---- */
+int fpb_cluster_poses_f32(const float* poses, int N, const float* sym, int S, float angle_deg, float dist,
+                          int32_t* out_keep_idx, int32_t* out_n_keep, void* stream);
+
+/* ---- crop windows: compute_crop_window_tf_batch(method='box_3d') src/Utils.py:577-621,
+ *      bbox2d_ori predict_pose_refine.py:44-45, render matrices src/Utils.py:159-181.
+ *      params layout per hypothesis (FPB_CROP_STRIDE floats):
+ *        [0:9) tf_to_crop  [9:13) bbox umin,vmin,umax,vmax  [13:29) P@glcam@pose
+ *        [29:33) render zoom tf00,tf11,tf30,tf31  [33:37) inverse i00,i02,i11,i12 ---- */
+#define FPB_CROP_STRIDE 40
+int fpb_crop_params(const float* poses, int N, const float* K9_h, float radius, int S, int H, int W,
+                    const float* P16_h, float* params, void* stream);
+
+/* ---- mesh handle: make_mesh_tensors src/Utils.py:104-130 (device arrays are COPIED) ---- */
+typedef struct fpb_mesh fpb_mesh;
+int fpb_mesh_create(fpb_mesh** out, const float* pos, const float* vnormals, int V, const int32_t* faces,
+                    int F, const float* vcolor, const float* uv, int Vt, const int32_t* uv_idx,
+                    const float* tex, int Ht, int Wt, void* stream);
+int fpb_mesh_destroy(fpb_mesh* m);
+
+/* ---- batched render at crop resolution + fused shading into network input A:
+ *      nvdiffrast_render src/Utils.py:133-219 + rgb*255 (predict_pose_refine.py:56) +
+ *      transform_batch (h5_dataset.py:79-127 / 137-179).
+ *      ws must hold fpb_render_ws_bytes(N,V,S) bytes.  out_A: [N,S,S,8] bf16 or fp32
+ *      (a_is_bf16).  Optional fp32 debug outputs (may be NULL): color [N,S,S,3],
+ *      xyz [N,S,S,3] (camera frame, un-normalised), tri [N,S,S] int32 (face id + 1). ---- */
+size_t fpb_render_ws_bytes(int N, int V, int S);
+int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
+                     float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16,
+                     float* out_color, float* out_xyz, int32_t* out_tri, void* stream);
+
+/* ---- observed-side crops into network input B: kornia warp_perspective call sites
+ *      predict_pose_refine.py:63,72; predict_score.py:89-90; h5_dataset.py:137-170.
+ *      mode 0 refiner (nearest xyz_map), mode 1 scorer (depth crop->full->xyz->crop).
+ *      rgb: uint8 [H,W,3] (rgb_is_u8) or fp32 [H,W,3] in 0..255. ---- */
+int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_hw3, const float* depth_hw, int H, int W,
+                   const float* poses, const float* params, const float* K9_h, int N, int S,
+                   float mesh_diameter, int mode, void* out_B, int b_is_bf16, void* stream);
+
+/* ---- pose update: predict_pose_refine.py:195-231, egocentric_delta_pose_to_pose
+ *      src/Utils.py:848-855, pytorch3d so3_exp_map.  tn3_h used when !normalize_xyz. ---- */
+int fpb_pose_update(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
+                    float rot_normalizer, const float* tn3_h, int normalize_xyz, float* out_poses,
+                    void* stream);
+
+/* ---- networks: learning/models/refine_network.py:26-93, score_network.py:27-90.
+ *      Weights arrive as a flat host blob produced by foundationpose_b200.nets.pack_* (BN folded). ---- */
+typedef struct fpb_net fpb_net;
+#define FPB_NET_REFINE 0
+#define FPB_NET_SCORE 1
+int fpb_net_create(fpb_net** out, int kind, int precision, const void* blob_h, size_t bytes, void* stream);
+int fpb_net_destroy(fpb_net* net);
+size_t fpb_net_ws_bytes(int kind, int precision, int N);
+/* AB: [2N,S,S,8] (first N = rendered A, last N = observed B), S = 160 */
+int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
+                       void* stream);
+int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream);
+int fpb_score_cross(const fpb_net* net, const float* feat, int L, int bs, void* ws, float* out_logits,
+                    void* stream);
+
+/* number of kernels this library launched on the calling thread since the last reset */
+long long fpb_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
