@@ -1,0 +1,386 @@
+// RefineNet / ScoreNetMultiPair forward orchestration over the GEMM kernels (net_ref.cu / net_tc.cu).
+//   RefineNet.forward           learning/models/refine_network.py:73-93
+//   ScoreNetMultiPair.forward   learning/models/score_network.py:60-90
+// Weights arrive as one flat fp32 blob (BatchNorm folded into per-channel scale/shift by
+// foundationpose_b200/nets.py); in bf16 mode a bf16 shadow of the blob feeds the tcgen05 kernel.
+#include "net_kernels.cuh"
+#include <stdlib.h>
+#include <vector>
+
+namespace {
+
+struct ConvSpec { int Cin, Cout, KH, KW, stride, pad, Hin, Ho; };
+const ConvSpec kConvs[15] = {
+    {8, 64, 7, 8, 2, 3, 160, 80},    {64, 128, 3, 3, 2, 1, 80, 40},   {128, 128, 3, 3, 1, 1, 40, 40},
+    {128, 128, 3, 3, 1, 1, 40, 40},  {128, 128, 3, 3, 1, 1, 40, 40},  {128, 128, 3, 3, 1, 1, 40, 40},
+    {256, 256, 3, 3, 1, 1, 40, 40},  {256, 256, 3, 3, 1, 1, 40, 40},  {256, 256, 3, 3, 1, 1, 40, 40},
+    {256, 256, 3, 3, 1, 1, 40, 40},  {256, 512, 3, 3, 2, 1, 40, 20},  {512, 512, 3, 3, 1, 1, 20, 20},
+    {512, 512, 3, 3, 1, 1, 20, 20},  {512, 512, 3, 3, 1, 1, 20, 20},  {512, 512, 3, 3, 1, 1, 20, 20}};
+
+constexpr int D = 512, HEADS = 4, DH = 128, TOK = 400, TOKP = 448;
+
+struct Lin { size_t w, b; int N, K; };            // offsets (in floats) into the blob
+struct Conv { size_t w, scale, shift; };
+struct Mha { Lin in, out; };
+struct EncLayer { Mha att; Lin l1, l2; size_t n1g, n1b, n2g, n2b; Lin fin; };
+
+}  // namespace
+
+struct fpb_net {
+  int kind, precision;
+  size_t n_floats;
+  float* w32;
+  __nv_bfloat16* w16;
+  Conv conv[15];
+  size_t pe;
+  EncLayer head[2];   // refine: trans, rot
+  Mha att, att_cross; // score
+  Lin lin;            // score
+};
+
+namespace {
+
+struct Cursor {
+  size_t off = 0;
+  size_t take(size_t n) { size_t o = off; off += (n + 7) & ~(size_t)7; return o; }   // keep 8-element alignment
+};
+
+Lin take_lin(Cursor& c, int N, int K) { Lin l; l.N = N; l.K = K; l.w = c.take((size_t)N * K); l.b = c.take(N); return l; }
+Mha take_mha(Cursor& c) { Mha m; m.in = take_lin(c, 3 * D, D); m.out = take_lin(c, D, D); return m; }
+
+size_t layout(fpb_net* n)
+{
+  Cursor c;
+  for (int i = 0; i < 15; i++) {
+    const ConvSpec& s = kConvs[i];
+    n->conv[i].w = c.take((size_t)s.Cout * s.KH * s.KW * s.Cin);
+    n->conv[i].scale = c.take(s.Cout);
+    n->conv[i].shift = c.take(s.Cout);
+  }
+  n->pe = c.take((size_t)TOK * D);
+  if (n->kind == FPB_NET_REFINE) {
+    for (int h = 0; h < 2; h++) {
+      EncLayer& e = n->head[h];
+      e.att = take_mha(c);
+      e.l1 = take_lin(c, D, D);
+      e.l2 = take_lin(c, D, D);
+      e.n1g = c.take(D); e.n1b = c.take(D); e.n2g = c.take(D); e.n2b = c.take(D);
+      e.fin = take_lin(c, 3, D);
+    }
+  } else {
+    n->att = take_mha(c);
+    n->att_cross = take_mha(c);
+    n->lin = take_lin(c, 1, D);
+  }
+  return c.off;
+}
+
+int net_chunk()
+{
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("FPB_NET_CHUNK");
+    v = e ? atoi(e) : 42;
+    if (v < 1) v = 1;
+  }
+  return v;
+}
+
+size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// workspace carve-up for a chunk of n hypotheses; esz = activation element size
+struct Ws {
+  char *c0, *c1, *c2, *c3, *ab0, *ab1, *ab2, *d0, *d1, *d2, *qkv, *P, *vt, *ctx, *y1, *y, *ff;
+  float *scores, *pooled;
+  size_t total;
+};
+
+Ws carve(char* base, int n, size_t esz)
+{
+  Ws w;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + o : nullptr; o += al(bytes); return p; };
+  w.c0 = take((size_t)2 * n * 6400 * 64 * esz);
+  w.c1 = take((size_t)2 * n * 1600 * 128 * esz);
+  w.c2 = take((size_t)2 * n * 1600 * 128 * esz);
+  w.c3 = take((size_t)2 * n * 1600 * 128 * esz);
+  w.ab0 = take((size_t)n * 1600 * 256 * esz);
+  w.ab1 = take((size_t)n * 1600 * 256 * esz);
+  w.ab2 = take((size_t)n * 1600 * 256 * esz);
+  w.d0 = take((size_t)n * TOK * D * esz);
+  w.d1 = take((size_t)n * TOK * D * esz);
+  w.d2 = take((size_t)n * TOK * D * esz);
+  w.qkv = take((size_t)n * TOK * 3 * D * esz);
+  w.P = take((size_t)n * HEADS * TOK * TOKP * esz);
+  w.vt = take((size_t)n * HEADS * DH * TOKP * esz);
+  w.ctx = take((size_t)n * TOK * D * esz);
+  w.y1 = take((size_t)n * TOK * D * esz);
+  w.y = take((size_t)n * TOK * D * esz);
+  w.ff = take((size_t)n * TOK * D * esz);
+  w.scores = (float*)take((size_t)n * HEADS * TOK * TOKP * sizeof(float));
+  w.pooled = (float*)take((size_t)n * D * sizeof(float));
+  w.total = o;
+  return w;
+}
+
+struct Ctx {
+  const fpb_net* net;
+  cudaStream_t st;
+  bool bf;
+  size_t esz;
+  const void* W(size_t off) const { return bf ? (const void*)(net->w16 + off) : (const void*)(net->w32 + off); }
+  const float* F(size_t off) const { return net->w32 + off; }
+  int gemm(const GemmProblem& p) const { return bf ? tc_gemm(p, st) : ref_gemm(p, st); }
+};
+
+#define RET(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+
+int run_conv(const Ctx& c, int li, const void* in, int nimg, void* out, const void* residual, int relu, bool pe,
+             int m_split, int split_off, int ldc)
+{
+  const ConvSpec& s = kConvs[li];
+  GemmProblem p = gemm_problem_default();
+  p.A = in; p.W = c.W(c.net->conv[li].w); p.C = out;
+  p.M = nimg * s.Ho * s.Ho; p.N = s.Cout; p.K = s.KH * s.KW * s.Cin;
+  p.Hin = p.Win = s.Hin; p.Cin = s.Cin; p.Ho = p.Wo = s.Ho; p.KH = s.KH; p.KW = s.KW; p.stride = s.stride; p.pad = s.pad;
+  p.pix_pitch = s.Cin; p.ldw = p.K;
+  p.scale = c.F(c.net->conv[li].scale); p.shift = c.F(c.net->conv[li].shift);
+  p.residual = residual; p.ldr = s.Cout; p.relu = relu;
+  if (pe) { p.pe = c.F(c.net->pe); p.pe_rows = TOK; p.pe_ld = D; }
+  p.ldc = ldc > 0 ? ldc : s.Cout;
+  if (m_split > 0) { p.m_split = m_split; p.split_col_off = split_off; }
+  p.out_bf16 = c.bf;
+  return c.gemm(p);
+}
+
+int run_linear(const Ctx& c, const Lin& l, const void* in, long long rows, void* out, const void* residual, int relu,
+               int out_bf16)
+{
+  GemmProblem p = gemm_problem_default();
+  p.A = in; p.W = c.W(l.w); p.C = out;
+  p.M = (int)rows; p.N = l.N; p.K = l.K; p.Cin = l.K; p.pix_pitch = l.K; p.ldw = l.K;
+  p.shift = c.F(l.b);
+  p.residual = residual; p.ldr = l.N; p.relu = relu; p.ldc = l.N; p.out_bf16 = out_bf16;
+  return c.gemm(p);
+}
+
+// both encoders: AB [2n,160,160,8] -> tokens (+pe) in w.d0 [n*400, 512]
+int run_encoders(const Ctx& c, const void* AB, int n, Ws& w)
+{
+  RET(run_conv(c, 0, AB, 2 * n, w.c0, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 1, w.c0, 2 * n, w.c1, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 2, w.c1, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 3, w.c2, 2 * n, w.c3, w.c1, 1, false, 0, 0, 0));
+  RET(run_conv(c, 4, w.c3, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0));
+  // last encodeA conv writes cat((a,b),1): rows of the first n images -> channels [0,128), last n -> [128,256)
+  RET(run_conv(c, 5, w.c2, 2 * n, w.ab0, w.c3, 1, false, n * 1600, 128, 256));
+  RET(run_conv(c, 6, w.ab0, n, w.ab1, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 7, w.ab1, n, w.ab2, w.ab0, 1, false, 0, 0, 0));
+  RET(run_conv(c, 8, w.ab2, n, w.ab1, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 9, w.ab1, n, w.ab0, w.ab2, 1, false, 0, 0, 0));
+  RET(run_conv(c, 10, w.ab0, n, w.d0, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 11, w.d0, n, w.d1, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 12, w.d1, n, w.d2, w.d0, 1, false, 0, 0, 0));
+  RET(run_conv(c, 13, w.d2, n, w.d1, nullptr, 1, false, 0, 0, 0));
+  RET(run_conv(c, 14, w.d1, n, w.d0, w.d2, 1, true, 0, 0, 0));   // + positional embedding -> tokens in d0
+  return FPB_OK;
+}
+
+// multi-head self-attention core on packed qkv [g*tokens, 3*D] -> ctx [g*tokens, D]
+int run_attention_core(const Ctx& c, const void* qkv, int g, int tokens, int tokp, float* scores, void* P, void* vt,
+                       void* ctx, bool bf)
+{
+  const size_t esz = bf ? 2 : 4;
+  RET(transpose_v(qkv, vt, bf, g, tokens, HEADS, DH, 3 * D, 2 * D, tokp, c.st));
+  GemmProblem p = gemm_problem_default();
+  p.A = qkv; p.W = (const char*)qkv + (size_t)D * esz; p.C = scores;
+  p.M = tokens; p.N = tokens; p.K = DH; p.Cin = DH; p.pix_pitch = 3 * D; p.ldw = 3 * D;
+  p.batch = g * HEADS; p.b_inner = HEADS;
+  p.A_outer = (long long)tokens * 3 * D; p.A_inner = DH; p.W_outer = p.A_outer; p.W_inner = DH;
+  p.C_outer = (long long)HEADS * tokens * tokp; p.C_inner = (long long)tokens * tokp; p.ldc = tokp;
+  p.alpha = 0.08838834764831845f;   // 1/sqrt(128)
+  p.n_valid = tokens; p.out_bf16 = 0;
+  RET(bf ? tc_gemm(p, c.st) : ref_gemm(p, c.st));
+  RET(softmax_rows(scores, P, bf, (long long)g * HEADS * tokens, tokens, tokp, tokp, c.st));
+  GemmProblem q = gemm_problem_default();
+  q.A = P; q.W = vt; q.C = ctx;
+  q.M = tokens; q.N = DH; q.K = tokp; q.Cin = tokp; q.pix_pitch = tokp; q.ldw = tokp;
+  q.batch = g * HEADS; q.b_inner = HEADS;
+  q.A_outer = (long long)HEADS * tokens * tokp; q.A_inner = (long long)tokens * tokp;
+  q.W_outer = (long long)HEADS * DH * tokp; q.W_inner = (long long)DH * tokp;
+  q.C_outer = (long long)tokens * D; q.C_inner = DH; q.ldc = D; q.out_bf16 = bf;
+  RET(bf ? tc_gemm(q, c.st) : ref_gemm(q, c.st));
+  return FPB_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+FPB_EXPORT int fpb_net_create(fpb_net** out, int kind, int precision, const void* blob_h, size_t bytes, void* stream)
+{
+  FPB_CHECK_ARG(out && blob_h && (kind == FPB_NET_REFINE || kind == FPB_NET_SCORE));
+  FPB_CHECK_ARG(precision == FPB_PREC_FP32 || precision == FPB_PREC_BF16);
+  cudaStream_t st = (cudaStream_t)stream;
+  fpb_net* n = new fpb_net();
+  memset(n, 0, sizeof(*n));
+  n->kind = kind; n->precision = precision;
+  n->n_floats = layout(n);
+  if (bytes != n->n_floats * sizeof(float)) {
+    fpb_set_error("fpb_net_create: blob has %zu bytes, expected %zu", bytes, n->n_floats * sizeof(float));
+    delete n;
+    return FPB_ERR_ARG;
+  }
+  FPB_CUDA(cudaMalloc((void**)&n->w32, bytes));
+  FPB_CUDA(cudaMemcpyAsync(n->w32, blob_h, bytes, cudaMemcpyHostToDevice, st));
+  if (precision == FPB_PREC_BF16) {
+    FPB_CUDA(cudaMalloc((void**)&n->w16, n->n_floats * sizeof(__nv_bfloat16)));
+    int rc = f32_to_bf16(n->w32, n->w16, (long long)n->n_floats, st);
+    if (rc) return rc;
+  }
+  FPB_CUDA(cudaStreamSynchronize(st));
+  *out = n;
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_net_destroy(fpb_net* n)
+{
+  if (!n) return FPB_OK;
+  cudaFree(n->w32);
+  cudaFree(n->w16);
+  delete n;
+  return FPB_OK;
+}
+
+FPB_EXPORT size_t fpb_net_ws_bytes(int kind, int precision, int N)
+{
+  (void)kind;
+  const int n = N < net_chunk() ? N : net_chunk();
+  return carve(nullptr, n, precision == FPB_PREC_BF16 ? 2 : 4).total + 1024;
+}
+
+FPB_EXPORT size_t fpb_net_blob_floats(int kind)
+{
+  fpb_net tmp;
+  memset(&tmp, 0, sizeof(tmp));
+  tmp.kind = kind;
+  return layout(&tmp);
+}
+
+static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* out3)
+{
+  const long long R = (long long)n * TOK;
+  RET(run_linear(c, e.att.in, w.d0, R, w.qkv, nullptr, 0, c.bf));
+  RET(run_attention_core(c, w.qkv, n, TOK, TOKP, w.scores, w.P, w.vt, w.ctx, c.bf));
+  RET(run_linear(c, e.att.out, w.ctx, R, w.y1, w.d0, 0, c.bf));                       // x + SA(x)
+  RET(layernorm_rows(w.y1, c.bf, c.F(e.n1g), c.F(e.n1b), w.y, c.bf, R, D, 1e-5f, c.st));
+  RET(run_linear(c, e.l1, w.y, R, w.ff, nullptr, 1, c.bf));
+  RET(run_linear(c, e.l2, w.ff, R, w.y1, w.y, 0, c.bf));                               // y + FF(y)
+  RET(layernorm_rows(w.y1, c.bf, c.F(e.n2g), c.F(e.n2b), w.ff, c.bf, R, D, 1e-5f, c.st));
+  RET(token_mean(w.ff, c.bf, w.pooled, n, TOK, D, c.st));                              // mean commutes with Linear
+  RET(small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, 3, c.st));
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
+                                  void* stream)
+{
+  FPB_CHECK_ARG(net && net->kind == FPB_NET_REFINE && AB && ws && out_trans && out_rot && N > 0);
+  Ctx c{net, (cudaStream_t)stream, net->precision == FPB_PREC_BF16, (size_t)(net->precision == FPB_PREC_BF16 ? 2 : 4)};
+  const int chunk = net_chunk();
+  char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+  const size_t img = (size_t)160 * 160 * 8 * c.esz;
+  // AB holds all N rendered crops first, then all N observed crops; a chunk needs them adjacent -> gather
+  for (int b0 = 0; b0 < N; b0 += chunk) {
+    const int n = (N - b0) < chunk ? (N - b0) : chunk;
+    Ws w = carve(base, n, c.esz);
+    const void* in = AB;
+    if (!(b0 == 0 && n == N)) {
+      // reuse c3/c2 region? keep it simple: stage the chunk's [A;B] pairs at the start of c1 (dead until conv1 runs)
+      char* stage = w.c1;
+      static_assert(2 * 1600 * 128 >= 2 * 160 * 160 * 8 / 2, "staging fits");
+      FPB_CUDA(cudaMemcpyAsync(stage, (const char*)AB + (size_t)b0 * img, (size_t)n * img, cudaMemcpyDeviceToDevice, c.st));
+      FPB_CUDA(cudaMemcpyAsync(stage + (size_t)n * img, (const char*)AB + (size_t)(N + b0) * img, (size_t)n * img,
+                               cudaMemcpyDeviceToDevice, c.st));
+      in = stage;
+    }
+    RET(run_encoders(c, in, n, w));
+    RET(encoder_layer(c, net->head[0], n, w, out_trans + (size_t)b0 * 3));
+    RET(encoder_layer(c, net->head[1], n, w, out_rot + (size_t)b0 * 3));
+  }
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream)
+{
+  FPB_CHECK_ARG(net && net->kind == FPB_NET_SCORE && AB && ws && out_feat_n512 && N > 0);
+  Ctx c{net, (cudaStream_t)stream, net->precision == FPB_PREC_BF16, (size_t)(net->precision == FPB_PREC_BF16 ? 2 : 4)};
+  const int chunk = net_chunk();
+  char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+  const size_t img = (size_t)160 * 160 * 8 * c.esz;
+  for (int b0 = 0; b0 < N; b0 += chunk) {
+    const int n = (N - b0) < chunk ? (N - b0) : chunk;
+    Ws w = carve(base, n, c.esz);
+    const void* in = AB;
+    if (!(b0 == 0 && n == N)) {
+      char* stage = w.c1;
+      FPB_CUDA(cudaMemcpyAsync(stage, (const char*)AB + (size_t)b0 * img, (size_t)n * img, cudaMemcpyDeviceToDevice, c.st));
+      FPB_CUDA(cudaMemcpyAsync(stage + (size_t)n * img, (const char*)AB + (size_t)(N + b0) * img, (size_t)n * img,
+                               cudaMemcpyDeviceToDevice, c.st));
+      in = stage;
+    }
+    RET(run_encoders(c, in, n, w));
+    const long long R = (long long)n * TOK;
+    RET(run_linear(c, net->att.in, w.d0, R, w.qkv, nullptr, 0, c.bf));
+    RET(run_attention_core(c, w.qkv, n, TOK, TOKP, w.scores, w.P, w.vt, w.ctx, c.bf));
+    RET(run_linear(c, net->att.out, w.ctx, R, w.y1, nullptr, 0, c.bf));
+    RET(token_mean(w.y1, c.bf, out_feat_n512 + (size_t)b0 * D, n, TOK, D, c.st));
+  }
+  return FPB_OK;
+}
+
+// cross-hypothesis attention + Linear(512,1): always fp32 SIMT (0.33 GMAC at L=252)
+FPB_EXPORT int fpb_score_cross(const fpb_net* net, const float* feat, int L, int bs, void* ws, float* out_logits,
+                               void* stream)
+{
+  FPB_CHECK_ARG(net && net->kind == FPB_NET_SCORE && feat && ws && out_logits && L > 0 && bs > 0);
+  cudaStream_t st = (cudaStream_t)stream;
+  Ctx c{net, st, false, 4};
+  const int Lp = (L + 3) & ~3;
+  const long long R = (long long)bs * L;
+  char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+  size_t o = 0;
+  auto take = [&](size_t bytes) { char* p = base + o; o += al(bytes); return p; };
+  float* qkv = (float*)take((size_t)R * 3 * D * 4);
+  float* scores = (float*)take((size_t)bs * HEADS * L * Lp * 4);
+  float* P = (float*)take((size_t)bs * HEADS * L * Lp * 4);
+  float* vt = (float*)take((size_t)bs * HEADS * DH * Lp * 4);
+  float* ctx = (float*)take((size_t)R * D * 4);
+  float* y = (float*)take((size_t)R * D * 4);
+  RET(run_linear(c, net->att_cross.in, feat, R, qkv, nullptr, 0, 0));
+  RET(run_attention_core(c, qkv, bs, L, Lp, scores, P, vt, ctx, false));
+  RET(run_linear(c, net->att_cross.out, ctx, R, y, nullptr, 0, 0));
+  RET(small_linear(y, c.F(net->lin.w), c.F(net->lin.b), out_logits, (int)R, D, 1, st));
+  return FPB_OK;
+}
+
+FPB_EXPORT size_t fpb_score_cross_ws_bytes(int L, int bs)
+{
+  const size_t Lp = (L + 3) & ~3, R = (size_t)bs * L;
+  return al(R * 3 * D * 4) + 2 * al((size_t)bs * HEADS * L * Lp * 4) + al((size_t)bs * HEADS * DH * Lp * 4) + 2 * al(R * D * 4) + 1024;
+}
+
+// Debug / unit-test entry: one implicit GEMM through either kernel family (see GemmProblem).
+//   precision 0: fp32 operands (SIMT); 1: bf16 operands (tcgen05).  out is fp32 unless out_bf16.
+FPB_EXPORT int fpb_debug_igemm(int precision, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
+                               int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad, const float* scale,
+                               const float* shift, const void* residual, int relu, int out_bf16, void* stream)
+{
+  GemmProblem p = gemm_problem_default();
+  p.A = A; p.W = W; p.C = C; p.M = M; p.N = N; p.K = K;
+  p.Hin = Hin; p.Win = Win; p.Cin = Cin; p.Ho = Ho; p.Wo = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
+  p.pix_pitch = Cin; p.ldw = K; p.scale = scale; p.shift = shift; p.residual = residual; p.ldr = N; p.relu = relu;
+  p.ldc = N; p.out_bf16 = out_bf16;
+  return precision ? tc_gemm(p, (cudaStream_t)stream) : ref_gemm(p, (cudaStream_t)stream);
+}

@@ -1,0 +1,205 @@
+"""FoundationPose -- drop-in for src/estimater.py:18-268 on top of libfpb200.so.
+
+register()/track_one() keep every intermediate on the device: depth stencils, masked-depth statistics, xyz map,
+render/warp/refine loop and scoring; the only device->host reads are the 8 statistics of guess_translation and the
+final 4x4 pose (the reference crosses the PCIe bus ~10 times per call).
+"""
+import logging
+import os
+
+import numpy as np
+import torch
+
+from . import mycpp
+from . import utils as U
+from .predict_pose_refine import PoseRefinePredictor
+from .predict_score import ScorePredictor
+
+
+def make_rotation_grid_host(min_n_views=40, inplane_step=60):
+  """src/estimater.py:106-118 before clustering: float64 [n_views*n_inplane, 4, 4] (host numpy, init-time)."""
+  cam_in_obs = U.sample_views_icosphere(n_views=min_n_views)
+  rot_grid = []
+  for i in range(len(cam_in_obs)):
+    for inplane_rot in np.deg2rad(np.arange(0, 360, inplane_step)):
+      cam_in_ob = cam_in_obs[i] @ U.euler_matrix(0, 0, inplane_rot)
+      rot_grid.append(np.linalg.inv(cam_in_ob))
+  return np.asarray(rot_grid)
+
+
+def guess_translation_cuda(depth_t, mask_t, K):
+  """src/estimater.py:137-156 with the reductions (bbox of the mask, exact median of the valid depths) on the
+  device; the 3x3 float64 tail stays on the host.  Returns np.float64 [3]."""
+  if mask_t.dtype != torch.uint8:
+    mask_t = (mask_t > 0).to(torch.uint8)
+  return _center_from_stats(U.mask_depth_stats(depth_t.contiguous(), mask_t.contiguous()), K)
+
+
+def _center_from_stats(stats, K):
+  umin, umax, vmin, vmax, n_mask, n_valid, lo, hi = stats
+  if n_mask == 0:
+    logging.info('mask is all zero')
+    return np.zeros((3))
+  uc = (umin + umax) / 2.0
+  vc = (vmin + vmax) / 2.0
+  if n_valid == 0:
+    logging.info('valid is empty')
+    return np.zeros((3))
+  zc = np.float32(np.float32(lo + hi) / np.float32(2.0))      # np.median of float32 data (mean of the two middles)
+  center = (np.linalg.inv(K) @ np.asarray([uc, vc, 1]).reshape(3, 1)) * zc
+  return center.reshape(3)
+
+
+class FoundationPose:
+  def __init__(self, model_pts, model_normals, symmetry_tfs=None, mesh=None, scorer: ScorePredictor = None,
+               refiner: PoseRefinePredictor = None, glctx=None, debug=0, debug_dir='/tmp/fpb200_debug/',
+               mesh_diameter=None):
+    self.gt_pose = None
+    self.ignore_normal_flip = True
+    self.debug = debug
+    self.debug_dir = debug_dir
+    if debug >= 1:
+      os.makedirs(debug_dir, exist_ok=True)
+    self._diameter_override = mesh_diameter
+    self.reset_object(model_pts, model_normals, symmetry_tfs=symmetry_tfs, mesh=mesh)
+    self.make_rotation_grid(min_n_views=40, inplane_step=60)
+    self.glctx = glctx      # accepted and ignored: there is no nvdiffrast context
+    self.scorer = scorer if scorer is not None else ScorePredictor()
+    self.refiner = refiner if refiner is not None else PoseRefinePredictor()
+    self.pose_last = None   # used for tracking; w.r.t. the centred mesh
+
+  def reset_object(self, model_pts, model_normals, symmetry_tfs=None, mesh=None):
+    """src/estimater.py:44-78 (the open3d voxel down-sampling only feeds utilities off the hot path; kept as a
+    plain numpy grid-average)."""
+    verts = np.asarray(mesh.vertices)
+    max_xyz = verts.max(axis=0)
+    min_xyz = verts.min(axis=0)
+    self.model_center = (min_xyz + max_xyz) / 2
+    self.mesh_ori = mesh.copy()
+    mesh = mesh.copy()
+    mesh.vertices = np.asarray(mesh.vertices) - self.model_center.reshape(1, 3)
+    model_pts = np.asarray(mesh.vertices)
+    if self._diameter_override is not None:
+      self.diameter = float(self._diameter_override)
+    else:
+      self.diameter = U.compute_mesh_diameter(model_pts=model_pts, n_sample=10000)
+    self.vox_size = max(self.diameter / 20.0, 0.003)
+    logging.info(f'self.diameter:{self.diameter}, vox_size:{self.vox_size}')
+    self.dist_bin = self.vox_size / 2
+    self.angle_bin = 20
+    keys = np.floor(model_pts / self.vox_size).astype(np.int64)
+    _, inv = np.unique(keys, axis=0, return_inverse=True)
+    inv = inv.reshape(-1)
+    cnt = np.bincount(inv).astype(np.float64)
+    pts = np.stack([np.bincount(inv, weights=model_pts[:, k]) / cnt for k in range(3)], 1)
+    nrm_src = np.asarray(model_normals) if model_normals is not None else np.asarray(mesh.vertex_normals)
+    nrm = np.stack([np.bincount(inv, weights=nrm_src[:, k]) / cnt for k in range(3)], 1)
+    self.max_xyz = pts.max(axis=0)
+    self.min_xyz = pts.min(axis=0)
+    dev = 'cuda' if torch.cuda.is_available() else 'cpu'
+    self.pts = torch.tensor(pts, dtype=torch.float32, device=dev)
+    self.normals = torch.nn.functional.normalize(torch.tensor(nrm, dtype=torch.float32, device=dev), dim=-1)
+    self.mesh_path = None
+    self.mesh = mesh
+    self.mesh_tensors = U.make_mesh_tensors(self.mesh, device=dev)
+    if symmetry_tfs is None:
+      self.symmetry_tfs = torch.eye(4).float().to(dev)[None]
+    else:
+      self.symmetry_tfs = torch.as_tensor(symmetry_tfs, device=dev, dtype=torch.float)
+    logging.info('reset done')
+
+  def get_tf_to_centered_mesh(self):
+    tf_to_center = torch.eye(4, dtype=torch.float, device='cuda')
+    tf_to_center[:3, 3] = -torch.as_tensor(self.model_center, device='cuda', dtype=torch.float)
+    return tf_to_center
+
+  def to_device(self, s='cuda:0'):
+    for k in self.__dict__:
+      if torch.is_tensor(self.__dict__[k]):
+        self.__dict__[k] = self.__dict__[k].to(s)
+    for k in self.mesh_tensors:
+      if torch.is_tensor(self.mesh_tensors[k]):
+        self.mesh_tensors[k] = self.mesh_tensors[k].to(s)
+
+  def make_rotation_grid(self, min_n_views=40, inplane_step=60):
+    """src/estimater.py:106-124"""
+    rot_grid = make_rotation_grid_host(min_n_views, inplane_step)
+    logging.info(f'rot_grid:{rot_grid.shape}')
+    rot_grid = mycpp.cluster_poses(30, 99999, rot_grid, self.symmetry_tfs.data.cpu().numpy())
+    rot_grid = np.asarray(rot_grid)
+    logging.info(f'after cluster, rot_grid:{rot_grid.shape}')
+    self.rot_grid = torch.as_tensor(rot_grid, device='cuda', dtype=torch.float)
+
+  def generate_random_pose_hypo(self, K, rgb, depth, mask, scene_pts=None):
+    """src/estimater.py:127-134"""
+    ob_in_cams = self.rot_grid.clone()
+    center = self.guess_translation(depth=depth, mask=mask, K=K)
+    ob_in_cams[:, :3, 3] = torch.tensor(center, device='cuda', dtype=torch.float).reshape(1, 3)
+    return ob_in_cams
+
+  def guess_translation(self, depth, mask, K):
+    """src/estimater.py:137-156 (numpy or cuda inputs)."""
+    depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float)
+    mask_t = torch.as_tensor(mask, device='cuda')
+    return guess_translation_cuda(depth_t, mask_t, np.asarray(K, dtype=np.float64))
+
+  @torch.inference_mode()
+  def register(self, K, rgb, depth, ob_mask, ob_id=None, glctx=None, iteration=5):
+    """src/estimater.py:159-240 -> np.ndarray [4,4] float32 (object pose in camera, un-centred mesh frame)."""
+    U.set_seed(0)
+    K = np.asarray(K, dtype=np.float64)
+    depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
+    rgb_t = torch.as_tensor(rgb, device='cuda').contiguous()
+    mask_t = (torch.as_tensor(ob_mask, device='cuda') > 0).to(torch.uint8).contiguous()
+    depth_t = U.erode_depth(depth_t, radius=2, device='cuda')
+    depth_t = U.bilateral_filter_depth(depth_t, radius=2, device='cuda')
+    stats = U.mask_depth_stats(depth_t, mask_t)
+    center = _center_from_stats(stats, K)
+    if stats[5] < 4:
+      logging.info('valid too small, return')
+      pose = np.eye(4)
+      pose[:3, 3] = center
+      return pose
+    self.H, self.W = depth_t.shape[:2]
+    self.K = K
+    self.ob_id = ob_id
+    self.ob_mask = ob_mask
+    poses = self.rot_grid.clone()
+    poses[:, :3, 3] = torch.as_tensor(center.reshape(1, 3), device='cuda', dtype=torch.float)
+    xyz_map = U.depth2xyzmap_cuda(depth_t, K, math_f64=True)
+    poses, _ = self.refiner.predict(mesh=self.mesh, mesh_tensors=self.mesh_tensors, rgb=rgb_t, depth=depth_t, K=K,
+                                    ob_in_cams=poses, normal_map=None, xyz_map=xyz_map, glctx=self.glctx,
+                                    mesh_diameter=self.diameter, iteration=iteration, get_vis=False)
+    scores, _ = self.scorer.predict(mesh=self.mesh, rgb=rgb_t, depth=depth_t, K=K, ob_in_cams=poses, normal_map=None,
+                                    mesh_tensors=self.mesh_tensors, glctx=self.glctx, mesh_diameter=self.diameter,
+                                    get_vis=False)
+    ids = torch.as_tensor(scores).argsort(descending=True)
+    scores = scores[ids]
+    poses = poses[ids]
+    best_pose = poses[0] @ self.get_tf_to_centered_mesh()
+    self.pose_last = poses[0]
+    self.best_id = ids[0]
+    self.poses = poses
+    self.scores = scores
+    return best_pose.data.cpu().numpy()
+
+  def compute_add_err_to_gt_pose(self, poses):
+    return -torch.ones(len(poses), device='cuda', dtype=torch.float)
+
+  @torch.inference_mode()
+  def track_one(self, rgb, depth, K, iteration, extra={}):
+    """src/estimater.py:250-268"""
+    if self.pose_last is None:
+      logging.info('Please init pose by register first')
+      raise RuntimeError
+    K = np.asarray(K, dtype=np.float64)
+    depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
+    depth_t = U.erode_depth(depth_t, radius=2, device='cuda')
+    depth_t = U.bilateral_filter_depth(depth_t, radius=2, device='cuda')
+    xyz_map = U.depth2xyzmap_cuda(depth_t, K.astype(np.float32).astype(np.float64), math_f64=False, zfar=np.inf)
+    pose, _ = self.refiner.predict(mesh=self.mesh, mesh_tensors=self.mesh_tensors, rgb=torch.as_tensor(rgb, device='cuda'),
+                                   depth=depth_t, K=K, ob_in_cams=self.pose_last.reshape(1, 4, 4), normal_map=None,
+                                   xyz_map=xyz_map, mesh_diameter=self.diameter, glctx=self.glctx, iteration=iteration,
+                                   get_vis=False)
+    self.pose_last = pose
+    return (pose @ self.get_tf_to_centered_mesh()).data.cpu().numpy().reshape(4, 4)

@@ -104,12 +104,20 @@ typedef struct fpb_net fpb_net;
 int fpb_net_create(fpb_net** out, int kind, int precision, const void* blob_h, size_t bytes, void* stream);
 int fpb_net_destroy(fpb_net* net);
 size_t fpb_net_ws_bytes(int kind, int precision, int N);
+size_t fpb_net_blob_floats(int kind);              /* expected blob length (host-only helper) */
+size_t fpb_score_cross_ws_bytes(int L, int bs);
 /* AB: [2N,S,S,8] (first N = rendered A, last N = observed B), S = 160 */
 int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
                        void* stream);
 int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream);
 int fpb_score_cross(const fpb_net* net, const float* feat, int L, int bs, void* ws, float* out_logits,
                     void* stream);
+
+/* unit-test entry: one implicit GEMM C = epi(im2col(A) . W^T) through the SIMT fp32 (precision 0) or the
+ * tcgen05 bf16 (precision 1) kernel; A is NHWC [*,Hin,Win,Cin], W is [N][K], K = KH*KW*Cin. */
+int fpb_debug_igemm(int precision, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
+                    int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad, const float* scale,
+                    const float* shift, const void* residual, int relu, int out_bf16, void* stream);
 
 /* number of kernels this library launched on the calling thread since the last reset */
 long long fpb_launch_count(int reset);

@@ -1,0 +1,183 @@
+"""GPU parity tests of the network path through the C ABI.
+  * fpb_debug_igemm: tcgen05 bf16 and SIMT fp32 implicit GEMM vs torch conv2d / matmul on the same operands
+    (bf16 operands are exact in fp32, so the tcgen05 result must match an fp32 reference to accumulation order:
+    tolerance 2e-3 relative to the output scale).
+  * RefineNet / ScoreNet forward, fp32 parity mode vs the fp32 oracle: <= 2e-4 absolute on outputs of O(0.1-1).
+  * bf16 mode vs the fp32 oracle: reported against the north-star bounds (1e-3 rad, 0.1 mm) in test_register_gpu.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _igemm(prec, x_nhwc, w_oihw, stride, pad, scale=None, shift=None, residual=None, relu=0, out_bf16=0):
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  nimg, Hin, Win, Cin = x_nhwc.shape
+  Cout, _, KH, KW = w_oihw.shape
+  Ho = (Hin + 2 * pad - KH) // stride + 1
+  Wo = (Win + 2 * pad - KW) // stride + 1
+  dt = torch.bfloat16 if prec else torch.float
+  A = x_nhwc.to(dt).contiguous()
+  W = w_oihw.permute(0, 2, 3, 1).reshape(Cout, -1).to(dt).contiguous()
+  M, K = nimg * Ho * Wo, KH * KW * Cin
+  C = torch.empty((M, Cout), dtype=torch.bfloat16 if out_bf16 else torch.float, device='cuda')
+  res = residual.to(dt).contiguous() if residual is not None else None
+  check(lib().fpb_debug_igemm(prec, ptr(A), ptr(W), ptr(C), M, Cout, K, Hin, Win, Cin, Ho, Wo, KH, KW, stride, pad,
+                              ptr(scale), ptr(shift), ptr(res), relu, out_bf16, stream()))
+  torch.cuda.synchronize()
+  return C.float().reshape(nimg, Ho, Wo, Cout)
+
+
+def _ref_conv(x_nhwc, w_oihw, stride, pad, scale=None, shift=None, residual=None, relu=0, bf16_ops=False):
+  x, w = x_nhwc, w_oihw
+  if bf16_ops:
+    x, w = x.bfloat16().float(), w.bfloat16().float()
+  y = F.conv2d(x.permute(0, 3, 1, 2).double(), w.double(), None, stride, pad).permute(0, 2, 3, 1)
+  if scale is not None:
+    y = y * scale.double() + shift.double()
+  elif shift is not None:
+    y = y + shift.double()
+  if residual is not None:
+    r = residual.bfloat16().float() if bf16_ops else residual
+    y = y + r.reshape(y.shape).double()
+  if relu:
+    y = torch.relu(y)
+  return y.float()
+
+
+CASES = [
+  # nimg, H, Cin, Cout, k, stride, pad
+  (2, 1, 512, 512, 1, 1, 0),        # plain GEMM, K=512, M=2 (one ragged tile)
+  (300, 1, 512, 1536, 1, 1, 0),     # in_proj shape, M ragged
+  (3, 20, 512, 512, 3, 1, 1),       # 3x3 @512, M=1200
+  (2, 40, 256, 256, 3, 1, 1),       # 3x3 @256
+  (2, 40, 256, 512, 3, 2, 1),       # stride 2
+  (2, 40, 128, 128, 3, 1, 1),       # BN=128 tile
+  (1, 80, 64, 128, 3, 2, 1),        # Cin=64
+  (2, 24, 64, 64, 3, 1, 1),         # BN=64 tile
+]
+
+
+@pytest.mark.parametrize('prec', [0, 1])
+@pytest.mark.parametrize('case', CASES)
+def test_igemm_matches_torch(prec, case):
+  nimg, H, Cin, Cout, k, stride, pad = case
+  g = torch.Generator(device='cuda').manual_seed(hash(case) % 1000)
+  x = torch.randn(nimg, H, H, Cin, device='cuda', generator=g)
+  w = torch.randn(Cout, Cin, k, k, device='cuda', generator=g) / (Cin * k * k) ** 0.5
+  scale = torch.rand(Cout, device='cuda', generator=g) + 0.5
+  shift = torch.randn(Cout, device='cuda', generator=g) * 0.1
+  Ho = (H + 2 * pad - k) // stride + 1
+  res = torch.randn(nimg * Ho * Ho, Cout, device='cuda', generator=g)
+  got = _igemm(prec, x, w, stride, pad, scale, shift, res, relu=1)
+  ref = _ref_conv(x, w, stride, pad, scale, shift, res, relu=1, bf16_ops=bool(prec))
+  err = (got - ref).abs().max().item()
+  assert err < (2e-3 if prec else 2e-4), err
+  got2 = _igemm(prec, x, w, stride, pad)             # no epilogue extras
+  ref2 = _ref_conv(x, w, stride, pad, bf16_ops=bool(prec))
+  assert (got2 - ref2).abs().max().item() < (2e-3 if prec else 2e-4)
+
+
+@pytest.mark.parametrize('prec', [0, 1])
+def test_first_conv_7x7_padded_layout(prec):
+  """7x7 stride-2 conv on the 8-channel padded input with the kernel row padded to 8 taps (csrc/net.cu kConvs[0])."""
+  g = torch.Generator(device='cuda').manual_seed(5)
+  x6 = torch.randn(2, 160, 160, 6, device='cuda', generator=g)
+  w6 = torch.randn(64, 6, 7, 7, device='cuda', generator=g) / (6 * 49) ** 0.5
+  x8 = torch.zeros(2, 160, 160, 8, device='cuda'); x8[..., :6] = x6
+  w8 = torch.zeros(64, 8, 7, 8, device='cuda'); w8[:, :6, :, :7] = w6
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  dt = torch.bfloat16 if prec else torch.float
+  A = x8.to(dt).contiguous()
+  W = w8.permute(0, 2, 3, 1).reshape(64, -1).to(dt).contiguous()
+  C = torch.empty((2 * 80 * 80, 64), dtype=torch.float, device='cuda')
+  check(lib().fpb_debug_igemm(prec, ptr(A), ptr(W), ptr(C), 2 * 6400, 64, 448, 160, 160, 8, 80, 80, 7, 8, 2, 3, None,
+                              None, None, 0, 0, stream()))
+  ref = _ref_conv(x6, w6, 2, 3, bf16_ops=bool(prec))
+  assert (C.reshape(2, 80, 80, 64) - ref).abs().max().item() < (2e-3 if prec else 2e-4)
+
+
+def _inputs(n, seed=0):
+  g = torch.Generator().manual_seed(seed)
+  AB = torch.zeros(2 * n, 160, 160, 8)
+  AB[..., :3] = torch.rand(2 * n, 160, 160, 3, generator=g)
+  AB[..., 3:6] = torch.randn(2 * n, 160, 160, 3, generator=g).clamp(-1.9, 1.9) * 0.5
+  # smooth it a little so it resembles image content
+  AB[..., :6] = F.avg_pool2d(AB[..., :6].permute(0, 3, 1, 2), 5, 1, 2).permute(0, 2, 3, 1)
+  return AB
+
+
+@pytest.mark.parametrize('n', [3, 5])
+def test_refine_fp32_matches_oracle(n, monkeypatch):
+  from foundationpose_b200 import nets
+  from oracle import nets as on
+  sd = nets.synthetic_state_dict(nets.REFINE)
+  AB = _inputs(n, 1)
+  ref_t, ref_r = on.forward_chunked(on.build('refine', sd), 'refine', AB[:n, ..., :6].numpy(), AB[n:, ..., :6].numpy())
+  net = nets.Net(nets.REFINE, sd, 'fp32')
+  t, r = net.refine(AB.cuda(), n)
+  assert np.abs(t.cpu().numpy() - ref_t).max() < 2e-4, np.abs(t.cpu().numpy() - ref_t).max()
+  assert np.abs(r.cpu().numpy() - ref_r).max() < 2e-4, np.abs(r.cpu().numpy() - ref_r).max()
+
+
+def test_refine_bf16_close_to_oracle():
+  from foundationpose_b200 import nets
+  from oracle import nets as on
+  sd = nets.synthetic_state_dict(nets.REFINE)
+  n = 6
+  AB = _inputs(n, 2)
+  ref_t, ref_r = on.forward_chunked(on.build('refine', sd), 'refine', AB[:n, ..., :6].numpy(), AB[n:, ..., :6].numpy())
+  net = nets.Net(nets.REFINE, sd, 'bf16')
+  t, r = net.refine(AB.cuda().bfloat16(), n)
+  et = np.abs(t.cpu().numpy() - ref_t).max(); er = np.abs(r.cpu().numpy() - ref_r).max()
+  print('bf16 refine err trans/rot', et, er, 'scale', np.abs(ref_t).max(), np.abs(ref_r).max())
+  assert et < 0.05 * max(1e-3, np.abs(ref_t).max()) + 5e-3 and er < 0.05 * max(1e-3, np.abs(ref_r).max()) + 5e-3
+
+
+def test_score_fp32_matches_oracle():
+  from foundationpose_b200 import nets
+  from oracle import nets as on
+  sd = nets.synthetic_state_dict(nets.SCORE)
+  n = 5
+  AB = _inputs(n, 3)
+  ref_logit, ref_feat = on.forward_chunked(on.build('score', sd), 'score', AB[:n, ..., :6].numpy(), AB[n:, ..., :6].numpy())
+  net = nets.Net(nets.SCORE, sd, 'fp32')
+  feat = net.score_features(AB.cuda(), n)
+  assert np.abs(feat.cpu().numpy() - ref_feat).max() < 2e-4
+  logit = net.score_cross(feat, n, 1).reshape(-1)
+  assert np.abs(logit.cpu().numpy() - ref_logit).max() < 5e-4
+  # cross attention with two groups (bs=2) equals two independent calls
+  f2 = torch.cat([feat, feat.flip(0)])
+  l2 = net.score_cross(f2, n, 2)
+  assert torch.allclose(l2[0], logit, atol=1e-5) and torch.allclose(l2[1], logit.flip(0), atol=1e-5)
+
+
+def test_score_bf16_close_to_oracle():
+  from foundationpose_b200 import nets
+  from oracle import nets as on
+  sd = nets.synthetic_state_dict(nets.SCORE)
+  n = 6
+  AB = _inputs(n, 4)
+  ref_logit, ref_feat = on.forward_chunked(on.build('score', sd), 'score', AB[:n, ..., :6].numpy(), AB[n:, ..., :6].numpy())
+  net = nets.Net(nets.SCORE, sd, 'bf16')
+  feat = net.score_features(AB.cuda().bfloat16(), n)
+  ef = np.abs(feat.cpu().numpy() - ref_feat).max()
+  print('bf16 score feat err', ef, 'scale', np.abs(ref_feat).max())
+  assert ef < 0.05 * np.abs(ref_feat).max() + 5e-3
+
+
+def test_chunking_is_transparent(monkeypatch):
+  """N larger than the hypothesis chunk gives the same result as chunk-sized calls."""
+  import os, subprocess, sys, json
+  code = ("import torch,sys;sys.path.insert(0,'.');from foundationpose_b200 import nets;from tests.test_nets_gpu import _inputs;"
+          "sd=nets.synthetic_state_dict(0);n=5;AB=_inputs(n,1).cuda().bfloat16();net=nets.Net(0,sd,'bf16');"
+          "t,r=net.refine(AB,n);print(torch.cat([t,r]).cpu().numpy().tolist())")
+  outs = []
+  for chunk in ('2', '42'):
+    env = dict(os.environ, FPB_NET_CHUNK=chunk)
+    out = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, env=env, check=True).stdout
+    outs.append(np.array(json.loads(out.strip().splitlines()[-1])))
+  assert np.abs(outs[0] - outs[1]).max() < 1e-6
