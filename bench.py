@@ -1,0 +1,278 @@
+#!/usr/bin/env python
+"""bench.py -- hypotheses/sec of the render-and-compare path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2]
+  torchrun --nproc-per-node N bench.py --gpus N ...        (one rank per GPU; hypotheses sharded, weak=false)
+
+A step = one full FoundationPose.register(): depth stencils, hypothesis generation, `iteration` x
+[crop windows, batched render, crop/warp, RefineNet, pose update], scorer render/warp, ScoreNet, ranking.
+Workload = BASELINE config 2: synthetic 20,480-face mesh, 640x480 RGB-D, 252 hypotheses, 5 refine iterations,
+160x160 crops, seeded random-init networks, bf16 tensor-core path.
+  value : hypotheses/s with the frame already resident in HBM (device tensors passed to register()).
+  e2e   : same call with HOST numpy buffers (pinned), H2D copies + the D2H read of the pose inside the timed region.
+--impl reference times the CPU restatement of the reference path (oracle/) on the host cores: a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_HYP, ITERS, S = 252, 5, 160
+FLOP_REFINE, FLOP_SCORE = 23.946e9, 21.938e9       # per hypothesis(-iteration), SURVEY 8(d)
+METRIC = 'hypotheses/sec (render+crop+refine+score)'
+
+
+def peaks():
+  p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+  if os.path.exists(p):
+    d = json.load(open(p))
+    return dict(hbm=d['hbm_gbs'], tf_burst=d['bf16_tflops'], tf_sust=d.get('bf16_tflops_sustained', d['bf16_tflops']),
+                src='measured')
+  return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src='fallback')
+
+
+class ClockSampler(threading.Thread):
+  def __init__(self, index=0):
+    super().__init__(daemon=True)
+    self.index, self.samples, self.stop_flag = index, [], False
+
+  def run(self):
+    q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
+        'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+    while not self.stop_flag:
+      try:
+        out = subprocess.run(['nvidia-smi', '-i', str(self.index), f'--query-gpu={q}', '--format=csv,noheader,nounits'],
+                             capture_output=True, text=True, timeout=5).stdout.strip().split(',')
+        self.samples.append([x.strip() for x in out])
+      except Exception:
+        pass
+      time.sleep(0.2)
+
+  def summary(self):
+    if not self.samples:
+      return dict(sm_mhz=None, sm_max_mhz=None, reasons=[])
+    sm = [float(s[0]) for s in self.samples if s[0].replace('.', '').isdigit()]
+    mx = [float(s[1]) for s in self.samples if s[1].replace('.', '').isdigit()]
+    names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+    reasons = sorted({names[i] for s in self.samples for i in range(4) if len(s) > 2 + i and s[2 + i].lower().startswith('active')})
+    return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None, reasons=reasons)
+
+
+def make_estimator(scene, precision='bf16'):
+  from foundationpose_b200 import nets
+  from foundationpose_b200.estimater import FoundationPose
+  from foundationpose_b200.predict_pose_refine import PoseRefinePredictor
+  from foundationpose_b200.predict_score import ScorePredictor
+  sd_r, sd_s = nets.synthetic_state_dict(nets.REFINE), nets.synthetic_state_dict(nets.SCORE)
+  est = FoundationPose(model_pts=scene['mesh'].vertices, model_normals=scene['mesh'].vertex_normals, mesh=scene['mesh'],
+                       refiner=PoseRefinePredictor(state_dict=sd_r, precision=precision),
+                       scorer=ScorePredictor(state_dict=sd_s, precision=precision), mesh_diameter=scene['diameter'])
+  return est, sd_r, sd_s
+
+
+def cpu_sample(scene, sd_r, sd_s, n_hyp, iters):
+  """Oracle (CPU restatement of the reference path) on a bounded sample: n_hyp hypotheses, full register()."""
+  import torch
+  from oracle.pipeline import OracleEstimator
+  from tests.helpers import mesh_np, centered
+  cores = len(os.sched_getaffinity(0))
+  torch.set_num_threads(cores)
+  mesh, _ = centered(scene)
+  orc = OracleEstimator(mesh_np(mesh), scene['diameter'], sd_r, sd_s)
+  t0 = time.perf_counter()
+  orc.register(scene['K'], scene['rgb'], scene['depth'], scene['mask'], iteration=iters, n_hyp=n_hyp)
+  dt = time.perf_counter() - t0
+  return dict(value=n_hyp / dt, unit='hypotheses/s', cores=cores, kind='port', seconds=dt,
+              sample=f'{n_hyp} of {N_HYP} hypotheses through the full register() ({iters} refine iterations + scoring), '
+                     f'torch-CPU fp32 networks + C/OpenMP raster/warp/stencil restatement')
+
+
+def run_reference(args):
+  """--impl reference: the CPU restatement of the reference path on all host cores (rank 0 only)."""
+  rank = int(os.environ.get('RANK', '0'))
+  if rank != 0:
+    return
+  from foundationpose_b200 import synthetic, nets
+  scene = synthetic.make_scene(2)
+  sd_r, sd_s = nets.synthetic_state_dict(nets.REFINE), nets.synthetic_state_dict(nets.SCORE)
+  n_hyp = args.ref_hyps
+  for _ in range(min(args.warmup, 1)):
+    cpu_sample(scene, sd_r, sd_s, 2, 1)
+  vals = []
+  for _ in range(min(args.steps, 3)):
+    vals.append(cpu_sample(scene, sd_r, sd_s, n_hyp, ITERS))
+  best = sorted(vals, key=lambda d: d['seconds'])[len(vals) // 2]
+  line = dict(metric=METRIC, value=best['value'], unit='hypotheses/s', n_gpus=args.gpus, steps=len(vals),
+              warmup=min(args.warmup, 1), ms_per_step=best['seconds'] * 1e3, higher_is_better=True, scaling='weak',
+              vs_baseline=None, dtype='f32', data='synthetic', impl='reference',
+              config=dict(workload=f'cfg2 sample: {n_hyp} of {N_HYP} hypotheses, 20480-face mesh, 640x480, {ITERS} iters'),
+              cpu_baseline=dict(value=best['value'], unit='hypotheses/s', cores=best['cores'], kind='port', sample=best['sample']),
+              e2e=dict(value=best['value'], unit='hypotheses/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+  print(json.dumps(line), flush=True)
+
+
+def time_dominant_kernel(torch, n_rep=20):
+  """CUDA-event timing of the dominant kernel in isolation: tc_gemm_kernel<256,4> on the 3x3 256->256 conv at
+  40x40 over one 42-hypothesis chunk (M=67200, N=256, K=2304); L2 flushed between launches."""
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  nimg, H, C = 42, 40, 256
+  x = torch.randn(nimg, H, H, C, device='cuda').bfloat16()
+  w = (torch.randn(C, 9 * C, device='cuda') / 48).bfloat16()
+  out = torch.empty(nimg * H * H, C, device='cuda', dtype=torch.bfloat16)
+  sc = torch.ones(C, device='cuda'); sh = torch.zeros(C, device='cuda')
+  flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
+  M, K = nimg * H * H, 9 * C
+
+  def launch():
+    check(lib().fpb_debug_igemm(1, ptr(x), ptr(w), ptr(out), M, C, K, H, H, C, H, H, 3, 3, 1, 1, ptr(sc), ptr(sh), None, 1, 1,
+                                stream()))
+  for _ in range(3):
+    launch()
+  ts = []
+  for _ in range(n_rep):
+    flush.zero_()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); launch(); e1.record()
+    torch.cuda.synchronize()
+    ts.append(e0.elapsed_time(e1))
+  ms = float(np.mean(ts))
+  flops = 2.0 * M * C * K
+  return dict(kernel='tc_gemm_kernel<256,4> conv3x3 256->256 @40x40 x42 hyps', ms=ms, flops=flops, tflops=flops / ms / 1e9)
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument('--gpus', type=int, default=1)
+  ap.add_argument('--steps', type=int, default=10)
+  ap.add_argument('--warmup', type=int, default=3)
+  ap.add_argument('--impl', default='ours')
+  ap.add_argument('--ref-hyps', type=int, default=24)
+  ap.add_argument('--cpu-hyps', type=int, default=12)
+  ap.add_argument('--no-cpu-baseline', action='store_true')
+  ap.add_argument('--precision', default='bf16')
+  args = ap.parse_args()
+  if args.impl == 'reference':
+    return run_reference(args)
+
+  import torch
+  import torch.distributed as dist
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  rank = int(os.environ.get('RANK', '0'))
+  local = int(os.environ.get('LOCAL_RANK', '0'))
+  torch.cuda.set_device(local)
+  if world > 1:
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+  from foundationpose_b200 import synthetic
+  from foundationpose_b200 import dist as fdist
+  from foundationpose_b200._lib import lib
+  scene = synthetic.make_scene(2)
+  est, sd_r, sd_s = make_estimator(scene, args.precision)
+  K, rgb, depth, mask = scene['K'], scene['rgb'], scene['depth'], scene['mask']
+  n_hyp = len(est.rot_grid)
+  assert n_hyp == N_HYP
+  # device-resident and pinned-host copies of the frame
+  d_rgb, d_depth, d_mask = torch.as_tensor(rgb).cuda(), torch.as_tensor(depth).cuda(), torch.as_tensor(mask).cuda()
+  p_rgb, p_depth, p_mask = torch.as_tensor(rgb).pin_memory(), torch.as_tensor(depth).pin_memory(), torch.as_tensor(mask).pin_memory()
+  h_rgb, h_depth, h_mask = p_rgb.numpy(), p_depth.numpy(), p_mask.numpy()
+
+  def barrier():
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+
+  def timed(fn, steps, warmup):
+    for _ in range(warmup):
+      fn()
+    barrier()
+    per = []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(steps):
+      s0 = time.perf_counter()
+      fn()
+      per.append(time.perf_counter() - s0)       # register() is synchronous (returns the host pose)
+    e1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    dev_ms = e0.elapsed_time(e1)
+    tot = torch.tensor([max(dev_ms, 0.0), wall * 1e3], device='cuda', dtype=torch.float64)
+    if world > 1:
+      dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    return float(tot[0]), float(tot[1]), per
+
+  # weak scaling: every rank registers its own object (same synthetic frame) -> N * 252 hypotheses per step
+  def step_device():
+    pose = est.register(K=K, rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
+    if world > 1:
+      fdist.gather_best(pose, est.scores[0])
+    return pose
+
+  def step_host():
+    pose = est.register(K=K, rgb=h_rgb, depth=h_depth, ob_mask=h_mask, iteration=ITERS)
+    if world > 1:
+      fdist.gather_best(pose, est.scores[0])
+    return pose
+
+  sampler = ClockSampler(local)
+  if rank == 0:
+    sampler.start()
+  lib().fpb_launch_count(1)
+  dev_ms, wall_ms, per = timed(step_device, args.steps, max(args.warmup, 3))
+  launches = lib().fpb_launch_count(0)
+  e_dev_ms, e_wall_ms, e_per = timed(step_host, args.steps, 1)
+  sampler.stop_flag = True
+  total_hyp = n_hyp * world * args.steps
+  value = total_hyp / (dev_ms / 1e3)
+  e2e_value = total_hyp / (e_wall_ms / 1e3)
+  strong = None
+  if world > 1:
+    def step_strong():
+      return fdist.register_sharded(est, K, h_rgb, h_depth, h_mask, iteration=ITERS)
+    s_dev, s_wall, s_per = timed(step_strong, args.steps, 2)
+    strong = dict(register_ms_p50=float(np.median(s_per) * 1e3), value=n_hyp * args.steps / (s_wall / 1e3), unit='hypotheses/s',
+                  note='one object, 252 hypotheses sharded over the ranks; features + poses all-gathered (NCCL)')
+  if rank != 0:
+    if world > 1:
+      dist.destroy_process_group()
+    return
+  pk = peaks()
+  dom = time_dominant_kernel(torch)
+  step_flops = n_hyp * (ITERS * FLOP_REFINE + FLOP_SCORE)
+  roof = dict(bound='tensor', achieved=dom['tflops'], peak=pk['tf_burst'], unit='TFLOP/s', frac=dom['tflops'] / pk['tf_burst'],
+              traffic=None, kernel=dom['kernel'], ms_per_launch=dom['ms'], flops_per_launch=dom['flops'], peak_source=pk['src'],
+              step_tflops=step_flops * world * args.steps / (dev_ms / 1e3) / 1e12 / world,
+              step_frac_of_sustained=step_flops * args.steps / (dev_ms / 1e3) / 1e12 / pk['tf_sust'])
+  cpu = None
+  if not args.no_cpu_baseline:
+    cpu = cpu_sample(scene, sd_r, sd_s, args.cpu_hyps, ITERS)
+    cpu.pop('seconds')
+  h2d = int(rgb.nbytes + depth.nbytes + mask.nbytes)
+  line = dict(metric=METRIC, value=value, unit='hypotheses/s', n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+              ms_per_step=dev_ms / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='bf16',
+              data='synthetic',
+              config=dict(workload='cfg2: synthetic 20480-face mesh, 640x480 RGB-D, 252 hyps (42 views x 6 in-plane), '
+                                   'est_refine_iter=5, 160x160 crops, full register(); N>1: one object per GPU',
+                          hypotheses=n_hyp, iterations=ITERS, precision=args.precision,
+                          l2='no flush needed: ~4 GB of activations stream through per step (>> 126 MB L2)'),
+              register_ms_p50=float(np.median(per) * 1e3), register_ms_p95=float(np.percentile(per, 95) * 1e3),
+              e2e=dict(value=e2e_value, unit='hypotheses/s', h2d_bytes_per_step=h2d, d2h_bytes_per_step=64 + 32,
+                       register_ms_p50=float(np.median(e_per) * 1e3)),
+              gpu_launches=int(launches), roofline=roof, cpu_baseline=cpu, clocks=sampler.summary())
+  if strong:
+    line['strong'] = strong
+  print(json.dumps(line), flush=True)
+  if world > 1:
+    dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+  main()

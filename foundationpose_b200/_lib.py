@@ -38,7 +38,7 @@ _SIGS = {
   'fpb_net_ws_bytes': (sz, [ci, ci, ci]),
   'fpb_net_blob_floats': (sz, [ci]),
   'fpb_score_cross_ws_bytes': (sz, [ci, ci]),
-  'fpb_debug_igemm': (ci, [ci, vp, vp, vp] + [ci] * 13 + [vp, vp, vp, ci, ci, vp]),
+  'fpb_debug_igemm': (ci, [ci, vp, vp, vp] + [ci] * 12 + [vp, vp, vp, ci, ci, vp]),
   'fpb_refine_forward': (ci, [vp, vp, ci, vp, vp, vp, vp]),
   'fpb_score_features': (ci, [vp, vp, ci, vp, vp, vp]),
   'fpb_score_cross': (ci, [vp, vp, ci, ci, vp, vp, vp]),

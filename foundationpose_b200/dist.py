@@ -1,0 +1,93 @@
+"""Multi-GPU execution of register(): one process per GPU, torch.distributed (NCCL over NVLink / NVSwitch).
+
+Two ways to shard:
+  * by hypothesis (`register_sharded`): every rank renders / refines / encodes its contiguous slice of the N
+    hypotheses; ScoreNet's cross-hypothesis attention needs all N feature vectors, so the [N/R,512] features and
+    the [N/R,4,4] refined poses are all-gathered (two collectives, < 1 MB), then every rank ranks redundantly.
+  * by object (`gather_best`): each rank runs a full register() of its own object; only the best pose + score per
+    object are all-gathered (BASELINE config 5).
+The reference has no distributed code; this is new.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import utils as U
+from .estimater import _center_from_stats
+
+
+def shard_bounds(n, rank, world):
+  """Contiguous, balanced slices: the first n % world ranks get one extra hypothesis."""
+  base, extra = divmod(n, world)
+  lo = rank * base + min(rank, extra)
+  return lo, lo + base + (1 if rank < extra else 0)
+
+
+def all_gather_ragged(x, n_total, world, group=None):
+  """all_gather of per-rank slices produced by shard_bounds (pads to the largest slice)."""
+  if world == 1:
+    return x
+  cap = -(-n_total // world)
+  pad = torch.zeros((cap,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+  pad[:len(x)] = x
+  out = torch.empty((world * cap,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+  dist.all_gather_into_tensor(out, pad, group=group)
+  parts = []
+  for r in range(world):
+    lo, hi = shard_bounds(n_total, r, world)
+    parts.append(out[r * cap:r * cap + (hi - lo)])
+  return torch.cat(parts, dim=0)
+
+
+@torch.inference_mode()
+def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None):
+  """FoundationPose.register (src/estimater.py:159-240) with the hypotheses sharded over the ranks of `group`.
+  Every rank returns the same best pose (np.ndarray [4,4])."""
+  world = dist.get_world_size(group) if dist.is_initialized() else 1
+  rank = dist.get_rank(group) if dist.is_initialized() else 0
+  U.set_seed(0)
+  K = np.asarray(K, dtype=np.float64)
+  depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
+  rgb_t = torch.as_tensor(rgb, device='cuda').contiguous()
+  mask_t = (torch.as_tensor(ob_mask, device='cuda') > 0).to(torch.uint8).contiguous()
+  depth_t = U.erode_depth(depth_t, radius=2, device='cuda')
+  depth_t = U.bilateral_filter_depth(depth_t, radius=2, device='cuda')
+  stats = U.mask_depth_stats(depth_t, mask_t)
+  center = _center_from_stats(stats, K)
+  if stats[5] < 4:
+    pose = np.eye(4)
+    pose[:3, 3] = center
+    return pose
+  n_total = len(est.rot_grid)
+  lo, hi = shard_bounds(n_total, rank, world)
+  poses = est.rot_grid[lo:hi].clone()
+  poses[:, :3, 3] = torch.as_tensor(center.reshape(1, 3), device='cuda', dtype=torch.float)
+  xyz_map = U.depth2xyzmap_cuda(depth_t, K, math_f64=True)
+  if hi > lo:
+    poses, _ = est.refiner.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=rgb_t, depth=depth_t, K=K,
+                                   ob_in_cams=poses, xyz_map=xyz_map, mesh_diameter=est.diameter, iteration=iteration)
+    feats = est.scorer.extract_features(rgb_t, depth_t, K, poses, mesh=est.mesh, mesh_tensors=est.mesh_tensors,
+                                        mesh_diameter=est.diameter)
+  else:
+    feats = torch.zeros((0, 512), dtype=torch.float, device='cuda')
+  feats = all_gather_ragged(feats, n_total, world, group)
+  poses = all_gather_ragged(poses.reshape(-1, 16), n_total, world, group).reshape(-1, 4, 4)
+  scores = est.scorer.score_from_features(feats)
+  ids = scores.argsort(descending=True)
+  est.poses, est.scores = poses[ids], scores[ids]
+  est.pose_last, est.best_id = est.poses[0], ids[0]
+  return (est.poses[0] @ est.get_tf_to_centered_mesh()).data.cpu().numpy()
+
+
+def gather_best(pose, score, group=None):
+  """Object-sharded mode: all_gather of each rank's best pose [4,4] and score -> ([R,4,4], [R])."""
+  world = dist.get_world_size(group) if dist.is_initialized() else 1
+  p = torch.as_tensor(pose, dtype=torch.float, device='cuda').reshape(1, 16)
+  s = torch.as_tensor(score, dtype=torch.float, device='cuda').reshape(1)
+  if world == 1:
+    return p.reshape(1, 4, 4), s
+  P = torch.empty((world, 16), dtype=torch.float, device='cuda')
+  Sc = torch.empty((world,), dtype=torch.float, device='cuda')
+  dist.all_gather_into_tensor(P, p, group=group)
+  dist.all_gather_into_tensor(Sc, s, group=group)
+  return P.reshape(world, 4, 4), Sc

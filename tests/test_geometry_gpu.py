@@ -183,7 +183,7 @@ def test_warp_bit_exact(cfg, mode, scene1, scene2):
     B = U.warp_crops(rgb_t, torch.as_tensor(xyz_map, device='cuda'), torch.as_tensor(d, device='cuda'), poses, params,
                      K, S, scene['diameter'], mode, bf16=False).cpu().numpy()
     assert np.array_equal(B[..., :6], ref) and (B[..., 6:] == 0).all()
-  assert (ref[3] == 0).mean() > 0.3 and np.abs(ref[..., 3:]).max() < 2
+  assert (ref[3] == 0).mean() > 0.2 and np.abs(ref[..., 3:]).max() < 2
 
 
 def test_pose_update_close():
