@@ -181,3 +181,33 @@ def test_chunking_is_transparent(monkeypatch):
     out = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, env=env, check=True).stdout
     outs.append(np.array(json.loads(out.strip().splitlines()[-1])))
   assert np.abs(outs[0] - outs[1]).max() < 1e-6
+
+
+def _golden_inputs(seed, n):
+  from foundationpose_b200.nets import _calibration_batch
+  x = _calibration_batch(torch.Generator().manual_seed(seed), n)            # [2n,6,160,160]
+  AB = torch.zeros(2 * n, 160, 160, 8)
+  AB[..., :6] = x.permute(0, 2, 3, 1)
+  return AB
+
+
+@pytest.mark.parametrize('prec,tol', [('fp32', 2e-4), ('bf16', 2e-2)])
+def test_cuda_nets_match_reference_golden(prec, tol):
+  """CUDA path vs outputs of the reference's own RefineNet / ScoreNetMultiPair (tests/golden/make_golden.py)."""
+  import os
+  from foundationpose_b200 import nets
+  gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+  dt = torch.float if prec == 'fp32' else torch.bfloat16
+  g = np.load(os.path.join(gold, 'refine_net.npz'))
+  n = int(g['n'])
+  net = nets.Net(nets.REFINE, nets.synthetic_state_dict(nets.REFINE), prec)
+  t, r = net.refine(_golden_inputs(int(g['seed']), n).cuda().to(dt), n)
+  assert np.abs(t.cpu().numpy() - g['trans']).max() < tol and np.abs(r.cpu().numpy() - g['rot']).max() < tol
+  g = np.load(os.path.join(gold, 'score_net.npz'))
+  n = int(g['n'])
+  net = nets.Net(nets.SCORE, nets.synthetic_state_dict(nets.SCORE), prec)
+  f = net.score_features(_golden_inputs(int(g['seed']), n).cuda().to(dt), n)
+  assert np.abs(f.cpu().numpy() - g['feats']).max() < tol * max(1.0, float(np.abs(g['feats']).max()))
+  if prec == 'fp32':
+    logit = net.score_cross(f, n, 1).reshape(-1).cpu().numpy()
+    assert np.abs(logit - g['logits'].reshape(-1)).max() < 5e-4
