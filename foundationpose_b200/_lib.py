@@ -30,8 +30,8 @@ _SIGS = {
   'fpb_mesh_create': (ci, [vp, vp, vp, ci, vp, ci, vp, vp, ci, vp, vp, ci, ci, vp]),
   'fpb_mesh_destroy': (ci, [vp]),
   'fpb_render_ws_bytes': (sz, [ci, ci, ci]),
-  'fpb_render_crops': (ci, [vp, vp, vp, ci, ci, cf, cf, vp, vp, ci, vp, vp, vp, vp]),
-  'fpb_warp_crops': (ci, [vp, ci, vp, vp, ci, ci, vp, vp, vp, ci, ci, cf, ci, vp, ci, vp]),
+  'fpb_render_crops': (ci, [vp, vp, vp, ci, ci, cf, cf, vp, vp, ci, ci, ci, vp, vp, vp, vp]),
+  'fpb_warp_crops': (ci, [vp, ci, vp, vp, ci, ci, vp, vp, vp, ci, ci, cf, ci, vp, ci, ci, ci, vp]),
   'fpb_pose_update': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, vp, vp]),
   'fpb_net_create': (ci, [vp, ci, ci, vp, sz, vp]),
   'fpb_net_destroy': (ci, [vp]),
@@ -39,6 +39,7 @@ _SIGS = {
   'fpb_net_blob_floats': (sz, [ci]),
   'fpb_score_cross_ws_bytes': (sz, [ci, ci]),
   'fpb_debug_igemm': (ci, [ci, vp, vp, vp] + [ci] * 12 + [vp, vp, vp, ci, ci, vp]),
+  'fpb_debug_igemm_ex': (ci, [ci, vp, vp, vp] + [ci] * 15 + [vp, vp, vp, ci, ci, vp]),
   'fpb_refine_forward': (ci, [vp, vp, ci, vp, vp, vp, vp]),
   'fpb_score_features': (ci, [vp, vp, ci, vp, vp, vp]),
   'fpb_score_cross': (ci, [vp, vp, ci, ci, vp, vp, vp]),

@@ -23,6 +23,7 @@ UNITS = [
   ('render.cu', ['-fmad=false']),
   ('net_ref.cu', []),
   ('net_tc.cu', []),
+  ('net_tc2.cu', []),
   ('net.cu', []),
 ]
 

@@ -10,8 +10,12 @@
 namespace {
 
 struct ConvSpec { int Cin, Cout, KH, KW, stride, pad, Hin, Ho; };
+// The 7x7 stride-2 stem reads the network input as [imgs,160,IN_PITCH,8] (6 channels padded to 8, IN_XOFF zero
+// pixels left of each row, >= 4 right) so that the 8 taps x 8 channels of one kernel row are 64 CONTIGUOUS
+// elements: it runs as a 7x1 convolution over 161 overlapping "wide pixels" of 64 channels (pad_w = -1).
+constexpr int IN_S = 160, IN_PITCH = 168, IN_XOFF = 4, IN_C = 8;
 const ConvSpec kConvs[15] = {
-    {8, 64, 7, 8, 2, 3, 160, 80},    {64, 128, 3, 3, 2, 1, 80, 40},   {128, 128, 3, 3, 1, 1, 40, 40},
+    {64, 64, 7, 1, 2, 3, 160, 80},   {64, 128, 3, 3, 2, 1, 80, 40},   {128, 128, 3, 3, 1, 1, 40, 40},
     {128, 128, 3, 3, 1, 1, 40, 40},  {128, 128, 3, 3, 1, 1, 40, 40},  {128, 128, 3, 3, 1, 1, 40, 40},
     {256, 256, 3, 3, 1, 1, 40, 40},  {256, 256, 3, 3, 1, 1, 40, 40},  {256, 256, 3, 3, 1, 1, 40, 40},
     {256, 256, 3, 3, 1, 1, 40, 40},  {256, 512, 3, 3, 2, 1, 40, 20},  {512, 512, 3, 3, 1, 1, 20, 20},
@@ -53,7 +57,7 @@ size_t layout(fpb_net* n)
   Cursor c;
   for (int i = 0; i < 15; i++) {
     const ConvSpec& s = kConvs[i];
-    n->conv[i].w = c.take((size_t)s.Cout * s.KH * s.KW * s.Cin);
+    n->conv[i].w = c.take((size_t)s.Cout * s.KH * s.KW * s.Cin);   // stem: 64 x 7 x (8 taps x 8 ch)
     n->conv[i].scale = c.take(s.Cout);
     n->conv[i].shift = c.take(s.Cout);
   }
@@ -80,7 +84,7 @@ int net_chunk()
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("FPB_NET_CHUNK");
-    v = e ? atoi(e) : 42;
+    v = e ? atoi(e) : 256;
     if (v < 1) v = 1;
   }
   return v;
@@ -130,7 +134,12 @@ struct Ctx {
   size_t esz;
   const void* W(size_t off) const { return bf ? (const void*)(net->w16 + off) : (const void*)(net->w32 + off); }
   const float* F(size_t off) const { return net->w32 + off; }
-  int gemm(const GemmProblem& p) const { return bf ? tc_gemm(p, st) : ref_gemm(p, st); }
+  int gemm(const GemmProblem& p) const
+  {
+    if (!bf) return ref_gemm(p, st);
+    const int rc = tc2_gemm(p, st);                       // persistent TMA kernel
+    return rc == FPB_ERR_UNSUPPORTED ? tc_gemm(p, st) : rc;  // batched / odd shapes: cp.async kernel
+  }
 };
 
 #define RET(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
@@ -142,8 +151,10 @@ int run_conv(const Ctx& c, int li, const void* in, int nimg, void* out, const vo
   GemmProblem p = gemm_problem_default();
   p.A = in; p.W = c.W(c.net->conv[li].w); p.C = out;
   p.M = nimg * s.Ho * s.Ho; p.N = s.Cout; p.K = s.KH * s.KW * s.Cin;
-  p.Hin = p.Win = s.Hin; p.Cin = s.Cin; p.Ho = p.Wo = s.Ho; p.KH = s.KH; p.KW = s.KW; p.stride = s.stride; p.pad = s.pad;
+  p.Hin = p.Win = s.Hin; p.Cin = s.Cin; p.Ho = p.Wo = s.Ho; p.KH = s.KH; p.KW = s.KW; p.stride = s.stride;
+  p.pad = p.pad_w = s.pad;
   p.pix_pitch = s.Cin; p.ldw = p.K;
+  if (li == 0) { p.Win = IN_PITCH - 7; p.row_pitch = IN_PITCH; p.pix_pitch = IN_C; p.pad_w = 3 - IN_XOFF; }
   p.scale = c.F(c.net->conv[li].scale); p.shift = c.F(c.net->conv[li].shift);
   p.residual = residual; p.ldr = s.Cout; p.relu = relu;
   if (pe) { p.pe = c.F(c.net->pe); p.pe_rows = TOK; p.pe_ld = D; }
@@ -290,7 +301,7 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
   Ctx c{net, (cudaStream_t)stream, net->precision == FPB_PREC_BF16, (size_t)(net->precision == FPB_PREC_BF16 ? 2 : 4)};
   const int chunk = net_chunk();
   char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
-  const size_t img = (size_t)160 * 160 * 8 * c.esz;
+  const size_t img = (size_t)IN_S * IN_PITCH * IN_C * c.esz;
   // AB holds all N rendered crops first, then all N observed crops; a chunk needs them adjacent -> gather
   for (int b0 = 0; b0 < N; b0 += chunk) {
     const int n = (N - b0) < chunk ? (N - b0) : chunk;
@@ -299,7 +310,7 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
     if (!(b0 == 0 && n == N)) {
       // reuse c3/c2 region? keep it simple: stage the chunk's [A;B] pairs at the start of c1 (dead until conv1 runs)
       char* stage = w.c1;
-      static_assert(2 * 1600 * 128 >= 2 * 160 * 160 * 8 / 2, "staging fits");
+      static_assert(2 * 1600 * 128 >= 2 * IN_S * IN_PITCH * IN_C / 2, "staging fits");
       FPB_CUDA(cudaMemcpyAsync(stage, (const char*)AB + (size_t)b0 * img, (size_t)n * img, cudaMemcpyDeviceToDevice, c.st));
       FPB_CUDA(cudaMemcpyAsync(stage + (size_t)n * img, (const char*)AB + (size_t)(N + b0) * img, (size_t)n * img,
                                cudaMemcpyDeviceToDevice, c.st));
@@ -318,7 +329,7 @@ FPB_EXPORT int fpb_score_features(const fpb_net* net, const void* AB, int N, voi
   Ctx c{net, (cudaStream_t)stream, net->precision == FPB_PREC_BF16, (size_t)(net->precision == FPB_PREC_BF16 ? 2 : 4)};
   const int chunk = net_chunk();
   char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
-  const size_t img = (size_t)160 * 160 * 8 * c.esz;
+  const size_t img = (size_t)IN_S * IN_PITCH * IN_C * c.esz;
   for (int b0 = 0; b0 < N; b0 += chunk) {
     const int n = (N - b0) < chunk ? (N - b0) : chunk;
     Ws w = carve(base, n, c.esz);
@@ -371,16 +382,39 @@ FPB_EXPORT size_t fpb_score_cross_ws_bytes(int L, int bs)
   return al(R * 3 * D * 4) + 2 * al((size_t)bs * HEADS * L * Lp * 4) + al((size_t)bs * HEADS * DH * Lp * 4) + 2 * al(R * D * 4) + 1024;
 }
 
-// Debug / unit-test entry: one implicit GEMM through either kernel family (see GemmProblem).
-//   precision 0: fp32 operands (SIMT); 1: bf16 operands (tcgen05).  out is fp32 unless out_bf16.
+// Debug / unit-test entry: one implicit GEMM through one kernel family (see GemmProblem).
+//   mode 0: fp32 operands (SIMT); 1: bf16 tcgen05 with cp.async producers; 2 / 3: bf16 tcgen05 persistent TMA
+//   kernel with cta_group 1 / 2.  out is fp32 unless out_bf16.  row_pitch / pix_pitch / pad_w: 0 / 0 / pad_h for
+//   dense NHWC; the stem uses (168, 8, -1) with Cin = 64 "wide pixels".
+FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
+                                  int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad_h, int pad_w, int row_pitch,
+                                  int pix_pitch, const float* scale, const float* shift, const void* residual, int relu,
+                                  int out_bf16, void* stream)
+{
+  GemmProblem p = gemm_problem_default();
+  p.A = A; p.W = W; p.C = C; p.M = M; p.N = N; p.K = K;
+  p.Hin = Hin; p.Win = Win; p.Cin = Cin; p.Ho = Ho; p.Wo = Wo; p.KH = KH; p.KW = KW; p.stride = stride;
+  p.pad = pad_h; p.pad_w = pad_w; p.row_pitch = row_pitch; p.pix_pitch = pix_pitch > 0 ? pix_pitch : Cin;
+  p.ldw = K; p.scale = scale; p.shift = shift; p.residual = residual; p.ldr = N; p.relu = relu;
+  p.ldc = N; p.out_bf16 = out_bf16;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (mode) {
+    case 0: return ref_gemm(p, st);
+    case 1: return tc_gemm(p, st);
+    case 2: tc2_force_cta_group(1); break;
+    case 3: tc2_force_cta_group(2); break;
+    default: fpb_set_error("fpb_debug_igemm: unknown mode %d", mode); return FPB_ERR_ARG;
+  }
+  const int rc = tc2_gemm(p, st);
+  tc2_force_cta_group(0);
+  if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_igemm: shape not supported by the TMA kernel");
+  return rc;
+}
+
 FPB_EXPORT int fpb_debug_igemm(int precision, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
                                int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad, const float* scale,
                                const float* shift, const void* residual, int relu, int out_bf16, void* stream)
 {
-  GemmProblem p = gemm_problem_default();
-  p.A = A; p.W = W; p.C = C; p.M = M; p.N = N; p.K = K;
-  p.Hin = Hin; p.Win = Win; p.Cin = Cin; p.Ho = Ho; p.Wo = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
-  p.pix_pitch = Cin; p.ldw = K; p.scale = scale; p.shift = shift; p.residual = residual; p.ldr = N; p.relu = relu;
-  p.ldc = N; p.out_bf16 = out_bf16;
-  return precision ? tc_gemm(p, (cudaStream_t)stream) : ref_gemm(p, (cudaStream_t)stream);
+  return fpb_debug_igemm_ex(precision, A, W, C, M, N, K, Hin, Win, Cin, Ho, Wo, KH, KW, stride, pad, pad, 0, 0, scale, shift,
+                            residual, relu, out_bf16, stream);
 }

@@ -6,7 +6,10 @@
 
 // One implicit-GEMM problem:  C[m][n] = epi( sum_k A(m,k) * W[n][k] )
 //   A(m,k): m -> (img, oy, ox) over Ho x Wo outputs; k -> (ky, kx, c) with c fastest;
-//           element = in[((img*Hin + oy*stride-pad+ky)*Win + ox*stride-pad+kx)*pix_pitch + c]  (0 outside)
+//           element = in[((img*Hin + oy*stride-pad+ky)*row_pitch + ox*stride-pad_w+kx)*pix_pitch + c]  (0 outside
+//           0 <= iy < Hin, 0 <= ix < Win); row_pitch (pixels per image row, 0 -> Win) and a separate, possibly
+//           negative pad_w let the 7x7 stem read "wide pixels" (8 taps x 8 channels = 64 contiguous elements)
+//           out of a row-padded image.
 //   plain GEMM: Hin=Win=Ho=Wo=1, KH=KW=1, Cin=K, pix_pitch = lda.
 //   W: [Ncols][K] row-major (K contiguous).
 // Batched: blockIdx.z = b;  X_off = (b / b_inner) * X_outer + (b % b_inner) * X_inner   (elements)
@@ -18,7 +21,7 @@ struct GemmProblem {
   const void* W;      // fp32 (ref) or bf16 (tc)
   void* C;            // fp32 or bf16 (out_bf16)
   int M, N, K;
-  int Hin, Win, Cin, Ho, Wo, KH, KW, stride, pad, pix_pitch;
+  int Hin, Win, Cin, Ho, Wo, KH, KW, stride, pad, pad_w, row_pitch, pix_pitch;
   int ldw;            // row pitch of W in elements (>= K)
   int batch, b_inner;
   long long A_outer, A_inner, W_outer, W_inner, C_outer, C_inner;
@@ -47,7 +50,9 @@ static inline GemmProblem gemm_problem_default()
 }
 
 int ref_gemm(const GemmProblem& p, cudaStream_t st);   // fp32 SIMT
-int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 accumulate
+int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 accumulate (cp.async producers)
+int tc2_gemm(const GemmProblem& p, cudaStream_t st);   // bf16 tcgen05, persistent TMA kernel; FPB_ERR_UNSUPPORTED -> use tc_gemm
+void tc2_force_cta_group(int cg);                      // tests: 0 = default, 1 / 2 = force
 
 // small ops (fp32 math; io dtype flags)
 int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int cols, int ld_in, int ld_out,

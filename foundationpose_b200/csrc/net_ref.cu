@@ -45,9 +45,9 @@ __global__ void __launch_bounds__(256) ref_gemm_kernel(GemmProblem p)
     if (mrow_ok && k < p.K) {
       const int tap = k / p.Cin, c = k - tap * p.Cin;
       const int ky = tap / p.KW, kx = tap - ky * p.KW;
-      const int iy = oy * p.stride - p.pad + ky, ix = ox * p.stride - p.pad + kx;
+      const int iy = oy * p.stride - p.pad + ky, ix = ox * p.stride - p.pad_w + kx;
       if (iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win)
-        av = *reinterpret_cast<const float4*>(A + ((long long)(img * p.Hin + iy) * p.Win + ix) * p.pix_pitch + c);
+        av = *reinterpret_cast<const float4*>(A + ((long long)(img * p.Hin + iy) * (p.row_pitch > 0 ? p.row_pitch : p.Win) + ix) * p.pix_pitch + c);
     }
     if (wrow_ok && k < p.K) wv = *reinterpret_cast<const float4*>(W + (long long)wn * p.ldw + k);
     As[lk + 0][lr] = av.x; As[lk + 1][lr] = av.y; As[lk + 2][lr] = av.z; As[lk + 3][lr] = av.w;

@@ -154,8 +154,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
       const int r = m - img * hw;
       oy = r / p.Wo; ox = r - oy * p.Wo;
     }
-    const int iy0 = oy * p.stride - p.pad, ix0 = ox * p.stride - p.pad;
-    const long long img_base = (long long)img * p.Hin * p.Win;
+    const int iy0 = oy * p.stride - p.pad, ix0 = ox * p.stride - p.pad_w;
+    const int rp = p.row_pitch > 0 ? p.row_pitch : p.Win;
+    const long long img_base = (long long)img * p.Hin * rp;
     const uint32_t sw = (uint32_t)(pt & 7);
     const bool cin64 = (p.Cin % KC) == 0;
     for (int it = 0; it < nk + LAG; it++) {
@@ -169,7 +170,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
           const int ky = tap / p.KW, kx = tap - ky * p.KW;
           const int iy = iy0 + ky, ix = ix0 + kx;
           const bool ok = m_ok && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win;
-          const __nv_bfloat16* src = ok ? A + (img_base + (long long)iy * p.Win + ix) * p.pix_pitch + c : A;
+          const __nv_bfloat16* src = ok ? A + (img_base + (long long)iy * rp + ix) * p.pix_pitch + c : A;
 #pragma unroll
           for (int j = 0; j < 8; j++) cp_async16(sa + ((j ^ sw) << 4), src + (ok ? j * 8 : 0), ok ? 16u : 0u);
         } else {
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
             const int ky = tap / p.KW, kx = tap - ky * p.KW;
             const int iy = iy0 + ky, ix = ix0 + kx;
             const bool ok = m_ok && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win;
-            const __nv_bfloat16* src = ok ? A + (img_base + (long long)iy * p.Win + ix) * p.pix_pitch + c : A;
+            const __nv_bfloat16* src = ok ? A + (img_base + (long long)iy * rp + ix) * p.pix_pitch + c : A;
             cp_async16(sa + ((j ^ sw) << 4), src, ok ? 16u : 0u);
           }
         }

@@ -1,0 +1,604 @@
+// Persistent, warp-specialised tcgen05 / TMEM / TMA bf16 implicit GEMM for sm_100a (second-generation kernel).
+//   ConvBNReLU / ResnetBasicBlock   learning/models/network_modules.py:37-50, 73-111
+//   encoders + heads                learning/models/refine_network.py:38-70, score_network.py:36-57
+//
+// One CTA (CG=1) or one CTA pair (CG=2, tcgen05 cta_group::2) per SM / TPC, looping over output tiles of
+// (128*CG) x BN.  Roles per CTA (6 warps):
+//   warp 0      TMA producer: A through an im2col tensor map (cp.async.bulk.tensor.4d...im2col: 128 output pixels x
+//               64 channels of one filter tap per request, zero-filled padding) or a tiled 2-D map (plain GEMM);
+//               W through a tiled 2-D map; both land in the 128B-swizzled K-major layout UMMA reads.
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer; accumulators are double-buffered in TMEM
+//               (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i+1.
+//   warps 2-5   epilogue: tcgen05.ld -> folded BN / bias, residual, ReLU, positional embedding -> bf16/fp32 stores.
+// Pipelines: smem full/empty mbarriers (TMA <-> MMA), TMEM full/empty mbarriers (MMA <-> epilogue).
+// In CG=2 mode each CTA loads its own 128 rows of A and half of the W rows; the leader CTA issues the MMAs for
+// both SMs and tcgen05.commit multicasts the barrier arrivals to the pair.
+#include "net_kernels.cuh"
+#include <cuda.h>
+#include <map>
+#include <mutex>
+#include <vector>
+
+namespace {
+
+constexpr int TM = 128;
+constexpr int KC = 64;
+constexpr int NTHREADS = 192;
+constexpr int A_STAGE_BYTES = TM * 128;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+  const uint32_t addr = smem_u32(bar);
+  uint32_t ok = 0;
+  long long t0 = 0;
+  for (uint32_t spin = 0; !ok; spin++) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (!ok && (spin & 1023u) == 1023u) {   // watchdog: a broken pipeline traps instead of hanging the GPU
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 8000000000LL) __trap();
+    }
+  }
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// arrive on the barrier at the same smem offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta)
+{
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "r"(cta)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t cta)
+{
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void cluster_sync_all()
+{
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank()
+{
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+
+// K-major SWIZZLE_128B smem matrix descriptor (see net_tc.cu)
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr)
+{
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n)
+{
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+template <int CG>
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum)
+{
+  if (CG == 1)
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(da), "l"(db), "r"(idesc), "r"(accum)
+        : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(da), "l"(db), "r"(idesc), "r"(accum)
+        : "memory");
+}
+template <int CG>
+__device__ __forceinline__ void umma_commit(uint64_t* bar)
+{
+  if (CG == 1)
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+  else
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"((uint16_t)3)
+        : "memory");
+}
+
+template <int CG>
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t mbar, int x, int y)
+{
+  if (CG == 1)
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+        "l"(map), "r"(mbar), "r"(x), "r"(y)
+        : "memory");
+  else
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+            "r"(dst),
+        "l"(map), "r"(mbar), "r"(x), "r"(y)
+        : "memory");
+}
+template <int CG>
+__device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* map, uint32_t mbar, int c, int w, int h,
+                                                int n, uint16_t ow, uint16_t oh)
+{
+  if (CG == 1)
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+        "l"(map), "r"(mbar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(ow), "h"(oh)
+        : "memory");
+  else
+    asm volatile(
+        "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+        "l"(map), "r"(mbar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(ow), "h"(oh)
+        : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
+{
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct Tc2Params {
+  GemmProblem p;
+  int a_im2col;          // 1: A through the im2col map, 0: tiled 2-D map over [M][K]
+  int lower_w, lower_h;  // im2col bounding-box lower corner (= -pad)
+  int m_tiles, n_tiles;  // tiles of (TM*CG) x BN
+};
+
+template <int STAGES>
+struct SmemCtl {
+  uint64_t full[STAGES];
+  uint64_t empty[STAGES];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+template <int BN, int CG>
+struct Cfg {
+  static constexpr int B_ROWS = BN / CG;                      // W rows loaded by each CTA
+  static constexpr int B_STAGE_BYTES = B_ROWS * 128;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + (int)sizeof(SmemCtl<STAGES>);
+};
+
+template <int BN, int CG>
+__global__ void __launch_bounds__(NTHREADS, 1)
+tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Tc2Params q)
+{
+  using C = Cfg<BN, CG>;
+  constexpr int STAGES = C::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  SmemCtl<STAGES>* ctl = (SmemCtl<STAGES>*)(smem + STAGES * C::STAGE_BYTES);
+  const GemmProblem& p = q.p;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+  const int cluster_id = blockIdx.x / CG, n_clusters = gridDim.x / CG;
+  const int total_tiles = q.m_tiles * q.n_tiles;
+  const int nk = p.K / KC;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; s++) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+    for (int a = 0; a < 2; a++) { mbar_init(&ctl->tmem_full[a], 1); mbar_init(&ctl->tmem_empty[a], 4 * CG); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    if (CG == 1)
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)),
+                   "r"((uint32_t)C::TMEM_COLS)
+                   : "memory");
+    else
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)),
+                   "r"((uint32_t)C::TMEM_COLS)
+                   : "memory");
+    if (CG == 1) asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    else asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (CG == 2) cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (one lane, every CTA)
+    if (lane == 0) {
+      const int hw = p.Ho * p.Wo;
+      uint32_t it = 0;
+      for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+        const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
+        const int m0 = (mt * CG + (int)rank) * TM;
+        const int nrow0 = nt * BN + (int)rank * C::B_ROWS;
+        int cw = 0, ch = 0, img = 0;
+        if (q.a_im2col) {
+          img = m0 / hw;
+          const int r = m0 - img * hw;
+          const int oy = r / p.Wo, ox = r - oy * p.Wo;
+          cw = ox * p.stride + q.lower_w;
+          ch = oy * p.stride + q.lower_h;
+        }
+        for (int kc = 0; kc < nk; kc++, it++) {
+          const int s = it % STAGES;
+          mbar_wait(&ctl->empty[s], ((it / STAGES) & 1) ^ 1);
+          const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
+          const uint32_t sb = sa + A_STAGE_BYTES;
+          uint32_t bar = smem_u32(&ctl->full[s]);
+          if (CG == 2) bar = mapa_u32(bar, 0);            // both CTAs signal the leader's barrier
+          if (rank == 0) mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(CG * C::STAGE_BYTES));
+          const int k0 = kc * KC;
+          if (q.a_im2col) {
+            const int tap = k0 / p.Cin, c0 = k0 - tap * p.Cin;
+            const int ky = tap / p.KW, kx = tap - ky * p.KW;
+            tma_load_im2col<CG>(sa, &mapA, bar, c0, cw, ch, img, (uint16_t)kx, (uint16_t)ky);
+          } else {
+            tma_load_2d<CG>(sa, &mapA, bar, k0, m0);
+          }
+          tma_load_2d<CG>(sb, &mapB, bar, k0, nrow0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA, one lane)
+    if (rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc(TM * CG, BN);
+      uint32_t it = 0, tc = 0;
+      for (int t = cluster_id; t < total_tiles; t += n_clusters, tc++) {
+        const uint32_t acc = tc & 1u;
+        mbar_wait(&ctl->tmem_empty[acc], ((tc >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kc = 0; kc < nk; kc++, it++) {
+          const int s = it % STAGES;
+          mbar_wait(&ctl->full[s], (it / STAGES) & 1);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
+          const uint64_t da = make_desc(sa), db = make_desc(sa + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < KC / 16; k++)
+            umma_bf16<CG>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
+          umma_commit<CG>(&ctl->empty[s]);
+        }
+        umma_commit<CG>(&ctl->tmem_full[acc]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 2..5)
+    const int quarter = warp & 3;                 // TMEM lanes 32*quarter .. +31 are accessible to this warp
+    const int row = quarter * 32 + lane;
+    const int nst = p.n_valid > 0 ? p.n_valid : p.N;
+    uint32_t tc = 0;
+    for (int t = cluster_id; t < total_tiles; t += n_clusters, tc++) {
+      const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
+      const int m = (mt * CG + (int)rank) * TM + row;
+      const int n0 = nt * BN;
+      const uint32_t acc = tc & 1u;
+      mbar_wait(&ctl->tmem_full[acc], (tc >> 1) & 1u);
+      tc_fence_after();
+      const bool m_ok = m < p.M;
+      const long long orow = m_ok ? (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off : 0;
+      const float* pe_row = (p.pe && m_ok) ? p.pe + (long long)(m % p.pe_rows) * p.pe_ld : nullptr;
+      const __nv_bfloat16* res_row = (p.residual && m_ok) ? (const __nv_bfloat16*)p.residual + (long long)m * p.ldr : nullptr;
+#pragma unroll 1
+      for (int chn = 0; chn < BN / 32; chn++) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + (uint32_t)(chn * 32), r);
+        const int nb = n0 + chn * 32;
+        if (!m_ok || nb >= nst) continue;
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]) * p.alpha;
+        const bool full = nb + 32 <= nst;
+        if (p.scale) {
+#pragma unroll
+          for (int i = 0; i < 32; i++)
+            if (full || nb + i < nst) v[i] = v[i] * __ldg(p.scale + nb + i) + (p.shift ? __ldg(p.shift + nb + i) : 0.0f);
+        } else if (p.shift) {
+#pragma unroll
+          for (int i = 0; i < 32; i++)
+            if (full || nb + i < nst) v[i] += __ldg(p.shift + nb + i);
+        }
+        if (res_row) {
+          if (full) {
+#pragma unroll
+            for (int qq = 0; qq < 4; qq++) {
+              const uint4 rv = *reinterpret_cast<const uint4*>(res_row + nb + qq * 8);
+              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rv);
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const float2 f = __bfloat1622float2(h[e]);
+                v[qq * 8 + e * 2] += f.x; v[qq * 8 + e * 2 + 1] += f.y;
+              }
+            }
+          } else {
+            for (int i = 0; i < 32 && nb + i < nst; i++) v[i] += __bfloat162float(res_row[nb + i]);
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int i = 0; i < 32; i++) v[i] = fmaxf(v[i], 0.0f);
+        }
+        if (pe_row) {
+#pragma unroll
+          for (int i = 0; i < 32; i++)
+            if (full || nb + i < nst) v[i] += __ldg(pe_row + nb + i);
+        }
+        if (p.out_bf16) {
+          __nv_bfloat16* o = (__nv_bfloat16*)p.C + orow + nb;
+          if (full) {
+#pragma unroll
+            for (int qq = 0; qq < 4; qq++) {
+              uint4 pk;
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[qq * 8 + 0], v[qq * 8 + 1]), h1 = __floats2bfloat162_rn(v[qq * 8 + 2], v[qq * 8 + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[qq * 8 + 4], v[qq * 8 + 5]), h3 = __floats2bfloat162_rn(v[qq * 8 + 6], v[qq * 8 + 7]);
+              pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
+              pk.z = *reinterpret_cast<uint32_t*>(&h2); pk.w = *reinterpret_cast<uint32_t*>(&h3);
+              *reinterpret_cast<uint4*>(o + qq * 8) = pk;
+            }
+          } else {
+            for (int i = 0; i < 32 && nb + i < nst; i++) o[i] = __float2bfloat16(v[i]);
+          }
+        } else {
+          float* o = (float*)p.C + orow + nb;
+          if (full) {
+#pragma unroll
+            for (int qq = 0; qq < 8; qq++)
+              *reinterpret_cast<float4*>(o + qq * 4) = make_float4(v[qq * 4], v[qq * 4 + 1], v[qq * 4 + 2], v[qq * 4 + 3]);
+          } else {
+            for (int i = 0; i < 32 && nb + i < nst; i++) o[i] = v[i];
+          }
+        }
+      }
+      // release this accumulator buffer to the MMA issuer (leader CTA's barrier)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (CG == 1) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&ctl->tmem_empty[acc])) : "memory");
+        else mbar_arrive_cluster(&ctl->tmem_empty[acc], 0);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (CG == 2) cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    if (CG == 1)
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS) : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side: tensor maps (driver entry points resolved at run time; no -lcuda link dependency)
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_tiled = nullptr;
+EncodeIm2colFn g_im2col = nullptr;
+int g_num_sms = 0;
+
+int resolve_driver()
+{
+  static std::once_flag once;
+  static int rc = FPB_OK;
+  std::call_once(once, [] {
+    cudaDriverEntryPointQueryResult qr;
+    void* f = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) != cudaSuccess || !f) { rc = FPB_ERR_CUDA; return; }
+    g_tiled = (EncodeTiledFn)f;
+    f = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &f, cudaEnableDefault, &qr) != cudaSuccess || !f) { rc = FPB_ERR_CUDA; return; }
+    g_im2col = (EncodeIm2colFn)f;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+  });
+  if (rc) fpb_set_error("cuTensorMapEncode* driver entry points are unavailable");
+  return rc;
+}
+
+struct MapKey {
+  const void* ptr;
+  long long v[12];
+  bool operator<(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) < 0; }
+};
+std::mutex g_map_mu;
+std::map<MapKey, CUtensorMap> g_maps;
+
+// tiled 2-D map over a row-major [rows][pitch] bf16 matrix; box = 64 columns x box_rows rows, 128B swizzle
+int get_tiled_map(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, CUtensorMap* out)
+{
+  MapKey k;
+  memset(&k, 0, sizeof(k));
+  k.ptr = ptr; k.v[0] = 1; k.v[1] = rows; k.v[2] = cols; k.v[3] = pitch; k.v[4] = box_rows;
+  std::lock_guard<std::mutex> lk(g_map_mu);
+  auto itf = g_maps.find(k);
+  if (itf != g_maps.end()) { *out = itf->second; return FPB_OK; }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+  cuuint32_t box[2] = {(cuuint32_t)KC, (cuuint32_t)box_rows};
+  cuuint32_t es[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = g_tiled(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)ptr, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                       CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fpb_set_error("cuTensorMapEncodeTiled failed (%d): rows=%lld cols=%lld pitch=%lld box_rows=%d", (int)r, rows, cols, pitch, box_rows);
+    return FPB_ERR_CUDA;
+  }
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps[k] = m;
+  *out = m;
+  return FPB_OK;
+}
+
+// im2col map over an NHWC bf16 activation: 128 output pixels x 64 channels per request
+int get_im2col_map(const GemmProblem& p, int nimg, CUtensorMap* out)
+{
+  const int row_pitch = p.row_pitch > 0 ? p.row_pitch : p.Win;
+  MapKey k;
+  memset(&k, 0, sizeof(k));
+  k.ptr = p.A; k.v[0] = 2; k.v[1] = nimg; k.v[2] = p.Hin; k.v[3] = p.Win; k.v[4] = p.Cin; k.v[5] = p.pix_pitch;
+  k.v[6] = p.KH; k.v[7] = p.KW; k.v[8] = p.stride; k.v[9] = p.pad; k.v[10] = p.pad_w; k.v[11] = ((long long)row_pitch << 20) | (p.Ho << 10) | p.Wo;
+  std::lock_guard<std::mutex> lk(g_map_mu);
+  auto itf = g_maps.find(k);
+  if (itf != g_maps.end()) { *out = itf->second; return FPB_OK; }
+  cuuint64_t dims[4] = {(cuuint64_t)p.Cin, (cuuint64_t)p.Win, (cuuint64_t)p.Hin, (cuuint64_t)nimg};
+  cuuint64_t strides[3] = {(cuuint64_t)p.pix_pitch * 2, (cuuint64_t)row_pitch * p.pix_pitch * 2,
+                           (cuuint64_t)p.Hin * row_pitch * p.pix_pitch * 2};
+  // bounding box of the filter-window origin: [lower, dim - 1 + upper]; it must hold exactly Wo x Ho origins
+  int lower[2] = {-p.pad_w, -p.pad};
+  int upper[2] = {(p.Wo - 1) * p.stride - p.pad_w - (p.Win - 1), (p.Ho - 1) * p.stride - p.pad - (p.Hin - 1)};
+  cuuint32_t es[4] = {1, (cuuint32_t)p.stride, (cuuint32_t)p.stride, 1};
+  CUtensorMap m;
+  CUresult r = g_im2col(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, (void*)p.A, dims, strides, lower, upper, (cuuint32_t)KC,
+                        (cuuint32_t)TM, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fpb_set_error("cuTensorMapEncodeIm2col failed (%d): nimg=%d H=%d W=%d C=%d pitch=%d k=%dx%d s=%d pad=%d,%d", (int)r, nimg,
+                  p.Hin, p.Win, p.Cin, p.pix_pitch, p.KH, p.KW, p.stride, p.pad, p.pad_w);
+    return FPB_ERR_CUDA;
+  }
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps[k] = m;
+  *out = m;
+  return FPB_OK;
+}
+
+template <int BN, int CG>
+int launch_tc2(const CUtensorMap& mA, const CUtensorMap& mB, const Tc2Params& q, cudaStream_t st)
+{
+  using C = Cfg<BN, CG>;
+  static bool configured = false;
+  if (!configured) {
+    FPB_CUDA(cudaFuncSetAttribute(tc2_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    configured = true;
+  }
+  const int total = q.m_tiles * q.n_tiles;
+  int clusters = g_num_sms / CG;
+  if (clusters > total) clusters = total;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(clusters * CG, 1, 1);
+  cfg.blockDim = dim3(NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = C::SMEM;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  FPB_CUDA(cudaLaunchKernelEx(&cfg, tc2_kernel<BN, CG>, mA, mB, q));
+  fpb_count_launch();
+  return FPB_OK;
+}
+
+int g_force_cg = 0;
+
+int tc2_cta_group()
+{
+  if (g_force_cg) return g_force_cg;
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("FPB_TC_CTA_GROUP");
+    v = e ? atoi(e) : 2;
+    if (v != 1 && v != 2) v = 2;
+  }
+  return v;
+}
+
+}  // namespace
+
+void tc2_force_cta_group(int cg) { g_force_cg = cg; }
+
+// Returns FPB_ERR_UNSUPPORTED (without setting up anything) when the problem does not fit this kernel, so the
+// caller can fall back to the first-generation cp.async kernel (tc_gemm).
+int tc2_gemm(const GemmProblem& p, cudaStream_t st)
+{
+  if (p.batch != 1 || p.K % KC != 0 || p.Cin % KC != 0 || p.pix_pitch % 8 != 0 || p.ldw % 8 != 0) return FPB_ERR_UNSUPPORTED;
+  if (((uintptr_t)p.A | (uintptr_t)p.W) & 15) return FPB_ERR_UNSUPPORTED;
+  const bool plain = p.KH == 1 && p.KW == 1 && p.stride == 1 && p.pad == 0 && p.pad_w == 0 && p.Ho == 1 && p.Wo == 1;
+  if (!plain && (p.pad > 127 || p.KH > 127)) return FPB_ERR_UNSUPPORTED;
+  int rc = resolve_driver();
+  if (rc) return rc;
+  const int ncols = p.n_valid > 0 ? p.n_valid : p.N;
+  const int BN = (ncols % 256 == 0 || ncols > 384) ? 256 : (ncols > 64 ? 128 : 64);
+  int CG = tc2_cta_group();
+  if (BN / CG < 64) CG = 1;                        // keep >= 64 W rows per CTA
+  Tc2Params q;
+  q.p = p;
+  q.a_im2col = plain ? 0 : 1;
+  q.lower_w = -p.pad_w; q.lower_h = -p.pad;
+  q.m_tiles = fpb_cdiv(p.M, TM * CG);
+  q.n_tiles = fpb_cdiv(ncols, BN);
+  CUtensorMap mA, mB;
+  if (plain) {
+    rc = get_tiled_map(p.A, p.M, p.K, p.pix_pitch, TM, &mA);
+  } else {
+    const int nimg = fpb_cdiv(p.M, p.Ho * p.Wo);
+    rc = get_im2col_map(p, nimg, &mA);
+  }
+  if (rc) return rc;
+  rc = get_tiled_map(p.W, p.N, p.K, p.ldw, BN / CG, &mB);
+  if (rc) return rc;
+#define TC2_LAUNCH(BN_, CG_) return launch_tc2<BN_, CG_>(mA, mB, q, st)
+  if (CG == 2) {
+    if (BN == 256) TC2_LAUNCH(256, 2);
+    TC2_LAUNCH(128, 2);
+  }
+  if (BN == 256) TC2_LAUNCH(256, 1);
+  if (BN == 128) TC2_LAUNCH(128, 1);
+  TC2_LAUNCH(64, 1);
+#undef TC2_LAUNCH
+}

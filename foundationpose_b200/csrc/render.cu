@@ -242,7 +242,8 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
                                                     const float4* __restrict__ camd,
                                                     const unsigned long long* __restrict__ zbuf,
                                                     const float* __restrict__ poses, int N, int S, float inv_radius,
-                                                    float zthr, void* __restrict__ outA, float* __restrict__ out_color,
+                                                    float zthr, void* __restrict__ outA, int out_pitch, int out_xoff,
+                                                    float* __restrict__ out_color,
                                                     float* __restrict__ out_xyz, int32_t* __restrict__ out_tri)
 {
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -308,7 +309,7 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
 #pragma unroll
   for (int k = 0; k < 3; k++) v6[k] = (col[k] * 255.0f) / 255.0f;
   xyz_norm(xyz, poses + (size_t)n * 16, inv_radius, zthr, v6 + 3);
-  store_px8<BF16>(outA, idx, v6);
+  store_px8<BF16>(outA, ((size_t)n * S + i) * out_pitch + out_xoff + j, v6);
 }
 
 __device__ __forceinline__ int nearest_src(float p, float scale, int size)
@@ -324,7 +325,8 @@ template <bool BF16, bool U8>
 __global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_, const float* __restrict__ xyz_map,
                                                    const float* __restrict__ depth, int H, int W,
                                                    const float* __restrict__ poses, const float* __restrict__ params, K9f K,
-                                                   int N, int S, float inv_radius, int mode, void* __restrict__ outB)
+                                                   int N, int S, float inv_radius, int mode, void* __restrict__ outB,
+                                                   int out_pitch, int out_xoff)
 {
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t total = (size_t)N * S * S;
@@ -384,7 +386,7 @@ __global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_
     }
   }
   xyz_norm(xyz, poses + (size_t)n * 16, inv_radius, zthr, v6 + 3);
-  store_px8<BF16>(outB, idx, v6);
+  store_px8<BF16>(outB, ((size_t)n * S + i) * out_pitch + out_xoff + j, v6);
 }
 
 }  // namespace
@@ -445,10 +447,11 @@ FPB_EXPORT size_t fpb_render_ws_bytes(int N, int V, int S)
 }
 
 FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
-                                float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, float* out_color,
-                                float* out_xyz, int32_t* out_tri, void* stream)
+                                float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch,
+                                int out_xoff, float* out_color, float* out_xyz, int32_t* out_tri, void* stream)
 {
   FPB_CHECK_ARG(mesh && poses && params && ws && out_A && N > 0 && S > 1 && S <= 4096 && N <= 65535);
+  FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff);
   cudaStream_t st = (cudaStream_t)stream;
   const int V = mesh->V, F = mesh->F;
   char* w = (char*)ws;
@@ -463,20 +466,22 @@ FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const 
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
   const int blocks = fpb_cdiv((long long)N * S * S, 256);
   if (a_is_bf16)
-    shade_kernel<true><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_color,
-                                               out_xyz, out_tri);
+    shade_kernel<true><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
+                                               out_xoff, out_color, out_xyz, out_tri);
   else
-    shade_kernel<false><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_color,
-                                                out_xyz, out_tri);
+    shade_kernel<false><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
+                                                out_xoff, out_color, out_xyz, out_tri);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }
 
 FPB_EXPORT int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_hw3, const float* depth_hw, int H, int W,
                               const float* poses, const float* params, const float* K9_h, int N, int S,
-                              float mesh_diameter, int mode, void* out_B, int b_is_bf16, void* stream)
+                              float mesh_diameter, int mode, void* out_B, int b_is_bf16, int out_pitch, int out_xoff,
+                              void* stream)
 {
   FPB_CHECK_ARG(rgb && poses && params && K9_h && out_B && N > 0 && S > 1 && H > 1 && W > 1);
+  FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff);
   FPB_CHECK_ARG(mode == 0 ? xyz_hw3 != nullptr : depth_hw != nullptr);
   cudaStream_t st = (cudaStream_t)stream;
   K9f K;
@@ -485,7 +490,7 @@ FPB_EXPORT int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_h
   const int blocks = fpb_cdiv((long long)N * S * S, 256);
 #define LAUNCH_WARP(BF, U8)                                                                                         \
   warp_kernel<BF, U8><<<blocks, 256, 0, st>>>(rgb, xyz_hw3, depth_hw, H, W, poses, params, K, N, S, inv_radius, mode, \
-                                              out_B)
+                                              out_B, out_pitch, out_xoff)
   if (b_is_bf16) { if (rgb_is_u8) LAUNCH_WARP(true, true); else LAUNCH_WARP(true, false); }
   else           { if (rgb_is_u8) LAUNCH_WARP(false, true); else LAUNCH_WARP(false, false); }
 #undef LAUNCH_WARP

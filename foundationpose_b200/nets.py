@@ -205,6 +205,15 @@ def _calibrate_batchnorm(kind, sd, g):
     x = conv_bn(i + 1, conv_bn(i, x), residual=x)
 
 
+def pad_input(AB):
+  """Dense [n,160,160,8] -> row-padded [n,160,168,8] (no-op if already padded); test convenience."""
+  if AB.shape[2] == 168:
+    return AB
+  out = torch.zeros((AB.shape[0], 160, 168, 8), dtype=AB.dtype, device=AB.device)
+  out[:, :, 4:164] = AB
+  return out
+
+
 class Net:
   """Device-side network handle (fpb_net) plus its workspace."""
 
@@ -231,15 +240,17 @@ class Net:
     return self._ws
 
   def refine(self, AB, N):
-    """AB [2N,160,160,8] -> (trans [N,3], rot [N,3]) fp32"""
-    assert AB.dtype == self.act_dtype and AB.shape == (2 * N, 160, 160, 8)
+    """AB [2N,160,168,8] (utils.net_input_buffer layout) -> (trans [N,3], rot [N,3]) fp32"""
+    AB = pad_input(AB)
+    assert AB.dtype == self.act_dtype and AB.shape == (2 * N, 160, 168, 8)
     trans = torch.empty((N, 3), dtype=torch.float, device='cuda')
     rot = torch.empty((N, 3), dtype=torch.float, device='cuda')
     check(lib().fpb_refine_forward(self.handle, ptr(AB), N, ptr(self.workspace(N)), ptr(trans), ptr(rot), stream()))
     return trans, rot
 
   def score_features(self, AB, N):
-    assert AB.dtype == self.act_dtype and AB.shape == (2 * N, 160, 160, 8)
+    AB = pad_input(AB)
+    assert AB.dtype == self.act_dtype and AB.shape == (2 * N, 160, 168, 8)
     feat = torch.empty((N, D), dtype=torch.float, device='cuda')
     check(lib().fpb_score_features(self.handle, ptr(AB), N, ptr(self.workspace(N)), ptr(feat), stream()))
     return feat

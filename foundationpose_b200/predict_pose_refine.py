@@ -40,7 +40,7 @@ def load_checkpoint_state_dict(path):
 def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_ratio, xyz_map, normal_map=None,
                          mesh_diameter=None, cfg=None, glctx=None, mesh_tensors=None, dataset=None, out_AB=None,
                          bf16=True):
-  """reference :26-89 fused: returns (AB [2N,S,S,8] with the rendered crops first and the observed crops second,
+  """reference :26-89 fused: returns (AB [2N,S,S+8,8] with the rendered crops first and the observed crops second,
   params [N,40]).  rgb uint8/float cuda [H,W,3], xyz_map cuda [H,W,3]."""
   S = int(render_size[0])
   H, W = rgb.shape[:2]
@@ -49,7 +49,7 @@ def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_rati
     mesh_tensors = U.make_mesh_tensors(mesh)
   params = U.crop_params(ob_in_cams, K, mesh_diameter, crop_ratio, S, H, W)
   if out_AB is None:
-    out_AB = torch.empty((2 * N, S, S, 8), dtype=torch.bfloat16 if bf16 else torch.float, device='cuda')
+    out_AB = U.net_input_buffer(N, S, torch.bfloat16 if bf16 else torch.float)
   U.render_crops(mesh_tensors, ob_in_cams, params, S, mesh_diameter, 0.001, out_A=out_AB[:N])
   U.warp_crops(rgb, xyz_map, None, ob_in_cams, params, K, S, mesh_diameter, 0, out_B=out_AB[N:])
   return out_AB, params
@@ -84,7 +84,7 @@ class PoseRefinePredictor:
 
   def _ab_buffer(self, N, S):
     if self._ab is None or self._ab.shape[0] != 2 * N or self._ab.shape[1] != S:
-      self._ab = torch.empty((2 * N, S, S, 8), dtype=self.model.act_dtype, device='cuda')
+      self._ab = U.net_input_buffer(N, S, self.model.act_dtype)
     return self._ab
 
   @torch.inference_mode()

@@ -23,7 +23,7 @@ def default_score_cfg():
 
 def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_ratio, normal_map=None, mesh_diameter=None,
                          glctx=None, mesh_tensors=None, dataset=None, cfg=None, out_AB=None, bf16=True):
-  """reference :57-114 + TripletH5Dataset.transform_batch fused -> (AB [2N,S,S,8], params)."""
+  """reference :57-114 + TripletH5Dataset.transform_batch fused -> (AB [2N,S,S+8,8], params)."""
   S = int(render_size[0])
   H, W = rgb.shape[:2]
   N = len(ob_in_cams)
@@ -31,7 +31,7 @@ def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_rati
     mesh_tensors = U.make_mesh_tensors(mesh)
   params = U.crop_params(ob_in_cams, K, mesh_diameter, crop_ratio, S, H, W)
   if out_AB is None:
-    out_AB = torch.empty((2 * N, S, S, 8), dtype=torch.bfloat16 if bf16 else torch.float, device='cuda')
+    out_AB = U.net_input_buffer(N, S, torch.bfloat16 if bf16 else torch.float)
   U.render_crops(mesh_tensors, ob_in_cams, params, S, mesh_diameter, 0.1, out_A=out_AB[:N])
   U.warp_crops(rgb, None, depth, ob_in_cams, params, K, S, mesh_diameter, 1, out_B=out_AB[N:])
   return out_AB, params
@@ -63,7 +63,7 @@ class ScorePredictor:
 
   def _ab_buffer(self, N, S):
     if self._ab is None or self._ab.shape[0] != 2 * N or self._ab.shape[1] != S:
-      self._ab = torch.empty((2 * N, S, S, 8), dtype=self.model.act_dtype, device='cuda')
+      self._ab = U.net_input_buffer(N, S, self.model.act_dtype)
     return self._ab
 
   @torch.inference_mode()

@@ -322,8 +322,19 @@ def mesh_handle_of(mesh_tensors):
 # ------------------------------------------------------------------------------------------------
 # render / warp / pose update
 # ------------------------------------------------------------------------------------------------
+IN_PITCH, IN_XOFF = 168, 4      # FPB_IN_PITCH / FPB_IN_XOFF of include/fpb200.h (S = 160)
+
+
+def net_input_buffer(N, S, dtype):
+  """Zeroed [2N,S,S+8,8] network input: rendered crops first, observed crops second; rows padded so the 7x7 stem can
+  read 8 taps x 8 channels as one 128-byte vector (csrc/net.cu).  Pad pixels stay zero (kernels never write them)."""
+  assert S + 2 * IN_XOFF == IN_PITCH
+  return torch.zeros((2 * N, S, IN_PITCH, 8), dtype=dtype, device='cuda')
+
+
 def render_crops(mesh_tensors, poses, params, S, mesh_diameter, zthr, out_A=None, bf16=True, debug=False):
-  """Render all N hypotheses at crop resolution and write network input A ([N,S,S,8]).
+  """Render all N hypotheses at crop resolution and write network input A ([N,S,P,8]; P = S for a dense buffer,
+  P = IN_PITCH for the row-padded layout the networks read, see net_input_buffer).
   Returns (A, extras) where extras holds fp32 color/xyz/tri when debug=True."""
   mh = mesh_handle_of(mesh_tensors)
   poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
@@ -339,7 +350,8 @@ def render_crops(mesh_tensors, poses, params, S, mesh_diameter, zthr, out_A=None
     t = torch.empty((N, S, S), dtype=torch.int32, device='cuda')
     extras = dict(color=c, xyz=x, tri=t)
   check(lib().fpb_render_crops(mh.handle, ptr(poses), ptr(params), N, S, float(mesh_diameter), float(zthr), ptr(ws),
-                               ptr(out_A), 1 if out_A.dtype == torch.bfloat16 else 0, ptr(c), ptr(x), ptr(t), stream()))
+                               ptr(out_A), 1 if out_A.dtype == torch.bfloat16 else 0, out_A.shape[2],
+                               (out_A.shape[2] - S) // 2, ptr(c), ptr(x), ptr(t), stream()))
   return out_A, extras
 
 
@@ -356,7 +368,8 @@ def warp_crops(rgb_t, xyz_map_t, depth_t, poses, params, K, S, mesh_diameter, mo
     rgb_t = rgb_t.float().contiguous()
   check(lib().fpb_warp_crops(ptr(rgb_t), 1 if is_u8 else 0, ptr(xyz_map_t), ptr(depth_t), H, W, ptr(poses), ptr(params),
                              hptr(K9), N, S, float(mesh_diameter), mode, ptr(out_B),
-                             1 if out_B.dtype == torch.bfloat16 else 0, stream()))
+                             1 if out_B.dtype == torch.bfloat16 else 0, out_B.shape[2], (out_B.shape[2] - S) // 2,
+                             stream()))
   return out_B
 
 

@@ -74,13 +74,14 @@ int fpb_mesh_destroy(fpb_mesh* m);
 /* ---- batched render at crop resolution + fused shading into network input A:
  *      nvdiffrast_render src/Utils.py:133-219 + rgb*255 (predict_pose_refine.py:56) +
  *      transform_batch (h5_dataset.py:79-127 / 137-179).
- *      ws must hold fpb_render_ws_bytes(N,V,S) bytes.  out_A: [N,S,S,8] bf16 or fp32
- *      (a_is_bf16).  Optional fp32 debug outputs (may be NULL): color [N,S,S,3],
+ *      ws must hold fpb_render_ws_bytes(N,V,S) bytes.  out_A: [N,S,out_pitch,8] bf16 or fp32
+ *      (a_is_bf16); crop column j is written at pixel column out_xoff + j (the networks take
+ *      out_pitch = FPB_IN_PITCH, out_xoff = FPB_IN_XOFF; pad pixels are never written).  Optional fp32 debug outputs (may be NULL): color [N,S,S,3],
  *      xyz [N,S,S,3] (camera frame, un-normalised), tri [N,S,S] int32 (face id + 1). ---- */
 size_t fpb_render_ws_bytes(int N, int V, int S);
 int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
-                     float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16,
-                     float* out_color, float* out_xyz, int32_t* out_tri, void* stream);
+                     float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch,
+                     int out_xoff, float* out_color, float* out_xyz, int32_t* out_tri, void* stream);
 
 /* ---- observed-side crops into network input B: kornia warp_perspective call sites
  *      predict_pose_refine.py:63,72; predict_score.py:89-90; h5_dataset.py:137-170.
@@ -88,7 +89,8 @@ int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* para
  *      rgb: uint8 [H,W,3] (rgb_is_u8) or fp32 [H,W,3] in 0..255. ---- */
 int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_hw3, const float* depth_hw, int H, int W,
                    const float* poses, const float* params, const float* K9_h, int N, int S,
-                   float mesh_diameter, int mode, void* out_B, int b_is_bf16, void* stream);
+                   float mesh_diameter, int mode, void* out_B, int b_is_bf16, int out_pitch, int out_xoff,
+                   void* stream);
 
 /* ---- pose update: predict_pose_refine.py:195-231, egocentric_delta_pose_to_pose
  *      src/Utils.py:848-855, pytorch3d so3_exp_map.  tn3_h used when !normalize_xyz. ---- */
@@ -106,18 +108,27 @@ int fpb_net_destroy(fpb_net* net);
 size_t fpb_net_ws_bytes(int kind, int precision, int N);
 size_t fpb_net_blob_floats(int kind);              /* expected blob length (host-only helper) */
 size_t fpb_score_cross_ws_bytes(int L, int bs);
-/* AB: [2N,S,S,8] (first N = rendered A, last N = observed B), S = 160 */
+/* AB: [2N,S,FPB_IN_PITCH,8] (first N = rendered A, last N = observed B), S = 160: rows are padded to
+ * FPB_IN_PITCH pixels, image pixels at columns [FPB_IN_XOFF, FPB_IN_XOFF+S), pad pixels must be zero. */
+#define FPB_IN_PITCH 168
+#define FPB_IN_XOFF 4
 int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
                        void* stream);
 int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream);
 int fpb_score_cross(const fpb_net* net, const float* feat, int L, int bs, void* ws, float* out_logits,
                     void* stream);
 
-/* unit-test entry: one implicit GEMM C = epi(im2col(A) . W^T) through the SIMT fp32 (precision 0) or the
- * tcgen05 bf16 (precision 1) kernel; A is NHWC [*,Hin,Win,Cin], W is [N][K], K = KH*KW*Cin. */
+/* unit-test entry: one implicit GEMM C = epi(im2col(A) . W^T); A is NHWC [*,Hin,Win,Cin], W is [N][K], K = KH*KW*Cin.
+ * precision/mode 0: SIMT fp32; 1: tcgen05 bf16 with cp.async producers; 2 / 3: persistent tcgen05 + TMA (im2col
+ * tensor maps) kernel with cta_group 1 / 2.  _ex adds the row-padded "wide pixel" addressing of the 7x7 stem. */
 int fpb_debug_igemm(int precision, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
                     int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad, const float* scale,
                     const float* shift, const void* residual, int relu, int out_bf16, void* stream);
+
+int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win, int Cin,
+                       int Ho, int Wo, int KH, int KW, int stride, int pad_h, int pad_w, int row_pitch, int pix_pitch,
+                       const float* scale, const float* shift, const void* residual, int relu, int out_bf16,
+                       void* stream);
 
 /* number of kernels this library launched on the calling thread since the last reset */
 long long fpb_launch_count(int reset);

@@ -34,7 +34,7 @@ def test_host_only_helpers():
   assert lib().fpb_version() == 100
   assert lib().fpb_net_blob_floats(0) == 17040784 and lib().fpb_net_blob_floats(1) == 15983496
   assert lib().fpb_render_ws_bytes(252, 10242, 160) > 252 * 160 * 160 * 8
-  assert lib().fpb_net_ws_bytes(0, 1, 252) == lib().fpb_net_ws_bytes(0, 1, 42)     # chunked
+  assert lib().fpb_net_ws_bytes(0, 1, 1000) == lib().fpb_net_ws_bytes(0, 1, 256)   # chunked (FPB_NET_CHUNK = 256)
 
 
 def test_no_cpu_fallback():

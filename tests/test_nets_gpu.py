@@ -58,10 +58,12 @@ CASES = [
   (2, 40, 128, 128, 3, 1, 1),       # BN=128 tile
   (1, 80, 64, 128, 3, 2, 1),        # Cin=64
   (2, 24, 64, 64, 3, 1, 1),         # BN=64 tile
+  (7, 40, 256, 256, 3, 1, 1),       # several tiles per CTA pair, tile spans images, ragged tail (M=11200)
+  (700, 1, 512, 512, 1, 1, 0),      # plain GEMM over 2 N tiles and 6 M tiles
 ]
 
 
-@pytest.mark.parametrize('prec', [0, 1])
+@pytest.mark.parametrize('prec', [0, 1, 2, 3])     # 0 SIMT fp32, 1 tcgen05+cp.async, 2/3 tcgen05+TMA cta_group 1/2
 @pytest.mark.parametrize('case', CASES)
 def test_igemm_matches_torch(prec, case):
   nimg, H, Cin, Cout, k, stride, pad = case
@@ -81,23 +83,25 @@ def test_igemm_matches_torch(prec, case):
   assert (got2 - ref2).abs().max().item() < (2e-3 if prec else 2e-4)
 
 
-@pytest.mark.parametrize('prec', [0, 1])
+@pytest.mark.parametrize('prec', [0, 1, 2, 3])
 def test_first_conv_7x7_padded_layout(prec):
-  """7x7 stride-2 conv on the 8-channel padded input with the kernel row padded to 8 taps (csrc/net.cu kConvs[0])."""
+  """7x7 stride-2 stem on the row-padded 8-channel input [n,160,168,8], evaluated as a 7x1 convolution over 161
+  overlapping 64-channel "wide pixels" (csrc/net.cu kConvs[0]); weights [64][7][8 taps][8 ch]."""
   g = torch.Generator(device='cuda').manual_seed(5)
-  x6 = torch.randn(2, 160, 160, 6, device='cuda', generator=g)
+  x6 = torch.randn(3, 160, 160, 6, device='cuda', generator=g)
   w6 = torch.randn(64, 6, 7, 7, device='cuda', generator=g) / (6 * 49) ** 0.5
-  x8 = torch.zeros(2, 160, 160, 8, device='cuda'); x8[..., :6] = x6
+  x8 = torch.zeros(3, 160, 168, 8, device='cuda'); x8[:, :, 4:164, :6] = x6
   w8 = torch.zeros(64, 8, 7, 8, device='cuda'); w8[:, :6, :, :7] = w6
   from foundationpose_b200._lib import lib, check, ptr, stream
   dt = torch.bfloat16 if prec else torch.float
   A = x8.to(dt).contiguous()
   W = w8.permute(0, 2, 3, 1).reshape(64, -1).to(dt).contiguous()
-  C = torch.empty((2 * 80 * 80, 64), dtype=torch.float, device='cuda')
-  check(lib().fpb_debug_igemm(prec, ptr(A), ptr(W), ptr(C), 2 * 6400, 64, 448, 160, 160, 8, 80, 80, 7, 8, 2, 3, None,
-                              None, None, 0, 0, stream()))
+  C = torch.empty((3 * 80 * 80, 64), dtype=torch.float, device='cuda')
+  check(lib().fpb_debug_igemm_ex(prec, ptr(A), ptr(W), ptr(C), 3 * 6400, 64, 448, 160, 161, 64, 80, 80, 7, 1, 2, 3, -1, 168, 8,
+                                 None, None, None, 0, 0, stream()))
+  torch.cuda.synchronize()
   ref = _ref_conv(x6, w6, 2, 3, bf16_ops=bool(prec))
-  assert (C.reshape(2, 80, 80, 64) - ref).abs().max().item() < (2e-3 if prec else 2e-4)
+  assert (C.reshape(3, 80, 80, 64) - ref).abs().max().item() < (2e-3 if prec else 2e-4)
 
 
 def _inputs(n, seed=0):
