@@ -15,6 +15,7 @@
 // both SMs and tcgen05.commit multicasts the barrier arrivals to the pair.
 #include "net_kernels.cuh"
 #include <cuda.h>
+#include <stdlib.h>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -178,11 +179,31 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[32])
+{
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// 16-byte chunk j of row r inside a [32 rows x 128 B] warp-private staging tile (XOR swizzle: conflict-free both for
+// "lane = row" accesses and for "8 lanes per row" coalesced accesses)
+__device__ __forceinline__ uint32_t stg_off(int r, int j) { return (uint32_t)(r * 128 + ((j ^ (r & 7)) << 4)); }
+
 struct Tc2Params {
   GemmProblem p;
   int a_im2col;          // 1: A through the im2col map, 0: tiled 2-D map over [M][K]
   int lower_w, lower_h;  // im2col bounding-box lower corner (= -pad)
   int m_tiles, n_tiles;  // tiles of (TM*CG) x BN
+  int fast_epi;          // 1: smem-transposed, fully coalesced bf16 epilogue (ncols % 64 == 0)
+  int dbg;               // FPB_TC2_DBG experiment bits: 1 no stores, 2 no scale/shift, 4 no residual, 8 no MMA
 };
 
 template <int STAGES>
@@ -199,9 +220,13 @@ struct Cfg {
   static constexpr int B_ROWS = BN / CG;                      // W rows loaded by each CTA
   static constexpr int B_STAGE_BYTES = B_ROWS * 128;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+  // per epilogue warp: 4 KB output staging + 4 KB residual staging + 4 KB positional-embedding staging + scale/shift
+  static constexpr int EPI_WARP_BYTES = 3 * 4096 + 2 * BN * 4;
+  static constexpr int EPI_BYTES = 4 * EPI_WARP_BYTES;
+  static constexpr int STAGES_RAW = (224 * 1024 - EPI_BYTES) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
-  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + (int)sizeof(SmemCtl<STAGES>);
+  static constexpr int SMEM = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + (int)sizeof(SmemCtl<STAGES>);
 };
 
 template <int BN, int CG>
@@ -212,7 +237,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   constexpr int STAGES = C::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  SmemCtl<STAGES>* ctl = (SmemCtl<STAGES>*)(smem + STAGES * C::STAGE_BYTES);
+  uint8_t* epi_smem = smem + STAGES * C::STAGE_BYTES;
+  SmemCtl<STAGES>* ctl = (SmemCtl<STAGES>*)(epi_smem + C::EPI_BYTES);
   const GemmProblem& p = q.p;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
@@ -300,6 +326,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
           const uint64_t da = make_desc(sa), db = make_desc(sa + A_STAGE_BYTES);
+          if (!(q.dbg & 8))
 #pragma unroll
           for (int k = 0; k < KC / 16; k++)
             umma_bf16<CG>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
@@ -321,6 +348,124 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       const uint32_t acc = tc & 1u;
       mbar_wait(&ctl->tmem_full[acc], (tc >> 1) & 1u);
       tc_fence_after();
+      if (q.fast_epi) {
+        // ---- coalesced path: TMEM -> registers (lane = row) -> math -> bf16 -> warp-private swizzled smem tile ->
+        //      8 lanes per row read it back and store 128 contiguous bytes per row; residual / positional embedding
+        //      travel the same way in the opposite direction.
+        uint8_t* ew = epi_smem + (warp - 2) * C::EPI_WARP_BYTES;
+        const uint32_t s_out = smem_u32(ew), s_res = s_out + 4096, s_pe = s_out + 8192;
+        float* ss = (float*)(ew + 12288);                       // scale[BN], shift[BN] of this n-tile
+        const int m_w = (mt * CG + (int)rank) * TM + quarter * 32;   // first row of this warp
+        const int sub = lane >> 3, cj = lane & 7;               // coalesced role: row 4i+sub, 16-byte chunk cj
+        __syncwarp();
+        for (int i = lane; i < BN; i += 32) {
+          const bool ok = n0 + i < nst;
+          ss[i] = (p.scale && ok && !(q.dbg & 2)) ? __ldg(p.scale + n0 + i) : 1.0f;
+          ss[BN + i] = (p.shift && ok && !(q.dbg & 2)) ? __ldg(p.shift + n0 + i) : 0.0f;
+        }
+        __syncwarp();
+        const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
+#pragma unroll 1
+        for (int g = 0; g < BN / 64; g++) {
+          const int nb = n0 + g * 64;
+          const bool g_ok = nb < nst;                           // warp-uniform
+          uint4 rr[8];
+          if (p.residual && g_ok && !(q.dbg & 4)) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+              const int mr = m_w + 4 * i + sub;
+              rr[i] = mr < p.M ? __ldg(reinterpret_cast<const uint4*>((const __nv_bfloat16*)p.residual + (long long)mr * p.ldr + nb) + cj)
+                               : make_uint4(0u, 0u, 0u, 0u);
+            }
+          }
+          uint32_t r0[32], r1[32];
+          tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
+          tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
+          tmem_ld_wait();
+          if (g == BN / 64 - 1) {
+            // release this accumulator buffer to the MMA issuer (leader CTA's barrier)
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (CG == 1) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&ctl->tmem_empty[acc])) : "memory");
+              else mbar_arrive_cluster(&ctl->tmem_empty[acc], 0);
+            }
+          }
+          if (!g_ok) continue;
+          float v[64];
+#pragma unroll
+          for (int i = 0; i < 32; i++) { v[i] = __uint_as_float(r0[i]) * p.alpha; v[32 + i] = __uint_as_float(r1[i]) * p.alpha; }
+#pragma unroll
+          for (int c4 = 0; c4 < 16; c4++) {
+            const float4 sc = *reinterpret_cast<const float4*>(ss + g * 64 + c4 * 4);
+            const float4 sh = *reinterpret_cast<const float4*>(ss + BN + g * 64 + c4 * 4);
+            v[c4 * 4 + 0] = v[c4 * 4 + 0] * sc.x + sh.x; v[c4 * 4 + 1] = v[c4 * 4 + 1] * sc.y + sh.y;
+            v[c4 * 4 + 2] = v[c4 * 4 + 2] * sc.z + sh.z; v[c4 * 4 + 3] = v[c4 * 4 + 3] * sc.w + sh.w;
+          }
+          if (p.residual && !(q.dbg & 4)) {
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(s_res + stg_off(4 * i + sub, cj)), "r"(rr[i].x), "r"(rr[i].y), "r"(rr[i].z), "r"(rr[i].w) : "memory");
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+              uint4 rv;
+              asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(rv.x), "=r"(rv.y), "=r"(rv.z), "=r"(rv.w) : "r"(s_res + stg_off(lane, j)) : "memory");
+              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rv);
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const float2 f = __bfloat1622float2(h[e]);
+                v[j * 8 + e * 2] += f.x; v[j * 8 + e * 2 + 1] += f.y;
+              }
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int i = 0; i < 64; i++) v[i] = fmaxf(v[i], 0.0f);
+          }
+          if (p.pe) {
+#pragma unroll
+            for (int hlf = 0; hlf < 2; hlf++) {                 // 32 fp32 columns = 128 B per row per half
+              __syncwarp();
+#pragma unroll
+              for (int i = 0; i < 8; i++) {
+                const int mr = m_w + 4 * i + sub;
+                const float4 pv = __ldg(reinterpret_cast<const float4*>(p.pe + (long long)(mr % p.pe_rows) * p.pe_ld + nb + hlf * 32) + cj);
+                asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(s_pe + stg_off(4 * i + sub, cj)), "f"(pv.x), "f"(pv.y), "f"(pv.z), "f"(pv.w) : "memory");
+              }
+              __syncwarp();
+#pragma unroll
+              for (int j = 0; j < 8; j++) {
+                float4 pv;
+                asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(pv.x), "=f"(pv.y), "=f"(pv.z), "=f"(pv.w) : "r"(s_pe + stg_off(lane, j)) : "memory");
+                v[hlf * 32 + j * 4 + 0] += pv.x; v[hlf * 32 + j * 4 + 1] += pv.y;
+                v[hlf * 32 + j * 4 + 2] += pv.z; v[hlf * 32 + j * 4 + 3] += pv.w;
+              }
+            }
+          }
+          if ((q.dbg & 1) && v[0] != 123456.0f) continue;
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j * 8 + 0], v[j * 8 + 1]), h1 = __floats2bfloat162_rn(v[j * 8 + 2], v[j * 8 + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j * 8 + 4], v[j * 8 + 5]), h3 = __floats2bfloat162_rn(v[j * 8 + 6], v[j * 8 + 7]);
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(s_out + stg_off(lane, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
+                         "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const int mr = m_w + 4 * i + sub;
+            uint4 ov;
+            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
+            if (mr < p.M) {
+              const long long orow_c = (long long)(mr % p.m_split) * p.ldc + (long long)(mr / p.m_split) * p.split_col_off;
+              *(reinterpret_cast<uint4*>((__nv_bfloat16*)p.C + orow_c + nb) + cj) = ov;
+            }
+          }
+          __syncwarp();
+        }
+        continue;
+      }
       const bool m_ok = m < p.M;
       const long long orow = m_ok ? (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off : 0;
       const float* pe_row = (p.pe && m_ok) ? p.pe + (long long)(m % p.pe_rows) * p.pe_ld : nullptr;
@@ -335,7 +480,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
         for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]) * p.alpha;
         const bool full = nb + 32 <= nst;
-        if (p.scale) {
+        if (p.scale && !(q.dbg & 2)) {
 #pragma unroll
           for (int i = 0; i < 32; i++)
             if (full || nb + i < nst) v[i] = v[i] * __ldg(p.scale + nb + i) + (p.shift ? __ldg(p.shift + nb + i) : 0.0f);
@@ -344,7 +489,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           for (int i = 0; i < 32; i++)
             if (full || nb + i < nst) v[i] += __ldg(p.shift + nb + i);
         }
-        if (res_row) {
+        if (res_row && !(q.dbg & 4)) {
           if (full) {
 #pragma unroll
             for (int qq = 0; qq < 4; qq++) {
@@ -369,6 +514,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           for (int i = 0; i < 32; i++)
             if (full || nb + i < nst) v[i] += __ldg(pe_row + nb + i);
         }
+        if ((q.dbg & 1) && v[0] != 123456.0f) continue;
         if (p.out_bf16) {
           __nv_bfloat16* o = (__nv_bfloat16*)p.C + orow + nb;
           if (full) {
@@ -580,6 +726,9 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
   q.p = p;
   q.a_im2col = plain ? 0 : 1;
   q.lower_w = -p.pad_w; q.lower_h = -p.pad;
+  { const char* e = getenv("FPB_TC2_DBG"); q.dbg = e ? atoi(e) : 0; }
+  q.fast_epi = (p.out_bf16 && ncols % 64 == 0 && !(q.dbg & 16) && (!p.residual || p.ldr % 8 == 0) && p.ldc % 8 == 0 &&
+                p.split_col_off % 8 == 0 && (!p.pe || p.pe_ld % 4 == 0)) ? 1 : 0;
   q.m_tiles = fpb_cdiv(p.M, TM * CG);
   q.n_tiles = fpb_cdiv(ncols, BN);
   CUtensorMap mA, mB;

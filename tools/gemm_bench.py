@@ -1,0 +1,60 @@
+"""Per-layer timing of the implicit-GEMM kernels at the bench workload's real shapes (dev tool).
+  python tools/gemm_bench.py [--modes 2,3] [--layers conv6,conv11] [--reps 10] [--nhyp 252]"""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+from foundationpose_b200._lib import lib, check, ptr, stream  # noqa: E402
+
+# name: (imgs_per_hyp, Hin, Cin, Cout, k, stride, residual, relu)
+LAYERS = {
+  'conv1': (2, 80, 64, 128, 3, 2, 0, 1), 'conv2': (2, 40, 128, 128, 3, 1, 0, 1), 'conv3': (2, 40, 128, 128, 3, 1, 1, 1),
+  'conv6': (1, 40, 256, 256, 3, 1, 0, 1), 'conv7': (1, 40, 256, 256, 3, 1, 1, 1), 'conv10': (1, 40, 256, 512, 3, 2, 0, 1),
+  'conv11': (1, 20, 512, 512, 3, 1, 0, 1), 'conv12': (1, 20, 512, 512, 3, 1, 1, 1),
+  'inproj': (400, 1, 512, 1536, 1, 1, 0, 0), 'lin': (400, 1, 512, 512, 1, 1, 1, 0),
+}
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument('--modes', default='2,3')
+  ap.add_argument('--layers', default=','.join(LAYERS))
+  ap.add_argument('--reps', type=int, default=10)
+  ap.add_argument('--nhyp', type=int, default=252)
+  ap.add_argument('--no-flush', action='store_true')
+  a = ap.parse_args()
+  flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
+  for name in a.layers.split(','):
+    ipn, H, Cin, Cout, k, stride, res, relu = LAYERS[name]
+    nimg = ipn * a.nhyp
+    pad = (k - 1) // 2
+    Ho = (H + 2 * pad - k) // stride + 1
+    M, K = nimg * Ho * Ho, k * k * Cin
+    x = torch.randn(nimg, H, H, Cin, device='cuda').bfloat16()
+    w = (torch.randn(Cout, K, device='cuda') / K ** 0.5).bfloat16()
+    out = torch.empty(M, Cout, device='cuda', dtype=torch.bfloat16)
+    r = torch.randn(M, Cout, device='cuda').bfloat16() if res else None
+    sc = torch.ones(Cout, device='cuda'); sh = torch.zeros(Cout, device='cuda')
+    for mode in [int(m) for m in a.modes.split(',')]:
+      def launch():
+        check(lib().fpb_debug_igemm(mode, ptr(x), ptr(w), ptr(out), M, Cout, K, H, H, Cin, Ho, Ho, k, k, stride, pad, ptr(sc),
+                                    ptr(sh), ptr(r), relu, 1, stream()))
+      for _ in range(2):
+        launch()
+      ts = []
+      for _ in range(a.reps):
+        if not a.no_flush:
+          flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); launch(); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+      ms = sorted(ts)[len(ts) // 2]
+      fl = 2.0 * M * Cout * K
+      print(f'{name:7s} mode {mode} M={M} N={Cout} K={K}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TFLOP/s', flush=True)
+
+
+if __name__ == '__main__':
+  main()
