@@ -120,10 +120,11 @@ def run_reference(args):
 
 
 def time_dominant_kernel(torch, n_rep=20):
-  """CUDA-event timing of the dominant kernel in isolation: tc_gemm_kernel<256,4> on the 3x3 256->256 conv at
-  40x40 over one 42-hypothesis chunk (M=67200, N=256, K=2304); L2 flushed between launches."""
+  """CUDA-event timing of the dominant kernel in isolation: tc2_kernel<256,2> (persistent tcgen05 + TMA im2col,
+  cta_group::2) on the 3x3 256->256 conv at 40x40 over all 252 hypotheses (M=403200, N=256, K=2304), the shape that
+  runs 4x per network pass; L2 flushed between launches."""
   from foundationpose_b200._lib import lib, check, ptr, stream
-  nimg, H, C = 42, 40, 256
+  nimg, H, C = N_HYP, 40, 256
   x = torch.randn(nimg, H, H, C, device='cuda').bfloat16()
   w = (torch.randn(C, 9 * C, device='cuda') / 48).bfloat16()
   out = torch.empty(nimg * H * H, C, device='cuda', dtype=torch.bfloat16)
@@ -132,7 +133,7 @@ def time_dominant_kernel(torch, n_rep=20):
   M, K = nimg * H * H, 9 * C
 
   def launch():
-    check(lib().fpb_debug_igemm(1, ptr(x), ptr(w), ptr(out), M, C, K, H, H, C, H, H, 3, 3, 1, 1, ptr(sc), ptr(sh), None, 1, 1,
+    check(lib().fpb_debug_igemm(3, ptr(x), ptr(w), ptr(out), M, C, K, H, H, C, H, H, 3, 3, 1, 1, ptr(sc), ptr(sh), None, 1, 1,
                                 stream()))
   for _ in range(3):
     launch()
@@ -145,7 +146,7 @@ def time_dominant_kernel(torch, n_rep=20):
     ts.append(e0.elapsed_time(e1))
   ms = float(np.mean(ts))
   flops = 2.0 * M * C * K
-  return dict(kernel='tc_gemm_kernel<256,4> conv3x3 256->256 @40x40 x42 hyps', ms=ms, flops=flops, tflops=flops / ms / 1e9)
+  return dict(kernel='tc2_kernel<256,2> conv3x3 256->256 @40x40 x252 hyps (M=403200,N=256,K=2304)', ms=ms, flops=flops, tflops=flops / ms / 1e9)
 
 
 def main():

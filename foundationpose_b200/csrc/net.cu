@@ -224,6 +224,28 @@ int run_attention_core(const Ctx& c, const void* qkv, int g, int tokens, int tok
   return FPB_OK;
 }
 
+// self-attention block input x [n*400, 512] -> ctx [n*400, 512] (before out_proj)
+int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
+{
+  const long long R = (long long)n * TOK;
+  if (!c.bf) {
+    RET(run_linear(c, m.in, x, R, w.qkv, nullptr, 0, 0));
+    return run_attention_core(c, w.qkv, n, TOK, TOKP, w.scores, w.P, w.vt, w.ctx, false);
+  }
+  // bf16: Q|K projection [R,1024]; V is produced already transposed, V^T = Wv . X^T  ([512, R], tokens contiguous),
+  // by swapping the GEMM operands, so the fused attention kernel can TMA it as a K-major B operand; the V bias is
+  // added to the attention output instead (softmax rows sum to 1).
+  __nv_bfloat16* qk = (__nv_bfloat16*)w.qkv;
+  __nv_bfloat16* vt = qk + R * 2 * D;
+  Lin lqk = m.in; lqk.N = 2 * D;
+  RET(run_linear(c, lqk, x, R, qk, nullptr, 0, 1));
+  GemmProblem p = gemm_problem_default();
+  p.A = c.W(m.in.w + (size_t)2 * D * D); p.W = x; p.C = vt;
+  p.M = D; p.N = (int)R; p.K = D; p.Cin = D; p.pix_pitch = D; p.ldw = D; p.ldc = (int)R; p.out_bf16 = 1;
+  RET(c.gemm(p));
+  return tc_attention(qk, vt, R, c.F(m.in.b + 2 * D), w.ctx, n, c.st);
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -282,8 +304,7 @@ FPB_EXPORT size_t fpb_net_blob_floats(int kind)
 static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* out3)
 {
   const long long R = (long long)n * TOK;
-  RET(run_linear(c, e.att.in, w.d0, R, w.qkv, nullptr, 0, c.bf));
-  RET(run_attention_core(c, w.qkv, n, TOK, TOKP, w.scores, w.P, w.vt, w.ctx, c.bf));
+  RET(run_self_attention(c, e.att, w.d0, n, w));
   RET(run_linear(c, e.att.out, w.ctx, R, w.y1, w.d0, 0, c.bf));                       // x + SA(x)
   RET(layernorm_rows(w.y1, c.bf, c.F(e.n1g), c.F(e.n1b), w.y, c.bf, R, D, 1e-5f, c.st));
   RET(run_linear(c, e.l1, w.y, R, w.ff, nullptr, 1, c.bf));
@@ -343,8 +364,7 @@ FPB_EXPORT int fpb_score_features(const fpb_net* net, const void* AB, int N, voi
     }
     RET(run_encoders(c, in, n, w));
     const long long R = (long long)n * TOK;
-    RET(run_linear(c, net->att.in, w.d0, R, w.qkv, nullptr, 0, c.bf));
-    RET(run_attention_core(c, w.qkv, n, TOK, TOKP, w.scores, w.P, w.vt, w.ctx, c.bf));
+    RET(run_self_attention(c, net->att, w.d0, n, w));
     RET(run_linear(c, net->att.out, w.ctx, R, w.y1, nullptr, 0, c.bf));
     RET(token_mean(w.y1, c.bf, out_feat_n512 + (size_t)b0 * D, n, TOK, D, c.st));
   }

@@ -1,0 +1,340 @@
+// Fused multi-head self-attention over the 400 tokens of one hypothesis (d_model 512, 4 heads of 128) on tcgen05.
+//   TransformerEncoderLayer.self_attn   learning/models/refine_network.py:56-70   (via nn.MultiheadAttention)
+//   ScoreNetMultiPair.att               learning/models/score_network.py:53,73
+// One CTA per (hypothesis, head); it walks the 4 query tiles of 128 rows:
+//   S = Q K^T      two tcgen05.mma (N = 208 + 192) per 16-wide k step, fp32 scores in TMEM columns 0..399
+//   P = exp2(..)   4 softmax warps (lane = query row): pass 1 row max, pass 2 un-normalised probabilities written as
+//                  bf16 into a 2-stage smem ring in the 128B-swizzled K-major layout UMMA reads
+//   O = P V        tcgen05.mma per 64-key chunk against V^T tiles (TMA ring); O overlays TMEM columns 0..127, which
+//                  is safe because the first P.V MMA waits until score columns 0..127 have been consumed
+//   epilogue       O / rowsum + V bias (softmax rows sum to 1, so the bias commutes) -> bf16 context rows
+// No score / probability tensor ever reaches HBM (the unfused path wrote 0.7 GB of fp32 scores per layer call).
+// Warp roles: 0 TMA producer, 1 TMEM allocator + MMA issuer, 2-5 softmax / epilogue.
+#include "net_kernels.cuh"
+#include <cuda.h>
+
+namespace {
+
+constexpr int TOK = 400, DH = 128, HEADS = 4, DM = 512;
+constexpr int NTHREADS = 192;
+constexpr int K_CHUNK_BYTES = TOK * 128;          // one 64-wide d chunk of K: 400 rows x 128 B
+constexpr int Q_CHUNK_BYTES = 128 * 128;
+constexpr int T16 = 16384;
+constexpr int N_KEY_CHUNKS = 7;                   // 6 x 64 + 16 keys
+constexpr int N1 = 208, N2 = 192;                 // S = [N1 | N2] columns
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+  const uint32_t addr = smem_u32(bar);
+  uint32_t ok = 0;
+  long long t0 = 0;
+  for (uint32_t spin = 0; !ok; spin++) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (!ok && (spin & 1023u) == 1023u) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 8000000000LL) __trap();
+    }
+  }
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr)      // K-major, SWIZZLE_128B (see net_tc.cu)
+{
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__host__ __device__ constexpr uint32_t make_idesc(int n)
+{
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum)
+{
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar)
+{
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint64_t* bar, int x, int y)
+{
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
+{
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[32])
+{
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct AttnCtl {
+  uint64_t k_full, q_full, q_empty, s_full, o_full, tmem_free;
+  uint64_t v_full[2], v_empty[2], p_full[2], p_empty[2];
+  uint32_t tmem_base;
+};
+
+constexpr int SMEM_K = 2 * K_CHUNK_BYTES, SMEM_Q = 2 * Q_CHUNK_BYTES, SMEM_V = 2 * T16, SMEM_P = 2 * T16;
+constexpr int SMEM_TOTAL = SMEM_K + SMEM_Q + SMEM_V + SMEM_P + 1024 + (int)sizeof(AttnCtl);
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapK,
+            const __grid_constant__ CUtensorMap mapV, const float* __restrict__ bv, __nv_bfloat16* __restrict__ ctx,
+            float c1)
+{
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sK = smem;
+  uint8_t* sQ = sK + SMEM_K;
+  uint8_t* sV = sQ + SMEM_Q;
+  uint8_t* sP = sV + SMEM_V;
+  AttnCtl* ctl = (AttnCtl*)(sP + SMEM_P);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.x / HEADS, h = blockIdx.x - g * HEADS;
+  const int row0 = g * TOK;                                  // first token row of this hypothesis
+  constexpr int N_MT = (TOK + 127) / 128;                    // 4 query tiles
+
+  if (threadIdx.x == 0) {
+    mbar_init(&ctl->k_full, 1); mbar_init(&ctl->q_full, 1); mbar_init(&ctl->q_empty, 1);
+    mbar_init(&ctl->s_full, 1); mbar_init(&ctl->o_full, 1); mbar_init(&ctl->tmem_free, 4);
+    for (int s = 0; s < 2; s++) {
+      mbar_init(&ctl->v_full[s], 1); mbar_init(&ctl->v_empty[s], 1);
+      mbar_init(&ctl->p_full[s], 128); mbar_init(&ctl->p_empty[s], 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  if (warp == 0) {
+    // ---------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&ctl->k_full, (uint32_t)SMEM_K);
+      for (int kc = 0; kc < 2; kc++)
+        for (int half = 0; half < 2; half++)
+          tma_load_2d(smem_u32(sK + kc * K_CHUNK_BYTES + half * 200 * 128), &mapK, &ctl->k_full, DM + h * DH + kc * 64,
+                      row0 + half * 200);
+      uint32_t gi = 0;
+      for (int mt = 0; mt < N_MT; mt++) {
+        mbar_wait(&ctl->q_empty, (uint32_t)((mt & 1) ^ 1));
+        mbar_arrive_expect_tx(&ctl->q_full, (uint32_t)SMEM_Q);
+        for (int kc = 0; kc < 2; kc++)
+          tma_load_2d(smem_u32(sQ + kc * Q_CHUNK_BYTES), &mapQ, &ctl->q_full, h * DH + kc * 64, row0 + mt * 128);
+        for (int j = 0; j < N_KEY_CHUNKS; j++, gi++) {
+          const uint32_t s = gi & 1u, use = gi >> 1;
+          mbar_wait(&ctl->v_empty[s], (use & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&ctl->v_full[s], (uint32_t)T16);
+          tma_load_2d(smem_u32(sV + s * T16), &mapV, &ctl->v_full[s], row0 + j * 64, h * DH);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t id1 = make_idesc(N1), id2 = make_idesc(N2), idv = make_idesc(DH);
+      mbar_wait(&ctl->k_full, 0);
+      uint32_t gi = 0;
+      for (int mt = 0; mt < N_MT; mt++) {
+        mbar_wait(&ctl->q_full, (uint32_t)(mt & 1));
+        mbar_wait(&ctl->tmem_free, (uint32_t)((mt & 1) ^ 1));
+        tc_fence_after();
+        for (int kc = 0; kc < 2; kc++) {
+          const uint64_t dq = make_desc(smem_u32(sQ + kc * Q_CHUNK_BYTES));
+          const uint64_t dk1 = make_desc(smem_u32(sK + kc * K_CHUNK_BYTES));
+          const uint64_t dk2 = make_desc(smem_u32(sK + kc * K_CHUNK_BYTES + N1 * 128));
+#pragma unroll
+          for (int k = 0; k < 4; k++) {
+            umma(tmem_base, dq + (uint64_t)(k * 2), dk1 + (uint64_t)(k * 2), id1, (kc | k) ? 1u : 0u);
+            umma(tmem_base + N1, dq + (uint64_t)(k * 2), dk2 + (uint64_t)(k * 2), id2, (kc | k) ? 1u : 0u);
+          }
+        }
+        umma_commit(&ctl->s_full);
+        umma_commit(&ctl->q_empty);
+        // O overlays score columns 0..127: chunks 0 and 1 of P must exist before the first P.V MMA
+        mbar_wait(&ctl->p_full[gi & 1u], (gi >> 1) & 1u);
+        mbar_wait(&ctl->p_full[(gi + 1) & 1u], ((gi + 1) >> 1) & 1u);
+        for (int j = 0; j < N_KEY_CHUNKS; j++, gi++) {
+          const uint32_t s = gi & 1u, use = gi >> 1;
+          mbar_wait(&ctl->v_full[s], use & 1u);
+          mbar_wait(&ctl->p_full[s], use & 1u);
+          tc_fence_after();
+          const uint64_t dp = make_desc(smem_u32(sP + s * T16)), dv = make_desc(smem_u32(sV + s * T16));
+          const int ksteps = j < N_KEY_CHUNKS - 1 ? 4 : (TOK - 64 * (N_KEY_CHUNKS - 1)) / 16;
+          for (int k = 0; k < ksteps; k++) umma(tmem_base, dp + (uint64_t)(k * 2), dv + (uint64_t)(k * 2), idv, (j | k) ? 1u : 0u);
+          umma_commit(&ctl->v_empty[s]);
+          umma_commit(&ctl->p_empty[s]);
+        }
+        umma_commit(&ctl->o_full);
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------- softmax + epilogue (warps 2..5)
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    uint32_t gi = 0;
+    for (int mt = 0; mt < N_MT; mt++) {
+      mbar_wait(&ctl->s_full, (uint32_t)(mt & 1));
+      tc_fence_after();
+      uint32_t r[32];
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < TOK / 32; c++) {
+        tmem_ld32(t_row + (uint32_t)(c * 32), r);
+#pragma unroll
+        for (int i = 0; i < 32; i++) mx = fmaxf(mx, __uint_as_float(r[i]));
+      }
+      tmem_ld16(t_row + (uint32_t)(TOK / 32 * 32), r);
+#pragma unroll
+      for (int i = 0; i < 16; i++) mx = fmaxf(mx, __uint_as_float(r[i]));
+      const float off = -mx * c1;
+      float sum = 0.0f;
+#pragma unroll 1
+      for (int j = 0; j < N_KEY_CHUNKS; j++, gi++) {
+        const uint32_t s = gi & 1u, use = gi >> 1;
+        mbar_wait(&ctl->p_empty[s], (use & 1u) ^ 1u);
+        const uint32_t sp = smem_u32(sP + s * T16) + (uint32_t)(row * 128);
+        const int nhalf = j < N_KEY_CHUNKS - 1 ? 2 : 1;
+        for (int hf = 0; hf < nhalf; hf++) {
+          const bool tail = j == N_KEY_CHUNKS - 1;
+          if (tail) tmem_ld16(t_row + (uint32_t)(j * 64), r);
+          else tmem_ld32(t_row + (uint32_t)(j * 64 + hf * 32), r);
+          const int n16 = tail ? 2 : 4;                      // 16-byte chunks (8 keys each) produced by this half
+#pragma unroll
+          for (int q8 = 0; q8 < 4; q8++) {
+            if (q8 < n16) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const float p0 = exp2f(fmaf(__uint_as_float(r[q8 * 8 + e * 2]), c1, off));
+                const float p1 = exp2f(fmaf(__uint_as_float(r[q8 * 8 + e * 2 + 1]), c1, off));
+                sum += p0 + p1;
+                __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+                pk[e] = *reinterpret_cast<uint32_t*>(&hh);
+              }
+              const int jj = hf * 4 + q8;
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sp + (uint32_t)((jj ^ (row & 7)) << 4)), "r"(pk[0]),
+                           "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                           : "memory");
+            }
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async();
+        mbar_arrive(&ctl->p_full[s]);
+      }
+      // ---- epilogue: O / sum + b_v -> ctx
+      mbar_wait(&ctl->o_full, (uint32_t)(mt & 1));
+      tc_fence_after();
+      const float inv = 1.0f / sum;
+      const int tok = mt * 128 + row;
+      __nv_bfloat16* orow = ctx + (long long)(row0 + tok) * DM + h * DH;
+#pragma unroll 1
+      for (int c = 0; c < DH / 32; c++) {
+        tmem_ld32(t_row + (uint32_t)(c * 32), r);
+        if (tok < TOK) {
+#pragma unroll
+          for (int q8 = 0; q8 < 4; q8++) {
+            uint4 pk;
+            uint32_t* pw = reinterpret_cast<uint32_t*>(&pk);
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              const int d = c * 32 + q8 * 8 + e * 2;
+              __nv_bfloat162 hh = __floats2bfloat162_rn(__uint_as_float(r[q8 * 8 + e * 2]) * inv + __ldg(bv + h * DH + d),
+                                                        __uint_as_float(r[q8 * 8 + e * 2 + 1]) * inv + __ldg(bv + h * DH + d + 1));
+              pw[e] = *reinterpret_cast<uint32_t*>(&hh);
+            }
+            *reinterpret_cast<uint4*>(orow + c * 32 + q8 * 8) = pk;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->tmem_free);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
+}  // namespace
+
+int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups, cudaStream_t st)
+{
+  FPB_CHECK_ARG(qk && vt && bv && ctx && groups > 0 && vt_pitch % 8 == 0);
+  const long long R = (long long)groups * TOK;
+  CUtensorMap mQ, mK, mV;
+  int rc;
+  if ((rc = fpb_tiled_map_bf16(qk, R, 2 * DM, 2 * DM, 128, &mQ, nullptr))) return rc;
+  if ((rc = fpb_tiled_map_bf16(qk, R, 2 * DM, 2 * DM, 200, &mK, nullptr))) return rc;
+  if ((rc = fpb_tiled_map_bf16(vt, DM, R, vt_pitch, 128, &mV, nullptr))) return rc;
+  static bool configured = false;
+  if (!configured) {
+    FPB_CUDA(cudaFuncSetAttribute(attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
+    configured = true;
+  }
+  const float c1 = 0.08838834764831845f * 1.4426950408889634f;   // 1/sqrt(128) * log2(e)
+  attn_kernel<<<groups * HEADS, NTHREADS, SMEM_TOTAL, st>>>(mQ, mK, mV, bv, (__nv_bfloat16*)ctx, c1);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}

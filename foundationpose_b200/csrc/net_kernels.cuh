@@ -54,6 +54,11 @@ int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 acc
 int tc2_gemm(const GemmProblem& p, cudaStream_t st);   // bf16 tcgen05, persistent TMA kernel; FPB_ERR_UNSUPPORTED -> use tc_gemm
 void tc2_force_cta_group(int cg);                      // tests: 0 = default, 1 / 2 = force
 
+int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms);
+// fused multi-head self-attention (bf16, tcgen05): qk [R][1024] (Q | K, head h at +128h), vt [512][vt_pitch]
+// (V transposed: row = h*128+d, column = token row), bv [512] fp32 V bias -> ctx [R][512];  R = groups * 400
+int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups, cudaStream_t st);
+
 // small ops (fp32 math; io dtype flags)
 int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int cols, int ld_in, int ld_out,
                  cudaStream_t st);                                     // pad columns [cols, ld_out) written as 0

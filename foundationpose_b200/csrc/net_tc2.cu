@@ -708,6 +708,15 @@ int tc2_cta_group()
 
 void tc2_force_cta_group(int cg) { g_force_cg = cg; }
 
+// shared with net_attn.cu: cached tiled 2-D bf16 tensor map (box = 64 columns x box_rows rows, 128B swizzle)
+int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms)
+{
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (num_sms) *num_sms = g_num_sms;
+  return get_tiled_map(ptr, rows, cols, pitch, box_rows, (CUtensorMap*)out_map);
+}
+
 // Returns FPB_ERR_UNSUPPORTED (without setting up anything) when the problem does not fit this kernel, so the
 // caller can fall back to the first-generation cp.async kernel (tc_gemm).
 int tc2_gemm(const GemmProblem& p, cudaStream_t st)
