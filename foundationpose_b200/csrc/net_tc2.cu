@@ -24,7 +24,7 @@ namespace {
 
 constexpr int TM = 128;
 constexpr int KC = 64;
-constexpr int NTHREADS = 192;
+constexpr int NTHREADS = 320;                 // 1 TMA warp + 1 MMA warp + 8 epilogue warps
 constexpr int A_STAGE_BYTES = TM * 128;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -221,8 +221,9 @@ struct Cfg {
   static constexpr int B_STAGE_BYTES = B_ROWS * 128;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   // per epilogue warp: 4 KB output staging + 4 KB residual staging + 4 KB positional-embedding staging + scale/shift
-  static constexpr int EPI_WARP_BYTES = 3 * 4096 + 2 * BN * 4;
-  static constexpr int EPI_BYTES = 4 * EPI_WARP_BYTES;
+  static constexpr int EPI_WARPS = BN >= 128 ? 8 : 4;         // 2 warps per TMEM lane quarter split the 64-column groups
+  static constexpr int EPI_WARP_BYTES = 2 * 4096 + 2 * BN * 4;
+  static constexpr int EPI_BYTES = 8 * EPI_WARP_BYTES;
   static constexpr int STAGES_RAW = (224 * 1024 - EPI_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
@@ -248,7 +249,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; s++) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
-    for (int a = 0; a < 2; a++) { mbar_init(&ctl->tmem_full[a], 1); mbar_init(&ctl->tmem_empty[a], 4 * CG); }
+    for (int a = 0; a < 2; a++) { mbar_init(&ctl->tmem_full[a], 1); mbar_init(&ctl->tmem_empty[a], C::EPI_WARPS * CG); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -336,11 +337,29 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..5)
+    // ------------------------------------------------------------------ epilogue (warps 2..9)
     const int quarter = warp & 3;                 // TMEM lanes 32*quarter .. +31 are accessible to this warp
+    const int ehalf = (warp - 2) >> 2;            // which of the two warps sharing this lane quarter
+    constexpr int GSTEP = C::EPI_WARPS / 4;       // 64-column groups are interleaved over the warps of a quarter
+    if (warp - 2 < C::EPI_WARPS) {
     const int row = quarter * 32 + lane;
     const int nst = p.n_valid > 0 ? p.n_valid : p.N;
     uint32_t tc = 0;
+    // residual tile of the NEXT 64-column group is fetched one group ahead (8 x 16 B per lane, coalesced)
+    uint4 rr[8];
+    const bool use_res = q.fast_epi && p.residual && !(q.dbg & 4);
+    auto load_res = [&](int tile, int grp) {
+      const int mt_ = tile / q.n_tiles, nt_ = tile - mt_ * q.n_tiles;
+      const int mw_ = (mt_ * CG + (int)rank) * TM + (warp & 3) * 32, nb_ = nt_ * BN + grp * 64;
+      if (nb_ >= nst) return;
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int mr = mw_ + 4 * i + (lane >> 3);
+        rr[i] = mr < p.M ? __ldg(reinterpret_cast<const uint4*>((const __nv_bfloat16*)p.residual + (long long)mr * p.ldr + nb_) + (lane & 7))
+                         : make_uint4(0u, 0u, 0u, 0u);
+      }
+    };
+    if (use_res && cluster_id < total_tiles) load_res(cluster_id, ehalf);
     for (int t = cluster_id; t < total_tiles; t += n_clusters, tc++) {
       const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
       const int m = (mt * CG + (int)rank) * TM + row;
@@ -353,10 +372,14 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         //      8 lanes per row read it back and store 128 contiguous bytes per row; residual / positional embedding
         //      travel the same way in the opposite direction.
         uint8_t* ew = epi_smem + (warp - 2) * C::EPI_WARP_BYTES;
-        const uint32_t s_out = smem_u32(ew), s_res = s_out + 4096, s_pe = s_out + 8192;
-        float* ss = (float*)(ew + 12288);                       // scale[BN], shift[BN] of this n-tile
+        const uint32_t s_out = smem_u32(ew), s_res = s_out + 4096, s_pe = s_res;   // pe reuses the residual tile
+        float* ss = (float*)(ew + 8192);                       // scale[BN], shift[BN] of this n-tile
         const int m_w = (mt * CG + (int)rank) * TM + quarter * 32;   // first row of this warp
         const int sub = lane >> 3, cj = lane & 7;               // coalesced role: row 4i+sub, 16-byte chunk cj
+        // a warp's 32 rows never straddle m_split (host guarantees m_split % 32 == 0 or m_split >= M)
+        const int seg = m_w / p.m_split;
+        __nv_bfloat16* out_w = (__nv_bfloat16*)p.C + (long long)(m_w - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
+        const int pe_r0 = p.pe ? m_w % p.pe_rows : 0;
         __syncwarp();
         for (int i = lane; i < BN; i += 32) {
           const bool ok = n0 + i < nst;
@@ -366,23 +389,19 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         __syncwarp();
         const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
 #pragma unroll 1
-        for (int g = 0; g < BN / 64; g++) {
+        for (int g = ehalf; g < BN / 64; g += GSTEP) {
           const int nb = n0 + g * 64;
           const bool g_ok = nb < nst;                           // warp-uniform
-          uint4 rr[8];
-          if (p.residual && g_ok && !(q.dbg & 4)) {
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-              const int mr = m_w + 4 * i + sub;
-              rr[i] = mr < p.M ? __ldg(reinterpret_cast<const uint4*>((const __nv_bfloat16*)p.residual + (long long)mr * p.ldr + nb) + cj)
-                               : make_uint4(0u, 0u, 0u, 0u);
-            }
-          }
+          auto prefetch_next = [&]() {
+            if (!use_res) return;
+            if (g + GSTEP < BN / 64) load_res(t, g + GSTEP);
+            else if (t + n_clusters < total_tiles) load_res(t + n_clusters, ehalf);
+          };
           uint32_t r0[32], r1[32];
           tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
           tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
           tmem_ld_wait();
-          if (g == BN / 64 - 1) {
+          if (g + GSTEP >= BN / 64) {
             // release this accumulator buffer to the MMA issuer (leader CTA's barrier)
             tc_fence_before();
             __syncwarp();
@@ -391,7 +410,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               else mbar_arrive_cluster(&ctl->tmem_empty[acc], 0);
             }
           }
-          if (!g_ok) continue;
+          if (!g_ok) { prefetch_next(); continue; }
           float v[64];
 #pragma unroll
           for (int i = 0; i < 32; i++) { v[i] = __uint_as_float(r0[i]) * p.alpha; v[32 + i] = __uint_as_float(r1[i]) * p.alpha; }
@@ -402,7 +421,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             v[c4 * 4 + 0] = v[c4 * 4 + 0] * sc.x + sh.x; v[c4 * 4 + 1] = v[c4 * 4 + 1] * sc.y + sh.y;
             v[c4 * 4 + 2] = v[c4 * 4 + 2] * sc.z + sh.z; v[c4 * 4 + 3] = v[c4 * 4 + 3] * sc.w + sh.w;
           }
-          if (p.residual && !(q.dbg & 4)) {
+          if (use_res) {
 #pragma unroll
             for (int i = 0; i < 8; i++)
               asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(s_res + stg_off(4 * i + sub, cj)), "r"(rr[i].x), "r"(rr[i].y), "r"(rr[i].z), "r"(rr[i].w) : "memory");
@@ -429,8 +448,9 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               __syncwarp();
 #pragma unroll
               for (int i = 0; i < 8; i++) {
-                const int mr = m_w + 4 * i + sub;
-                const float4 pv = __ldg(reinterpret_cast<const float4*>(p.pe + (long long)(mr % p.pe_rows) * p.pe_ld + nb + hlf * 32) + cj);
+                int per = pe_r0 + 4 * i + sub;
+                if (per >= p.pe_rows) per -= p.pe_rows;
+                const float4 pv = __ldg(reinterpret_cast<const float4*>(p.pe + (long long)per * p.pe_ld + nb + hlf * 32) + cj);
                 asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(s_pe + stg_off(4 * i + sub, cj)), "f"(pv.x), "f"(pv.y), "f"(pv.z), "f"(pv.w) : "memory");
               }
               __syncwarp();
@@ -443,7 +463,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               }
             }
           }
-          if ((q.dbg & 1) && v[0] != 123456.0f) continue;
+          if ((q.dbg & 1) && v[0] != 123456.0f) { prefetch_next(); continue; }
 #pragma unroll
           for (int j = 0; j < 8; j++) {
             __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j * 8 + 0], v[j * 8 + 1]), h1 = __floats2bfloat162_rn(v[j * 8 + 2], v[j * 8 + 3]);
@@ -452,15 +472,13 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                          "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
           }
           __syncwarp();
+          prefetch_next();
 #pragma unroll
           for (int i = 0; i < 8; i++) {
             const int mr = m_w + 4 * i + sub;
             uint4 ov;
             asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
-            if (mr < p.M) {
-              const long long orow_c = (long long)(mr % p.m_split) * p.ldc + (long long)(mr / p.m_split) * p.split_col_off;
-              *(reinterpret_cast<uint4*>((__nv_bfloat16*)p.C + orow_c + nb) + cj) = ov;
-            }
+            if (mr < p.M) *(reinterpret_cast<uint4*>(out_w + (long long)(4 * i + sub) * p.ldc + nb) + cj) = ov;
           }
           __syncwarp();
         }
@@ -471,7 +489,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       const float* pe_row = (p.pe && m_ok) ? p.pe + (long long)(m % p.pe_rows) * p.pe_ld : nullptr;
       const __nv_bfloat16* res_row = (p.residual && m_ok) ? (const __nv_bfloat16*)p.residual + (long long)m * p.ldr : nullptr;
 #pragma unroll 1
-      for (int chn = 0; chn < BN / 32; chn++) {
+      for (int chn = ehalf; chn < BN / 32; chn += GSTEP) {
         uint32_t r[32];
         tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + (uint32_t)(chn * 32), r);
         const int nb = n0 + chn * 32;
@@ -548,6 +566,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         if (CG == 1) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&ctl->tmem_empty[acc])) : "memory");
         else mbar_arrive_cluster(&ctl->tmem_empty[acc], 0);
       }
+    }
     }
   }
   tc_fence_before();
@@ -731,13 +750,15 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
   const int BN = (ncols % 256 == 0 || ncols > 384) ? 256 : (ncols > 64 ? 128 : 64);
   int CG = tc2_cta_group();
   if (BN / CG < 64) CG = 1;                        // keep >= 64 W rows per CTA
+  if (!g_force_cg && !getenv("FPB_TC_CTA_GROUP") && (p.K < 2304 || BN < 256)) CG = 1;   // measured: pairs pay off only for long K
   Tc2Params q;
   q.p = p;
   q.a_im2col = plain ? 0 : 1;
   q.lower_w = -p.pad_w; q.lower_h = -p.pad;
   { const char* e = getenv("FPB_TC2_DBG"); q.dbg = e ? atoi(e) : 0; }
   q.fast_epi = (p.out_bf16 && ncols % 64 == 0 && !(q.dbg & 16) && (!p.residual || p.ldr % 8 == 0) && p.ldc % 8 == 0 &&
-                p.split_col_off % 8 == 0 && (!p.pe || p.pe_ld % 4 == 0)) ? 1 : 0;
+                p.split_col_off % 8 == 0 && (!p.pe || (p.pe_ld % 4 == 0 && p.pe_rows >= 32)) &&
+                (p.m_split % 32 == 0 || p.m_split >= p.M)) ? 1 : 0;
   q.m_tiles = fpb_cdiv(p.M, TM * CG);
   q.n_tiles = fpb_cdiv(ncols, BN);
   CUtensorMap mA, mB;
