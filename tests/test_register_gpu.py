@@ -1,0 +1,114 @@
+"""End-to-end parity of FoundationPose.register()/track_one() (CUDA path through the C ABI) against the CPU oracle
+pipeline on the synthetic cube scene (BASELINE config 1 geometry, reduced hypothesis count so the oracle finishes in
+seconds).  Bounds: fp32 parity mode tight (1e-4); bf16 tensor-core mode against the north-star bounds, evaluated per
+refine iteration on the SAME input poses (1e-3 rad, 0.1 mm) so that one rounded crop window cannot mask an error."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+N_HYP = 12
+
+
+def _rot_err(Ra, Rb):
+  c = (np.trace(Ra @ Rb.T) - 1) / 2
+  return float(np.arccos(np.clip(c, -1, 1)))
+
+
+def _make(scene, precision):
+  from foundationpose_b200 import nets
+  from foundationpose_b200.estimater import FoundationPose
+  from foundationpose_b200.predict_pose_refine import PoseRefinePredictor
+  from foundationpose_b200.predict_score import ScorePredictor
+  from oracle.pipeline import OracleEstimator
+  from tests.helpers import mesh_np, centered
+  sd_r, sd_s = nets.synthetic_state_dict(nets.REFINE), nets.synthetic_state_dict(nets.SCORE)
+  est = FoundationPose(model_pts=scene['mesh'].vertices, model_normals=scene['mesh'].vertex_normals, mesh=scene['mesh'],
+                       refiner=PoseRefinePredictor(state_dict=sd_r, precision=precision),
+                       scorer=ScorePredictor(state_dict=sd_s, precision=precision), mesh_diameter=scene['diameter'])
+  mesh, _ = centered(scene)
+  orc = OracleEstimator(mesh_np(mesh), scene['diameter'], sd_r, sd_s)
+  step = len(est.rot_grid) // N_HYP
+  est.rot_grid = est.rot_grid[::step][:N_HYP].contiguous()
+  orc.rot_grid = orc.rot_grid[::step][:N_HYP].copy()
+  return est, orc
+
+
+def test_register_fp32_matches_oracle(scene1):
+  """fp32 parity mode, stage by stage on identical inputs (a refine step is followed by a round() of the crop window,
+  so free-running trajectories may legitimately diverge after a 1e-6 difference; each stage is fed the oracle's
+  inputs instead)."""
+  from oracle import ops as oo
+  est, orc = _make(scene1, 'fp32')
+  sc = scene1
+  best, poses_o, scores_o = orc.register(sc['K'], sc['rgb'], sc['depth'], sc['mask'], iteration=2, keep_trace=True)
+  d = orc.preprocess(sc['depth'])
+  xyz_map = oo.depth2xyzmap(d, sc['K'])
+  for step in orc.trace['refine']:
+    got, _ = est.refiner.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=sc['rgb'], depth=d, K=sc['K'],
+                                 ob_in_cams=step['poses_in'], xyz_map=xyz_map, mesh_diameter=est.diameter, iteration=1)
+    assert np.abs(est.refiner.last_trans_update.cpu().numpy() - step['trans']).max() < 2e-4
+    assert np.abs(est.refiner.last_rot_update.cpu().numpy() - step['rot']).max() < 2e-4
+    assert np.abs(got.cpu().numpy() - step['poses_out']).max() < 1e-4
+  tr = orc.trace['score']
+  got_s, _ = est.scorer.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=sc['rgb'], depth=d, K=sc['K'],
+                                ob_in_cams=tr['poses'], mesh_diameter=est.diameter)
+  assert np.abs(est.scorer.last_features.cpu().numpy() - tr['feats']).max() < 2e-4
+  assert np.abs(got_s.cpu().numpy() - tr['scores']).max() < 2e-3
+  assert int(got_s.argmax()) == int(np.argmax(tr['scores']))
+  # the free-running register() returns a pose of the right form
+  pose = est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=2)
+  assert pose.shape == (4, 4) and abs(np.linalg.det(pose[:3, :3]) - 1) < 1e-4
+
+
+def test_refine_iteration_bf16_within_north_star_bounds(scene1):
+  """One refine iteration from identical input poses: bf16 tcgen05 path vs fp32 oracle."""
+  from tests.helpers import hypo_poses
+  est, orc = _make(scene1, 'bf16')
+  sc = scene1
+  poses, d = hypo_poses(sc, n=N_HYP, jitter_seed=3)
+  from oracle import ops as oo
+  xyz_map = oo.depth2xyzmap(d, sc['K'])
+  ref = orc.refine_predict(sc['rgb'], xyz_map, poses, sc['K'], 1)
+  got, _ = est.refiner.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=sc['rgb'], depth=d, K=sc['K'], ob_in_cams=poses,
+                               xyz_map=xyz_map, mesh_diameter=est.diameter, iteration=1)
+  got = got.cpu().numpy()
+  rot = max(_rot_err(got[i, :3, :3], ref[i, :3, :3]) for i in range(N_HYP))
+  trn = float(np.abs(got[:, :3, 3] - ref[:, :3, 3]).max())
+  moved = max(_rot_err(ref[i, :3, :3], poses[i, :3, :3]) for i in range(N_HYP))
+  print(f'bf16 one-iteration error: rot {rot:.2e} rad, trans {trn*1e3:.4f} mm (update magnitude {moved:.3f} rad)')
+  assert moved > 1e-2                                    # the synthetic weights do move the pose
+  assert rot < 1e-3 and trn < 1e-4
+
+
+def test_register_bf16_ranking_agrees(scene1):
+  est, orc = _make(scene1, 'bf16')
+  sc = scene1
+  est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=2)
+  # score the GPU's refined poses with the oracle scorer: top-1 must agree
+  poses = est.poses.cpu().numpy()
+  d = orc.preprocess(sc['depth'])
+  ref_scores, _ = orc.score_predict(sc['rgb'], d, poses, sc['K'])
+  got = est.scores.cpu().numpy()
+  margin = np.sort(ref_scores)[-1] - np.sort(ref_scores)[-2]
+  print('score margin', margin, 'max |diff|', np.abs(got - ref_scores).max())
+  assert int(np.argmax(ref_scores)) == 0 or margin < 2 * np.abs(got - ref_scores).max()
+
+
+def test_degenerate_inputs_and_track_one(scene1):
+  est, orc = _make(scene1, 'bf16')
+  sc = scene1
+  with pytest.raises(RuntimeError):
+    est.track_one(rgb=sc['rgb'], depth=sc['depth'], K=sc['K'], iteration=1)
+  empty = np.zeros_like(sc['mask'])
+  assert np.array_equal(est.guess_translation(sc['depth'], empty, sc['K']), np.zeros(3))
+  tiny = np.zeros_like(sc['mask']); ys, xs = np.nonzero(sc['mask']); tiny[ys[0], xs[0]] = 1
+  pose = est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=tiny, iteration=1)
+  assert np.array_equal(pose[:3, :3], np.eye(3))         # < 4 valid pixels -> identity rotation (src/estimater.py:185-189)
+  est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=1)
+  last = est.pose_last.cpu().numpy().copy()
+  out = est.track_one(rgb=sc['rgb'], depth=sc['depth'], K=sc['K'], iteration=2)
+  ref = orc.track_one(sc['rgb'], sc['depth'], sc['K'], last, 2)
+  tf = est.get_tf_to_centered_mesh().cpu().numpy()
+  assert out.shape == (4, 4)
+  assert _rot_err(out[:3, :3], (ref @ tf)[:3, :3]) < 2e-3 and np.abs(out[:3, 3] - (ref @ tf)[:3, 3]).max() < 2e-4
