@@ -248,8 +248,12 @@ def main():
   pk = peaks()
   dom = time_dominant_kernel(torch)
   step_flops = n_hyp * (ITERS * FLOP_REFINE + FLOP_SCORE)
+  traffic = None
+  prof = os.path.join(ROOT, 'profiles', 'ncu_conv6_r01.json')      # dram__bytes_read+write of this kernel, one ncu --set full capture
+  if os.path.exists(prof):
+    traffic = json.load(open(prof)).get('traffic_bytes_per_launch')
   roof = dict(bound='tensor', achieved=dom['tflops'], peak=pk['tf_burst'], unit='TFLOP/s', frac=dom['tflops'] / pk['tf_burst'],
-              traffic=None, kernel=dom['kernel'], ms_per_launch=dom['ms'], flops_per_launch=dom['flops'], peak_source=pk['src'],
+              traffic=traffic, kernel=dom['kernel'], ms_per_launch=dom['ms'], flops_per_launch=dom['flops'], peak_source=pk['src'],
               step_tflops=step_flops * world * args.steps / (dev_ms / 1e3) / 1e12 / world,
               step_frac_of_sustained=step_flops * args.steps / (dev_ms / 1e3) / 1e12 / pk['tf_sust'])
   cpu = None
