@@ -431,6 +431,13 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
   return rc;
 }
 
+// unit-test entry of the fused self-attention kernel (net_attn.cu)
+FPB_EXPORT int fpb_debug_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups,
+                                   void* stream)
+{
+  return tc_attention(qk, vt, vt_pitch, bv, ctx, groups, (cudaStream_t)stream);
+}
+
 FPB_EXPORT int fpb_debug_igemm(int precision, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
                                int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad, const float* scale,
                                const float* shift, const void* residual, int relu, int out_bf16, void* stream)

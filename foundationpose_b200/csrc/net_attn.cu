@@ -106,6 +106,19 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t* r)
+{
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[32])
 {
   asm volatile(
@@ -234,47 +247,61 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
       tc_fence_after();
       uint32_t r[32];
       float mx = -INFINITY;
+      {
+        // pass 1: row max; four 32-column TMEM loads in flight per wait, four independent max chains
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
-      for (int c = 0; c < TOK / 32; c++) {
-        tmem_ld32(t_row + (uint32_t)(c * 32), r);
+        for (int c = 0; c < TOK / 128; c++) {
+          uint32_t rb[128];
 #pragma unroll
-        for (int i = 0; i < 32; i++) mx = fmaxf(mx, __uint_as_float(r[i]));
+          for (int b = 0; b < 4; b++) tmem_ld32_nowait(t_row + (uint32_t)(c * 128 + b * 32), rb + b * 32);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 128; i++) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(rb[i]));
+        }
+        tmem_ld16(t_row + (uint32_t)(TOK / 128 * 128), r);
+#pragma unroll
+        for (int i = 0; i < 16; i++) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(r[i]));
+        mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
       }
-      tmem_ld16(t_row + (uint32_t)(TOK / 32 * 32), r);
-#pragma unroll
-      for (int i = 0; i < 16; i++) mx = fmaxf(mx, __uint_as_float(r[i]));
       const float off = -mx * c1;
       float sum = 0.0f;
 #pragma unroll 1
       for (int j = 0; j < N_KEY_CHUNKS; j++, gi++) {
         const uint32_t s = gi & 1u, use = gi >> 1;
-        mbar_wait(&ctl->p_empty[s], (use & 1u) ^ 1u);
+        const bool tail = j == N_KEY_CHUNKS - 1;
+        uint32_t r2[64];
+        if (tail) {
+          tmem_ld16(t_row + (uint32_t)(j * 64), r);
+#pragma unroll
+          for (int i = 0; i < 16; i++) r2[i] = r[i];
+        } else {
+          tmem_ld32_nowait(t_row + (uint32_t)(j * 64), r2);
+          tmem_ld32_nowait(t_row + (uint32_t)(j * 64 + 32), r2 + 32);
+        }
+        mbar_wait(&ctl->p_empty[s], (use & 1u) ^ 1u);        // overlaps the TMEM load latency
+        tmem_ld_wait();
         const uint32_t sp = smem_u32(sP + s * T16) + (uint32_t)(row * 128);
-        const int nhalf = j < N_KEY_CHUNKS - 1 ? 2 : 1;
-        for (int hf = 0; hf < nhalf; hf++) {
-          const bool tail = j == N_KEY_CHUNKS - 1;
-          if (tail) tmem_ld16(t_row + (uint32_t)(j * 64), r);
-          else tmem_ld32(t_row + (uint32_t)(j * 64 + hf * 32), r);
-          const int n16 = tail ? 2 : 4;                      // 16-byte chunks (8 keys each) produced by this half
+        const int n16 = tail ? 2 : 8;                          // 16-byte chunks (8 keys each) of this key chunk
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int q8 = 0; q8 < 4; q8++) {
-            if (q8 < n16) {
-              uint32_t pk[4];
+        for (int jj = 0; jj < 8; jj++) {
+          if (jj < n16) {
+            uint32_t pk[4];
 #pragma unroll
-              for (int e = 0; e < 4; e++) {
-                const float p0 = exp2f(fmaf(__uint_as_float(r[q8 * 8 + e * 2]), c1, off));
-                const float p1 = exp2f(fmaf(__uint_as_float(r[q8 * 8 + e * 2 + 1]), c1, off));
-                sum += p0 + p1;
-                __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
-                pk[e] = *reinterpret_cast<uint32_t*>(&hh);
-              }
-              const int jj = hf * 4 + q8;
-              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sp + (uint32_t)((jj ^ (row & 7)) << 4)), "r"(pk[0]),
-                           "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
-                           : "memory");
+            for (int e = 0; e < 4; e++) {
+              const float p0 = exp2f(fmaf(__uint_as_float(r2[jj * 8 + e * 2]), c1, off));
+              const float p1 = exp2f(fmaf(__uint_as_float(r2[jj * 8 + e * 2 + 1]), c1, off));
+              s4[e] += p0 + p1;
+              __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+              pk[e] = *reinterpret_cast<uint32_t*>(&hh);
             }
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sp + (uint32_t)((jj ^ (row & 7)) << 4)), "r"(pk[0]),
+                         "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                         : "memory");
           }
         }
+        sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
         tc_fence_before();
         fence_proxy_async();
         mbar_arrive(&ctl->p_full[s]);

@@ -130,6 +130,12 @@ int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* C, int M, i
                        const float* scale, const float* shift, const void* residual, int relu, int out_bf16,
                        void* stream);
 
+/* unit-test entry: fused bf16 multi-head self-attention over groups x 400 tokens (4 heads x 128):
+ * qk [R][1024] = Q | K projections, vt [512][vt_pitch] = V^T (row h*128+d, column = token row), bv fp32 [512] V bias,
+ * ctx [R][512] out;  R = groups*400.  Replaces nn.MultiheadAttention's core (refine_network.py:56-70). */
+int fpb_debug_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups,
+                        void* stream);
+
 /* number of kernels this library launched on the calling thread since the last reset */
 long long fpb_launch_count(int reset);
 

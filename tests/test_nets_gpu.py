@@ -215,3 +215,25 @@ def test_cuda_nets_match_reference_golden(prec, tol):
   if prec == 'fp32':
     logit = net.score_cross(f, n, 1).reshape(-1).cpu().numpy()
     assert np.abs(logit - g['logits'].reshape(-1)).max() < 5e-4
+
+
+@pytest.mark.parametrize('groups', [1, 3])
+def test_fused_attention_matches_torch(groups):
+  """net_attn.cu vs torch softmax attention on the same bf16 operands (fp32 math): 400 tokens, 4 heads x 128."""
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  g = torch.Generator(device='cuda').manual_seed(11 + groups)
+  R = groups * 400
+  qk = (torch.randn(R, 1024, device='cuda', generator=g) * 1.5).bfloat16()
+  v = torch.randn(R, 512, device='cuda', generator=g).bfloat16()
+  bv = torch.randn(512, device='cuda', generator=g) * 0.1
+  vt = v.t().contiguous()                                   # [512, R]
+  ctx = torch.empty(R, 512, device='cuda', dtype=torch.bfloat16)
+  check(lib().fpb_debug_attention(ptr(qk), ptr(vt), R, ptr(bv), ptr(ctx), groups, stream()))
+  torch.cuda.synchronize()
+  q = qk[:, :512].float().reshape(groups, 400, 4, 128).permute(0, 2, 1, 3)
+  k = qk[:, 512:].float().reshape(groups, 400, 4, 128).permute(0, 2, 1, 3)
+  vv = v.float().reshape(groups, 400, 4, 128).permute(0, 2, 1, 3)
+  p = torch.softmax(q @ k.transpose(-1, -2) / 128 ** 0.5, dim=-1)
+  ref = (p @ vv).permute(0, 2, 1, 3).reshape(R, 512) + bv
+  err = (ctx.float() - ref).abs().max().item()
+  assert err < 2e-2, err                                    # bf16 probabilities + bf16 output rounding
