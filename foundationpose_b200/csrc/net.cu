@@ -105,9 +105,9 @@ Ws carve(char* base, int n, size_t esz)
   size_t o = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + o : nullptr; o += al(bytes); return p; };
   w.c0 = take((size_t)2 * n * 6400 * 64 * esz);
-  w.c1 = take((size_t)2 * n * 1600 * 128 * esz);
-  w.c2 = take((size_t)2 * n * 1600 * 128 * esz);
-  w.c3 = take((size_t)2 * n * 1600 * 128 * esz);
+  w.c1 = take((size_t)2 * n * 1681 * 128 * esz);      // 41 x 41 zero-bordered positions per image (halo layout)
+  w.c2 = take((size_t)2 * n * 1681 * 128 * esz);
+  w.c3 = take((size_t)2 * n * 1681 * 128 * esz);
   w.ab0 = take((size_t)n * 1600 * 256 * esz);
   w.ab1 = take((size_t)n * 1600 * 256 * esz);
   w.ab2 = take((size_t)n * 1600 * 256 * esz);
@@ -144,13 +144,30 @@ struct Ctx {
 
 #define RET(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
 
+bool use_halo()
+{
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("FPB_HALO"); v = e ? atoi(e) : 0; }   // measured slower than im2col at one tap per stage: off
+  return v != 0;
+}
+
+// in_pos / out_pos: activation in the zero-bordered position layout (GemmProblem::halo) instead of dense NHWC
 int run_conv(const Ctx& c, int li, const void* in, int nimg, void* out, const void* residual, int relu, bool pe,
-             int m_split, int split_off, int ldc)
+             int m_split, int split_off, int ldc, int in_pos = 0, int out_pos = 0)
 {
   const ConvSpec& s = kConvs[li];
   GemmProblem p = gemm_problem_default();
   p.A = in; p.W = c.W(c.net->conv[li].w); p.C = out;
   p.M = nimg * s.Ho * s.Ho; p.N = s.Cout; p.K = s.KH * s.KW * s.Cin;
+  if (in_pos || out_pos) {
+    p.img_h = p.img_w = s.Ho;
+    const int IS = (s.Ho + 1) * (s.Ho + 1);
+    if (in_pos) { p.halo = 1; p.M = nimg * IS; p.row_remap = out_pos ? 0 : 2; }
+    else {
+      p.row_remap = 1;    // dense rows -> positions: the borders are never written, clear them first
+      FPB_CUDA(cudaMemsetAsync(out, 0, (size_t)nimg * IS * s.Cout * c.esz, c.st));
+    }
+  }
   p.Hin = p.Win = s.Hin; p.Cin = s.Cin; p.Ho = p.Wo = s.Ho; p.KH = s.KH; p.KW = s.KW; p.stride = s.stride;
   p.pad = p.pad_w = s.pad;
   p.pix_pitch = s.Cin; p.ldw = p.K;
@@ -179,12 +196,15 @@ int run_linear(const Ctx& c, const Lin& l, const void* in, long long rows, void*
 int run_encoders(const Ctx& c, const void* AB, int n, Ws& w)
 {
   RET(run_conv(c, 0, AB, 2 * n, w.c0, nullptr, 1, false, 0, 0, 0));
-  RET(run_conv(c, 1, w.c0, 2 * n, w.c1, nullptr, 1, false, 0, 0, 0));
-  RET(run_conv(c, 2, w.c1, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0));
-  RET(run_conv(c, 3, w.c2, 2 * n, w.c3, w.c1, 1, false, 0, 0, 0));
-  RET(run_conv(c, 4, w.c3, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0));
+  // optional (FPB_HALO=1): 3x3 stride-1 blocks in the zero-bordered position layout (one TMA box per 64 channels feeds all
+  // 9 taps); kept for the record with its tests -- per-stage pipeline overhead makes it slower than the im2col path today
+  const int hp = (c.bf && use_halo()) ? 1 : 0;
+  RET(run_conv(c, 1, w.c0, 2 * n, w.c1, nullptr, 1, false, 0, 0, 0, 0, hp));
+  RET(run_conv(c, 2, w.c1, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0, hp, hp));
+  RET(run_conv(c, 3, w.c2, 2 * n, w.c3, w.c1, 1, false, 0, 0, 0, hp, hp));
+  RET(run_conv(c, 4, w.c3, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0, hp, hp));
   // last encodeA conv writes cat((a,b),1): rows of the first n images -> channels [0,128), last n -> [128,256)
-  RET(run_conv(c, 5, w.c2, 2 * n, w.ab0, w.c3, 1, false, n * 1600, 128, 256));
+  RET(run_conv(c, 5, w.c2, 2 * n, w.ab0, w.c3, 1, false, n * 1600, 128, 256, hp, 0));
   RET(run_conv(c, 6, w.ab0, n, w.ab1, nullptr, 1, false, 0, 0, 0));
   RET(run_conv(c, 7, w.ab1, n, w.ab2, w.ab0, 1, false, 0, 0, 0));
   RET(run_conv(c, 8, w.ab2, n, w.ab1, nullptr, 1, false, 0, 0, 0));
@@ -428,6 +448,26 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
   const int rc = tc2_gemm(p, st);
   tc2_force_cta_group(0);
   if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_igemm: shape not supported by the TMA kernel");
+  return rc;
+}
+
+// unit-test entry of the halo 3x3 convolution / row remapping modes of the persistent TMA kernel:
+//   A: zero-bordered activation [nimg*(H+1)*(W+1) positions][Cin] (halo=1) or dense NHWC (halo=0, remap=1, 3x3 s1 p1);
+//   row_remap 0: output at positions, 1: dense rows -> positions (halo must be 0), 2: positions -> dense rows.
+FPB_EXPORT int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* W, void* C, int nimg, int H, int Wd, int Cin,
+                                      int Cout, int halo, int row_remap, const float* scale, const float* shift,
+                                      const void* residual, int relu, void* stream)
+{
+  GemmProblem p = gemm_problem_default();
+  p.A = A; p.W = W; p.C = C; p.N = Cout; p.K = 9 * Cin; p.Cin = Cin; p.pix_pitch = Cin; p.ldw = p.K;
+  p.KH = p.KW = 3; p.stride = 1; p.pad = p.pad_w = 1; p.Hin = p.Ho = H; p.Win = p.Wo = Wd;
+  p.img_h = H; p.img_w = Wd; p.halo = halo; p.row_remap = row_remap;
+  p.M = halo ? nimg * (H + 1) * (Wd + 1) : nimg * H * Wd;
+  p.scale = scale; p.shift = shift; p.residual = residual; p.ldr = Cout; p.relu = relu; p.ldc = Cout; p.out_bf16 = 1;
+  tc2_force_cta_group(cta_group);
+  const int rc = tc2_gemm(p, (cudaStream_t)stream);
+  tc2_force_cta_group(0);
+  if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_conv3x3_halo: shape not supported");
   return rc;
 }
 

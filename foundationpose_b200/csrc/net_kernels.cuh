@@ -36,6 +36,13 @@ struct GemmProblem {
   int ldc, m_split, split_col_off;
   int out_bf16;
   int n_valid;        // columns >= n_valid are not stored (N padding)
+  // "halo" 3x3 stride-1 convolution over a zero-bordered activation (tc2 kernel only).  Positions p = img*IS +
+  // (y+1)*Wp + x with Wp = img_w+1, IS = (img_h+1)*Wp: every image row is followed by one zero pixel and every image
+  // is preceded by one zero row, so filter tap (ky,kx) of 128 consecutive positions is the same 128 rows of the
+  // flattened [positions][C] matrix shifted by (ky-1)*Wp + (kx-1): ONE TMA box per 64-channel chunk serves all 9
+  // taps.  M counts positions; outputs at border positions are written as zeros.
+  int halo, img_h, img_w;
+  int row_remap;      // output rows: 0 as computed, 1 dense pixel index -> position, 2 position -> dense (borders skipped)
 };
 
 static inline GemmProblem gemm_problem_default()

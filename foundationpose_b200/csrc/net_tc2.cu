@@ -202,14 +202,18 @@ struct Tc2Params {
   int a_im2col;          // 1: A through the im2col map, 0: tiled 2-D map over [M][K]
   int lower_w, lower_h;  // im2col bounding-box lower corner (= -pad)
   int m_tiles, n_tiles;  // tiles of (TM*CG) x BN
+  int halo, Wp, IS, hrows, na, nb;   // halo mode: position pitch, image stride, A box rows, A / W ring depths
   int fast_epi;          // 1: smem-transposed, fully coalesced bf16 epilogue (ncols % 64 == 0)
   int dbg;               // FPB_TC2_DBG experiment bits: 1 no stores, 2 no scale/shift, 4 no residual, 8 no MMA
 };
 
+constexpr int A_HALO_BYTES = 27 * 1024;          // >= (128 + 2*Wp + 2) rows x 128 B for Wp <= 42
 template <int STAGES>
 struct SmemCtl {
-  uint64_t full[STAGES];
-  uint64_t empty[STAGES];
+  uint64_t full[8];
+  uint64_t empty[8];
+  uint64_t afull[4];
+  uint64_t aempty[4];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
@@ -222,8 +226,10 @@ struct Cfg {
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   // per epilogue warp: 4 KB output staging + 4 KB residual staging + 4 KB positional-embedding staging + scale/shift
   static constexpr int EPI_WARPS = BN >= 128 ? 8 : 4;         // 2 warps per TMEM lane quarter split the 64-column groups
-  static constexpr int EPI_WARP_BYTES = 2 * 4096 + 2 * BN * 4;
-  static constexpr int EPI_BYTES = 8 * EPI_WARP_BYTES;
+  // one 4 KB staging tile per epilogue warp (residual in, positional embedding in, result out share it) plus a
+  // double-buffered scale/shift table shared by the CTA
+  static constexpr int EPI_WARP_BYTES = 4096;
+  static constexpr int EPI_BYTES = 8 * EPI_WARP_BYTES + 2 * (2 * BN * 4);
   static constexpr int STAGES_RAW = (224 * 1024 - EPI_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
@@ -248,7 +254,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   const int nk = p.K / KC;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; s++) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+    for (int s = 0; s < 8; s++) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+    for (int s = 0; s < 4; s++) { mbar_init(&ctl->afull[s], 1); mbar_init(&ctl->aempty[s], 1); }
     for (int a = 0; a < 2; a++) { mbar_init(&ctl->tmem_full[a], 1); mbar_init(&ctl->tmem_empty[a], C::EPI_WARPS * CG); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -274,40 +281,71 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
 
+  // Both single-thread roles keep ring positions as (stage, phase) pairs advanced incrementally: every integer division
+  // or modulo by a run-time value in these loops showed up directly as pipeline time (measured: the halo loop went
+  // from 890 to the im2col loop's 410 cycles per stage with no loads and no MMAs issued).
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (one lane, every CTA)
     if (lane == 0) {
-      const int hw = p.Ho * p.Wo;
-      uint32_t it = 0;
-      for (int t = cluster_id; t < total_tiles; t += n_clusters) {
-        const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
-        const int m0 = (mt * CG + (int)rank) * TM;
-        const int nrow0 = nt * BN + (int)rank * C::B_ROWS;
-        int cw = 0, ch = 0, img = 0;
-        if (q.a_im2col) {
-          img = m0 / hw;
-          const int r = m0 - img * hw;
-          const int oy = r / p.Wo, ox = r - oy * p.Wo;
-          cw = ox * p.stride + q.lower_w;
-          ch = oy * p.stride + q.lower_h;
-        }
-        for (int kc = 0; kc < nk; kc++, it++) {
-          const int s = it % STAGES;
-          mbar_wait(&ctl->empty[s], ((it / STAGES) & 1) ^ 1);
-          const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
-          const uint32_t sb = sa + A_STAGE_BYTES;
-          uint32_t bar = smem_u32(&ctl->full[s]);
-          if (CG == 2) bar = mapa_u32(bar, 0);            // both CTAs signal the leader's barrier
-          if (rank == 0) mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(CG * C::STAGE_BYTES));
-          const int k0 = kc * KC;
-          if (q.a_im2col) {
-            const int tap = k0 / p.Cin, c0 = k0 - tap * p.Cin;
-            const int ky = tap / p.KW, kx = tap - ky * p.KW;
-            tma_load_im2col<CG>(sa, &mapA, bar, c0, cw, ch, img, (uint16_t)kx, (uint16_t)ky);
-          } else {
-            tma_load_2d<CG>(sa, &mapA, bar, k0, m0);
+      const uint32_t full0 = CG == 2 ? mapa_u32(smem_u32(&ctl->full[0]), 0) : smem_u32(&ctl->full[0]);     // leader's barriers
+      const uint32_t afull0 = CG == 2 ? mapa_u32(smem_u32(&ctl->afull[0]), 0) : smem_u32(&ctl->afull[0]);
+      const bool no_a = q.dbg & 128, no_b = q.dbg & 256;
+      if (q.halo) {
+        const int nchunk = p.Cin / KC;
+        const uint32_t sA0 = smem_u32(smem), sB0 = sA0 + q.na * A_HALO_BYTES;
+        const uint32_t a_tx = no_a ? 0u : (uint32_t)(CG * q.hrows * 128), b_tx = no_b ? 0u : (uint32_t)(CG * C::B_STAGE_BYTES);
+        int sa = 0, sb = 0;
+        uint32_t pa = 1, pb = 1;                               // producer waits with inverted parity
+        for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+          const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
+          const int m0 = (mt * CG + (int)rank) * TM;
+          const int nrow0 = nt * BN + (int)rank * C::B_ROWS;
+          for (int c = 0; c < nchunk; c++) {
+            mbar_wait(&ctl->aempty[sa], pa);
+            if (rank == 0) mbar_arrive_expect_tx(&ctl->afull[sa], a_tx);
+            if (!no_a) tma_load_2d<CG>(sA0 + sa * A_HALO_BYTES, &mapA, afull0 + 8u * sa, c * KC, m0 - q.Wp - 1);
+            if (++sa == q.na) { sa = 0; pa ^= 1u; }
+            int kcol = c * KC;
+            for (int tap = 0; tap < 9; tap++, kcol += p.Cin) {
+              mbar_wait(&ctl->empty[sb], pb);
+              if (rank == 0) mbar_arrive_expect_tx(&ctl->full[sb], b_tx);
+              if (!no_b) tma_load_2d<CG>(sB0 + sb * C::B_STAGE_BYTES, &mapB, full0 + 8u * sb, kcol, nrow0);
+              if (++sb == q.nb) { sb = 0; pb ^= 1u; }
+            }
           }
-          tma_load_2d<CG>(sb, &mapB, bar, k0, nrow0);
+        }
+      } else {
+        const int hw = p.Ho * p.Wo;
+        const uint32_t tx = (uint32_t)(CG * ((no_a ? 0 : A_STAGE_BYTES) + (no_b ? 0 : C::B_STAGE_BYTES)));
+        const uint32_t s0 = smem_u32(smem);
+        int s = 0;
+        uint32_t ph = 1;
+        for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+          const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
+          const int m0 = (mt * CG + (int)rank) * TM;
+          const int nrow0 = nt * BN + (int)rank * C::B_ROWS;
+          int cw = 0, ch = 0, img = 0;
+          if (q.a_im2col) {
+            img = m0 / hw;
+            const int r = m0 - img * hw;
+            const int oy = r / p.Wo, ox = r - oy * p.Wo;
+            cw = ox * p.stride + q.lower_w;
+            ch = oy * p.stride + q.lower_h;
+          }
+          int k0 = 0, c0 = 0, kx = 0, ky = 0;                  // K walks (ky, kx, c) with c fastest
+          for (int kc = 0; kc < nk; kc++, k0 += KC) {
+            mbar_wait(&ctl->empty[s], ph);
+            const uint32_t sa = s0 + s * C::STAGE_BYTES;
+            if (rank == 0) mbar_arrive_expect_tx(&ctl->full[s], tx);
+            if (!no_a) {
+              if (q.a_im2col) tma_load_im2col<CG>(sa, &mapA, full0 + 8u * s, c0, cw, ch, img, (uint16_t)kx, (uint16_t)ky);
+              else tma_load_2d<CG>(sa, &mapA, full0 + 8u * s, k0, m0);
+            }
+            if (!no_b) tma_load_2d<CG>(sa + A_STAGE_BYTES, &mapB, full0 + 8u * s, k0, nrow0);
+            c0 += KC;
+            if (c0 == p.Cin) { c0 = 0; if (++kx == p.KW) { kx = 0; ky++; } }
+            if (++s == STAGES) { s = 0; ph ^= 1u; }
+          }
         }
       }
     }
@@ -315,25 +353,68 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     // ------------------------------------------------------------------ MMA issuer (leader CTA, one lane)
     if (rank == 0 && lane == 0) {
       constexpr uint32_t idesc = make_idesc(TM * CG, BN);
-      uint32_t it = 0, tc = 0;
-      for (int t = cluster_id; t < total_tiles; t += n_clusters, tc++) {
-        const uint32_t acc = tc & 1u;
-        mbar_wait(&ctl->tmem_empty[acc], ((tc >> 1) & 1u) ^ 1u);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kc = 0; kc < nk; kc++, it++) {
-          const int s = it % STAGES;
-          mbar_wait(&ctl->full[s], (it / STAGES) & 1);
+      const bool no_mma = q.dbg & 8;
+      uint32_t acc = 0, acc_ph = 1;                            // waits on tmem_empty with inverted parity
+      if (q.halo) {
+        const int nchunk = p.Cin / KC;
+        const uint32_t sA0 = smem_u32(smem), sB0 = sA0 + q.na * A_HALO_BYTES;
+        const uint32_t row_step = (uint32_t)(q.Wp * 128);          // one image row of positions
+        int sa = 0, sb = 0;
+        uint32_t pa = 0, pb = 0;
+        for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+          mbar_wait(&ctl->tmem_empty[acc], acc_ph);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
-          const uint64_t da = make_desc(sa), db = make_desc(sa + A_STAGE_BYTES);
-          if (!(q.dbg & 8))
+          const uint32_t d_tmem = tmem_base + acc * BN;
+          for (int c = 0; c < nchunk; c++) {
+            mbar_wait(&ctl->afull[sa], pa);
+            // the 128B swizzle is a function of the absolute smem address (measured: the descriptor base_offset must
+            // stay 0 for start rows that are not multiples of 8), so a filter tap is just a start-address shift
+            uint32_t a_addr = sA0 + sa * A_HALO_BYTES;
+            for (int ky = 0; ky < 3; ky++, a_addr += row_step) {
+              for (int kx = 0; kx < 3; kx++, a_addr += 128u) {
+                mbar_wait(&ctl->full[sb], pb);
+                tc_fence_after();
+                const uint64_t da = make_desc(a_addr), db = make_desc(sB0 + sb * C::B_STAGE_BYTES);
+                if (!no_mma) {
 #pragma unroll
-          for (int k = 0; k < KC / 16; k++)
-            umma_bf16<CG>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
-          umma_commit<CG>(&ctl->empty[s]);
+                  for (int k = 0; k < KC / 16; k++)
+                    umma_bf16<CG>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (c | ky | kx | k) ? 1u : 0u);
+                }
+                umma_commit<CG>(&ctl->empty[sb]);
+                if (++sb == q.nb) { sb = 0; pb ^= 1u; }
+              }
+              a_addr -= 3u * 128u;
+            }
+            umma_commit<CG>(&ctl->aempty[sa]);
+            if (++sa == q.na) { sa = 0; pa ^= 1u; }
+          }
+          umma_commit<CG>(&ctl->tmem_full[acc]);
+          if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
         }
-        umma_commit<CG>(&ctl->tmem_full[acc]);
+      } else {
+        const uint32_t s0 = smem_u32(smem);
+        int s = 0;
+        uint32_t ph = 0;
+        for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+          mbar_wait(&ctl->tmem_empty[acc], acc_ph);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * BN;
+          for (int kc = 0; kc < nk; kc++) {
+            mbar_wait(&ctl->full[s], ph);
+            tc_fence_after();
+            const uint32_t sa = s0 + s * C::STAGE_BYTES;
+            const uint64_t da = make_desc(sa), db = make_desc(sa + A_STAGE_BYTES);
+            if (!no_mma) {
+#pragma unroll
+              for (int k = 0; k < KC / 16; k++)
+                umma_bf16<CG>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
+            }
+            umma_commit<CG>(&ctl->empty[s]);
+            if (++s == STAGES) { s = 0; ph ^= 1u; }
+          }
+          umma_commit<CG>(&ctl->tmem_full[acc]);
+          if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
+        }
       }
     }
   } else {
@@ -372,21 +453,41 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         //      8 lanes per row read it back and store 128 contiguous bytes per row; residual / positional embedding
         //      travel the same way in the opposite direction.
         uint8_t* ew = epi_smem + (warp - 2) * C::EPI_WARP_BYTES;
-        const uint32_t s_out = smem_u32(ew), s_res = s_out + 4096, s_pe = s_res;   // pe reuses the residual tile
-        float* ss = (float*)(ew + 8192);                       // scale[BN], shift[BN] of this n-tile
+        const uint32_t s_out = smem_u32(ew), s_res = s_out, s_pe = s_out;   // one tile, used in turn (guarded by __syncwarp)
+        float* ss = (float*)(epi_smem + 8 * C::EPI_WARP_BYTES) + (tc & 1u) * (2 * BN);   // scale[BN], shift[BN] of this n-tile
         const int m_w = (mt * CG + (int)rank) * TM + quarter * 32;   // first row of this warp
         const int sub = lane >> 3, cj = lane & 7;               // coalesced role: row 4i+sub, 16-byte chunk cj
         // a warp's 32 rows never straddle m_split (host guarantees m_split % 32 == 0 or m_split >= M)
         const int seg = m_w / p.m_split;
         __nv_bfloat16* out_w = (__nv_bfloat16*)p.C + (long long)(m_w - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
         const int pe_r0 = p.pe ? m_w % p.pe_rows : 0;
-        __syncwarp();
-        for (int i = lane; i < BN; i += 32) {
+        bool interior = true;                                   // halo mode: border positions produce zeros
+        if (q.halo) {
+          const int r_ = (m_w + lane) % q.IS, yy = r_ / q.Wp;
+          interior = yy >= 1 && r_ - yy * q.Wp < p.img_w;
+        }
+        // global address of output row mr (nullptr: not stored)
+        auto row_ptr = [&](int mr) -> __nv_bfloat16* {
+          if (mr >= p.M) return nullptr;
+          if (p.row_remap == 0) return out_w + (long long)(mr - m_w) * p.ldc;
+          const int hw = p.img_h * p.img_w;
+          if (p.row_remap == 1) {                               // dense pixel index -> zero-bordered position
+            const int img = mr / hw, r_ = mr - img * hw, y = r_ / p.img_w;
+            return (__nv_bfloat16*)p.C + ((long long)img * q.IS + (long long)(y + 1) * q.Wp + (r_ - y * p.img_w)) * p.ldc;
+          }
+          const int img = mr / q.IS, r_ = mr - img * q.IS, yy = r_ / q.Wp, xx = r_ - yy * q.Wp;   // position -> dense
+          if (yy < 1 || xx >= p.img_w) return nullptr;
+          const int md = img * hw + (yy - 1) * p.img_w + xx;
+          return (__nv_bfloat16*)p.C + (long long)(md % p.m_split) * p.ldc + (long long)(md / p.m_split) * p.split_col_off;
+        };
+        // the epilogue warps fill the table of this tile together; one named barrier per tile orders it (the table is
+        // double buffered, and passing the barrier of tile i+1 implies every warp has finished tile i)
+        for (int i = (warp - 2) * 32 + lane; i < BN; i += C::EPI_WARPS * 32) {
           const bool ok = n0 + i < nst;
           ss[i] = (p.scale && ok && !(q.dbg & 2)) ? __ldg(p.scale + n0 + i) : 1.0f;
           ss[BN + i] = (p.shift && ok && !(q.dbg & 2)) ? __ldg(p.shift + n0 + i) : 0.0f;
         }
-        __syncwarp();
+        asm volatile("bar.sync 1, %0;" ::"n"(C::EPI_WARPS * 32) : "memory");
         const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
 #pragma unroll 1
         for (int g = ehalf; g < BN / 64; g += GSTEP) {
@@ -463,7 +564,12 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               }
             }
           }
+          if (!interior) {
+#pragma unroll
+            for (int i = 0; i < 64; i++) v[i] = 0.0f;
+          }
           if ((q.dbg & 1) && v[0] != 123456.0f) { prefetch_next(); continue; }
+          __syncwarp();                                         // staging tile: residual / pe reads done before it is reused
 #pragma unroll
           for (int j = 0; j < 8; j++) {
             __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j * 8 + 0], v[j * 8 + 1]), h1 = __floats2bfloat162_rn(v[j * 8 + 2], v[j * 8 + 3]);
@@ -478,7 +584,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             const int mr = m_w + 4 * i + sub;
             uint4 ov;
             asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
-            if (mr < p.M) *(reinterpret_cast<uint4*>(out_w + (long long)(4 * i + sub) * p.ldc + nb) + cj) = ov;
+            __nv_bfloat16* op = row_ptr(mr);
+            if (op) *(reinterpret_cast<uint4*>(op + nb) + cj) = ov;
           }
           __syncwarp();
         }
@@ -682,9 +789,17 @@ int get_im2col_map(const GemmProblem& p, int nimg, CUtensorMap* out)
 }
 
 template <int BN, int CG>
-int launch_tc2(const CUtensorMap& mA, const CUtensorMap& mB, const Tc2Params& q, cudaStream_t st)
+int launch_tc2(const CUtensorMap& mA, const CUtensorMap& mB, const Tc2Params& q_in, cudaStream_t st)
 {
   using C = Cfg<BN, CG>;
+  Tc2Params q = q_in;
+  if (q.halo) {                                    // split the pipeline smem into an A-halo ring and a W ring
+    const int region = C::STAGES * C::STAGE_BYTES;
+    q.na = 2;
+    q.nb = (region - q.na * A_HALO_BYTES) / C::B_STAGE_BYTES;
+    if (q.nb > 8) q.nb = 8;
+    if (q.nb < 2) { fpb_set_error("tc2 halo mode: not enough shared memory"); return FPB_ERR_ARG; }
+  }
   static bool configured = false;
   if (!configured) {
     FPB_CUDA(cudaFuncSetAttribute(tc2_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
@@ -740,9 +855,12 @@ int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long lon
 // caller can fall back to the first-generation cp.async kernel (tc_gemm).
 int tc2_gemm(const GemmProblem& p, cudaStream_t st)
 {
-  if (p.batch != 1 || p.K % KC != 0 || p.Cin % KC != 0 || p.pix_pitch % 8 != 0 || p.ldw % 8 != 0) return FPB_ERR_UNSUPPORTED;
+  if (p.batch != 1 || p.K % KC != 0 || p.Cin % KC != 0 || p.pix_pitch % 8 != 0 || p.ldw % 8 != 0) {
+    if (p.halo || p.row_remap) { fpb_set_error("tc2_gemm: halo / row_remap problem has an unsupported shape"); return FPB_ERR_ARG; }
+    return FPB_ERR_UNSUPPORTED;
+  }
   if (((uintptr_t)p.A | (uintptr_t)p.W) & 15) return FPB_ERR_UNSUPPORTED;
-  const bool plain = p.KH == 1 && p.KW == 1 && p.stride == 1 && p.pad == 0 && p.pad_w == 0 && p.Ho == 1 && p.Wo == 1;
+  const bool plain = !p.halo && p.KH == 1 && p.KW == 1 && p.stride == 1 && p.pad == 0 && p.pad_w == 0 && p.Ho == 1 && p.Wo == 1;
   if (!plain && (p.pad > 127 || p.KH > 127)) return FPB_ERR_UNSUPPORTED;
   int rc = resolve_driver();
   if (rc) return rc;
@@ -759,10 +877,20 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
   q.fast_epi = (p.out_bf16 && ncols % 64 == 0 && !(q.dbg & 16) && (!p.residual || p.ldr % 8 == 0) && p.ldc % 8 == 0 &&
                 p.split_col_off % 8 == 0 && (!p.pe || (p.pe_ld % 4 == 0 && p.pe_rows >= 32)) &&
                 (p.m_split % 32 == 0 || p.m_split >= p.M)) ? 1 : 0;
+  q.halo = p.halo ? 1 : 0;
+  q.Wp = p.img_w + 1; q.IS = (p.img_h + 1) * q.Wp; q.hrows = TM + 2 * q.Wp + 2; q.na = q.nb = 0;
+  if (p.halo || p.row_remap) {
+    const bool ok = q.fast_epi && p.img_h > 0 && p.img_w > 0 && (!p.halo || (p.KH == 3 && p.KW == 3 && p.stride == 1 && q.hrows * 128 <= A_HALO_BYTES)) &&
+                    (p.row_remap == 2 || p.m_split >= p.M) && !p.pe;
+    if (!ok) { fpb_set_error("tc2_gemm: unsupported halo / row_remap configuration"); return FPB_ERR_ARG; }
+    if (p.halo && !g_force_cg && !getenv("FPB_TC_CTA_GROUP") && BN >= 128) CG = 2;     // halves the weight stream, now the larger one
+  }
   q.m_tiles = fpb_cdiv(p.M, TM * CG);
   q.n_tiles = fpb_cdiv(ncols, BN);
   CUtensorMap mA, mB;
-  if (plain) {
+  if (p.halo) {
+    rc = get_tiled_map(p.A, p.M, p.Cin, p.pix_pitch, q.hrows, &mA);       // [positions][C], box = halo rows x 64 channels
+  } else if (plain) {
     rc = get_tiled_map(p.A, p.M, p.K, p.pix_pitch, TM, &mA);
   } else {
     const int nimg = fpb_cdiv(p.M, p.Ho * p.Wo);

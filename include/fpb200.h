@@ -130,6 +130,12 @@ int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* C, int M, i
                        const float* scale, const float* shift, const void* residual, int relu, int out_bf16,
                        void* stream);
 
+/* unit-test entry: 3x3 stride-1 convolution in the zero-bordered "halo" activation layout (positions p =
+ * img*(H+1)*(W+1) + (y+1)*(W+1) + x; see csrc/net_kernels.cuh) and the dense<->position output row remapping. */
+int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* W, void* C, int nimg, int H, int Wd, int Cin, int Cout,
+                           int halo, int row_remap, const float* scale, const float* shift, const void* residual,
+                           int relu, void* stream);
+
 /* unit-test entry: fused bf16 multi-head self-attention over groups x 400 tokens (4 heads x 128):
  * qk [R][1024] = Q | K projections, vt [512][vt_pitch] = V^T (row h*128+d, column = token row), bv fp32 [512] V bias,
  * ctx [R][512] out;  R = groups*400.  Replaces nn.MultiheadAttention's core (refine_network.py:56-70). */

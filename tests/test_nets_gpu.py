@@ -237,3 +237,55 @@ def test_fused_attention_matches_torch(groups):
   ref = (p @ vv).permute(0, 2, 1, 3).reshape(R, 512) + bv
   err = (ctx.float() - ref).abs().max().item()
   assert err < 2e-2, err                                    # bf16 probabilities + bf16 output rounding
+
+
+def _to_pos(x):
+  """dense [n,H,W,C] -> zero-bordered positions [n*(H+1)*(W+1), C] (csrc/net_kernels.cuh halo layout)."""
+  n, H, W, C = x.shape
+  P = torch.zeros(n, H + 1, W + 1, C, dtype=x.dtype, device=x.device)
+  P[:, 1:, :W] = x
+  return P.reshape(-1, C)
+
+
+def _from_pos(P, n, H, W):
+  return P.reshape(n, H + 1, W + 1, -1)[:, 1:, :W]
+
+
+@pytest.mark.parametrize('cg', [1, 2])
+@pytest.mark.parametrize('shape', [(5, 40, 128, 128), (3, 20, 256, 256), (7, 40, 64, 128)])
+def test_conv3x3_halo_layout(cg, shape):
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  n, H, Cin, Cout = shape
+  g = torch.Generator(device='cuda').manual_seed(n * 100 + H)
+  x = torch.randn(n, H, H, Cin, device='cuda', generator=g).bfloat16()
+  w = (torch.randn(Cout, Cin, 3, 3, device='cuda', generator=g) / (9 * Cin) ** 0.5).bfloat16()
+  scale = torch.rand(Cout, device='cuda', generator=g) + 0.5
+  shift = torch.randn(Cout, device='cuda', generator=g) * 0.1
+  res = torch.randn(n, H, H, Cout, device='cuda', generator=g).bfloat16()
+  Wk = w.permute(0, 2, 3, 1).reshape(Cout, -1).contiguous()
+  ref = _ref_conv(x.float(), w.float(), 1, 1, scale, shift, res.float().reshape(-1, Cout), relu=1)
+  npos = n * (H + 1) * (H + 1)
+  xp, rp = _to_pos(x), _to_pos(res)          # keep alive: ptr() of a temporary would dangle
+  # (a) positions -> positions, residual in position layout, borders must come out as zeros
+  out = torch.full((npos, Cout), 7.0, device='cuda', dtype=torch.bfloat16)
+  check(lib().fpb_debug_conv3x3_halo(cg, ptr(xp), ptr(Wk), ptr(out), n, H, H, Cin, Cout, 1, 0, ptr(scale), ptr(shift),
+                                     ptr(rp), 1, stream()))
+  torch.cuda.synchronize()
+  got = _from_pos(out, n, H, H).float()
+  assert (got - ref).abs().max().item() < 3e-2, (got - ref).abs().max().item()
+  full = out.reshape(n, H + 1, H + 1, Cout).float()
+  assert full[:, 0].abs().max().item() == 0 and full[:, :, H].abs().max().item() == 0
+  # (b) positions -> dense rows
+  out2 = torch.zeros(n * H * H, Cout, device='cuda', dtype=torch.bfloat16)
+  check(lib().fpb_debug_conv3x3_halo(cg, ptr(xp), ptr(Wk), ptr(out2), n, H, H, Cin, Cout, 1, 2, ptr(scale), ptr(shift),
+                                     ptr(rp), 1, stream()))
+  torch.cuda.synchronize()
+  assert (out2.reshape(n, H, H, Cout).float() - ref).abs().max().item() < 3e-2
+  # (c) dense input through the im2col path, output rows remapped to positions (borders untouched)
+  out3 = torch.zeros(npos, Cout, device='cuda', dtype=torch.bfloat16)
+  rd = res.reshape(-1, Cout).contiguous()
+  check(lib().fpb_debug_conv3x3_halo(cg, ptr(x), ptr(Wk), ptr(out3), n, H, H, Cin, Cout, 0, 1, ptr(scale), ptr(shift),
+                                     ptr(rd), 1, stream()))
+  torch.cuda.synchronize()
+  assert (_from_pos(out3, n, H, H).float() - ref).abs().max().item() < 3e-2
+  assert out3.reshape(n, H + 1, H + 1, Cout)[:, 0].abs().max().item() == 0
