@@ -24,6 +24,7 @@ UNITS = [
   ('net_ref.cu', []),
   ('net_tc.cu', []),
   ('net_tc2.cu', []),
+  ('net_tc3.cu', []),
   ('net_attn.cu', []),
   ('net.cu', []),
 ]

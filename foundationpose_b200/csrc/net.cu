@@ -137,7 +137,8 @@ struct Ctx {
   int gemm(const GemmProblem& p) const
   {
     if (!bf) return ref_gemm(p, st);
-    const int rc = tc2_gemm(p, st);                       // persistent TMA kernel
+    int rc = tc3_gemm(p, st, 0);                          // narrow layers (Cout 64 / 128): operand-swapped kernel
+    if (rc == FPB_ERR_UNSUPPORTED) rc = tc2_gemm(p, st);  // persistent TMA kernel
     return rc == FPB_ERR_UNSUPPORTED ? tc_gemm(p, st) : rc;  // batched / odd shapes: cp.async kernel
   }
 };
@@ -424,7 +425,7 @@ FPB_EXPORT size_t fpb_score_cross_ws_bytes(int L, int bs)
 
 // Debug / unit-test entry: one implicit GEMM through one kernel family (see GemmProblem).
 //   mode 0: fp32 operands (SIMT); 1: bf16 tcgen05 with cp.async producers; 2 / 3: bf16 tcgen05 persistent TMA
-//   kernel with cta_group 1 / 2.  out is fp32 unless out_bf16.  row_pitch / pix_pitch / pad_w: 0 / 0 / pad_h for
+//   kernel with cta_group 1 / 2; 4: operand-swapped kernel for 64 / 128 output channels.  out is fp32 unless out_bf16.  row_pitch / pix_pitch / pad_w: 0 / 0 / pad_h for
 //   dense NHWC; the stem uses (168, 8, -1) with Cin = 64 "wide pixels".
 FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
                                   int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad_h, int pad_w, int row_pitch,
@@ -443,6 +444,11 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
     case 1: return tc_gemm(p, st);
     case 2: tc2_force_cta_group(1); break;
     case 3: tc2_force_cta_group(2); break;
+    case 4: {
+      const int rc3 = tc3_gemm(p, st, 1);
+      if (rc3 == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_igemm: shape not supported by the operand-swapped kernel");
+      return rc3;
+    }
     default: fpb_set_error("fpb_debug_igemm: unknown mode %d", mode); return FPB_ERR_ARG;
   }
   const int rc = tc2_gemm(p, st);
@@ -464,6 +470,11 @@ FPB_EXPORT int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* 
   p.img_h = H; p.img_w = Wd; p.halo = halo; p.row_remap = row_remap;
   p.M = halo ? nimg * (H + 1) * (Wd + 1) : nimg * H * Wd;
   p.scale = scale; p.shift = shift; p.residual = residual; p.ldr = Cout; p.relu = relu; p.ldc = Cout; p.out_bf16 = 1;
+  if (cta_group == 3) {                              // operand-swapped kernel (net_tc3.cu)
+    const int rc3 = tc3_gemm(p, (cudaStream_t)stream, 1);
+    if (rc3 == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_conv3x3_halo: shape not supported by the operand-swapped kernel");
+    return rc3;
+  }
   tc2_force_cta_group(cta_group);
   const int rc = tc2_gemm(p, (cudaStream_t)stream);
   tc2_force_cta_group(0);

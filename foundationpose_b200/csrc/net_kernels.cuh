@@ -59,9 +59,11 @@ static inline GemmProblem gemm_problem_default()
 int ref_gemm(const GemmProblem& p, cudaStream_t st);   // fp32 SIMT
 int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 accumulate (cp.async producers)
 int tc2_gemm(const GemmProblem& p, cudaStream_t st);   // bf16 tcgen05, persistent TMA kernel; FPB_ERR_UNSUPPORTED -> use tc_gemm
+int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force);   // bf16 tcgen05, operand-swapped (Cout 64 / 128); FPB_ERR_UNSUPPORTED -> tc2_gemm
 void tc2_force_cta_group(int cg);                      // tests: 0 = default, 1 / 2 = force
 
 int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms);
+int fpb_im2col_map_bf16(const GemmProblem& p, int nimg, void* out_map);   // 128 output pixels x 64 channels per request
 // fused multi-head self-attention (bf16, tcgen05): qk [R][1024] (Q | K, head h at +128h), vt [512][vt_pitch]
 // (V transposed: row = h*128+d, column = token row), bv [512] fp32 V bias -> ctx [R][512];  R = groups * 400
 int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups, cudaStream_t st);

@@ -14,6 +14,7 @@
 // In CG=2 mode each CTA loads its own 128 rows of A and half of the W rows; the leader CTA issues the MMAs for
 // both SMs and tcgen05.commit multicasts the barrier arrivals to the pair.
 #include "net_kernels.cuh"
+#include "tc_ptx.cuh"
 #include <cuda.h>
 #include <stdlib.h>
 #include <map>
@@ -27,182 +28,13 @@ constexpr int KC = 64;
 constexpr int NTHREADS = 320;                 // 1 TMA warp + 1 MMA warp + 8 epilogue warps
 constexpr int A_STAGE_BYTES = TM * 128;
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
-{
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
-{
-  const uint32_t addr = smem_u32(bar);
-  uint32_t ok = 0;
-  long long t0 = 0;
-  for (uint32_t spin = 0; !ok; spin++) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.b32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (!ok && (spin & 1023u) == 1023u) {   // watchdog: a broken pipeline traps instead of hanging the GPU
-      const long long now = clock64();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 8000000000LL) __trap();
-    }
-  }
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// arrive on the barrier at the same smem offset in CTA `cta` of the cluster
-__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta)
-{
-  asm volatile(
-      "{\n\t.reg .b32 ra;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
-      "r"(cta)
-      : "memory");
-}
-__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t cta)
-{
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
-  return r;
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void cluster_sync_all()
-{
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ uint32_t cluster_ctarank()
-{
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-
-// K-major SWIZZLE_128B smem matrix descriptor (see net_tc.cu)
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr)
-{
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)1 << 16;
-  d |= (uint64_t)(1024 >> 4) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
-  return d;
-}
-__host__ __device__ constexpr uint32_t make_idesc(int m, int n)
-{
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-
-template <int CG>
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum)
-{
-  if (CG == 1)
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-        "l"(da), "l"(db), "r"(idesc), "r"(accum)
-        : "memory");
-  else
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-        "l"(da), "l"(db), "r"(idesc), "r"(accum)
-        : "memory");
-}
-template <int CG>
-__device__ __forceinline__ void umma_commit(uint64_t* bar)
-{
-  if (CG == 1)
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
-  else
-    asm volatile(
-        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-            smem_u32(bar)),
-        "h"((uint16_t)3)
-        : "memory");
-}
-
-template <int CG>
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t mbar, int x, int y)
-{
-  if (CG == 1)
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-        "l"(map), "r"(mbar), "r"(x), "r"(y)
-        : "memory");
-  else
-    asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
-            "r"(dst),
-        "l"(map), "r"(mbar), "r"(x), "r"(y)
-        : "memory");
-}
-template <int CG>
-__device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* map, uint32_t mbar, int c, int w, int h,
-                                                int n, uint16_t ow, uint16_t oh)
-{
-  if (CG == 1)
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
-        "l"(map), "r"(mbar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(ow), "h"(oh)
-        : "memory");
-  else
-    asm volatile(
-        "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
-        "l"(map), "r"(mbar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(ow), "h"(oh)
-        : "memory");
-}
-
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
-{
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[32])
-{
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// 16-byte chunk j of row r inside a [32 rows x 128 B] warp-private staging tile (XOR swizzle: conflict-free both for
-// "lane = row" accesses and for "8 lanes per row" coalesced accesses)
-__device__ __forceinline__ uint32_t stg_off(int r, int j) { return (uint32_t)(r * 128 + ((j ^ (r & 7)) << 4)); }
 
 struct Tc2Params {
   GemmProblem p;
   int a_im2col;          // 1: A through the im2col map, 0: tiled 2-D map over [M][K]
   int lower_w, lower_h;  // im2col bounding-box lower corner (= -pad)
   int m_tiles, n_tiles;  // tiles of (TM*CG) x BN
-  int halo, Wp, IS, hrows, na, nb;   // halo mode: position pitch, image stride, A box rows, A / W ring depths
+  int halo, Wp, IS, hrows, na, nb, tps;   // halo mode: position pitch, image stride, A box rows, A / W ring depths, taps per W stage
   int fast_epi;          // 1: smem-transposed, fully coalesced bf16 epilogue (ncols % 64 == 0)
   int dbg;               // FPB_TC2_DBG experiment bits: 1 no stores, 2 no scale/shift, 4 no residual, 8 no MMA
 };
@@ -306,10 +138,11 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             if (!no_a) tma_load_2d<CG>(sA0 + sa * A_HALO_BYTES, &mapA, afull0 + 8u * sa, c * KC, m0 - q.Wp - 1);
             if (++sa == q.na) { sa = 0; pa ^= 1u; }
             int kcol = c * KC;
-            for (int tap = 0; tap < 9; tap++, kcol += p.Cin) {
+            for (int tap = 0; tap < 9; tap += q.tps) {           // q.tps filter taps (one kernel row when 3) share a stage
               mbar_wait(&ctl->empty[sb], pb);
-              if (rank == 0) mbar_arrive_expect_tx(&ctl->full[sb], b_tx);
-              if (!no_b) tma_load_2d<CG>(sB0 + sb * C::B_STAGE_BYTES, &mapB, full0 + 8u * sb, kcol, nrow0);
+              if (rank == 0) mbar_arrive_expect_tx(&ctl->full[sb], b_tx * q.tps);
+              for (int u = 0; u < q.tps; u++, kcol += p.Cin)
+                if (!no_b) tma_load_2d<CG>(sB0 + (sb * q.tps + u) * C::B_STAGE_BYTES, &mapB, full0 + 8u * sb, kcol, nrow0);
               if (++sb == q.nb) { sb = 0; pb ^= 1u; }
             }
           }
@@ -371,19 +204,23 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             // stay 0 for start rows that are not multiples of 8), so a filter tap is just a start-address shift
             uint32_t a_addr = sA0 + sa * A_HALO_BYTES;
             for (int ky = 0; ky < 3; ky++, a_addr += row_step) {
-              for (int kx = 0; kx < 3; kx++, a_addr += 128u) {
-                mbar_wait(&ctl->full[sb], pb);
-                tc_fence_after();
-                const uint64_t da = make_desc(a_addr), db = make_desc(sB0 + sb * C::B_STAGE_BYTES);
+              for (int kx = 0; kx < 3; kx++) {
+                const int u = q.tps == 3 ? kx : 0;
+                if (u == 0) {
+                  mbar_wait(&ctl->full[sb], pb);
+                  tc_fence_after();
+                }
+                const uint64_t da = make_desc(a_addr + 128u * kx), db = make_desc(sB0 + (sb * q.tps + u) * C::B_STAGE_BYTES);
                 if (!no_mma) {
 #pragma unroll
                   for (int k = 0; k < KC / 16; k++)
                     umma_bf16<CG>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (c | ky | kx | k) ? 1u : 0u);
                 }
-                umma_commit<CG>(&ctl->empty[sb]);
-                if (++sb == q.nb) { sb = 0; pb ^= 1u; }
+                if (u == q.tps - 1) {
+                  umma_commit<CG>(&ctl->empty[sb]);
+                  if (++sb == q.nb) { sb = 0; pb ^= 1u; }
+                }
               }
-              a_addr -= 3u * 128u;
             }
             umma_commit<CG>(&ctl->aempty[sa]);
             if (++sa == q.na) { sa = 0; pa ^= 1u; }
@@ -796,7 +633,8 @@ int launch_tc2(const CUtensorMap& mA, const CUtensorMap& mB, const Tc2Params& q_
   if (q.halo) {                                    // split the pipeline smem into an A-halo ring and a W ring
     const int region = C::STAGES * C::STAGE_BYTES;
     q.na = 2;
-    q.nb = (region - q.na * A_HALO_BYTES) / C::B_STAGE_BYTES;
+    q.tps = C::B_STAGE_BYTES <= 8192 ? 3 : 1;                 // small W tiles: one stage = one kernel row (3 taps)
+    q.nb = (region - q.na * A_HALO_BYTES) / (C::B_STAGE_BYTES * q.tps);
     if (q.nb > 8) q.nb = 8;
     if (q.nb < 2) { fpb_set_error("tc2 halo mode: not enough shared memory"); return FPB_ERR_ARG; }
   }
@@ -851,6 +689,13 @@ int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long lon
   return get_tiled_map(ptr, rows, cols, pitch, box_rows, (CUtensorMap*)out_map);
 }
 
+int fpb_im2col_map_bf16(const GemmProblem& p, int nimg, void* out_map)
+{
+  int rc = resolve_driver();
+  if (rc) return rc;
+  return get_im2col_map(p, nimg, (CUtensorMap*)out_map);
+}
+
 // Returns FPB_ERR_UNSUPPORTED (without setting up anything) when the problem does not fit this kernel, so the
 // caller can fall back to the first-generation cp.async kernel (tc_gemm).
 int tc2_gemm(const GemmProblem& p, cudaStream_t st)
@@ -878,7 +723,7 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
                 p.split_col_off % 8 == 0 && (!p.pe || (p.pe_ld % 4 == 0 && p.pe_rows >= 32)) &&
                 (p.m_split % 32 == 0 || p.m_split >= p.M)) ? 1 : 0;
   q.halo = p.halo ? 1 : 0;
-  q.Wp = p.img_w + 1; q.IS = (p.img_h + 1) * q.Wp; q.hrows = TM + 2 * q.Wp + 2; q.na = q.nb = 0;
+  q.Wp = p.img_w + 1; q.IS = (p.img_h + 1) * q.Wp; q.hrows = TM + 2 * q.Wp + 2; q.na = q.nb = 0; q.tps = 1;
   if (p.halo || p.row_remap) {
     const bool ok = q.fast_epi && p.img_h > 0 && p.img_w > 0 && (!p.halo || (p.KH == 3 && p.KW == 3 && p.stride == 1 && q.hrows * 128 <= A_HALO_BYTES)) &&
                     (p.row_remap == 2 || p.m_split >= p.M) && !p.pe;

@@ -24,9 +24,16 @@ def main():
   ap.add_argument('--reps', type=int, default=10)
   ap.add_argument('--nhyp', type=int, default=252)
   ap.add_argument('--no-flush', action='store_true')
+  ap.add_argument('--custom', default='', help='extra layer: name:ipn,H,Cin,Cout,k,stride,res,relu (repeat with ;)')
   a = ap.parse_args()
+  for spec in filter(None, a.custom.split(';')):
+    nm, v = spec.split(':')
+    LAYERS[nm] = tuple(int(t) for t in v.split(','))
   flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
   for name in a.layers.split(','):
+    if name == 'stem':
+      stem(a)
+      continue
     ipn, H, Cin, Cout, k, stride, res, relu = LAYERS[name]
     nimg = ipn * a.nhyp
     pad = (k - 1) // 2
@@ -38,6 +45,8 @@ def main():
     r = torch.randn(M, Cout, device='cuda').bfloat16() if res else None
     sc = torch.ones(Cout, device='cuda'); sh = torch.zeros(Cout, device='cuda')
     for mode in [int(m) for m in a.modes.split(',')]:
+      if mode == 4 and Cout > 128:
+        continue
       def launch():
         check(lib().fpb_debug_igemm(mode, ptr(x), ptr(w), ptr(out), M, Cout, K, H, H, Cin, Ho, Ho, k, k, stride, pad, ptr(sc),
                                     ptr(sh), ptr(r), relu, 1, stream()))
@@ -54,6 +63,31 @@ def main():
       ms = sorted(ts)[len(ts) // 2]
       fl = 2.0 * M * Cout * K
       print(f'{name:7s} mode {mode} M={M} N={Cout} K={K}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TFLOP/s', flush=True)
+
+
+def stem(a):
+  """7x7 stem as a 7x1 conv over wide pixels of the row-padded input (tests/test_nets_gpu.py::test_first_conv_7x7_padded_layout)"""
+  flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
+  n = 2 * a.nhyp
+  x = torch.randn(n, 160, 168, 8, device='cuda').bfloat16()
+  w = (torch.randn(64, 448, device='cuda') / 20).bfloat16()
+  out = torch.empty(n * 6400, 64, device='cuda', dtype=torch.bfloat16)
+  sc = torch.ones(64, device='cuda'); sh = torch.zeros(64, device='cuda')
+  for mode in [int(m) for m in a.modes.split(',')]:
+    def launch():
+      check(lib().fpb_debug_igemm_ex(mode, ptr(x), ptr(w), ptr(out), n * 6400, 64, 448, 160, 161, 64, 80, 80, 7, 1, 2, 3, -1, 168, 8,
+                                     ptr(sc), ptr(sh), None, 1, 1, stream()))
+    for _ in range(2):
+      launch()
+    ts = []
+    for _ in range(a.reps):
+      flush.zero_()
+      e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+      e0.record(); launch(); e1.record()
+      torch.cuda.synchronize()
+      ts.append(e0.elapsed_time(e1))
+    ms = sorted(ts)[len(ts) // 2]
+    print(f'stem    mode {mode} M={n*6400} N=64 K=448: {ms*1e3:8.1f} us  {2.0*n*6400*64*448/ms/1e9:7.1f} TFLOP/s', flush=True)
 
 
 if __name__ == '__main__':
