@@ -266,9 +266,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     // residual tile of the NEXT 64-column group is fetched one group ahead (8 x 16 B per lane, coalesced)
     uint4 rr[8];
     const bool use_res = q.fast_epi && p.residual && !(q.dbg & 4);
-    auto load_res = [&](int tile, int grp) {
-      const int mt_ = tile / q.n_tiles, nt_ = tile - mt_ * q.n_tiles;
-      const int mw_ = (mt_ * CG + (int)rank) * TM + (warp & 3) * 32, nb_ = nt_ * BN + grp * 64;
+    auto load_res = [&](int mw_, int nb_) {                  // mw_: first row of this warp, nb_: first column of the group
       if (nb_ >= nst) return;
 #pragma unroll
       for (int i = 0; i < 8; i++) {
@@ -277,7 +275,17 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                          : make_uint4(0u, 0u, 0u, 0u);
       }
     };
-    if (use_res && cluster_id < total_tiles) load_res(cluster_id, ehalf);
+    // first row of this warp / first column of tile `tile`
+    auto tile_mw = [&](int tile, int& mw_, int& n0_) {
+      const int mt_ = tile / q.n_tiles;
+      mw_ = (mt_ * CG + (int)rank) * TM + (warp & 3) * 32;
+      n0_ = (tile - mt_ * q.n_tiles) * BN;
+    };
+    if (use_res && cluster_id < total_tiles) {
+      int mw0, n00;
+      tile_mw(cluster_id, mw0, n00);
+      load_res(mw0, n00 + ehalf * 64);
+    }
     for (int t = cluster_id; t < total_tiles; t += n_clusters, tc++) {
       const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
       const int m = (mt * CG + (int)rank) * TM + row;
@@ -294,8 +302,10 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         float* ss = (float*)(epi_smem + 8 * C::EPI_WARP_BYTES) + (tc & 1u) * (2 * BN);   // scale[BN], shift[BN] of this n-tile
         const int m_w = (mt * CG + (int)rank) * TM + quarter * 32;   // first row of this warp
         const int sub = lane >> 3, cj = lane & 7;               // coalesced role: row 4i+sub, 16-byte chunk cj
+        int mw_next = 0, n0_next = 0;
+        if (use_res && t + n_clusters < total_tiles) tile_mw(t + n_clusters, mw_next, n0_next);
         // a warp's 32 rows never straddle m_split (host guarantees m_split % 32 == 0 or m_split >= M)
-        const int seg = m_w / p.m_split;
+        const int seg = p.m_split >= p.M ? 0 : m_w / p.m_split;
         __nv_bfloat16* out_w = (__nv_bfloat16*)p.C + (long long)(m_w - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
         const int pe_r0 = p.pe ? m_w % p.pe_rows : 0;
         bool interior = true;                                   // halo mode: border positions produce zeros
@@ -321,7 +331,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         // double buffered, and passing the barrier of tile i+1 implies every warp has finished tile i)
         for (int i = (warp - 2) * 32 + lane; i < BN; i += C::EPI_WARPS * 32) {
           const bool ok = n0 + i < nst;
-          ss[i] = (p.scale && ok && !(q.dbg & 2)) ? __ldg(p.scale + n0 + i) : 1.0f;
+          ss[i] = ((p.scale && ok && !(q.dbg & 2)) ? __ldg(p.scale + n0 + i) : 1.0f) * p.alpha;
           ss[BN + i] = (p.shift && ok && !(q.dbg & 2)) ? __ldg(p.shift + n0 + i) : 0.0f;
         }
         asm volatile("bar.sync 1, %0;" ::"n"(C::EPI_WARPS * 32) : "memory");
@@ -332,8 +342,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           const bool g_ok = nb < nst;                           // warp-uniform
           auto prefetch_next = [&]() {
             if (!use_res) return;
-            if (g + GSTEP < BN / 64) load_res(t, g + GSTEP);
-            else if (t + n_clusters < total_tiles) load_res(t + n_clusters, ehalf);
+            if (g + GSTEP < BN / 64) load_res(m_w, nb + GSTEP * 64);
+            else if (t + n_clusters < total_tiles) load_res(mw_next, n0_next + ehalf * 64);
           };
           uint32_t r0[32], r1[32];
           tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
@@ -351,13 +361,15 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           if (!g_ok) { prefetch_next(); continue; }
           float v[64];
 #pragma unroll
-          for (int i = 0; i < 32; i++) { v[i] = __uint_as_float(r0[i]) * p.alpha; v[32 + i] = __uint_as_float(r1[i]) * p.alpha; }
+          for (int i = 0; i < 32; i++) { v[i] = __uint_as_float(r0[i]); v[32 + i] = __uint_as_float(r1[i]); }
+          const uint32_t ss_a = smem_u32(ss) + (uint32_t)(g * 256);
 #pragma unroll
-          for (int c4 = 0; c4 < 16; c4++) {
-            const float4 sc = *reinterpret_cast<const float4*>(ss + g * 64 + c4 * 4);
-            const float4 sh = *reinterpret_cast<const float4*>(ss + BN + g * 64 + c4 * 4);
-            v[c4 * 4 + 0] = v[c4 * 4 + 0] * sc.x + sh.x; v[c4 * 4 + 1] = v[c4 * 4 + 1] * sc.y + sh.y;
-            v[c4 * 4 + 2] = v[c4 * 4 + 2] * sc.z + sh.z; v[c4 * 4 + 3] = v[c4 * 4 + 3] * sc.w + sh.w;
+          for (int c4 = 0; c4 < 16; c4++) {                   // alpha is folded into the scale table
+            float4 sc, sh;
+            asm("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(sc.x), "=f"(sc.y), "=f"(sc.z), "=f"(sc.w) : "r"(ss_a + c4 * 16));
+            asm("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(sh.x), "=f"(sh.y), "=f"(sh.z), "=f"(sh.w) : "r"(ss_a + BN * 4 + c4 * 16));
+            v[c4 * 4 + 0] = fmaf(v[c4 * 4 + 0], sc.x, sh.x); v[c4 * 4 + 1] = fmaf(v[c4 * 4 + 1], sc.y, sh.y);
+            v[c4 * 4 + 2] = fmaf(v[c4 * 4 + 2], sc.z, sh.z); v[c4 * 4 + 3] = fmaf(v[c4 * 4 + 3], sc.w, sh.w);
           }
           if (use_res) {
 #pragma unroll
@@ -376,7 +388,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               }
             }
           }
-          if (p.relu) {
+          const bool relu_packed = p.relu && !p.pe;             // max(bf16(x), 0) == bf16(max(x, 0))
+          if (p.relu && p.pe) {
 #pragma unroll
             for (int i = 0; i < 64; i++) v[i] = fmaxf(v[i], 0.0f);
           }
@@ -407,22 +420,37 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           }
           if ((q.dbg & 1) && v[0] != 123456.0f) { prefetch_next(); continue; }
           __syncwarp();                                         // staging tile: residual / pe reads done before it is reused
+          const __nv_bfloat162 zero2 = __floats2bfloat162_rn(0.0f, 0.0f);
 #pragma unroll
           for (int j = 0; j < 8; j++) {
             __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j * 8 + 0], v[j * 8 + 1]), h1 = __floats2bfloat162_rn(v[j * 8 + 2], v[j * 8 + 3]);
             __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j * 8 + 4], v[j * 8 + 5]), h3 = __floats2bfloat162_rn(v[j * 8 + 6], v[j * 8 + 7]);
+            if (relu_packed) { h0 = __hmax2(h0, zero2); h1 = __hmax2(h1, zero2); h2 = __hmax2(h2, zero2); h3 = __hmax2(h3, zero2); }
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(s_out + stg_off(lane, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
                          "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
           }
           __syncwarp();
           prefetch_next();
+          if (p.row_remap == 0) {
+            char* ob = (char*)(out_w + (long long)sub * p.ldc + nb + cj * 8);
+            uint32_t pitch4 = (uint32_t)p.ldc * 8u;            // 4 rows, in bytes
+            asm volatile("" : "+r"(pitch4));                  // one IMAD.WIDE per store instead of 8 live 64-bit offsets
+            const int rows_left = p.M - m_w - sub;             // row 4i+sub is stored iff 4i < rows_left
 #pragma unroll
-          for (int i = 0; i < 8; i++) {
-            const int mr = m_w + 4 * i + sub;
-            uint4 ov;
-            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
-            __nv_bfloat16* op = row_ptr(mr);
-            if (op) *(reinterpret_cast<uint4*>(op + nb) + cj) = ov;
+            for (int i = 0; i < 8; i++) {
+              uint4 ov;
+              asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
+              if (4 * i < rows_left) *reinterpret_cast<uint4*>(ob + (unsigned long long)i * pitch4) = ov;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+              const int mr = m_w + 4 * i + sub;
+              uint4 ov;
+              asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
+              __nv_bfloat16* op = row_ptr(mr);
+              if (op) *(reinterpret_cast<uint4*>(op + nb) + cj) = ov;
+            }
           }
           __syncwarp();
         }
