@@ -119,30 +119,47 @@ __device__ inline bool px_valid(const float* depth, const uint8_t* mask, int i, 
   return mask[i] != 0 && d >= 0.001f;
 }
 
-__device__ uint32_t radix_select(const float* depth, const uint8_t* mask, int n, uint32_t rank, uint32_t* hist,
-                                 uint32_t* sh)
+// exact rank-th smallest valid depth inside the mask's bounding box [u0, u0+bw) x [v0, v0+bh) (4 x 8-bit radix passes)
+__device__ uint32_t radix_select(const float* depth, const uint8_t* mask, int W, int u0, int v0, int bw, int bh, uint32_t rank,
+                                 uint32_t* hist, uint32_t* sh)
 {
   uint32_t prefix = 0, pmask = 0;
+  const int n = bw * bh;
   for (int shift = 24; shift >= 0; shift -= 8) {
     for (int i = threadIdx.x; i < 256; i += ST) hist[i] = 0;
     __syncthreads();
     for (int i = threadIdx.x; i < n; i += ST) {
+      const int r = i / bw;
       float d;
-      if (px_valid(depth, mask, i, d)) {
+      if (px_valid(depth, mask, (v0 + r) * W + u0 + (i - r * bw), d)) {
         uint32_t b = __float_as_uint(d);
         if ((b & pmask) == prefix) atomicAdd(&hist[(b >> shift) & 255u], 1u);
       }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t acc = 0, r = rank;
-      int bin = 0;
-      for (; bin < 256; bin++) {
-        if (acc + hist[bin] > r) break;
-        acc += hist[bin];
+    if (threadIdx.x < 32) {                       // warp 0: first bin whose inclusive prefix count exceeds the rank
+      const int lane = threadIdx.x;
+      uint32_t c[8], tot = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) { c[k] = hist[lane * 8 + k]; tot += c[k]; }
+      uint32_t incl = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
       }
-      sh[0] = (uint32_t)bin;
-      sh[1] = r - acc;
+      const uint32_t excl = incl - tot;
+      const bool mine = excl <= rank && rank < incl;          // exactly one lane when rank < total count
+      if (mine) {
+        uint32_t acc = excl;
+        int k = 0;
+        for (; k < 8; k++) {
+          if (acc + c[k] > rank) break;
+          acc += c[k];
+        }
+        sh[0] = (uint32_t)(lane * 8 + k);
+        sh[1] = rank - acc;
+      }
     }
     __syncthreads();
     prefix |= sh[0] << shift;
@@ -153,6 +170,8 @@ __device__ uint32_t radix_select(const float* depth, const uint8_t* mask, int n,
   return prefix;
 }
 
+// One block: (1) bounding box + counts over the whole mask, 16 mask bytes per load (most of the frame is outside the
+// mask); (2) the two middle order statistics of the valid depths by radix selection restricted to the bounding box.
 __global__ void __launch_bounds__(ST) mask_stats_kernel(const float* __restrict__ depth, const uint8_t* __restrict__ mask,
                                                         int H, int W, int32_t* out_i, float* out_f)
 {
@@ -163,22 +182,36 @@ __global__ void __launch_bounds__(ST) mask_stats_kernel(const float* __restrict_
   if (threadIdx.x == 0) { s_umin = W; s_umax = -1; s_vmin = H; s_vmax = -1; s_nmask = 0; s_nvalid = 0; }
   __syncthreads();
   int umin = W, umax = -1, vmin = H, vmax = -1, nm = 0, nv = 0;
-  for (int i = threadIdx.x; i < n; i += ST) {
-    if (mask[i]) {
-      int v = i / W, u = i - v * W;
-      umin = min(umin, u); umax = max(umax, u); vmin = min(vmin, v); vmax = max(vmax, v);
-      nm++;
-      if (depth[i] >= 0.001f) nv++;
-    }
+  auto visit = [&](int i) {
+    const int v = i / W, u = i - v * W;
+    umin = min(umin, u); umax = max(umax, u); vmin = min(vmin, v); vmax = max(vmax, v);
+    nm++;
+    if (depth[i] >= 0.001f) nv++;
+  };
+  const int head = min(n, (int)((16 - ((uintptr_t)mask & 15)) & 15));       // bytes before the first 16-byte boundary
+  const int nvec = (n - head) / 16;
+  for (int i = threadIdx.x; i < head; i += ST)
+    if (mask[i]) visit(i);
+  const uint4* mv = reinterpret_cast<const uint4*>(mask + head);
+  for (int q = threadIdx.x; q < nvec; q += ST) {
+    const uint4 m = __ldg(mv + q);
+    if ((m.x | m.y | m.z | m.w) == 0u) continue;
+    const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if ((w[k >> 2] >> ((k & 3) * 8)) & 255u) visit(head + q * 16 + k);
   }
+  for (int i = head + nvec * 16 + threadIdx.x; i < n; i += ST)
+    if (mask[i]) visit(i);
   atomicMin(&s_umin, umin); atomicMax(&s_umax, umax); atomicMin(&s_vmin, vmin); atomicMax(&s_vmax, vmax);
   atomicAdd(&s_nmask, nm); atomicAdd(&s_nvalid, nv);
   __syncthreads();
   const int nvalid = s_nvalid;
   float m0 = 0.0f, m1 = 0.0f;
   if (nvalid > 0) {
-    uint32_t a = radix_select(depth, mask, n, (uint32_t)((nvalid - 1) / 2), hist, sh);
-    uint32_t b = radix_select(depth, mask, n, (uint32_t)(nvalid / 2), hist, sh);
+    const int u0 = s_umin, v0 = s_vmin, bw = s_umax - s_umin + 1, bh = s_vmax - s_vmin + 1;
+    uint32_t a = radix_select(depth, mask, W, u0, v0, bw, bh, (uint32_t)((nvalid - 1) / 2), hist, sh);
+    uint32_t b = (nvalid & 1) ? a : radix_select(depth, mask, W, u0, v0, bw, bh, (uint32_t)(nvalid / 2), hist, sh);
     m0 = __uint_as_float(a);
     m1 = __uint_as_float(b);
   }

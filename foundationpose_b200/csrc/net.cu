@@ -330,8 +330,12 @@ static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* o
   RET(layernorm_rows(w.y1, c.bf, c.F(e.n1g), c.F(e.n1b), w.y, c.bf, R, D, 1e-5f, c.st));
   RET(run_linear(c, e.l1, w.y, R, w.ff, nullptr, 1, c.bf));
   RET(run_linear(c, e.l2, w.ff, R, w.y1, w.y, 0, c.bf));                               // y + FF(y)
-  RET(layernorm_rows(w.y1, c.bf, c.F(e.n2g), c.F(e.n2b), w.ff, c.bf, R, D, 1e-5f, c.st));
-  RET(token_mean(w.ff, c.bf, w.pooled, n, TOK, D, c.st));                              // mean commutes with Linear
+  if (c.bf && D == 512) {                                                              // LayerNorm + token mean in one pass
+    RET(layernorm_token_mean_512(w.y1, c.F(e.n2g), c.F(e.n2b), w.pooled, n, TOK, 1e-5f, c.st));
+  } else {
+    RET(layernorm_rows(w.y1, c.bf, c.F(e.n2g), c.F(e.n2b), w.ff, c.bf, R, D, 1e-5f, c.st));
+    RET(token_mean(w.ff, c.bf, w.pooled, n, TOK, D, c.st));                            // mean commutes with Linear
+  }
   RET(small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, 3, c.st));
   return FPB_OK;
 }

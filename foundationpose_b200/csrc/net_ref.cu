@@ -147,6 +147,98 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__
   }
 }
 
+
+// ---- bf16 fast paths for 512-wide rows (the transformer heads): one warp per row, the row lives in registers
+//      (lane l holds columns 8l..8l+7 and 256+8l..256+8l+7: two 16-byte loads, 512 contiguous bytes per warp each)
+struct Ln512 {
+  float v[16];
+  __device__ __forceinline__ void load(const __nv_bfloat16* row, int lane)
+  {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(row) + lane), b = __ldg(reinterpret_cast<const uint4*>(row) + 32 + lane);
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 8; i++) { v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+  }
+  // (x - mean) * rstd * gamma + beta, in place
+  __device__ __forceinline__ void normalize(const float (&g)[16], const float (&b)[16], float eps)
+  {
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 16; i++) s += v[i];
+    const float mean = warp_sum(s) * (1.0f / 512.0f);
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 16; i++) { const float d = v[i] - mean; q += d * d; }
+    const float rstd = rsqrtf(warp_sum(q) * (1.0f / 512.0f) + eps);
+#pragma unroll
+    for (int i = 0; i < 16; i++) v[i] = (v[i] - mean) * rstd * g[i] + b[i];
+  }
+};
+__device__ __forceinline__ void ln512_params(const float* gamma, const float* beta, int lane, float (&g)[16], float (&b)[16])
+{
+#pragma unroll
+  for (int h = 0; h < 2; h++)
+#pragma unroll
+    for (int i = 0; i < 8; i++) { g[h * 8 + i] = __ldg(gamma + h * 256 + lane * 8 + i); b[h * 8 + i] = __ldg(beta + h * 256 + lane * 8 + i); }
+}
+
+__global__ void __launch_bounds__(256) ln512_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                                                    const float* __restrict__ beta, __nv_bfloat16* __restrict__ out,
+                                                    long long rows, float eps)
+{
+  const int lane = threadIdx.x & 31;
+  float g[16], b[16];
+  ln512_params(gamma, beta, lane, g, b);
+  const long long nw = (long long)gridDim.x * 8;
+  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < rows; row += nw) {
+    Ln512 r;
+    r.load(x + row * 512, lane);
+    r.normalize(g, b, eps);
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(r.v[2 * i], r.v[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    uint4* o = reinterpret_cast<uint4*>(out + row * 512);
+    o[lane] = make_uint4(w[0], w[1], w[2], w[3]);
+    o[32 + lane] = make_uint4(w[4], w[5], w[6], w[7]);
+  }
+}
+
+// LayerNorm followed by the mean over a group's tokens (the normalised rows are never written): one block per group,
+// 8 warps stride over the tokens, fixed-order reduction over warps in shared memory (deterministic).
+__global__ void __launch_bounds__(256) ln512_token_mean_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta, float* __restrict__ out,
+                                                               int tokens, float eps)
+{
+  __shared__ float part[8][512];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float g[16], b[16], acc[16];
+  ln512_params(gamma, beta, lane, g, b);
+#pragma unroll
+  for (int i = 0; i < 16; i++) acc[i] = 0.0f;
+  const __nv_bfloat16* xg = x + (long long)blockIdx.x * tokens * 512;
+  for (int t = warp; t < tokens; t += 8) {
+    Ln512 r;
+    r.load(xg + (long long)t * 512, lane);
+    r.normalize(g, b, eps);
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[i] += r.v[i];
+  }
+#pragma unroll
+  for (int h = 0; h < 2; h++)
+#pragma unroll
+    for (int i = 0; i < 8; i++) part[warp][h * 256 + lane * 8 + i] = acc[h * 8 + i];
+  __syncthreads();
+  for (int c = threadIdx.x; c < 512; c += 256) {
+    float s = 0.0f;
+#pragma unroll
+    for (int w = 0; w < 8; w++) s += part[w][c];
+    out[(long long)blockIdx.x * 512 + c] = s / (float)tokens;
+  }
+}
+
 // out[g][c] = mean_t x[g][t][c]; one block per (g, 64-column slab), 256 threads = 4 token lanes x 64 cols
 template <bool XBF>
 __global__ void __launch_bounds__(256) token_mean_kernel(const void* __restrict__ x_, float* __restrict__ out, int tokens,
@@ -229,8 +321,21 @@ int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int c
 int layernorm_rows(const void* x, int x_bf16, const float* gamma, const float* beta, void* out, int out_bf16,
                    long long rows, int cols, float eps, cudaStream_t st)
 {
-  if (x_bf16) layernorm_kernel<true><<<fpb_cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, out, out_bf16, rows, cols, eps);
+  if (x_bf16 && out_bf16 && cols == 512 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0) {
+    const long long blocks = fpb_cdiv(rows, 8);
+    ln512_kernel<<<(unsigned)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)out, rows, eps);
+  } else if (x_bf16) layernorm_kernel<true><<<fpb_cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, out, out_bf16, rows, cols, eps);
   else layernorm_kernel<false><<<fpb_cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, out, out_bf16, rows, cols, eps);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+// out[g][c] = mean_t LayerNorm(x[g][t][:])[c]  (bf16 rows of 512 columns; the normalised rows stay in registers, fp32)
+int layernorm_token_mean_512(const void* x, const float* gamma, const float* beta, float* out, int groups, int tokens, float eps,
+                             cudaStream_t st)
+{
+  if ((uintptr_t)x & 15) { fpb_set_error("layernorm_token_mean_512: unaligned input"); return FPB_ERR_ARG; }
+  ln512_token_mean_kernel<<<groups, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }
