@@ -254,8 +254,8 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
     return run_attention_core(c, w.qkv, n, TOK, TOKP, w.scores, w.P, w.vt, w.ctx, false);
   }
   // bf16: Q|K projection [R,1024]; V is produced already transposed, V^T = Wv . X^T  ([512, R], tokens contiguous),
-  // by swapping the GEMM operands, so the fused attention kernel can TMA it as a K-major B operand; the V bias is
-  // added to the attention output instead (softmax rows sum to 1).
+  // by swapping the GEMM operands, so the fused attention kernel can TMA it as a K-major B operand; the V bias is a
+  // per-row term of that transposed product (row_shift).
   __nv_bfloat16* qk = (__nv_bfloat16*)w.qkv;
   __nv_bfloat16* vt = qk + R * 2 * D;
   Lin lqk = m.in; lqk.N = 2 * D;
@@ -263,8 +263,9 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
   GemmProblem p = gemm_problem_default();
   p.A = c.W(m.in.w + (size_t)2 * D * D); p.W = x; p.C = vt;
   p.M = D; p.N = (int)R; p.K = D; p.Cin = D; p.pix_pitch = D; p.ldw = D; p.ldc = (int)R; p.out_bf16 = 1;
+  p.row_shift = c.F(m.in.b + 2 * D);
   RET(c.gemm(p));
-  return tc_attention(qk, vt, R, c.F(m.in.b + 2 * D), w.ctx, n, c.st);
+  return tc_attention(qk, vt, R, nullptr, w.ctx, n, c.st);
 }
 
 }  // namespace

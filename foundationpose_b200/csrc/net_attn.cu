@@ -3,25 +3,36 @@
 //   ScoreNetMultiPair.att               learning/models/score_network.py:53,73
 // One CTA per (hypothesis, head); it walks the 4 query tiles of 128 rows:
 //   S = Q K^T      two tcgen05.mma (N = 208 + 192) per 16-wide k step, fp32 scores in TMEM columns 0..399
-//   P = exp2(..)   4 softmax warps (lane = query row): pass 1 row max, pass 2 un-normalised probabilities written as
-//                  bf16 into a 2-stage smem ring in the 128B-swizzled K-major layout UMMA reads
-//   O = P V        tcgen05.mma per 64-key chunk against V^T tiles (TMA ring); O overlays TMEM columns 0..127, which
-//                  is safe because the first P.V MMA waits until score columns 0..127 have been consumed
-//   epilogue       O / rowsum + V bias (softmax rows sum to 1, so the bias commutes) -> bf16 context rows
+//   P = exp2(..)   8 softmax warps (lane = query row, two warps per TMEM lane quarter taking alternate 64-key chunks):
+//                  pass 1 row max (halves combined through smem), pass 2 un-normalised probabilities written as bf16
+//                  into a 2-stage smem ring in the 128B-swizzled K-major layout UMMA reads
+//   O = P V'       tcgen05.mma (N = 144) per 64-key chunk against V^T tiles (TMA ring) extended by a constant row of
+//                  ones, so column 128 of the accumulator is the softmax denominator computed from the same bf16 P as
+//                  the numerator (no per-element adds in the softmax warps).  O overlays TMEM columns 368..511, i.e.
+//                  the score columns of the two LAST key chunks; chunks are therefore processed in reverse order and
+//                  the first P.V MMA waits until both have been consumed.
+//   epilogue       O / rowsum (+ V bias when not already folded into V^T: softmax rows sum to 1, so the bias commutes)
 // No score / probability tensor ever reaches HBM (the unfused path wrote 0.7 GB of fp32 scores per layer call).
-// Warp roles: 0 TMA producer, 1 TMEM allocator + MMA issuer, 2-5 softmax / epilogue.
+// Warp roles: 0 TMA producer, 1 TMEM allocator + MMA issuer, 2-9 softmax / epilogue.
+// Measured: with 4 softmax warps (one per scheduler) every tcgen05.wait / mbarrier wait was exposed and the kernel
+// ran at 272 us per call with all MMAs and exps disabled it still took 168 us; see DESIGN.md 4.3.
 #include "net_kernels.cuh"
 #include <cuda.h>
+#include <stdlib.h>
 
 namespace {
 
 constexpr int TOK = 400, DH = 128, HEADS = 4, DM = 512;
-constexpr int NTHREADS = 192;
+constexpr int NTHREADS = 320;
 constexpr int K_CHUNK_BYTES = TOK * 128;          // one 64-wide d chunk of K: 400 rows x 128 B
 constexpr int Q_CHUNK_BYTES = 128 * 128;
 constexpr int T16 = 16384;
 constexpr int N_KEY_CHUNKS = 7;                   // 6 x 64 + 16 keys
 constexpr int N1 = 208, N2 = 192;                 // S = [N1 | N2] columns
+constexpr int NO = 144;                           // P.V accumulator columns: 128 head dims + the ones row (+ pad to 16)
+constexpr int O_COL = 512 - NO;                   // 368: O overlays the scores of key chunks 5 (partly) and 6
+constexpr int V_STAGE = T16 + 2048;               // V^T tile + 16 constant rows (row 128 = ones)
+constexpr int NV = 2;                             // ring depth (a third V^T stage measured no gain: the stream is not the bound)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
@@ -119,6 +130,19 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t* r)
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float tmem_ld1(uint32_t taddr)
+{
+  uint32_t r;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float ex2(float x)
+{
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[32])
 {
   asm volatile(
@@ -133,13 +157,18 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[32])
 
 struct AttnCtl {
   uint64_t k_full, q_full, q_empty, s_full, o_full, tmem_free;
-  uint64_t v_full[2], v_empty[2], p_full[2], p_empty[2];
+  uint64_t slot_full[2], slot_empty[2];       // ring slot = V^T tile (TMA) + P tile (softmax warps)
   uint32_t tmem_base;
 };
 
-constexpr int SMEM_K = 2 * K_CHUNK_BYTES, SMEM_Q = 2 * Q_CHUNK_BYTES, SMEM_V = 2 * T16, SMEM_P = 2 * T16;
-constexpr int SMEM_TOTAL = SMEM_K + SMEM_Q + SMEM_V + SMEM_P + 1024 + (int)sizeof(AttnCtl);
+constexpr int SMEM_K = 2 * K_CHUNK_BYTES, SMEM_Q = 2 * Q_CHUNK_BYTES, SMEM_V = NV * V_STAGE, SMEM_P = 2 * T16;
+constexpr int SMEM_MAX = 2 * 2 * 128 * 4;         // partial row maxima: [tile parity][warp set][row]
+constexpr int SMEM_TOTAL = SMEM_K + SMEM_Q + SMEM_V + SMEM_P + SMEM_MAX + 1024 + (int)sizeof(AttnCtl);
+static_assert(SMEM_TOTAL <= 227 * 1024, "attention shared memory budget");
 
+// DBG (FPB_ATTN_DBG, timing experiments only; results are wrong when != 0): 1 no row-max pass, 2 no exp2, 4 no P.V MMAs,
+// 8 no ctx stores, 16 no S MMAs
+template <int DBG>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapK,
             const __grid_constant__ CUtensorMap mapV, const float* __restrict__ bv, __nv_bfloat16* __restrict__ ctx,
@@ -151,7 +180,8 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
   uint8_t* sQ = sK + SMEM_K;
   uint8_t* sV = sQ + SMEM_Q;
   uint8_t* sP = sV + SMEM_V;
-  AttnCtl* ctl = (AttnCtl*)(sP + SMEM_P);
+  float* smax = (float*)(sP + SMEM_P);
+  AttnCtl* ctl = (AttnCtl*)(sP + SMEM_P + SMEM_MAX);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = blockIdx.x / HEADS, h = blockIdx.x - g * HEADS;
   const int row0 = g * TOK;                                  // first token row of this hypothesis
@@ -159,13 +189,17 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
 
   if (threadIdx.x == 0) {
     mbar_init(&ctl->k_full, 1); mbar_init(&ctl->q_full, 1); mbar_init(&ctl->q_empty, 1);
-    mbar_init(&ctl->s_full, 1); mbar_init(&ctl->o_full, 1); mbar_init(&ctl->tmem_free, 4);
-    for (int s = 0; s < 2; s++) {
-      mbar_init(&ctl->v_full[s], 1); mbar_init(&ctl->v_empty[s], 1);
-      mbar_init(&ctl->p_full[s], 128); mbar_init(&ctl->p_empty[s], 1);
-    }
+    mbar_init(&ctl->s_full, 1); mbar_init(&ctl->o_full, 1); mbar_init(&ctl->tmem_free, 8);
+    for (int s = 0; s < 2; s++) { mbar_init(&ctl->slot_full[s], 129); mbar_init(&ctl->slot_empty[s], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  for (int i = threadIdx.x; i < NV * 128; i += NTHREADS) {
+    // the 16 constant rows behind each V^T stage: row 128 = ones (its dot product with P is the row sum), the rest 0
+    const int s = i >> 7, o = (i & 127) * 16;
+    const uint32_t w = o < 128 ? 0x3F803F80u : 0u;
+    *reinterpret_cast<uint4*>(sV + s * V_STAGE + T16 + o) = make_uint4(w, w, w, w);
+  }
+  fence_proxy_async();
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)), "r"(512u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -174,6 +208,12 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
+  // DBG & 32: block 0 records clock64 stamps (warp 1 lane 0 -> slots 0..63, warp 2 lane 0 -> 64..127, warp 6 lane 0 -> 128..191)
+  long long* stamps = reinterpret_cast<long long*>(ctx);
+  int n_st = 0;
+  auto stamp = [&](int base) {
+    if ((DBG & 32) && blockIdx.x == 0 && lane == 0 && n_st < 64 && base < 1000) stamps[base + n_st++] = clock64();
+  };
 
   if (warp == 0) {
     // ---------------------------------------------------------------- TMA producer
@@ -189,110 +229,149 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
         mbar_arrive_expect_tx(&ctl->q_full, (uint32_t)SMEM_Q);
         for (int kc = 0; kc < 2; kc++)
           tma_load_2d(smem_u32(sQ + kc * Q_CHUNK_BYTES), &mapQ, &ctl->q_full, h * DH + kc * 64, row0 + mt * 128);
-        for (int j = 0; j < N_KEY_CHUNKS; j++, gi++) {
+        for (int oi = 0; oi < N_KEY_CHUNKS; oi++, gi++) {       // key chunks in reverse order (see header)
           const uint32_t s = gi & 1u, use = gi >> 1;
-          mbar_wait(&ctl->v_empty[s], (use & 1u) ^ 1u);
-          mbar_arrive_expect_tx(&ctl->v_full[s], (uint32_t)T16);
-          tma_load_2d(smem_u32(sV + s * T16), &mapV, &ctl->v_full[s], row0 + j * 64, h * DH);
+          mbar_wait(&ctl->slot_empty[s], (use & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&ctl->slot_full[s], (uint32_t)T16);
+          tma_load_2d(smem_u32(sV + s * V_STAGE), &mapV, &ctl->slot_full[s], row0 + (N_KEY_CHUNKS - 1 - oi) * 64, h * DH);
         }
       }
     }
   } else if (warp == 1) {
     // ---------------------------------------------------------------- MMA issuer
+    // Measured with clock stamps (FPB_ATTN_DBG=32): this thread's per-chunk turnaround (two waits, two commits) was
+    // ~1000 cycles and paced the whole CTA, so a ring slot couples the V^T tile and the P tile behind ONE full barrier
+    // (128 softmax arrivals + the TMA transaction) and ONE empty barrier, and all descriptors are hoisted.
     if (lane == 0) {
-      constexpr uint32_t id1 = make_idesc(N1), id2 = make_idesc(N2), idv = make_idesc(DH);
+      constexpr uint32_t id1 = make_idesc(N1), id2 = make_idesc(N2), idv = make_idesc(NO);
+      const uint64_t dq0 = make_desc(smem_u32(sQ)), dq1 = make_desc(smem_u32(sQ + Q_CHUNK_BYTES));
+      const uint64_t dka0 = make_desc(smem_u32(sK)), dka1 = make_desc(smem_u32(sK + K_CHUNK_BYTES));
+      const uint64_t dkb0 = make_desc(smem_u32(sK + N1 * 128)), dkb1 = make_desc(smem_u32(sK + K_CHUNK_BYTES + N1 * 128));
+      const uint64_t dps[2] = {make_desc(smem_u32(sP)), make_desc(smem_u32(sP + T16))};
+      const uint64_t dvs[2] = {make_desc(smem_u32(sV)), make_desc(smem_u32(sV + V_STAGE))};
+      // scores of keys 0..207 (TMEM columns 0..207) / keys 208..399 (columns 208..399)
+      auto issue_s1 = [&]() {
+        if (DBG & 16) return;
+#pragma unroll
+        for (int k = 0; k < 4; k++) umma(tmem_base, dq0 + (uint64_t)(k * 2), dka0 + (uint64_t)(k * 2), id1, k ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 4; k++) umma(tmem_base, dq1 + (uint64_t)(k * 2), dka1 + (uint64_t)(k * 2), id1, 1u);
+      };
+      auto issue_s2 = [&]() {
+        if (DBG & 16) return;
+#pragma unroll
+        for (int k = 0; k < 4; k++) umma(tmem_base + N1, dq0 + (uint64_t)(k * 2), dkb0 + (uint64_t)(k * 2), id2, k ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 4; k++) umma(tmem_base + N1, dq1 + (uint64_t)(k * 2), dkb1 + (uint64_t)(k * 2), id2, 1u);
+      };
       mbar_wait(&ctl->k_full, 0);
+      mbar_wait(&ctl->q_full, 0);
+      tc_fence_after();
+      issue_s1();
       uint32_t gi = 0;
       for (int mt = 0; mt < N_MT; mt++) {
-        mbar_wait(&ctl->q_full, (uint32_t)(mt & 1));
+        // the first half of this tile's scores was issued early (below); the second half overlaps the previous tile's
+        // O columns and has to wait for its epilogue
         mbar_wait(&ctl->tmem_free, (uint32_t)((mt & 1) ^ 1));
         tc_fence_after();
-        for (int kc = 0; kc < 2; kc++) {
-          const uint64_t dq = make_desc(smem_u32(sQ + kc * Q_CHUNK_BYTES));
-          const uint64_t dk1 = make_desc(smem_u32(sK + kc * K_CHUNK_BYTES));
-          const uint64_t dk2 = make_desc(smem_u32(sK + kc * K_CHUNK_BYTES + N1 * 128));
-#pragma unroll
-          for (int k = 0; k < 4; k++) {
-            umma(tmem_base, dq + (uint64_t)(k * 2), dk1 + (uint64_t)(k * 2), id1, (kc | k) ? 1u : 0u);
-            umma(tmem_base + N1, dq + (uint64_t)(k * 2), dk2 + (uint64_t)(k * 2), id2, (kc | k) ? 1u : 0u);
-          }
-        }
+        issue_s2();
+        stamp(0);                                             // S MMAs issued
         umma_commit(&ctl->s_full);
         umma_commit(&ctl->q_empty);
-        // O overlays score columns 0..127: chunks 0 and 1 of P must exist before the first P.V MMA
-        mbar_wait(&ctl->p_full[gi & 1u], (gi >> 1) & 1u);
-        mbar_wait(&ctl->p_full[(gi + 1) & 1u], ((gi + 1) >> 1) & 1u);
-        for (int j = 0; j < N_KEY_CHUNKS; j++, gi++) {
-          const uint32_t s = gi & 1u, use = gi >> 1;
-          mbar_wait(&ctl->v_full[s], use & 1u);
-          mbar_wait(&ctl->p_full[s], use & 1u);
+        // O overlays score columns 368..399 (key chunks 6 and 5 = the first two in processing order): both must
+        // have been turned into P before the first P.V MMA
+        mbar_wait(&ctl->slot_full[gi & 1u], (gi >> 1) & 1u);
+        mbar_wait(&ctl->slot_full[(gi + 1) & 1u], ((gi + 1) >> 1) & 1u);
+        tc_fence_after();
+        if (!(DBG & 4)) umma(tmem_base + O_COL, dps[gi & 1u], dvs[gi & 1u], idv, 0u);   // 16-key tail chunk: one k step
+        stamp(0);
+        umma_commit(&ctl->slot_empty[gi & 1u]);
+        gi++;
+#pragma unroll 1
+        for (int oi = 1; oi < N_KEY_CHUNKS; oi++, gi++) {
+          const uint32_t s = gi & 1u;
+          mbar_wait(&ctl->slot_full[s], (gi >> 1) & 1u);
           tc_fence_after();
-          const uint64_t dp = make_desc(smem_u32(sP + s * T16)), dv = make_desc(smem_u32(sV + s * T16));
-          const int ksteps = j < N_KEY_CHUNKS - 1 ? 4 : (TOK - 64 * (N_KEY_CHUNKS - 1)) / 16;
-          for (int k = 0; k < ksteps; k++) umma(tmem_base, dp + (uint64_t)(k * 2), dv + (uint64_t)(k * 2), idv, (j | k) ? 1u : 0u);
-          umma_commit(&ctl->v_empty[s]);
-          umma_commit(&ctl->p_empty[s]);
+          if (!(DBG & 4)) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) umma(tmem_base + O_COL, dps[s] + (uint64_t)(k * 2), dvs[s] + (uint64_t)(k * 2), idv, 1u);
+          }
+          stamp(0);                                           // P.V MMAs of chunk oi issued
+          umma_commit(&ctl->slot_empty[s]);
         }
         umma_commit(&ctl->o_full);
+        if (mt + 1 < N_MT) {
+          // every softmax warp has consumed this tile's scores (all slot_full waits passed): the next tile's first 208
+          // score columns do not touch the O columns and can be computed under this tile's epilogue
+          mbar_wait(&ctl->q_full, (uint32_t)((mt + 1) & 1));
+          tc_fence_after();
+          issue_s1();
+        }
       }
     }
   } else {
-    // ---------------------------------------------------------------- softmax + epilogue (warps 2..5)
-    const int quarter = warp & 3;
+    // ---------------------------------------------------------------- softmax + epilogue (warps 2..9)
+    const int quarter = warp & 3;                 // TMEM lanes (query rows) 32*quarter .. +31
+    const int set = (warp - 2) >> 2;              // set 0: key chunks 6,4,2,0; set 1: key chunks 5,3,1
     const int row = quarter * 32 + lane;
     const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    uint32_t gi = 0;
     for (int mt = 0; mt < N_MT; mt++) {
+      stamp(warp == 2 ? 64 : (warp == 6 ? 128 : 10000000));
       mbar_wait(&ctl->s_full, (uint32_t)(mt & 1));
       tc_fence_after();
-      uint32_t r[32];
-      float mx = -INFINITY;
-      {
-        // pass 1: row max; four 32-column TMEM loads in flight per wait, four independent max chains
-        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      stamp(warp == 2 ? 64 : (warp == 6 ? 128 : 10000000));  // scores ready
+      // ---- pass 1: row max over this warp's key chunks, then combined with the partner warp's
+      float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
-        for (int c = 0; c < TOK / 128; c++) {
-          uint32_t rb[128];
+      for (int c = 1 - set; c < ((DBG & 1) ? 0 : N_KEY_CHUNKS - 1); c += 2) {
+        uint32_t rb[64];
+        tmem_ld32_nowait(t_row + (uint32_t)(c * 64), rb);
+        tmem_ld32_nowait(t_row + (uint32_t)(c * 64 + 32), rb + 32);
+        tmem_ld_wait();
 #pragma unroll
-          for (int b = 0; b < 4; b++) tmem_ld32_nowait(t_row + (uint32_t)(c * 128 + b * 32), rb + b * 32);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 128; i++) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(rb[i]));
-        }
-        tmem_ld16(t_row + (uint32_t)(TOK / 128 * 128), r);
+        for (int i = 0; i < 64; i++) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(rb[i]));
+      }
+      if (set == 0) {
+        uint32_t r[32];
+        tmem_ld16(t_row + (uint32_t)((N_KEY_CHUNKS - 1) * 64), r);
 #pragma unroll
         for (int i = 0; i < 16; i++) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(r[i]));
-        mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
       }
+      float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      float* sm = smax + (mt & 1) * 256;
+      sm[set * 128 + row] = mx;
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + quarter) : "memory");
+      mx = fmaxf(mx, sm[(set ^ 1) * 128 + row]);
       const float off = -mx * c1;
-      float sum = 0.0f;
+      stamp(warp == 2 ? 64 : (warp == 6 ? 128 : 10000000));  // row max done
+      // ---- pass 2: un-normalised probabilities of this warp's chunks -> bf16 P tiles in the smem ring
 #pragma unroll 1
-      for (int j = 0; j < N_KEY_CHUNKS; j++, gi++) {
-        const uint32_t s = gi & 1u, use = gi >> 1;
-        const bool tail = j == N_KEY_CHUNKS - 1;
+      for (int oi = set; oi < N_KEY_CHUNKS; oi += 2) {
+        const uint32_t gi = (uint32_t)(mt * N_KEY_CHUNKS + oi), s = gi & 1u, use = gi >> 1;
+        const int c = N_KEY_CHUNKS - 1 - oi;
+        const bool tail = oi == 0;
         uint32_t r2[64];
         if (tail) {
-          tmem_ld16(t_row + (uint32_t)(j * 64), r);
+          uint32_t r[32];
+          tmem_ld16(t_row + (uint32_t)(c * 64), r);
 #pragma unroll
           for (int i = 0; i < 16; i++) r2[i] = r[i];
         } else {
-          tmem_ld32_nowait(t_row + (uint32_t)(j * 64), r2);
-          tmem_ld32_nowait(t_row + (uint32_t)(j * 64 + 32), r2 + 32);
+          tmem_ld32_nowait(t_row + (uint32_t)(c * 64), r2);
+          tmem_ld32_nowait(t_row + (uint32_t)(c * 64 + 32), r2 + 32);
         }
-        mbar_wait(&ctl->p_empty[s], (use & 1u) ^ 1u);        // overlaps the TMEM load latency
+        mbar_wait(&ctl->slot_empty[s], (use & 1u) ^ 1u);     // overlaps the TMEM load latency
         tmem_ld_wait();
         const uint32_t sp = smem_u32(sP + s * T16) + (uint32_t)(row * 128);
         const int n16 = tail ? 2 : 8;                          // 16-byte chunks (8 keys each) of this key chunk
-        float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int jj = 0; jj < 8; jj++) {
           if (jj < n16) {
             uint32_t pk[4];
 #pragma unroll
             for (int e = 0; e < 4; e++) {
-              const float p0 = exp2f(fmaf(__uint_as_float(r2[jj * 8 + e * 2]), c1, off));
-              const float p1 = exp2f(fmaf(__uint_as_float(r2[jj * 8 + e * 2 + 1]), c1, off));
-              s4[e] += p0 + p1;
+              float p0 = fmaf(__uint_as_float(r2[jj * 8 + e * 2]), c1, off), p1 = fmaf(__uint_as_float(r2[jj * 8 + e * 2 + 1]), c1, off);
+              if (!(DBG & 2)) { p0 = ex2(p0); p1 = ex2(p1); }
               __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
               pk[e] = *reinterpret_cast<uint32_t*>(&hh);
             }
@@ -301,39 +380,52 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
                          : "memory");
           }
         }
-        sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
         tc_fence_before();
         fence_proxy_async();
-        mbar_arrive(&ctl->p_full[s]);
+        mbar_arrive(&ctl->slot_full[s]);
+        stamp(warp == 2 ? 64 : (warp == 6 ? 128 : 10000000));  // P chunk written
       }
-      // ---- epilogue: O / sum + b_v -> ctx
+      // ---- epilogue: O / rowsum (+ b_v) -> ctx; set 0 writes head dims 0..63, set 1 dims 64..127
       mbar_wait(&ctl->o_full, (uint32_t)(mt & 1));
       tc_fence_after();
-      const float inv = 1.0f / sum;
-      const int tok = mt * 128 + row;
-      __nv_bfloat16* orow = ctx + (long long)(row0 + tok) * DM + h * DH;
-#pragma unroll 1
-      for (int c = 0; c < DH / 32; c++) {
-        tmem_ld32(t_row + (uint32_t)(c * 32), r);
-        if (tok < TOK) {
+      stamp(warp == 2 ? 64 : (warp == 6 ? 128 : 10000000));  // O ready
+      const float inv = 1.0f / tmem_ld1(t_row + (uint32_t)(O_COL + DH));
+      uint32_t o[64];
+      tmem_ld32_nowait(t_row + (uint32_t)(O_COL + set * 64), o);
+      tmem_ld32_nowait(t_row + (uint32_t)(O_COL + set * 64 + 32), o + 32);
+      tmem_ld_wait();
+      // rows of 64 head dims (128 B) are transposed through this warp's 4 KB slice of the P ring (idle here: every P.V
+      // MMA of the tile has completed) so that 8 lanes store one contiguous 128-byte row segment; tmem_free is only
+      // released afterwards because the next tile's P tiles reuse the ring
+      const uint32_t stg = smem_u32(sP) + (uint32_t)((warp - 2) * 4096);
 #pragma unroll
-          for (int q8 = 0; q8 < 4; q8++) {
-            uint4 pk;
-            uint32_t* pw = reinterpret_cast<uint32_t*>(&pk);
+      for (int q8 = 0; q8 < 8; q8++) {
+        uint32_t pw[4];
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
-              const int d = c * 32 + q8 * 8 + e * 2;
-              __nv_bfloat162 hh = __floats2bfloat162_rn(__uint_as_float(r[q8 * 8 + e * 2]) * inv + __ldg(bv + h * DH + d),
-                                                        __uint_as_float(r[q8 * 8 + e * 2 + 1]) * inv + __ldg(bv + h * DH + d + 1));
-              pw[e] = *reinterpret_cast<uint32_t*>(&hh);
-            }
-            *reinterpret_cast<uint4*>(orow + c * 32 + q8 * 8) = pk;
-          }
+        for (int e = 0; e < 4; e++) {
+          float a = __uint_as_float(o[q8 * 8 + e * 2]) * inv, b = __uint_as_float(o[q8 * 8 + e * 2 + 1]) * inv;
+          if (bv) { a += __ldg(bv + h * DH + set * 64 + q8 * 8 + e * 2); b += __ldg(bv + h * DH + set * 64 + q8 * 8 + e * 2 + 1); }
+          __nv_bfloat162 hh = __floats2bfloat162_rn(a, b);
+          pw[e] = *reinterpret_cast<uint32_t*>(&hh);
         }
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + (uint32_t)(lane * 128 + ((q8 ^ (lane & 7)) << 4))), "r"(pw[0]),
+                     "r"(pw[1]), "r"(pw[2]), "r"(pw[3]) : "memory");
+      }
+      __syncwarp();
+      const int sub = lane >> 3, cj = lane & 7;
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int rr = 4 * i + sub;                           // row within this warp's 32 query rows
+        uint4 ov;
+        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w)
+                     : "r"(stg + (uint32_t)(rr * 128 + ((cj ^ (rr & 7)) << 4))) : "memory");
+        const int tk = mt * 128 + quarter * 32 + rr;
+        if (tk < TOK && !(DBG & (8 | 32)))
+          *reinterpret_cast<uint4*>(ctx + (long long)(row0 + tk) * DM + h * DH + set * 64 + cj * 8) = ov;
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->tmem_free);
+      if (lane == 0) mbar_arrive(&ctl->tmem_free);          // TMEM reads and staging reads of this warp are done
     }
   }
   tc_fence_before();
@@ -346,22 +438,41 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
 
 }  // namespace
 
+// bv may be null when the V bias is already part of vt (folded into the V^T projection, see net.cu)
 int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups, cudaStream_t st)
 {
-  FPB_CHECK_ARG(qk && vt && bv && ctx && groups > 0 && vt_pitch % 8 == 0);
+  FPB_CHECK_ARG(qk && vt && ctx && groups > 0 && vt_pitch % 8 == 0);
   const long long R = (long long)groups * TOK;
   CUtensorMap mQ, mK, mV;
   int rc;
   if ((rc = fpb_tiled_map_bf16(qk, R, 2 * DM, 2 * DM, 128, &mQ, nullptr))) return rc;
   if ((rc = fpb_tiled_map_bf16(qk, R, 2 * DM, 2 * DM, 200, &mK, nullptr))) return rc;
   if ((rc = fpb_tiled_map_bf16(vt, DM, R, vt_pitch, 128, &mV, nullptr))) return rc;
-  static bool configured = false;
-  if (!configured) {
-    FPB_CUDA(cudaFuncSetAttribute(attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
-    configured = true;
-  }
+  static int dbg = -1;
+  if (dbg < 0) { const char* e = getenv("FPB_ATTN_DBG"); dbg = e ? atoi(e) : 0; }
   const float c1 = 0.08838834764831845f * 1.4426950408889634f;   // 1/sqrt(128) * log2(e)
-  attn_kernel<<<groups * HEADS, NTHREADS, SMEM_TOTAL, st>>>(mQ, mK, mV, bv, (__nv_bfloat16*)ctx, c1);
+#define ATTN_LAUNCH(D)                                                                                             \
+  do {                                                                                                             \
+    static bool configured = false;                                                                                \
+    if (!configured) {                                                                                             \
+      FPB_CUDA(cudaFuncSetAttribute(attn_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));     \
+      configured = true;                                                                                           \
+    }                                                                                                              \
+    attn_kernel<D><<<groups * HEADS, NTHREADS, SMEM_TOTAL, st>>>(mQ, mK, mV, bv, (__nv_bfloat16*)ctx, c1);          \
+  } while (0)
+  switch (dbg) {
+    case 0: ATTN_LAUNCH(0); break;
+    case 1: ATTN_LAUNCH(1); break;
+    case 2: ATTN_LAUNCH(2); break;
+    case 4: ATTN_LAUNCH(4); break;
+    case 16: ATTN_LAUNCH(16); break;
+    case 20: ATTN_LAUNCH(20); break;
+    case 23: ATTN_LAUNCH(23); break;
+    case 31: ATTN_LAUNCH(31); break;
+    case 32: ATTN_LAUNCH(32); break;
+    default: fpb_set_error("FPB_ATTN_DBG=%d is not an instantiated experiment", dbg); return FPB_ERR_ARG;
+  }
+#undef ATTN_LAUNCH
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }

@@ -371,6 +371,11 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             v[c4 * 4 + 0] = fmaf(v[c4 * 4 + 0], sc.x, sh.x); v[c4 * 4 + 1] = fmaf(v[c4 * 4 + 1], sc.y, sh.y);
             v[c4 * 4 + 2] = fmaf(v[c4 * 4 + 2], sc.z, sh.z); v[c4 * 4 + 3] = fmaf(v[c4 * 4 + 3], sc.w, sh.w);
           }
+          if (p.row_shift) {
+            const float rs = m < p.M ? __ldg(p.row_shift + m) : 0.0f;
+#pragma unroll
+            for (int i = 0; i < 64; i++) v[i] += rs;
+          }
           if (use_res) {
 #pragma unroll
             for (int i = 0; i < 8; i++)
@@ -478,6 +483,11 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
           for (int i = 0; i < 32; i++)
             if (full || nb + i < nst) v[i] += __ldg(p.shift + nb + i);
+        }
+        if (p.row_shift) {
+          const float rs = __ldg(p.row_shift + m);
+#pragma unroll
+          for (int i = 0; i < 32; i++) v[i] += rs;
         }
         if (res_row && !(q.dbg & 4)) {
           if (full) {

@@ -415,7 +415,7 @@ int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force)
   if (!force && !tc3_enabled()) return FPB_ERR_UNSUPPORTED;
   const int ncols = p.n_valid > 0 ? p.n_valid : p.N;
   if (p.batch != 1 || p.K % KC != 0 || p.Cin % KC != 0 || p.pix_pitch % 8 != 0 || p.ldw % 8 != 0) return FPB_ERR_UNSUPPORTED;
-  if ((ncols != 64 && ncols != 128) || p.N != ncols || !p.out_bf16 || p.pe) return FPB_ERR_UNSUPPORTED;
+  if ((ncols != 64 && ncols != 128) || p.N != ncols || !p.out_bf16 || p.pe || p.row_shift) return FPB_ERR_UNSUPPORTED;
   if (p.ldc % 8 != 0 || p.split_col_off % 8 != 0 || (p.residual && p.ldr % 8 != 0)) return FPB_ERR_UNSUPPORTED;
   if (p.m_split < p.M && p.m_split % 32 != 0) return FPB_ERR_UNSUPPORTED;
   if (((uintptr_t)p.A | (uintptr_t)p.W | (uintptr_t)p.C | (uintptr_t)p.residual) & 15) return FPB_ERR_UNSUPPORTED;

@@ -21,3 +21,9 @@ for i in range(8):
 ms = sorted(ts[2:])[len(ts[2:]) // 2]
 fl = 2.0 * G * 4 * 400 * 400 * 128 * 2
 print(f'attention G={G}: {ms*1e3:.1f} us  {fl/ms/1e9:.1f} TFLOP/s')
+if os.environ.get('FPB_ATTN_DBG') == '32':
+  torch.cuda.synchronize()
+  st = ctx.view(torch.int64).flatten()[:192].cpu().numpy()
+  t0 = min(int(v) for v in st if v > 0)
+  for name, b in (('mma', 0), ('softmax set0 (warp 2)', 64), ('softmax set1 (warp 6)', 128)):
+    print(name, [int(v - t0) for v in st[b:b + 64] if v > 0])
