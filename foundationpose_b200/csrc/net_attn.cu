@@ -163,7 +163,8 @@ struct AttnCtl {
 
 constexpr int SMEM_K = 2 * K_CHUNK_BYTES, SMEM_Q = 2 * Q_CHUNK_BYTES, SMEM_V = NV * V_STAGE, SMEM_P = 2 * T16;
 constexpr int SMEM_MAX = 2 * 2 * 128 * 4;         // partial row maxima: [tile parity][warp set][row]
-constexpr int SMEM_TOTAL = SMEM_K + SMEM_Q + SMEM_V + SMEM_P + SMEM_MAX + 1024 + (int)sizeof(AttnCtl);
+constexpr int SMEM_STAGE = 8 * 2048;              // context staging: 2 KB per softmax warp
+constexpr int SMEM_TOTAL = SMEM_K + SMEM_Q + SMEM_V + SMEM_P + SMEM_MAX + SMEM_STAGE + 1024 + (int)sizeof(AttnCtl);
 static_assert(SMEM_TOTAL <= 227 * 1024, "attention shared memory budget");
 
 // DBG (FPB_ATTN_DBG, timing experiments only; results are wrong when != 0): 1 no row-max pass, 2 no exp2, 4 no P.V MMAs,
@@ -181,7 +182,8 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
   uint8_t* sV = sQ + SMEM_Q;
   uint8_t* sP = sV + SMEM_V;
   float* smax = (float*)(sP + SMEM_P);
-  AttnCtl* ctl = (AttnCtl*)(sP + SMEM_P + SMEM_MAX);
+  uint8_t* sStage = sP + SMEM_P + SMEM_MAX;
+  AttnCtl* ctl = (AttnCtl*)(sStage + SMEM_STAGE);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = blockIdx.x / HEADS, h = blockIdx.x - g * HEADS;
   const int row0 = g * TOK;                                  // first token row of this hypothesis
@@ -394,38 +396,42 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
       tmem_ld32_nowait(t_row + (uint32_t)(O_COL + set * 64), o);
       tmem_ld32_nowait(t_row + (uint32_t)(O_COL + set * 64 + 32), o + 32);
       tmem_ld_wait();
-      // rows of 64 head dims (128 B) are transposed through this warp's 4 KB slice of the P ring (idle here: every P.V
-      // MMA of the tile has completed) so that 8 lanes store one contiguous 128-byte row segment; tmem_free is only
-      // released afterwards because the next tile's P tiles reuse the ring
-      const uint32_t stg = smem_u32(sP) + (uint32_t)((warp - 2) * 4096);
-#pragma unroll
-      for (int q8 = 0; q8 < 8; q8++) {
-        uint32_t pw[4];
-#pragma unroll
-        for (int e = 0; e < 4; e++) {
-          float a = __uint_as_float(o[q8 * 8 + e * 2]) * inv, b = __uint_as_float(o[q8 * 8 + e * 2 + 1]) * inv;
-          if (bv) { a += __ldg(bv + h * DH + set * 64 + q8 * 8 + e * 2); b += __ldg(bv + h * DH + set * 64 + q8 * 8 + e * 2 + 1); }
-          __nv_bfloat162 hh = __floats2bfloat162_rn(a, b);
-          pw[e] = *reinterpret_cast<uint32_t*>(&hh);
-        }
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + (uint32_t)(lane * 128 + ((q8 ^ (lane & 7)) << 4))), "r"(pw[0]),
-                     "r"(pw[1]), "r"(pw[2]), "r"(pw[3]) : "memory");
-      }
-      __syncwarp();
-      const int sub = lane >> 3, cj = lane & 7;
-#pragma unroll
-      for (int i = 0; i < 8; i++) {
-        const int rr = 4 * i + sub;                           // row within this warp's 32 query rows
-        uint4 ov;
-        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w)
-                     : "r"(stg + (uint32_t)(rr * 128 + ((cj ^ (rr & 7)) << 4))) : "memory");
-        const int tk = mt * 128 + quarter * 32 + rr;
-        if (tk < TOK && !(DBG & (8 | 32)))
-          *reinterpret_cast<uint4*>(ctx + (long long)(row0 + tk) * DM + h * DH + set * 64 + cj * 8) = ov;
-      }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->tmem_free);          // TMEM reads and staging reads of this warp are done
+      if (lane == 0) mbar_arrive(&ctl->tmem_free);          // all TMEM reads of this warp for this tile are done
+      // 32 rows x 32 head dims (64 B) at a time are transposed through this warp's private 2 KB staging tile so that 4
+      // lanes store one contiguous 64-byte row segment (two full sectors)
+      const uint32_t stg = smem_u32(sStage) + (uint32_t)((warp - 2) * 2048);
+      const int srow = lane >> 2, sc = lane & 3;
+#pragma unroll
+      for (int half = 0; half < 2; half++) {
+#pragma unroll
+        for (int q8 = 0; q8 < 4; q8++) {
+          uint32_t pw[4];
+#pragma unroll
+          for (int e = 0; e < 4; e++) {
+            const int d = half * 32 + q8 * 8 + e * 2;
+            float a = __uint_as_float(o[d]) * inv, b = __uint_as_float(o[d + 1]) * inv;
+            if (bv) { a += __ldg(bv + h * DH + set * 64 + d); b += __ldg(bv + h * DH + set * 64 + d + 1); }
+            __nv_bfloat162 hh = __floats2bfloat162_rn(a, b);
+            pw[e] = *reinterpret_cast<uint32_t*>(&hh);
+          }
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + (uint32_t)(lane * 64 + ((q8 ^ ((lane >> 1) & 3)) << 4))), "r"(pw[0]),
+                       "r"(pw[1]), "r"(pw[2]), "r"(pw[3]) : "memory");
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const int rr = 8 * i + srow;                        // row within this warp's 32 query rows
+          uint4 ov;
+          asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w)
+                       : "r"(stg + (uint32_t)(rr * 64 + ((sc ^ ((rr >> 1) & 3)) << 4))) : "memory");
+          const int tk = mt * 128 + quarter * 32 + rr;
+          if (tk < TOK && !(DBG & (8 | 32)))
+            *reinterpret_cast<uint4*>(ctx + (long long)(row0 + tk) * DM + h * DH + set * 64 + half * 32 + sc * 8) = ov;
+        }
+        __syncwarp();
+      }
     }
   }
   tc_fence_before();

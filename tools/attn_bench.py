@@ -21,7 +21,7 @@ for i in range(8):
 ms = sorted(ts[2:])[len(ts[2:]) // 2]
 fl = 2.0 * G * 4 * 400 * 400 * 128 * 2
 print(f'attention G={G}: {ms*1e3:.1f} us  {fl/ms/1e9:.1f} TFLOP/s')
-if os.environ.get('FPB_ATTN_DBG') == '32':
+if int(os.environ.get('FPB_ATTN_DBG', '0')) & 32:
   torch.cuda.synchronize()
   st = ctx.view(torch.int64).flatten()[:192].cpu().numpy()
   t0 = min(int(v) for v in st if v > 0)
