@@ -25,6 +25,8 @@ _SIGS = {
   'fpb_bilateral_depth_f32': (ci, [vp, vp, ci, ci, ci, cf, cf, cf, vp]),
   'fpb_depth_to_xyz': (ci, [vp, vp, cf, vp, ci, ci, ci, vp]),
   'fpb_mask_depth_stats': (ci, [vp, vp, ci, ci, vp, vp, vp]),
+  'fpb_hypotheses_from_stats': (ci, [vp, vp, vp, vp, ci, ci, vp, vp, vp]),
+  'fpb_register_prologue': (ci, [vp, vp, ci, ci, vp, vp, vp, vp, vp, vp, ci, ci, vp, vp, vp, vp, vp]),
   'fpb_cluster_poses_f32': (ci, [vp, ci, vp, ci, cf, cf, vp, vp, vp]),
   'fpb_crop_params': (ci, [vp, ci, vp, cf, ci, ci, ci, vp, vp, vp]),
   'fpb_mesh_create': (ci, [vp, vp, vp, ci, vp, ci, vp, vp, ci, vp, vp, ci, ci, vp]),

@@ -128,6 +128,34 @@ __global__ void pose_update_kernel(const float* __restrict__ poses, const float*
   o[12] = 0.f; o[13] = 0.f; o[14] = 0.f; o[15] = 1.f;
 }
 
+
+// ---- hypotheses from the mask statistics, on the device (src/estimater.py:127-156 without the host round trip) ----
+struct Mat3d { double v[9]; };
+__global__ void hypo_from_stats_kernel(const int32_t* __restrict__ si, const float* __restrict__ sf, Mat3d Kinv,
+                                       const float* __restrict__ rot_grid, int N, int min_valid, float* __restrict__ poses,
+                                       double* __restrict__ center_out)
+{
+  // same operation order as _center_from_stats (float64 bbox centre, float32 median of the two middle depths)
+  double c[3] = {0.0, 0.0, 0.0};
+  const bool ok = si[4] > 0 && si[5] > 0;
+  if (ok) {
+    const double uc = (double)(si[0] + si[1]) / 2.0, vc = (double)(si[2] + si[3]) / 2.0;
+    const float zc = (sf[0] + sf[1]) / 2.0f;
+    for (int i = 0; i < 3; i++) c[i] = (Kinv.v[i * 3 + 0] * uc + Kinv.v[i * 3 + 1] * vc + Kinv.v[i * 3 + 2]) * (double)zc;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && center_out) { center_out[0] = c[0]; center_out[1] = c[1]; center_out[2] = c[2]; }
+  // fewer than min_valid valid pixels: register() returns early on the host; the pipeline that is already enqueued
+  // runs on a harmless dummy translation instead of a degenerate one
+  float t[3] = {(float)c[0], (float)c[1], (float)c[2]};
+  if (si[5] < min_valid) { t[0] = 0.0f; t[1] = 0.0f; t[2] = 1.0f; }
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const float* g = rot_grid + (size_t)n * 16;
+  float* o = poses + (size_t)n * 16;
+  for (int i = 0; i < 16; i++) o[i] = g[i];
+  o[3] = t[0]; o[7] = t[1]; o[11] = t[2];
+}
+
 }  // namespace
 
 FPB_EXPORT int fpb_cluster_poses_f32(const float* poses, int N, const float* sym, int S, float angle_deg, float dist,
@@ -161,6 +189,19 @@ FPB_EXPORT int fpb_pose_update(const float* poses, const float* trans, const flo
   if (tn3_h) for (int i = 0; i < 3; i++) tn.v[i] = tn3_h[i];
   pose_update_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(poses, trans, rot, N, mesh_diameter / 2.0f,
                                                                        rot_normalizer, tn, normalize_xyz, out_poses);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_hypotheses_from_stats(const int32_t* stats_i32, const float* stats_f32, const double* Kinv9_h,
+                                         const float* rot_grid, int N, int min_valid, float* poses_out, double* center_out,
+                                         void* stream)
+{
+  FPB_CHECK_ARG(stats_i32 && stats_f32 && Kinv9_h && rot_grid && poses_out && N > 0);
+  Mat3d Ki;
+  for (int i = 0; i < 9; i++) Ki.v[i] = Kinv9_h[i];
+  hypo_from_stats_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(stats_i32, stats_f32, Ki, rot_grid, N, min_valid,
+                                                                              poses_out, center_out);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }

@@ -109,9 +109,13 @@ class FoundationPose:
     logging.info('reset done')
 
   def get_tf_to_centered_mesh(self):
-    tf_to_center = torch.eye(4, dtype=torch.float, device='cuda')
-    tf_to_center[:3, 3] = -torch.as_tensor(self.model_center, device='cuda', dtype=torch.float)
-    return tf_to_center
+    # cached per model_center: building it costs a pageable host-to-device copy, which would synchronise register()
+    key = tuple(np.asarray(self.model_center, dtype=np.float64).reshape(-1).tolist())
+    if getattr(self, '_tf_to_center', None) is None or self._tf_to_center[0] != key:
+      tf_to_center = torch.eye(4, dtype=torch.float, device='cuda')
+      tf_to_center[:3, 3] = -torch.as_tensor(self.model_center, device='cuda', dtype=torch.float)
+      self._tf_to_center = (key, tf_to_center)
+    return self._tf_to_center[1].clone()
 
   def to_device(self, s='cuda:0'):
     for k in self.__dict__:
@@ -150,23 +154,17 @@ class FoundationPose:
     K = np.asarray(K, dtype=np.float64)
     depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
     rgb_t = torch.as_tensor(rgb, device='cuda').contiguous()
-    mask_t = (torch.as_tensor(ob_mask, device='cuda') > 0).to(torch.uint8).contiguous()
-    depth_t = U.erode_depth(depth_t, radius=2, device='cuda')
-    depth_t = U.bilateral_filter_depth(depth_t, radius=2, device='cuda')
-    stats = U.mask_depth_stats(depth_t, mask_t)
-    center = _center_from_stats(stats, K)
-    if stats[5] < 4:
-      logging.info('valid too small, return')
-      pose = np.eye(4)
-      pose[:3, 3] = center
-      return pose
-    self.H, self.W = depth_t.shape[:2]
-    self.K = K
-    self.ob_id = ob_id
-    self.ob_mask = ob_mask
-    poses = self.rot_grid.clone()
-    poses[:, :3, 3] = torch.as_tensor(center.reshape(1, 3), device='cuda', dtype=torch.float)
-    xyz_map = U.depth2xyzmap_cuda(depth_t, K, math_f64=True)
+    mask_t = torch.as_tensor(ob_mask, device='cuda')
+    mask_t = (mask_t if mask_t.dtype == torch.uint8 else (mask_t > 0).to(torch.uint8)).contiguous()
+    # The whole call is enqueued without a host round trip (the reference crosses the bus ~10 times): the translation
+    # guess and the hypotheses are produced on the device, the mask statistics travel to pinned host memory
+    # asynchronously and the "too few valid pixels" early exit (src/estimater.py:176-180) is evaluated after the one
+    # synchronisation at the end (in that case the enqueued work ran on a dummy translation and is discarded).
+    depth_t, xyz_map, poses, si, sf, _ = U.register_prologue(depth_t, mask_t, K, self.rot_grid, min_valid=4)
+    if getattr(self, '_stats_host', None) is None:
+      self._stats_host = (torch.empty(6, dtype=torch.int32, pin_memory=True), torch.empty(2, dtype=torch.float, pin_memory=True))
+    self._stats_host[0].copy_(si, non_blocking=True)
+    self._stats_host[1].copy_(sf, non_blocking=True)
     poses, _ = self.refiner.predict(mesh=self.mesh, mesh_tensors=self.mesh_tensors, rgb=rgb_t, depth=depth_t, K=K,
                                     ob_in_cams=poses, normal_map=None, xyz_map=xyz_map, glctx=self.glctx,
                                     mesh_diameter=self.diameter, iteration=iteration, get_vis=False)
@@ -176,12 +174,23 @@ class FoundationPose:
     ids = torch.as_tensor(scores).argsort(descending=True)
     scores = scores[ids]
     poses = poses[ids]
-    best_pose = poses[0] @ self.get_tf_to_centered_mesh()
+    best_pose = (poses[0] @ self.get_tf_to_centered_mesh()).data.cpu().numpy()        # the only synchronisation
+    oi, of = self._stats_host[0].numpy(), self._stats_host[1].numpy()
+    stats = (int(oi[0]), int(oi[1]), int(oi[2]), int(oi[3]), int(oi[4]), int(oi[5]), of[0], of[1])
+    if stats[5] < 4:
+      logging.info('valid too small, return')
+      pose = np.eye(4)
+      pose[:3, 3] = _center_from_stats(stats, K)
+      return pose
+    self.H, self.W = depth_t.shape[:2]
+    self.K = K
+    self.ob_id = ob_id
+    self.ob_mask = ob_mask
     self.pose_last = poses[0]
     self.best_id = ids[0]
     self.poses = poses
     self.scores = scores
-    return best_pose.data.cpu().numpy()
+    return best_pose
 
   def compute_add_err_to_gt_pose(self, poses):
     return -torch.ones(len(poses), device='cuda', dtype=torch.float)

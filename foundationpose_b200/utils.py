@@ -105,6 +105,29 @@ def mask_depth_stats(depth_t, mask_t):
   return int(oi[0]), int(oi[1]), int(oi[2]), int(oi[3]), int(oi[4]), int(oi[5]), of[0], of[1]
 
 
+def register_prologue(depth_t, mask_t, K, rot_grid, min_valid=4):
+  """FoundationPose.register() up to the first refiner call (src/estimater.py:159-205) in one C-ABI call and without a
+  host synchronisation: erode_depth -> bilateral_filter_depth -> guess_translation -> hypotheses -> depth2xyzmap.
+  Returns (depth [H,W], xyz_map [H,W,3], poses [N,4,4], stats_i32 [6], stats_f32 [2], center [3] float64) -- all
+  device tensors; the statistics are those of mask_depth_stats."""
+  H, W = depth_t.shape
+  K = np.asarray(K, dtype=np.float64)
+  K9 = np.ascontiguousarray(K.reshape(9))
+  Ki9 = np.ascontiguousarray(np.linalg.inv(K).reshape(9))
+  dev = depth_t.device
+  tmp = torch.empty_like(depth_t)
+  out = torch.empty_like(depth_t)
+  xyz = torch.empty((H, W, 3), dtype=torch.float, device=dev)
+  N = rot_grid.shape[0]
+  poses = torch.empty((N, 4, 4), dtype=torch.float, device=dev)
+  si = torch.empty(6, dtype=torch.int32, device=dev)
+  sf = torch.empty(2, dtype=torch.float, device=dev)
+  center = torch.empty(3, dtype=torch.double, device=dev)
+  check(lib().fpb_register_prologue(ptr(depth_t), ptr(mask_t), H, W, hptr(K9), hptr(Ki9), ptr(tmp), ptr(out), ptr(xyz),
+                                    ptr(rot_grid), N, int(min_valid), ptr(poses), ptr(si), ptr(sf), ptr(center), stream()))
+  return out, xyz, poses, si, sf, center
+
+
 # ------------------------------------------------------------------------------------------------
 # hypothesis generation helpers (host, float64 -- init-time only in the reference too)
 # ------------------------------------------------------------------------------------------------

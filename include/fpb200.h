@@ -50,6 +50,23 @@ int fpb_depth_to_xyz(const float* depth, const double* K9_h, float zfar, float* 
 int fpb_mask_depth_stats(const float* depth, const uint8_t* mask, int H, int W, int32_t* out_i32,
                          float* out_f32, void* stream);
 
+/* ---- hypotheses on the device: generate_random_pose_hypo + guess_translation, src/estimater.py:127-156.
+ *      poses_out[N,4,4] = rot_grid with translation inv(K) @ [uc, vc, 1] * median depth (float64 math as on the
+ *      host); center_out[3] (device float64, may be NULL) = that translation, zeros for an empty mask / no valid
+ *      depth.  With fewer than min_valid valid pixels the poses get the dummy translation (0,0,1): register() returns
+ *      early in that case (src/estimater.py:176-180) and the caller discards whatever was enqueued. ---- */
+int fpb_hypotheses_from_stats(const int32_t* stats_i32, const float* stats_f32, const double* Kinv9_h,
+                              const float* rot_grid, int N, int min_valid, float* poses_out, double* center_out,
+                              void* stream);
+
+/* ---- register() prologue in one call, no host synchronisation: src/estimater.py:159-205
+ *      (erode_depth -> bilateral_filter_depth -> guess_translation -> hypotheses -> depth2xyzmap).
+ *      depth_tmp / depth_out [H,W], xyz_out [H,W,3]; stats as fpb_mask_depth_stats. ---- */
+int fpb_register_prologue(const float* depth_in, const uint8_t* mask, int H, int W, const double* K9_h,
+                          const double* Kinv9_h, float* depth_tmp, float* depth_out, float* xyz_out,
+                          const float* rot_grid, int N, int min_valid, float* poses_out, int32_t* stats_i32,
+                          float* stats_f32, double* center_out, void* stream);
+
 /* ---- cluster_poses: mycpp/src/app/pybind_api.cpp:24-68.
  *      out_keep_idx[N] receives kept input indices, out_n_keep[1] their count. ---- */
 int fpb_cluster_poses_f32(const float* poses, int N, const float* sym, int S, float angle_deg, float dist,

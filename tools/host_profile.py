@@ -28,4 +28,7 @@ pr = cProfile.Profile()
 pr.enable()
 est.register(K=scene['K'], rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
 pr.disable()
-pstats.Stats(pr).sort_stats('cumulative').print_stats(45)
+pstats.Stats(pr).sort_stats('tottime').print_stats(22)
+import time as _t
+from foundationpose_b200 import utils as U
+t0 = _t.perf_counter(); U.set_seed(0); t1 = _t.perf_counter(); print('set_seed ms', (t1 - t0) * 1e3)

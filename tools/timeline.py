@@ -16,12 +16,20 @@ for _ in range(3):
   est.register(K=scene['K'], rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-  est.register(K=scene['K'], rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
+  with torch.profiler.record_function('fpb_register'):
+    est.register(K=scene['K'], rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
   torch.cuda.synchronize()
 evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
 evs.sort(key=lambda e: e.time_range.start)
 t0, t1 = evs[0].time_range.start, max(e.time_range.end for e in evs)
 busy = sum(e.time_range.end - e.time_range.start for e in evs)
+reg = [e for e in prof.events() if e.name == 'fpb_register' and e.device_type == torch.autograd.DeviceType.CPU]
+if reg:
+  r = reg[0].time_range
+  print(f'host call {(r.end - r.start) / 1e3:.2f} ms; first device activity {(t0 - r.start) / 1e3:.2f} ms after entry; return {(r.end - t1) / 1e3:.2f} ms after the last device activity')
+  first = evs[:12]
+  for e in first:
+    print(f'   +{(e.time_range.start - r.start) / 1e3:7.3f} ms  {(e.time_range.end - e.time_range.start):7.1f} us  {e.name[:70]}')
 print(f'{len(evs)} device activities, span {(t1 - t0) / 1e3:.2f} ms, sum of durations {busy / 1e3:.2f} ms')
 gaps = []
 end = evs[0].time_range.end
