@@ -188,6 +188,7 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
   const int g = blockIdx.x / HEADS, h = blockIdx.x - g * HEADS;
   const int row0 = g * TOK;                                  // first token row of this hypothesis
   constexpr int N_MT = (TOK + 127) / 128;                    // 4 query tiles
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // programmatic dependent launch, see tc_ptx.cuh
 
   if (threadIdx.x == 0) {
     mbar_init(&ctl->k_full, 1); mbar_init(&ctl->q_full, 1); mbar_init(&ctl->q_empty, 1);
@@ -210,6 +211,7 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
+  asm volatile("griddepcontrol.wait;" ::: "memory");         // predecessor outputs (Q|K, V^T) complete from here on
   // DBG & 32: block 0 records clock64 stamps (warp 1 lane 0 -> slots 0..63, warp 2 lane 0 -> 64..127, warp 6 lane 0 -> 128..191)
   long long* stamps = reinterpret_cast<long long*>(ctx);
   int n_st = 0;
@@ -464,7 +466,18 @@ int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float
       FPB_CUDA(cudaFuncSetAttribute(attn_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));     \
       configured = true;                                                                                           \
     }                                                                                                              \
-    attn_kernel<D><<<groups * HEADS, NTHREADS, SMEM_TOTAL, st>>>(mQ, mK, mV, bv, (__nv_bfloat16*)ctx, c1);          \
+    cudaLaunchConfig_t cfg;                                                                                        \
+    memset(&cfg, 0, sizeof(cfg));                                                                                  \
+    cfg.gridDim = dim3(groups * HEADS, 1, 1);                                                                      \
+    cfg.blockDim = dim3(NTHREADS, 1, 1);                                                                           \
+    cfg.dynamicSmemBytes = SMEM_TOTAL;                                                                             \
+    cfg.stream = st;                                                                                               \
+    cudaLaunchAttribute attr[1];                                                                                   \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                               \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                                        \
+    cfg.attrs = attr;                                                                                              \
+    cfg.numAttrs = fpb_pdl_enabled() ? 1 : 0;                                                                      \
+    FPB_CUDA(cudaLaunchKernelEx(&cfg, attn_kernel<D>, mQ, mK, mV, bv, (__nv_bfloat16*)ctx, c1));                    \
   } while (0)
   switch (dbg) {
     case 0: ATTN_LAUNCH(0); break;

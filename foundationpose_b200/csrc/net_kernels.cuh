@@ -57,6 +57,9 @@ static inline GemmProblem gemm_problem_default()
   return p;
 }
 
+// 1 unless FPB_PDL=0: launch the tcgen05 kernels with programmatic stream serialization (see tc_ptx.cuh)
+int fpb_pdl_enabled();
+
 int ref_gemm(const GemmProblem& p, cudaStream_t st);   // fp32 SIMT
 int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 accumulate (cp.async producers)
 int tc2_gemm(const GemmProblem& p, cudaStream_t st);   // bf16 tcgen05, persistent TMA kernel; FPB_ERR_UNSUPPORTED -> use tc_gemm

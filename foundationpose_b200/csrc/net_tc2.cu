@@ -84,6 +84,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   const int cluster_id = blockIdx.x / CG, n_clusters = gridDim.x / CG;
   const int total_tiles = q.m_tiles * q.n_tiles;
   const int nk = p.K / KC;
+  pdl_launch_dependents();
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 8; s++) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
@@ -112,6 +113,12 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   if (CG == 2) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
+  pdl_wait();                                   // the predecessor's outputs (our inputs) are complete from here on
+  // FPB_TC2_DBG & 2048: CTA 0 records clock64 stamps into the output buffer (slots: warp 0 -> 0.., warp 1 -> 64.., warp 2 -> 128..)
+  int n_st = 0;
+  auto stamp = [&](int base) {
+    if ((q.dbg & 2048) && blockIdx.x == 0 && lane == 0 && n_st < 64) reinterpret_cast<long long*>(p.C)[base + n_st++] = clock64();
+  };
 
   // Both single-thread roles keep ring positions as (stage, phase) pairs advanced incrementally: every integer division
   // or modulo by a run-time value in these loops showed up directly as pipeline time (measured: the halo loop went
@@ -235,6 +242,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         for (int t = cluster_id; t < total_tiles; t += n_clusters) {
           mbar_wait(&ctl->tmem_empty[acc], acc_ph);
           tc_fence_after();
+          stamp(64);                                             // accumulator buffer free
           const uint32_t d_tmem = tmem_base + acc * BN;
           for (int kc = 0; kc < nk; kc++) {
             mbar_wait(&ctl->full[s], ph);
@@ -249,6 +257,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             umma_commit<CG>(&ctl->empty[s]);
             if (++s == STAGES) { s = 0; ph ^= 1u; }
           }
+          stamp(64);                                             // all MMAs of the tile issued
           umma_commit<CG>(&ctl->tmem_full[acc]);
           if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
         }
@@ -291,8 +300,10 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       const int m = (mt * CG + (int)rank) * TM + row;
       const int n0 = nt * BN;
       const uint32_t acc = tc & 1u;
+      if (warp == 2) stamp(128);
       mbar_wait(&ctl->tmem_full[acc], (tc >> 1) & 1u);
       tc_fence_after();
+      if (warp == 2) stamp(128);                               // accumulator ready
       if (q.fast_epi) {
         // ---- coalesced path: TMEM -> registers (lane = row) -> math -> bf16 -> warp-private swizzled smem tile ->
         //      8 lanes per row read it back and store 128 contiguous bytes per row; residual / positional embedding
@@ -335,6 +346,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           ss[BN + i] = (p.shift && ok && !(q.dbg & 2)) ? __ldg(p.shift + n0 + i) : 0.0f;
         }
         asm volatile("bar.sync 1, %0;" ::"n"(C::EPI_WARPS * 32) : "memory");
+        if (warp == 2) stamp(128);                             // scale/shift table ready
         const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
 #pragma unroll 1
         for (int g = ehalf; g < BN / 64; g += GSTEP) {
@@ -445,7 +457,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             for (int i = 0; i < 8; i++) {
               uint4 ov;
               asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
-              if (4 * i < rows_left) *reinterpret_cast<uint4*>(ob + (unsigned long long)i * pitch4) = ov;
+              if (4 * i < rows_left && !(q.dbg & 2048)) *reinterpret_cast<uint4*>(ob + (unsigned long long)i * pitch4) = ov;
             }
           } else {
 #pragma unroll
@@ -454,10 +466,11 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               uint4 ov;
               asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
               __nv_bfloat16* op = row_ptr(mr);
-              if (op) *(reinterpret_cast<uint4*>(op + nb) + cj) = ov;
+              if (op && !(q.dbg & 2048)) *(reinterpret_cast<uint4*>(op + nb) + cj) = ov;
             }
           }
           __syncwarp();
+          if (warp == 2) stamp(128);                           // 64-column group done
         }
         continue;
       }
@@ -690,17 +703,20 @@ int launch_tc2(const CUtensorMap& mA, const CUtensorMap& mB, const Tc2Params& q_
   cfg.blockDim = dim3(NTHREADS, 1, 1);
   cfg.dynamicSmemBytes = C::SMEM;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = fpb_pdl_enabled() ? 2 : 1;
   FPB_CUDA(cudaLaunchKernelEx(&cfg, tc2_kernel<BN, CG>, mA, mB, q));
   fpb_count_launch();
   return FPB_OK;
 }
 
 int g_force_cg = 0;
+
 
 int tc2_cta_group()
 {
@@ -717,6 +733,16 @@ int tc2_cta_group()
 }  // namespace
 
 void tc2_force_cta_group(int cg) { g_force_cg = cg; }
+
+int fpb_pdl_enabled()
+{
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("FPB_PDL");
+    v = e ? (atoi(e) != 0) : 1;
+  }
+  return v;
+}
 
 // shared with net_attn.cu: cached tiled 2-D bf16 tensor map (box = 64 columns x box_rows rows, 128B swizzle)
 int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms)

@@ -72,6 +72,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = p.K / KC;
   const bool halo = q.mode == 2;
+  pdl_launch_dependents();
 
   if (q.ch == 64) {
     // rows 64..127 of every weight slot are the zero half of the M operand; TMA only ever writes rows 0..63
@@ -101,6 +102,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
+  pdl_wait();
   const uint32_t w_tx = (q.dbg & 256) ? 0u : (uint32_t)(q.ch * 128);
   const bool no_a = q.dbg & 128, no_w = q.dbg & 256;
 
@@ -456,8 +458,18 @@ int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force)
     configured = true;
   }
   const int grid = q.tiles < num_sms ? q.tiles : num_sms;
-  tc3_kernel<<<grid, NT3, SMEM3, st>>>(mA, mA2, mW, q);
-  FPB_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(NT3, 1, 1);
+  cfg.dynamicSmemBytes = SMEM3;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = fpb_pdl_enabled() ? 1 : 0;
+  FPB_CUDA(cudaLaunchKernelEx(&cfg, tc3_kernel, mA, mA2, mW, q));
   fpb_count_launch();
   return FPB_OK;
 }

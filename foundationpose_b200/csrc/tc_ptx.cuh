@@ -7,6 +7,14 @@
 
 namespace {
 
+// Programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may become
+// resident while its predecessor in the stream is still draining.  Every kernel calls pdl_launch_dependents() first
+// thing (its successor may be scheduled as soon as all of this grid's CTAs have started) and pdl_wait() after its
+// private set-up (barrier init, TMEM allocation, tensor-map prefetch) and before ANY global memory access: the wait
+// returns once the predecessor grid has completed and its writes are visible.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)

@@ -63,6 +63,12 @@ def main():
       ms = sorted(ts)[len(ts) // 2]
       fl = 2.0 * M * Cout * K
       print(f'{name:7s} mode {mode} M={M} N={Cout} K={K}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TFLOP/s', flush=True)
+      if int(os.environ.get('FPB_TC2_DBG', '0')) & 2048:
+        out.zero_(); launch(); torch.cuda.synchronize()
+        st = out.view(torch.int64).flatten()[:192].cpu().numpy()
+        t0 = min(int(v) for v in st if v > 0)
+        for nm, b in (('mma', 64), ('epi warp 2', 128)):
+          print('  ', nm, [int(v - t0) for v in st[b:b + 64] if v > 0][:40])
 
 
 def stem(a):
