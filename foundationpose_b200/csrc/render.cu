@@ -91,6 +91,7 @@ struct TriSetup {
   long long X[3], Y[3];
   int px0, px1, py0, py1;
   int ok;
+  int small;          // every |X|, |Y| <= 16383 (within ~1000 pixels of the crop): the edge functions fit 32-bit integers
 };
 
 __device__ __forceinline__ long long floordiv16(long long a) { return a >> 4; }
@@ -99,6 +100,7 @@ __device__ __forceinline__ long long ceildiv16(long long a) { return -((-a) >> 4
 __device__ __forceinline__ void tri_setup(const float4 c0, const float4 c1, const float4 c2, int S, TriSetup& t)
 {
   t.ok = 0;
+  t.small = 0;
   if (!(c0.w > 0.0f && c1.w > 0.0f && c2.w > 0.0f)) return;
   const float sub = (float)(8 * S);
   const float4 cc[3] = {c0, c1, c2};
@@ -123,6 +125,7 @@ __device__ __forceinline__ void tri_setup(const float4 c0, const float4 c1, cons
   if (px0 > px1 || py0 > py1) return;
   t.px0 = (int)px0; t.px1 = (int)px1; t.py0 = (int)py0; t.py1 = (int)py1;
   t.ok = 1;
+  t.small = xmin >= -16383 && xmax <= 16383 && ymin >= -16383 && ymax <= 16383;
 }
 
 __device__ __forceinline__ bool covers(const TriSetup& t, int px, int py)
@@ -137,6 +140,35 @@ __device__ __forceinline__ bool covers(const TriSetup& t, int px, int py)
     if (E == 0 && !(dy > 0 || (dy == 0 && dx < 0))) return false;
   }
   return true;
+}
+
+// the same test in 32-bit arithmetic for triangles whose vertices lie within ~1000 pixels of the crop (exact, hence
+// identical results): |dx|, |dy|, |cx - X|, |cy - Y| < 2^15 -> |E| < 2^31
+struct Tri32 { int X[3], Y[3]; };
+__device__ __forceinline__ bool covers32(const Tri32& t, int px, int py)
+{
+  const int cx = 16 * px + 8, cy = 16 * py + 8;
+#pragma unroll
+  for (int e = 0; e < 3; e++) {
+    const int a = e, b = (e + 1) % 3;
+    const int dx = t.X[b] - t.X[a], dy = t.Y[b] - t.Y[a];
+    const int E = dx * (cy - t.Y[a]) - dy * (cx - t.X[a]);
+    if (E < 0) return false;
+    if (E == 0 && !(dy > 0 || (dy == 0 && dx < 0))) return false;
+  }
+  return true;
+}
+
+__device__ __forceinline__ void shade_fragment(const float4 c0, const float4 c1, const float4 c2, int px, int py, int S,
+                                               uint32_t face, unsigned long long* zb)
+{
+  const float xs = 2.0f / (float)S, xo = 1.0f / (float)S - 1.0f;
+  float fx = (float)px * xs + xo, fy = (float)py * xs + xo;
+  float b0, b1, zw;
+  bary_zw(c0, c1, c2, fx, fy, b0, b1, zw);
+  if (zw != zw) return;
+  unsigned long long key = ((unsigned long long)f2ord(zw) << 32) | face;
+  atomicMin(zb + (size_t)py * S + px, key);
 }
 
 __device__ __forceinline__ void raster_pixel(const TriSetup& t, const float4 c0, const float4 c1, const float4 c2, int px,
@@ -154,7 +186,7 @@ __device__ __forceinline__ void raster_pixel(const TriSetup& t, const float4 c0,
 
 constexpr int SMALL_TRI_PIXELS = 16;
 
-__global__ void __launch_bounds__(256) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
+__global__ void __launch_bounds__(256, 4) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
                                                      const float4* __restrict__ clip, int S,
                                                      unsigned long long* __restrict__ zbuf)
 {
@@ -173,11 +205,15 @@ __global__ void __launch_bounds__(256) raster_kernel(const int32_t* __restrict__
   int big = 0;
   if (t.ok) {
     int npx = (t.px1 - t.px0 + 1) * (t.py1 - t.py0 + 1);
-    if (npx <= SMALL_TRI_PIXELS) {
+    if (npx <= SMALL_TRI_PIXELS && t.small) {
+      Tri32 q;
+#pragma unroll
+      for (int k = 0; k < 3; k++) { q.X[k] = (int)t.X[k]; q.Y[k] = (int)t.Y[k]; }
       for (int py = t.py0; py <= t.py1; py++)
-        for (int px = t.px0; px <= t.px1; px++) raster_pixel(t, c0, c1, c2, px, py, S, (uint32_t)f, zb);
+        for (int px = t.px0; px <= t.px1; px++)
+          if (covers32(q, px, py)) shade_fragment(c0, c1, c2, px, py, S, (uint32_t)f, zb);
     } else {
-      big = 1;
+      big = 1;       // large footprint, or coordinates beyond the 32-bit fast path: warp-cooperative 64-bit path
     }
   }
   // triangles with a large footprint: the whole warp sweeps the bounding box together
