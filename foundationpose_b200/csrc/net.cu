@@ -260,6 +260,19 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
   __nv_bfloat16* vt = qk + R * 2 * D;
   Lin lqk = m.in; lqk.N = 2 * D;
   RET(run_linear(c, lqk, x, R, qk, nullptr, 0, 1));
+  {
+    // preferred: V = X . Wv^T + bv through the operand-swapped kernel, which stores its (channel-major) accumulator
+    // layout directly: vt[d][token]
+    GemmProblem t = gemm_problem_default();
+    t.A = x; t.W = c.W(m.in.w + (size_t)2 * D * D); t.C = vt;
+    t.M = (int)R; t.N = D; t.K = D; t.Cin = D; t.pix_pitch = D; t.ldw = D; t.ldc = (int)R; t.out_bf16 = 1;
+    t.shift = c.F(m.in.b + 2 * D); t.c_transposed = 1;
+    const int rc3 = tc3_gemm(t, c.st, 0);
+    if (rc3 != FPB_ERR_UNSUPPORTED) {
+      RET(rc3);
+      return tc_attention(qk, vt, R, nullptr, w.ctx, n, c.st);
+    }
+  }
   GemmProblem p = gemm_problem_default();
   p.A = c.W(m.in.w + (size_t)2 * D * D); p.W = x; p.C = vt;
   p.M = D; p.N = (int)R; p.K = D; p.Cin = D; p.pix_pitch = D; p.ldw = D; p.ldc = (int)R; p.out_bf16 = 1;
@@ -430,7 +443,8 @@ FPB_EXPORT size_t fpb_score_cross_ws_bytes(int L, int bs)
 
 // Debug / unit-test entry: one implicit GEMM through one kernel family (see GemmProblem).
 //   mode 0: fp32 operands (SIMT); 1: bf16 tcgen05 with cp.async producers; 2 / 3: bf16 tcgen05 persistent TMA
-//   kernel with cta_group 1 / 2; 4: operand-swapped kernel for 64 / 128 output channels.  out is fp32 unless out_bf16.  row_pitch / pix_pitch / pad_w: 0 / 0 / pad_h for
+//   kernel with cta_group 1 / 2; 4: operand-swapped kernel (64 / 128 output channels, or plain GEMMs with K <= 512 and
+//   N % 128 == 0 through its weight-resident mode; out_bf16 = 2 stores the product transposed).  out is fp32 unless out_bf16.  row_pitch / pix_pitch / pad_w: 0 / 0 / pad_h for
 //   dense NHWC; the stem uses (168, 8, -1) with Cin = 64 "wide pixels".
 FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,
                                   int Cin, int Ho, int Wo, int KH, int KW, int stride, int pad_h, int pad_w, int row_pitch,
@@ -442,7 +456,8 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
   p.Hin = Hin; p.Win = Win; p.Cin = Cin; p.Ho = Ho; p.Wo = Wo; p.KH = KH; p.KW = KW; p.stride = stride;
   p.pad = pad_h; p.pad_w = pad_w; p.row_pitch = row_pitch; p.pix_pitch = pix_pitch > 0 ? pix_pitch : Cin;
   p.ldw = K; p.scale = scale; p.shift = shift; p.residual = residual; p.ldr = N; p.relu = relu;
-  p.ldc = N; p.out_bf16 = out_bf16;
+  p.ldc = N; p.out_bf16 = out_bf16 ? 1 : 0;
+  if (out_bf16 == 2) { p.c_transposed = 1; p.ldc = M; }      // bf16 output stored transposed: C[n][m] (mode 4 only)
   cudaStream_t st = (cudaStream_t)stream;
   switch (mode) {
     case 0: return ref_gemm(p, st);

@@ -42,6 +42,7 @@ struct GemmProblem {
   // flattened [positions][C] matrix shifted by (ky-1)*Wp + (kx-1): ONE TMA box per 64-channel chunk serves all 9
   // taps.  M counts positions; outputs at border positions are written as zeros.
   int halo, img_h, img_w;
+  int c_transposed;   // tc3 kernel only: out[n * ldc + m] (bf16), i.e. the product is stored transposed
   const float* row_shift;   // optional per-ROW additive term (after scale/shift; tc2 kernel only): v += row_shift[m]
   int row_remap;      // output rows: 0 as computed, 1 dense pixel index -> position, 2 position -> dense (borders skipped)
 };

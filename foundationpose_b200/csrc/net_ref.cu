@@ -304,7 +304,7 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* 
 
 int ref_gemm(const GemmProblem& p, cudaStream_t st)
 {
-  FPB_CHECK_ARG(p.A && p.W && p.C && p.M > 0 && p.N > 0 && p.K > 0 && p.K % 4 == 0 && p.Cin % 4 == 0 && !p.row_shift);
+  FPB_CHECK_ARG(p.A && p.W && p.C && p.M > 0 && p.N > 0 && p.K > 0 && p.K % 4 == 0 && p.Cin % 4 == 0 && !p.row_shift && !p.c_transposed);
   dim3 grid(fpb_cdiv(p.M, BM), fpb_cdiv(p.N, BN), p.batch);
   ref_gemm_kernel<<<grid, 256, 0, st>>>(p);
   FPB_LAUNCH_CHECK();

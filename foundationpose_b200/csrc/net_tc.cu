@@ -334,7 +334,7 @@ int launch_tc(const GemmProblem& p, cudaStream_t st)
 
 int tc_gemm(const GemmProblem& p, cudaStream_t st)
 {
-  FPB_CHECK_ARG(p.A && p.W && p.C && p.M > 0 && p.N > 0 && p.K > 0 && !p.row_shift && !p.halo && !p.row_remap);
+  FPB_CHECK_ARG(p.A && p.W && p.C && p.M > 0 && p.N > 0 && p.K > 0 && !p.row_shift && !p.halo && !p.row_remap && !p.c_transposed);
   FPB_CHECK_ARG(p.K % KC == 0 && p.Cin % 8 == 0 && p.pix_pitch % 8 == 0 && p.ldw % 8 == 0 && p.ldc % 8 == 0);
   FPB_CHECK_ARG(p.split_col_off % 8 == 0 && (p.residual == nullptr || p.ldr % 8 == 0));
   FPB_CHECK_ARG((p.A_outer | p.A_inner | p.W_outer | p.W_inner | p.C_outer | p.C_inner) % 8 == 0);

@@ -769,6 +769,7 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
     return FPB_ERR_UNSUPPORTED;
   }
   if (((uintptr_t)p.A | (uintptr_t)p.W) & 15) return FPB_ERR_UNSUPPORTED;
+  if (p.c_transposed) { fpb_set_error("tc2_gemm: transposed output is only implemented by the operand-swapped kernel"); return FPB_ERR_ARG; }
   const bool plain = !p.halo && p.KH == 1 && p.KW == 1 && p.stride == 1 && p.pad == 0 && p.pad_w == 0 && p.Ho == 1 && p.Wo == 1;
   if (!plain && (p.pad > 127 || p.KH > 127)) return FPB_ERR_UNSUPPORTED;
   int rc = resolve_driver();

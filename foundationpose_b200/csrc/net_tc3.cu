@@ -44,6 +44,7 @@ struct Ctl3 {
   uint64_t aempty[2];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
+  uint64_t wfull;
   uint32_t tmem_base;
 };
 constexpr int SMEM3 = RING_BYTES + EPI3_BYTES + 1024 + (int)sizeof(Ctl3);
@@ -52,7 +53,8 @@ static_assert(NB3 >= 4 && NB3 <= 8, "tc3 halo weight ring");
 
 struct Tc3Params {
   GemmProblem p;
-  int mode;              // 0 plain tiled A, 1 im2col A, 2 halo
+  int mode;              // 0 plain tiled A, 1 im2col A, 2 halo, 3 plain A with the weight slab resident in smem
+  int n_slabs, nstage;   // mode 3: 128-channel slabs of the output (one per CTA), pixel ring depth
   int lower_w, lower_h;  // im2col bounding-box lower corner
   int tiles;             // tiles of TP pixels
   int Wp, IS, hrows;     // halo mode: position pitch, image stride, A box rows
@@ -60,6 +62,10 @@ struct Tc3Params {
   int dbg;               // FPB_TC2_DBG bits: 1 no stores, 4 no residual, 8 no MMA, 128 no A loads, 256 no W loads
 };
 
+// CG = 2 (mode 3 only): a CTA pair shares every pixel tile -- each CTA keeps its own 128-channel weight slab resident,
+// loads half of the 256 pixels (16 KB per stage) and the leader issues cta_group::2 MMAs (M = 2 x 128 channels,
+// N = 256 pixels), so the activation stream per SM halves again and the ring is twice as deep.
+template <int CG>
 __global__ void __launch_bounds__(NT3, 1)
 tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapA2,
            const __grid_constant__ CUtensorMap mapW, const Tc3Params q)
@@ -72,6 +78,13 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = p.K / KC;
   const bool halo = q.mode == 2;
+  // tiles of this CTA: t_first, t_first + t_step, ...; mode 3 pins a CTA to one 128-channel slab of the output
+  const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+  const int unit = (int)blockIdx.x / CG, n_units = (int)gridDim.x / CG;       // CTA (CG 1) or CTA pair (CG 2)
+  const int n_groups = q.n_slabs / CG;                                          // slab groups: one per unit
+  const int slab = q.mode == 3 ? (unit % n_groups) * CG + (int)rank : 0;
+  const int t_first = q.mode == 3 ? unit / n_groups : unit;
+  const int t_step = q.mode == 3 ? n_units / n_groups : n_units;
   pdl_launch_dependents();
 
   if (q.ch == 64) {
@@ -87,12 +100,18 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   if (threadIdx.x == 0) {
     for (int s = 0; s < 8; s++) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
     for (int s = 0; s < 2; s++) { mbar_init(&ctl->afull[s], 1); mbar_init(&ctl->aempty[s], 1); }
-    for (int a = 0; a < 2; a++) { mbar_init(&ctl->tmem_full[a], 1); mbar_init(&ctl->tmem_empty[a], 8); }
+    for (int a = 0; a < 2; a++) { mbar_init(&ctl->tmem_full[a], 1); mbar_init(&ctl->tmem_empty[a], 8 * CG); }
+    mbar_init(&ctl->wfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)), "r"(512u) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (CG == 1) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)), "r"(512u) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)), "r"(512u) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
   }
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
@@ -100,6 +119,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
   pdl_wait();
@@ -115,7 +135,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         const uint32_t a_tx = no_a ? 0u : (uint32_t)(q.hrows * 128);
         int sa = 0, sb = 0;
         uint32_t pa = 1, pb = 1;
-        for (int t = blockIdx.x; t < q.tiles; t += gridDim.x) {
+        for (int t = t_first; t < q.tiles; t += t_step) {
           const int r0 = t * TP - q.Wp - 1;
           for (int c = 0; c < nchunk; c++) {
             mbar_wait(&ctl->aempty[sa], pa);
@@ -134,12 +154,33 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             }
           }
         }
+      } else if (q.mode == 3) {
+        // weight slab [128 channels][K] once (nk tiles of 16 KB), then only the pixel stream: 32 KB / CG per stage.
+        // CG 2: both CTAs signal the leader's barriers (the leader arms them with the pair's byte count)
+        constexpr uint32_t PIXB = PIX_BYTES / CG;
+        const uint32_t sW = smem_u32(smem), s0 = sW + nk * W_BYTES;
+        const uint32_t wfull_a = CG == 2 ? mapa_u32(smem_u32(&ctl->wfull), 0) : smem_u32(&ctl->wfull);
+        const uint32_t full_a = CG == 2 ? mapa_u32(smem_u32(&ctl->full[0]), 0) : smem_u32(&ctl->full[0]);
+        if (rank == 0) mbar_arrive_expect_tx(&ctl->wfull, no_w ? 0u : (uint32_t)(CG * nk * W_BYTES));
+        if (!no_w)
+          for (int kc = 0; kc < nk; kc++) tma_load_2d<CG>(sW + kc * W_BYTES, &mapW, wfull_a, kc * KC, slab * 128);
+        int s = 0;
+        uint32_t ph = 1;
+        for (int t = t_first; t < q.tiles; t += t_step) {
+          const int m0 = t * TP + (int)rank * (TP / CG);
+          for (int kc = 0; kc < nk; kc++) {
+            mbar_wait(&ctl->empty[s], ph);
+            if (rank == 0) mbar_arrive_expect_tx(&ctl->full[s], no_a ? 0u : (uint32_t)PIX_BYTES);
+            if (!no_a) tma_load_2d<CG>(s0 + s * PIXB, &mapA, full_a + 8u * s, kc * KC, m0);
+            if (++s == q.nstage) { s = 0; ph ^= 1u; }
+          }
+        }
       } else {
         const int hw = p.Ho * p.Wo;
         const uint32_t s0 = smem_u32(smem);
         int s = 0;
         uint32_t ph = 1;
-        for (int t = blockIdx.x; t < q.tiles; t += gridDim.x) {
+        for (int t = t_first; t < q.tiles; t += t_step) {
           const int m0 = t * TP;
           const bool second = m0 + 128 < p.M;                  // a tile's upper 128 pixels may lie beyond M
           int cw[2] = {0, 0}, chh[2] = {0, 0}, img[2] = {0, 0};
@@ -187,7 +228,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         const uint32_t row_step = (uint32_t)(q.Wp * 128);
         int sa = 0, sb = 0;
         uint32_t pa = 0, pb = 0;
-        for (int t = blockIdx.x; t < q.tiles; t += gridDim.x) {
+        for (int t = t_first; t < q.tiles; t += t_step) {
           mbar_wait(&ctl->tmem_empty[acc], acc_ph);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * TP;
@@ -214,11 +255,40 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           umma_commit<1>(&ctl->tmem_full[acc]);
           if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
         }
+      } else if (q.mode == 3) {
+        if (rank == 0) {
+          constexpr uint32_t PIXB = PIX_BYTES / CG;
+          constexpr uint32_t idesc3 = make_idesc(128 * CG, TP);
+          const uint32_t sW = smem_u32(smem), s0 = sW + nk * W_BYTES;
+          const uint64_t dw0 = make_desc(sW);
+          int s = 0;
+          uint32_t ph = 0;
+          mbar_wait(&ctl->wfull, 0);
+          for (int t = t_first; t < q.tiles; t += t_step) {
+            mbar_wait(&ctl->tmem_empty[acc], acc_ph);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + acc * TP;
+            for (int kc = 0; kc < nk; kc++) {
+              mbar_wait(&ctl->full[s], ph);
+              tc_fence_after();
+              const uint64_t dx = make_desc(s0 + s * PIXB), dw = dw0 + (uint64_t)(kc * (W_BYTES >> 4));
+              if (!no_mma) {
+#pragma unroll
+                for (int k = 0; k < KC / 16; k++)
+                  umma_bf16<CG>(d_tmem, dw + (uint64_t)(k * 2), dx + (uint64_t)(k * 2), idesc3, (kc | k) ? 1u : 0u);
+              }
+              umma_commit<CG>(&ctl->empty[s]);
+              if (++s == q.nstage) { s = 0; ph ^= 1u; }
+            }
+            umma_commit<CG>(&ctl->tmem_full[acc]);
+            if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
+          }
+        }
       } else {
         const uint32_t s0 = smem_u32(smem);
         int s = 0;
         uint32_t ph = 0;
-        for (int t = blockIdx.x; t < q.tiles; t += gridDim.x) {
+        for (int t = t_first; t < q.tiles; t += t_step) {
           mbar_wait(&ctl->tmem_empty[acc], acc_ph);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * TP;
@@ -244,8 +314,8 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     // ------------------------------------------------------------------ epilogue (warps 2..9)
     const int quarter = warp & 3;                 // TMEM lanes (= channels) 32*quarter .. +31
     const int half = (warp - 2) >> 2;             // pixel columns 128*half .. +127 of the tile
-    const int ch0 = quarter * 32;
-    const bool active = ch0 < q.ch;
+    const int ch0 = slab * 128 + quarter * 32;     // first output channel of this warp
+    const bool active = quarter * 32 < q.ch;
     const float sc = ((active && p.scale) ? __ldg(p.scale + ch0 + lane) : 1.0f) * p.alpha;
     const float sh = (active && p.shift) ? __ldg(p.shift + ch0 + lane) : 0.0f;
     const uint32_t s_out = smem_u32(epi_smem + (warp - 2) * EPI3_WARP_BYTES), s_res = s_out + 2048;
@@ -298,9 +368,9 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                          : make_uint4(0u, 0u, 0u, 0u);
       }
     };
-    if (use_res && (int)blockIdx.x < q.tiles) load_res(blockIdx.x * TP + half * 128);
+    if (use_res && t_first < q.tiles) load_res(t_first * TP + half * 128);
     uint32_t tc = 0;
-    for (int t = blockIdx.x; t < q.tiles; t += gridDim.x, tc++) {
+    for (int t = t_first; t < q.tiles; t += t_step, tc++) {
       const uint32_t acc = tc & 1u;
       mbar_wait(&ctl->tmem_full[acc], (tc >> 1) & 1u);
       tc_fence_after();
@@ -314,7 +384,10 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         if (g == 3) {                               // all TMEM reads of this warp are done: release the accumulator
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&ctl->tmem_empty[acc])) : "memory");
+          if (lane == 0) {
+            if (CG == 1) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&ctl->tmem_empty[acc])) : "memory");
+            else mbar_arrive_cluster(&ctl->tmem_empty[acc], 0);
+          }
         }
         if (!active || mg >= p.M) continue;         // warp-uniform
         float v[32];
@@ -325,25 +398,51 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
             for (int j = 0; j < 32; j++) v[j] += __uint_as_float((uint32_t)rq[j] << 16);
             if (g < 3) load_res_direct(mg + 32);
-            else if (t + (int)gridDim.x < q.tiles) load_res_direct((t + gridDim.x) * TP + half * 128);
+            else if (t + t_step < q.tiles) load_res_direct((t + t_step) * TP + half * 128);
           }
           if (p.relu) {
 #pragma unroll
             for (int i = 0; i < 32; i++) v[i] = fmaxf(v[i], 0.0f);
           }
           if ((q.dbg & 1) && v[0] != 123456.0f) continue;
+          if (p.c_transposed) {
+            // out[channel][pixel]: the accumulator layout itself; 32 pixels of this lane's channel = 64 contiguous bytes
+            __nv_bfloat16* ot = (__nv_bfloat16*)p.C + (long long)(ch0 + lane) * p.ldc + mg;
+            if (mg + 32 <= p.M) {
+#pragma unroll
+              for (int j4 = 0; j4 < 4; j4++) {
+                uint4 pk;
+                uint32_t* pw = reinterpret_cast<uint32_t*>(&pk);
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                  __nv_bfloat162 hh = __floats2bfloat162_rn(v[j4 * 8 + e * 2], v[j4 * 8 + e * 2 + 1]);
+                  pw[e] = *reinterpret_cast<uint32_t*>(&hh);
+                }
+                reinterpret_cast<uint4*>(ot)[j4] = pk;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; j++)
+                if (mg + j < p.M) ot[j] = __float2bfloat16(v[j]);
+            }
+            continue;
+          }
           // a group of 32 pixels never straddles m_split (host: m_split % 32 == 0 or m_split >= M)
           const int seg = p.m_split >= p.M ? 0 : mg / p.m_split;
-          char* op = (char*)((__nv_bfloat16*)p.C + (long long)(mg - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off + ch0 + lane);
-          uint32_t pitch = (uint32_t)p.ldc * 2u;
-          asm volatile("" : "+r"(pitch));
-          if (mg + 32 <= p.M) {
+          // Sub-word stores pace the LSU (measured: 32 STG.U16 per group made the epilogue the bound of the short-K
+          // layers), so neighbouring lanes swap one value per pixel pair and every lane stores a bf16x2: even lanes
+          // write channels (c, c+1) of pixel j, odd lanes channels (c-1, c) of pixel j+1 -- 16 four-byte stores.
+          const int odd = lane & 1;
+          char* op = (char*)((__nv_bfloat16*)p.C + (long long)(mg - seg * p.m_split + odd) * p.ldc + (long long)seg * p.split_col_off + ch0 + (lane & ~1));
+          uint32_t pitch2 = (uint32_t)p.ldc * 4u;            // two pixel rows, in bytes
+          asm volatile("" : "+r"(pitch2));
+          const int left = p.M - mg - odd;                   // pixel j + odd is stored iff j < left
 #pragma unroll
-            for (int j = 0; j < 32; j++) *(__nv_bfloat16*)(op + (unsigned long long)j * pitch) = __float2bfloat16(v[j]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; j++)
-              if (mg + j < p.M) *(__nv_bfloat16*)(op + (unsigned long long)j * pitch) = __float2bfloat16(v[j]);
+          for (int jj = 0; jj < 16; jj++) {
+            const float mine_keep = odd ? v[2 * jj + 1] : v[2 * jj];
+            const float other = __shfl_xor_sync(0xffffffffu, odd ? v[2 * jj] : v[2 * jj + 1], 1);
+            const __nv_bfloat162 hh = odd ? __floats2bfloat162_rn(other, mine_keep) : __floats2bfloat162_rn(mine_keep, other);
+            if (2 * jj < left) *(__nv_bfloat162*)(op + (unsigned long long)jj * pitch2) = hh;
           }
           continue;
         }
@@ -360,7 +459,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           }
           // prefetch the residual of the next 32 pixels (next group, or the first group of the next tile)
           if (g < 3) load_res(mg + 32);
-          else if (t + (int)gridDim.x < q.tiles) load_res((t + gridDim.x) * TP + half * 128);
+          else if (t + t_step < q.tiles) load_res((t + t_step) * TP + half * 128);
         }
         if (p.relu) {
 #pragma unroll
@@ -392,9 +491,11 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    if (CG == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
   }
 }
 
@@ -417,7 +518,16 @@ int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force)
   if (!force && !tc3_enabled()) return FPB_ERR_UNSUPPORTED;
   const int ncols = p.n_valid > 0 ? p.n_valid : p.N;
   if (p.batch != 1 || p.K % KC != 0 || p.Cin % KC != 0 || p.pix_pitch % 8 != 0 || p.ldw % 8 != 0) return FPB_ERR_UNSUPPORTED;
-  if ((ncols != 64 && ncols != 128) || p.N != ncols || !p.out_bf16 || p.pe || p.row_shift) return FPB_ERR_UNSUPPORTED;
+  const bool plain0 = !p.halo && p.KH == 1 && p.KW == 1 && p.stride == 1 && p.pad == 0 && p.pad_w == 0 && p.Ho == 1 && p.Wo == 1;
+  // wide plain GEMMs with a short K (the transformer linears, K = 512): one 128-channel weight slab stays resident
+  // in shared memory per CTA and only the activations stream (measured: these layers are bound by the operand
+  // stream from L2, ~57 B/clk/SM, and 2/3 of that stream were weights)
+  static int wres_env = -1;
+  if (wres_env < 0) { const char* e = getenv("FPB_TC3_WRES"); wres_env = e ? atoi(e) : 1; }
+  const bool wres = (wres_env || force) && plain0 && ncols % 128 == 0 && ncols >= 256 && p.N == ncols && p.K <= 512 && !p.row_remap && p.m_split >= p.M;
+  if (!wres && ((ncols != 64 && ncols != 128) || p.N != ncols)) return FPB_ERR_UNSUPPORTED;
+  if (!p.out_bf16 || p.pe || p.row_shift) return FPB_ERR_UNSUPPORTED;
+  if (p.c_transposed && (p.residual || p.halo || p.row_remap || p.m_split < p.M)) return FPB_ERR_UNSUPPORTED;
   if (p.ldc % 8 != 0 || p.split_col_off % 8 != 0 || (p.residual && p.ldr % 8 != 0)) return FPB_ERR_UNSUPPORTED;
   if (p.m_split < p.M && p.m_split % 32 != 0) return FPB_ERR_UNSUPPORTED;
   if (((uintptr_t)p.A | (uintptr_t)p.W | (uintptr_t)p.C | (uintptr_t)p.residual) & 15) return FPB_ERR_UNSUPPORTED;
@@ -425,9 +535,16 @@ int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force)
   if (!plain && (p.pad > 127 || p.KH > 127)) return FPB_ERR_UNSUPPORTED;
   Tc3Params q;
   q.p = p;
-  q.mode = p.halo ? 2 : (plain ? 0 : 1);
+  q.mode = p.halo ? 2 : (wres ? 3 : (plain ? 0 : 1));
   q.lower_w = -p.pad_w; q.lower_h = -p.pad;
-  q.ch = ncols;
+  q.ch = wres ? 128 : ncols;
+  q.n_slabs = wres ? ncols / 128 : 1;
+  // pairs (cta_group::2) whenever the slabs pair up; FPB_TC3_CG=1 forces single CTAs
+  static int cg_env = -1;
+  if (cg_env < 0) { const char* e = getenv("FPB_TC3_CG"); cg_env = e ? atoi(e) : 2; }
+  const int CGn = (wres && q.n_slabs % 2 == 0 && cg_env == 2) ? 2 : 1;
+  q.nstage = wres ? (RING_BYTES + EPI3_BYTES - (p.K / KC) * W_BYTES) / (PIX_BYTES / CGn) : NSTAGE3;
+  if (q.nstage > 8) q.nstage = 8;
   { const char* e = getenv("FPB_TC2_DBG"); q.dbg = e ? atoi(e) : 0; }
   q.Wp = p.img_w + 1; q.IS = (p.img_h + 1) * q.Wp; q.hrows = TP + 2 * q.Wp + 2;
   if (p.halo || p.row_remap) {
@@ -443,33 +560,44 @@ int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force)
     rc = fpb_tiled_map_bf16(p.A, p.M, p.Cin, p.pix_pitch, TP, &mA, &num_sms);
     if (!rc) rc = fpb_tiled_map_bf16(p.A, p.M, p.Cin, p.pix_pitch, q.hrows - TP, &mA2, &num_sms);
   } else if (plain) {
-    rc = fpb_tiled_map_bf16(p.A, p.M, p.K, p.pix_pitch, TP, &mA, &num_sms);
+    rc = fpb_tiled_map_bf16(p.A, p.M, p.K, p.pix_pitch, TP / CGn, &mA, &num_sms);
     mA2 = mA;
   } else {
     rc = fpb_im2col_map_bf16(p, fpb_cdiv(p.M, p.Ho * p.Wo), &mA);
     mA2 = mA;
   }
   if (rc) return rc;
-  rc = fpb_tiled_map_bf16(p.W, p.N, p.K, p.ldw, ncols, &mW, &num_sms);
+  rc = fpb_tiled_map_bf16(p.W, p.N, p.K, p.ldw, wres ? 128 : ncols, &mW, &num_sms);
   if (rc) return rc;
   static bool configured = false;
   if (!configured) {
-    FPB_CUDA(cudaFuncSetAttribute(tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3));
+    FPB_CUDA(cudaFuncSetAttribute(tc3_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3));
+    FPB_CUDA(cudaFuncSetAttribute(tc3_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3));
     configured = true;
   }
-  const int grid = q.tiles < num_sms ? q.tiles : num_sms;
+  int grid = q.tiles < num_sms ? q.tiles : num_sms;
+  if (wres) {                                       // CTAs (pairs) per slab (pair) x number of slab groups
+    const int groups = q.n_slabs / CGn;
+    int per = (num_sms / CGn) / groups;
+    if (per > q.tiles) per = q.tiles;
+    if (per < 1) return FPB_ERR_UNSUPPORTED;
+    grid = per * groups * CGn;
+  }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid, 1, 1);
   cfg.blockDim = dim3(NT3, 1, 1);
   cfg.dynamicSmemBytes = SMEM3;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CGn; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = fpb_pdl_enabled() ? 1 : 0;
-  FPB_CUDA(cudaLaunchKernelEx(&cfg, tc3_kernel, mA, mA2, mW, q));
+  cfg.numAttrs = fpb_pdl_enabled() ? 2 : 1;
+  if (CGn == 2) FPB_CUDA(cudaLaunchKernelEx(&cfg, tc3_kernel<2>, mA, mA2, mW, q));
+  else FPB_CUDA(cudaLaunchKernelEx(&cfg, tc3_kernel<1>, mA, mA2, mW, q));
   fpb_count_launch();
   return FPB_OK;
 }

@@ -69,8 +69,8 @@ CASES = [
                                           (1, 10, 64, 64, 3, 1, 1)])
 def test_igemm_matches_torch(prec, case):
   nimg, H, Cin, Cout, k, stride, pad = case
-  if prec == 4 and Cout not in (64, 128):
-    pytest.skip('operand-swapped kernel covers 64 / 128 output channels')
+  if prec == 4 and Cout not in (64, 128) and not (k == 1 and H == 1 and Cout % 128 == 0 and Cin <= 512):
+    pytest.skip('operand-swapped kernel: 64 / 128 output channels, or plain GEMMs with K <= 512 (weight-resident mode)')
   g = torch.Generator(device='cuda').manual_seed(hash(case) % 1000)
   x = torch.randn(nimg, H, H, Cin, device='cuda', generator=g)
   w = torch.randn(Cout, Cin, k, k, device='cuda', generator=g) / (Cin * k * k) ** 0.5
@@ -87,6 +87,27 @@ def test_igemm_matches_torch(prec, case):
   got2 = _igemm(prec, x, w, stride, pad, out_bf16=ob)             # no epilogue extras
   ref2 = _ref_conv(x, w, stride, pad, bf16_ops=bool(prec))
   assert (got2 - ref2).abs().max().item() < tol
+
+
+@pytest.mark.parametrize('shape', [(1000, 512, 512), (72, 512, 1024), (4096, 256, 256)])
+def test_weight_resident_gemm_transposed_output(shape):
+  """V^T projection form: out[n][m] = sum_k x[m][k] w[n][k] + b[n], stored channel-major (net_tc3.cu mode 3)."""
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  M, K, N = shape
+  g = torch.Generator(device='cuda').manual_seed(M)
+  x = torch.randn(M, K, device='cuda', generator=g).bfloat16()
+  w = (torch.randn(N, K, device='cuda', generator=g) / K ** 0.5).bfloat16()
+  b = torch.randn(N, device='cuda', generator=g)
+  Mp = (M + 7) // 8 * 8                                   # row pitch of the transposed output (multiple of 8)
+  out = torch.full((N, Mp), 7.0, device='cuda', dtype=torch.bfloat16)
+  # ldc = M inside the debug entry: use an M that is already a multiple of 8
+  assert Mp == M or True
+  xs = x[:Mp] if Mp == M else x
+  check(lib().fpb_debug_igemm_ex(4, ptr(xs), ptr(w), ptr(out), M, N, K, 1, 1, K, 1, 1, 1, 1, 1, 0, 0, 0, 0, None, ptr(b), None, 0, 2,
+                                 stream()))
+  torch.cuda.synchronize()
+  ref = (x.float() @ w.float().t() + b).t()
+  assert (out[:, :M].float() - ref).abs().max().item() < 3e-2
 
 
 @pytest.mark.parametrize('prec', [0, 1, 2, 3, 4])

@@ -45,7 +45,7 @@ def main():
     r = torch.randn(M, Cout, device='cuda').bfloat16() if res else None
     sc = torch.ones(Cout, device='cuda'); sh = torch.zeros(Cout, device='cuda')
     for mode in [int(m) for m in a.modes.split(',')]:
-      if mode == 4 and Cout > 128:
+      if mode == 4 and Cout > 128 and not (k == 1 and K <= 512 and Cout % 128 == 0):
         continue
       def launch():
         check(lib().fpb_debug_igemm(mode, ptr(x), ptr(w), ptr(out), M, Cout, K, H, H, Cin, Ho, Ho, k, k, stride, pad, ptr(sc),
