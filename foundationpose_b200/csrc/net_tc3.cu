@@ -123,6 +123,11 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
   pdl_wait();
+  // FPB_TC2_DBG & 2048: CTA 0 records clock64 stamps into the output buffer (MMA thread -> slots 64.., warp 2 -> 128..)
+  int n_st = 0;
+  auto stamp = [&](int base) {
+    if ((q.dbg & 2048) && blockIdx.x == 0 && lane == 0 && n_st < 64) reinterpret_cast<long long*>(p.C)[base + n_st++] = clock64();
+  };
   const uint32_t w_tx = (q.dbg & 256) ? 0u : (uint32_t)(q.ch * 128);
   const bool no_a = q.dbg & 128, no_w = q.dbg & 256;
 
@@ -267,6 +272,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           for (int t = t_first; t < q.tiles; t += t_step) {
             mbar_wait(&ctl->tmem_empty[acc], acc_ph);
             tc_fence_after();
+            stamp(64);
             const uint32_t d_tmem = tmem_base + acc * TP;
             for (int kc = 0; kc < nk; kc++) {
               mbar_wait(&ctl->full[s], ph);
@@ -280,6 +286,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               umma_commit<CG>(&ctl->empty[s]);
               if (++s == q.nstage) { s = 0; ph ^= 1u; }
             }
+            stamp(64);
             umma_commit<CG>(&ctl->tmem_full[acc]);
             if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
           }
@@ -372,8 +379,10 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     uint32_t tc = 0;
     for (int t = t_first; t < q.tiles; t += t_step, tc++) {
       const uint32_t acc = tc & 1u;
+      if (warp == 2) stamp(128);
       mbar_wait(&ctl->tmem_full[acc], (tc >> 1) & 1u);
       tc_fence_after();
+      if (warp == 2) stamp(128);
       const int mh = t * TP + half * 128;          // first pixel of this warp's columns
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * TP + (uint32_t)(half * 128);
 #pragma unroll 1
@@ -381,6 +390,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         const int mg = mh + g * 32;
         uint32_t r[32];
         if (active) tmem_ld32(t_addr + (uint32_t)(g * 32), r);
+        if (warp == 2) stamp(128);                   // TMEM load of this group returned
         if (g == 3) {                               // all TMEM reads of this warp are done: release the accumulator
           tc_fence_before();
           __syncwarp();
@@ -442,7 +452,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             const float mine_keep = odd ? v[2 * jj + 1] : v[2 * jj];
             const float other = __shfl_xor_sync(0xffffffffu, odd ? v[2 * jj] : v[2 * jj + 1], 1);
             const __nv_bfloat162 hh = odd ? __floats2bfloat162_rn(other, mine_keep) : __floats2bfloat162_rn(mine_keep, other);
-            if (2 * jj < left) *(__nv_bfloat162*)(op + (unsigned long long)jj * pitch2) = hh;
+            if (2 * jj < left && !(q.dbg & 2048)) *(__nv_bfloat162*)(op + (unsigned long long)jj * pitch2) = hh;
           }
           continue;
         }

@@ -45,13 +45,17 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
 {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-// arrive on the barrier at the same smem offset in CTA `cta` of the cluster
+// arrive on the barrier at the same smem offset in CTA `cta` of the cluster.  RELAXED on purpose: the only user hands a
+// TMEM accumulator buffer back to the MMA issuer, which is ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync
+// on this side and tcgen05.fence::after_thread_sync on the other.  The default .release.cluster form also waits for
+// every earlier GLOBAL store of the thread to become visible cluster-wide -- measured with clock stamps: ~2200 cycles per
+// tile in the epilogue of the cta_group::2 kernels, which made the short-K layers epilogue-bound.
 __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta)
 {
   asm volatile(
       "{\n\t.reg .b32 ra;\n\t"
       "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
       "r"(cta)
       : "memory");
 }
