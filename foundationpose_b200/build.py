@@ -25,6 +25,7 @@ UNITS = [
   ('net_tc.cu', []),
   ('net_tc2.cu', []),
   ('net_tc3.cu', []),
+  ('net_stem.cu', []),
   ('net_attn.cu', []),
   ('net.cu', []),
 ]

@@ -35,6 +35,7 @@ struct fpb_net {
   size_t n_floats;
   float* w32;
   __nv_bfloat16* w16;
+  __nv_bfloat16* w_stem;   // stem weights stacked for net_stem.cu ([9][128][64], bf16 mode only)
   Conv conv[15];
   size_t pe;
   EncLayer head[2];   // refine: trans, rot
@@ -196,7 +197,11 @@ int run_linear(const Ctx& c, const Lin& l, const void* in, long long rows, void*
 // both encoders: AB [2n,160,160,8] -> tokens (+pe) in w.d0 [n*400, 512]
 int run_encoders(const Ctx& c, const void* AB, int n, Ws& w)
 {
-  RET(run_conv(c, 0, AB, 2 * n, w.c0, nullptr, 1, false, 0, 0, 0));
+  int rc0 = FPB_ERR_UNSUPPORTED;
+  if (c.bf && c.net->w_stem)      // dedicated stem kernel: input rows loaded once, two output rows stacked in the MMA M dimension
+    rc0 = stem_conv(AB, 2 * n, c.net->w_stem, c.F(c.net->conv[0].scale), c.F(c.net->conv[0].shift), 1, w.c0, c.st, 0);
+  if (rc0 == FPB_ERR_UNSUPPORTED) rc0 = run_conv(c, 0, AB, 2 * n, w.c0, nullptr, 1, false, 0, 0, 0);
+  RET(rc0);
   // optional (FPB_HALO=1): 3x3 stride-1 blocks in the zero-bordered position layout (one TMA box per 64 channels feeds all
   // 9 taps); kept for the record with its tests -- per-stage pipeline overhead makes it slower than the im2col path today
   const int hp = (c.bf && use_halo()) ? 1 : 0;
@@ -306,6 +311,9 @@ FPB_EXPORT int fpb_net_create(fpb_net** out, int kind, int precision, const void
     FPB_CUDA(cudaMalloc((void**)&n->w16, n->n_floats * sizeof(__nv_bfloat16)));
     int rc = f32_to_bf16(n->w32, n->w16, (long long)n->n_floats, st);
     if (rc) return rc;
+    FPB_CUDA(cudaMalloc((void**)&n->w_stem, (size_t)9 * 128 * 64 * sizeof(__nv_bfloat16)));
+    rc = stem_pack_weights(n->w32 + n->conv[0].w, 0, n->w_stem, st);
+    if (rc) return rc;
   }
   FPB_CUDA(cudaStreamSynchronize(st));
   *out = n;
@@ -317,6 +325,7 @@ FPB_EXPORT int fpb_net_destroy(fpb_net* n)
   if (!n) return FPB_OK;
   cudaFree(n->w32);
   cudaFree(n->w16);
+  cudaFree(n->w_stem);
   delete n;
   return FPB_OK;
 }
@@ -468,6 +477,19 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
       const int rc3 = tc3_gemm(p, st, 1);
       if (rc3 == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_igemm: shape not supported by the operand-swapped kernel");
       return rc3;
+    }
+    case 5: {                                      // dedicated stem kernel; W = packed stem weights [64][7][8][8] bf16
+      if (!(Hin == 160 && row_pitch == 168 && pix_pitch == 8 && K == 448 && N == 64 && Ho == 80 && M % 6400 == 0 && out_bf16 == 1 && !residual)) {
+        fpb_set_error("fpb_debug_igemm: mode 5 is the 7x7 stem on the row-padded input only");
+        return FPB_ERR_ARG;
+      }
+      void* ws = nullptr;
+      FPB_CUDA(cudaMalloc(&ws, (size_t)9 * 128 * 64 * 2));
+      int rc5 = stem_pack_weights(W, 1, ws, st);
+      if (!rc5) rc5 = stem_conv(A, M / 6400, ws, scale, shift, relu, C, st, 1);
+      cudaStreamSynchronize(st);
+      cudaFree(ws);
+      return rc5;
     }
     default: fpb_set_error("fpb_debug_igemm: unknown mode %d", mode); return FPB_ERR_ARG;
   }

@@ -65,6 +65,10 @@ int ref_gemm(const GemmProblem& p, cudaStream_t st);   // fp32 SIMT
 int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 accumulate (cp.async producers)
 int tc2_gemm(const GemmProblem& p, cudaStream_t st);   // bf16 tcgen05, persistent TMA kernel; FPB_ERR_UNSUPPORTED -> use tc_gemm
 int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force);   // bf16 tcgen05, operand-swapped (Cout 64 / 128); FPB_ERR_UNSUPPORTED -> tc2_gemm
+// dedicated 7x7 stride-2 stem kernel (net_stem.cu): row-padded input [nimg,160,168,8] bf16 -> [nimg*6400,64] bf16
+int stem_pack_weights(const void* w_packed, int is_bf16, void* w_stacked, cudaStream_t st);   // [64][7][8][8] -> [9][128][64] bf16
+int stem_conv(const void* in, int nimg, const void* w_stacked, const float* scale, const float* shift, int relu, void* out,
+              cudaStream_t st, int force);
 void tc2_force_cta_group(int cg);                      // tests: 0 = default, 1 / 2 = force
 
 int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms);

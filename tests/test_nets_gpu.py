@@ -110,7 +110,7 @@ def test_weight_resident_gemm_transposed_output(shape):
   assert (out[:, :M].float() - ref).abs().max().item() < 3e-2
 
 
-@pytest.mark.parametrize('prec', [0, 1, 2, 3, 4])
+@pytest.mark.parametrize('prec', [0, 1, 2, 3, 4, 5])
 def test_first_conv_7x7_padded_layout(prec):
   """7x7 stride-2 stem on the row-padded 8-channel input [n,160,168,8], evaluated as a 7x1 convolution over 161
   overlapping 64-channel "wide pixels" (csrc/net.cu kConvs[0]); weights [64][7][8 taps][8 ch]."""
@@ -123,13 +123,37 @@ def test_first_conv_7x7_padded_layout(prec):
   dt = torch.bfloat16 if prec else torch.float
   A = x8.to(dt).contiguous()
   W = w8.permute(0, 2, 3, 1).reshape(64, -1).to(dt).contiguous()
-  ob = int(prec == 4)
+  ob = int(prec >= 4)          # 4: operand-swapped im2col kernel, 5: dedicated stem kernel (csrc/net_stem.cu)
   C = torch.empty((3 * 80 * 80, 64), dtype=torch.bfloat16 if ob else torch.float, device='cuda')
   check(lib().fpb_debug_igemm_ex(prec, ptr(A), ptr(W), ptr(C), 3 * 6400, 64, 448, 160, 161, 64, 80, 80, 7, 1, 2, 3, -1, 168, 8,
                                  None, None, None, 0, ob, stream()))
   torch.cuda.synchronize()
   ref = _ref_conv(x6, w6, 2, 3, bf16_ops=bool(prec))
   assert (C.float().reshape(3, 80, 80, 64) - ref).abs().max().item() < (2e-2 if ob else 2e-3 if prec else 2e-4)
+
+
+@pytest.mark.parametrize('nimg', [1, 7, 300])
+def test_stem_kernel_matches_im2col_kernel(nimg):
+  """Dedicated stem kernel (plane loads, two output rows stacked in M) against the im2col kernel on the same bf16
+  operands, with folded BatchNorm + ReLU; 300 images = more tiles than SMs (persistent loop, both accumulators)."""
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  g = torch.Generator(device='cuda').manual_seed(11 + nimg)
+  A = torch.zeros(nimg, 160, 168, 8, device='cuda', dtype=torch.bfloat16)
+  A[:, :, 4:164, :6] = torch.randn(nimg, 160, 160, 6, device='cuda', generator=g).bfloat16()
+  w8 = torch.zeros(64, 7, 8, 8, device='cuda'); w8[:, :, :7, :6] = torch.randn(64, 7, 7, 6, device='cuda', generator=g) / 17
+  W = w8.reshape(64, -1).bfloat16().contiguous()
+  sc = torch.rand(64, device='cuda', generator=g) + 0.5
+  sh = torch.randn(64, device='cuda', generator=g) * 0.3
+  outs = []
+  for mode in (4, 5):
+    C = torch.full((nimg * 6400, 64), float('nan'), dtype=torch.bfloat16, device='cuda')
+    check(lib().fpb_debug_igemm_ex(mode, ptr(A), ptr(W), ptr(C), nimg * 6400, 64, 448, 160, 161, 64, 80, 80, 7, 1, 2, 3, -1, 168, 8,
+                                   ptr(sc), ptr(sh), None, 1, 1, stream()))
+    torch.cuda.synchronize()
+    outs.append(C.float())
+  assert torch.isfinite(outs[1]).all()
+  assert ((outs[0] - outs[1]).abs() <= outs[0].abs() * 2 ** -7 + 1e-3).all()       # at most one bf16 ulp
+  assert (outs[0] != outs[1]).float().mean().item() < 0.02     # same products, fp32 accumulation: only rounding-boundary flips
 
 
 def _inputs(n, seed=0):

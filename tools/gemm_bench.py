@@ -80,7 +80,7 @@ def stem(a):
   out = torch.empty(n * 6400, 64, device='cuda', dtype=torch.bfloat16)
   sc = torch.ones(64, device='cuda'); sh = torch.zeros(64, device='cuda')
   for mode in [int(m) for m in a.modes.split(',')]:
-    def launch():
+    def launch():   # mode 5 (dedicated stem kernel) includes the debug entry's weight repack + cudaMalloc: use tools/stem_bench.py
       check(lib().fpb_debug_igemm_ex(mode, ptr(x), ptr(w), ptr(out), n * 6400, 64, 448, 160, 161, 64, 80, 80, 7, 1, 2, 3, -1, 168, 8,
                                      ptr(sc), ptr(sh), None, 1, 1, stream()))
     for _ in range(2):
