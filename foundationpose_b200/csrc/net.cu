@@ -483,12 +483,10 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
         fpb_set_error("fpb_debug_igemm: mode 5 is the 7x7 stem on the row-padded input only");
         return FPB_ERR_ARG;
       }
-      void* ws = nullptr;
-      FPB_CUDA(cudaMalloc(&ws, (size_t)9 * 128 * 64 * 2));
+      static void* ws = nullptr;                   // debug entry only: never freed, re-packed on every call
+      if (!ws) FPB_CUDA(cudaMalloc(&ws, (size_t)9 * 128 * 64 * 2));
       int rc5 = stem_pack_weights(W, 1, ws, st);
       if (!rc5) rc5 = stem_conv(A, M / 6400, ws, scale, shift, relu, C, st, 1);
-      cudaStreamSynchronize(st);
-      cudaFree(ws);
       return rc5;
     }
     default: fpb_set_error("fpb_debug_igemm: unknown mode %d", mode); return FPB_ERR_ARG;

@@ -32,8 +32,7 @@ constexpr int ST_PAIRS = ST_PITCH / 2;             // 84 pixel pairs per input r
 constexpr int ST_PROWS = ST_IMG / 4;               // 40 rows per plane = 40 double output rows
 constexpr int ST_TROWS = 3;                        // double rows per tile
 constexpr int ST_TILES_PER_IMG = (ST_PROWS + ST_TROWS - 1) / ST_TROWS;   // 14
-constexpr int ST_BOX_ROWS = 5;                     // plane rows per load: r0-1 .. r0+3 (plane 0: r0 .. r0+4)
-constexpr int ST_BOX_BYTES = ST_BOX_ROWS * ST_PAIRS * 32;   // 13440
+constexpr int ST_BOX_BYTES = 5 * ST_PAIRS * 32;    // largest box: 5 plane rows (plane 1), the others 4
 constexpr int ST_SLOT = 13824;                     // >= (2*84 + 3 + 256) * 32 = 13664, multiple of 256
 constexpr int ST_NSLOT = 6;
 constexpr int ST_WCHUNK = 128 * 128;               // one kernel row ky': 128 stacked rows x 64 K elements
@@ -56,12 +55,15 @@ struct StemParams {
   const float* shift;
   __nv_bfloat16* out;      // [nimg][80][80][64]
   int nimg, relu;
+  int dbg;                 // FPB_STEM_DBG bits: 1 no stores, 8 no MMA, 128 no input loads (timing experiments)
 };
 
-// planes in issue order; per plane the kernel rows ky' it serves and their row shift relative to the first box row
-__constant__ int c_plane_n[4] = {2, 3, 2, 2};
-__constant__ int c_plane_ky[4][3] = {{3, 7, 0}, {0, 4, 8}, {1, 5, 0}, {2, 6, 0}};
-__constant__ int c_plane_first[4] = {0, -1, -1, -1};   // first box row relative to the tile's first double row
+// plane pl = input rows with (row mod 4) == pl; it serves the kernel rows ky' = ((pl + 3) & 3) + 4 i, i < plane_n(pl), whose
+// operand starts i plane rows below the first row of the box; the box starts plane_first(pl) rows from the tile's first
+// double row and has plane_n(pl) + 2 rows
+__device__ __forceinline__ constexpr int plane_n(int pl) { return pl == 1 ? 3 : 2; }
+__device__ __forceinline__ constexpr int plane_ky(int pl, int i) { return ((pl + 3) & 3) + 4 * i; }
+__device__ __forceinline__ constexpr int plane_first(int pl) { return pl == 0 ? 0 : -1; }
 
 // K-major SWIZZLE_32B descriptor: 32-byte rows, 8-row groups 256 B apart
 __device__ __forceinline__ uint64_t make_desc_sw32(uint32_t saddr)
@@ -84,7 +86,8 @@ __device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* map
 }
 
 __global__ void __launch_bounds__(ST_NT, 1)
-stem_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapW, const StemParams q)
+stem_kernel(const __grid_constant__ CUtensorMap mapX4, const __grid_constant__ CUtensorMap mapX5, const __grid_constant__ CUtensorMap mapW,
+            const StemParams q)
 {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -99,7 +102,8 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CU
     for (int a = 0; a < 2; a++) { mbar_init(&ctl->tmem_full[a], 1); mbar_init(&ctl->tmem_empty[a], 8); }
     mbar_init(&ctl->wfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX4) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX5) : "memory");
     // the weights are constants of the network: fetch them while the predecessor kernel is still draining
     mbar_arrive_expect_tx(&ctl->wfull, (uint32_t)ST_WBYTES);
     for (int k = 0; k < 9; k++) tma_load_2d<1>(smem_u32(smem + k * ST_WCHUNK), &mapW, smem_u32(&ctl->wfull), 0, k * 128);
@@ -121,10 +125,13 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CU
       uint32_t ph = 1;                                     // waits on empty with inverted parity
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int img = t / ST_TILES_PER_IMG, r0 = (t - img * ST_TILES_PER_IMG) * ST_TROWS;
+#pragma unroll
         for (int pl = 0; pl < 4; pl++) {
           mbar_wait(&ctl->empty[s], ph);
-          mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)ST_BOX_BYTES);
-          tma_load_5d(smem_u32(ring + s * ST_SLOT), &mapX, smem_u32(&ctl->full[s]), 0, 0, pl, r0 + c_plane_first[pl], img);
+          const uint32_t bytes = (uint32_t)((plane_n(pl) + 2) * ST_PAIRS * 32);
+          mbar_arrive_expect_tx(&ctl->full[s], (q.dbg & 128) ? 0u : bytes);
+          if (!(q.dbg & 128))
+            tma_load_5d(smem_u32(ring + s * ST_SLOT), pl == 1 ? &mapX5 : &mapX4, smem_u32(&ctl->full[s]), 0, 0, pl, r0 + plane_first(pl), img);
           if (++s == ST_NSLOT) { s = 0; ph ^= 1u; }
         }
       }
@@ -141,18 +148,19 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CU
         mbar_wait(&ctl->tmem_empty[acc], acc_ph);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
-        uint32_t first = 0;
+#pragma unroll
         for (int pl = 0; pl < 4; pl++) {
           mbar_wait(&ctl->full[s], ph);
           tc_fence_after();
           const uint32_t sb = sR + s * ST_SLOT;
-          for (int i = 0; i < c_plane_n[pl]; i++) {
-            const uint64_t dw = make_desc(sW + c_plane_ky[pl][i] * ST_WCHUNK);
-            const uint32_t bx = sb + (uint32_t)(i * ST_PAIRS * 32);
+          if (!(q.dbg & 8)) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-              umma_bf16<1>(d_tmem, dw + (uint64_t)(k * 2), make_desc_sw32(bx + k * 32), idesc, first);
-              first = 1u;
+            for (int i = 0; i < plane_n(pl); i++) {
+              const uint64_t dw = make_desc(sW + plane_ky(pl, i) * ST_WCHUNK);
+              const uint64_t db = make_desc_sw32(sb + (uint32_t)(i * ST_PAIRS * 32));
+#pragma unroll
+              for (int k = 0; k < 4; k++)
+                umma_bf16<1>(d_tmem, dw + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (pl | i | k) ? 1u : 0u);
             }
           }
           umma_commit<1>(&ctl->empty[s]);
@@ -171,6 +179,7 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CU
     const float sc = q.scale ? __ldg(q.scale + ch0 + lane) : 1.0f;
     const float sh = q.shift ? __ldg(q.shift + ch0 + lane) : 0.0f;
     const int odd = lane & 1;
+    const float lo = q.relu ? 0.0f : -INFINITY;
     uint32_t tc = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, tc++) {
       const uint32_t acc = tc & 1u;
@@ -190,24 +199,38 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CU
         }
         float v[32];
 #pragma unroll
-        for (int i = 0; i < 32; i++) {
-          v[i] = fmaf(__uint_as_float(r[i]), sc, sh);
-          if (q.relu) v[i] = fmaxf(v[i], 0.0f);
-        }
+        for (int i = 0; i < 32; i++) v[i] = fmaxf(fmaf(__uint_as_float(r[i]), sc, sh), lo);
         // flat pixel n = 84 * (double row) + ox; neighbouring lanes swap one value per pixel pair so that every lane
         // stores a bf16x2: even lanes channels (c, c+1) of pixel 2jj, odd lanes channels (c-1, c) of pixel 2jj+1
-        const int n0 = half * 128 + g * 32;
-        const int rl0 = n0 / ST_PAIRS, ox0 = n0 - rl0 * ST_PAIRS;
+        uint32_t hh[16];
 #pragma unroll
         for (int jj = 0; jj < 16; jj++) {
           const float mine_keep = odd ? v[2 * jj + 1] : v[2 * jj];
           const float other = __shfl_xor_sync(0xffffffffu, odd ? v[2 * jj] : v[2 * jj + 1], 1);
-          const __nv_bfloat162 hh = odd ? __floats2bfloat162_rn(other, mine_keep) : __floats2bfloat162_rn(mine_keep, other);
-          int ox = ox0 + 2 * jj + odd, rl = rl0;
-          if (ox >= ST_PAIRS) { ox -= ST_PAIRS; rl++; }
-          const int dr = r0 + rl;
-          if (ox < ST_OUT && rl < ST_TROWS && dr < ST_PROWS)
-            *(__nv_bfloat162*)(obase + ((2 * dr + par) * ST_OUT + ox) * ST_CH) = hh;
+          const __nv_bfloat162 h2 = odd ? __floats2bfloat162_rn(other, mine_keep) : __floats2bfloat162_rn(mine_keep, other);
+          hh[jj] = *reinterpret_cast<const uint32_t*>(&h2);
+        }
+        // The 32 pixels of a group cross at most one row end.  Pixel 2jj + odd of this lane sits at ox = oxm + 2jj: it is
+        // stored through p0 while ox < 80 (jj < ja), skipped for the 4 junk columns, and stored through p1 (next double
+        // row: + 160 - 84 pixels) from ox >= 84 on (jj >= jb).  Branch-free: two predicated stores with immediate offsets
+        // (measured: per-pixel index arithmetic + divergent branches made this epilogue the bound of the kernel).
+        const int n0 = half * 128 + g * 32;
+        const int rl0 = n0 / ST_PAIRS, oxm = n0 - rl0 * ST_PAIRS + odd;
+        const bool va = r0 + rl0 < ST_PROWS && !(q.dbg & 1);
+        const bool vb = rl0 + 1 < ST_TROWS && r0 + rl0 + 1 < ST_PROWS && !(q.dbg & 1);
+        const int ja = va ? (ST_OUT - oxm + 1) >> 1 : 0;                   // first jj with ox >= 80 (may exceed 16)
+        const int jb = vb ? (ST_PAIRS - oxm + 1) >> 1 : 16;                // first jj with ox >= 84
+        char* p0 = (char*)(obase + ((2 * (r0 + rl0) + par) * ST_OUT + oxm) * ST_CH);
+        char* p1 = p0 + (2 * ST_OUT - ST_PAIRS) * ST_CH * 2;
+#pragma unroll
+        for (int jj = 0; jj < 16; jj++) {
+          asm volatile(
+              "{\n\t.reg .pred pa, pb;\n\t"
+              "setp.gt.s32 pa, %3, %5;\n\t"
+              "setp.le.s32 pb, %4, %5;\n\t"
+              "@pa st.global.b32 [%0], %2;\n\t"
+              "@pb st.global.b32 [%1], %2;\n\t}" ::"l"(p0 + jj * (2 * ST_CH * 2)), "l"(p1 + jj * (2 * ST_CH * 2)), "r"(hh[jj]), "r"(ja), "r"(jb), "r"(jj)
+              : "memory");
         }
       }
     }
@@ -282,27 +305,28 @@ int stem_conv(const void* in, int nimg, const void* w_stacked, const float* scal
     cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
     FPB_CUDA(cudaFuncSetAttribute(stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
   }
-  CUtensorMap mX, mW;
-  auto key = std::make_pair(in, nimg);
-  auto it = g_xmaps.find(key);
-  if (it != g_xmaps.end()) mX = it->second;
-  else {
+  CUtensorMap mX[2], mW;                                   // boxes of 4 and 5 plane rows
+  for (int bi = 0; bi < 2; bi++) {
+    auto key = std::make_pair(in, nimg * 2 + bi);
+    auto it = g_xmaps.find(key);
+    if (it != g_xmaps.end()) { mX[bi] = it->second; continue; }
     const cuuint64_t row_b = (cuuint64_t)ST_PITCH * ST_C * 2;                  // 2688 B per input row
     cuuint64_t dims[5] = {16, (cuuint64_t)ST_PAIRS, 4, (cuuint64_t)ST_PROWS, (cuuint64_t)nimg};
     cuuint64_t strides[4] = {32, row_b, 4 * row_b, (cuuint64_t)ST_IMG * row_b};
-    cuuint32_t box[5] = {16, (cuuint32_t)ST_PAIRS, 1, (cuuint32_t)ST_BOX_ROWS, 1};
+    cuuint32_t box[5] = {16, (cuuint32_t)ST_PAIRS, 1, (cuuint32_t)(4 + bi), 1};
     cuuint32_t es[5] = {1, 1, 1, 1, 1};
-    CUresult r = g_encode(&mX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, (void*)in, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    CUresult r = g_encode(&mX[bi], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, (void*)in, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                           CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { fpb_set_error("stem_conv: cuTensorMapEncodeTiled (input) failed (%d)", (int)r); return FPB_ERR_CUDA; }
     if (g_xmaps.size() > 256) g_xmaps.clear();
-    g_xmaps[key] = mX;
+    g_xmaps[key] = mX[bi];
   }
   int sms = 0;
   int rc = fpb_tiled_map_bf16(w_stacked, 9 * 128, 64, 64, 128, &mW, &sms);
   if (rc) return rc;
   StemParams q;
   q.scale = scale; q.shift = shift; q.out = (__nv_bfloat16*)out; q.nimg = nimg; q.relu = relu;
+  { const char* e = getenv("FPB_STEM_DBG"); q.dbg = e ? atoi(e) : 0; }
   const int tiles = nimg * ST_TILES_PER_IMG;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -314,8 +338,8 @@ int stem_conv(const void* in, int nimg, const void* w_stacked, const float* scal
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = fpb_pdl_enabled() ? 1 : 0;
-  FPB_CUDA(cudaLaunchKernelEx(&cfg, stem_kernel, mX, mW, q));
+  cfg.numAttrs = (fpb_pdl_enabled() && !force) ? 1 : 0;   // force = debug entry: the weights were packed by the previous kernel
+  FPB_CUDA(cudaLaunchKernelEx(&cfg, stem_kernel, mX[0], mX[1], mW, q));
   fpb_count_launch();
   return FPB_OK;
 }
