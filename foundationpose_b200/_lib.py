@@ -28,6 +28,8 @@ _SIGS = {
   'fpb_hypotheses_from_stats': (ci, [vp, vp, vp, vp, ci, ci, vp, vp, vp]),
   'fpb_register_prologue': (ci, [vp, vp, ci, ci, vp, vp, vp, vp, vp, vp, ci, ci, vp, vp, vp, vp, vp]),
   'fpb_cluster_poses_f32': (ci, [vp, ci, vp, ci, cf, cf, vp, vp, vp]),
+  'fpb_add_err': (ci, [vp, vp, ci, vp, ci, ci, vp, vp]),
+  'fpb_adds_err': (ci, [vp, vp, ci, vp, ci, ci, vp, vp]),
   'fpb_crop_params': (ci, [vp, ci, vp, cf, ci, ci, ci, vp, vp, vp]),
   'fpb_mesh_create': (ci, [vp, vp, vp, ci, vp, ci, vp, vp, ci, vp, vp, ci, ci, vp]),
   'fpb_mesh_destroy': (ci, [vp]),

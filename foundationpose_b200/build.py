@@ -21,6 +21,7 @@ UNITS = [
   ('depth.cu', ['-fmad=false']),
   ('hypo.cu', ['-fmad=false']),
   ('render.cu', ['-fmad=false']),
+  ('metrics.cu', ['-fmad=false']),
   ('net_ref.cu', []),
   ('net_tc.cu', []),
   ('net_tc2.cu', []),

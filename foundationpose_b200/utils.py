@@ -469,3 +469,54 @@ def egocentric_delta_pose_to_pose(A_in_cam, trans_delta, rot_mat_delta):
   B_in_cam[:, :3, 3] = A_in_cam[:, :3, 3] + trans_delta
   B_in_cam[:, :3, :3] = rot_mat_delta @ A_in_cam[:, :3, :3]
   return B_in_cam
+
+
+def symmetry_tfs_from_info(info, rot_angle_discrete=5):
+  """src/Utils.py:806-834: BOP models_info entry -> [S,4,4] symmetry transforms (identity first; discrete ones with
+  millimetre translations converted to metres; one continuous axis sampled every `rot_angle_discrete` degrees)."""
+  symmetry_tfs = [np.eye(4)]
+  if 'symmetries_discrete' in info:
+    tfs = np.array(info['symmetries_discrete'], dtype=np.float64).reshape(-1, 4, 4)
+    tfs[..., :3, 3] *= 0.001
+    symmetry_tfs = [np.eye(4)] + list(tfs)
+  if 'symmetries_continuous' in info:
+    axis = np.array(info['symmetries_continuous'][0]['axis']).reshape(3)
+    offset = info['symmetries_continuous'][0]['offset']
+    rxs, rys, rzs = [0], [0], [0]
+    steps = np.arange(0, 360, rot_angle_discrete) / 180.0 * np.pi
+    if axis[0] > 0:
+      rxs = steps
+    elif axis[1] > 0:
+      rys = steps
+    elif axis[2] > 0:
+      rzs = steps
+    for rx in rxs:
+      for ry in rys:
+        for rz in rzs:
+          tf = euler_matrix(rx, ry, rz)
+          tf[:3, 3] = offset
+          symmetry_tfs.append(tf)
+  return np.array(symmetry_tfs)
+
+
+def _pose_errors(fn, pred, gt, model_pts):
+  single = np.ndim(pred) == 2
+  p = _as_cuda_f32(pred).reshape(-1, 4, 4).contiguous()
+  g = _as_cuda_f32(gt).reshape(-1, 4, 4).contiguous()
+  if g.shape[0] not in (1, p.shape[0]):
+    raise ValueError('gt must be one pose or one per prediction')
+  pts = _as_cuda_f32(model_pts).reshape(-1, 3).contiguous()
+  out = torch.empty(p.shape[0], dtype=torch.float, device=p.device)
+  check(getattr(lib(), fn)(ptr(p), ptr(g), int(g.shape[0] > 1), ptr(pts), pts.shape[0], p.shape[0], ptr(out), stream()))
+  return float(out.item()) if single else out
+
+
+def add_err(pred, gt, model_pts, symetry_tfs=None):
+  """src/Utils.py:232-240 (the reference ignores `symetry_tfs` too).  A single 4x4 returns a float, [B,4,4] a CUDA
+  tensor [B]."""
+  return _pose_errors('fpb_add_err', pred, gt, model_pts)
+
+
+def adds_err(pred, gt, model_pts):
+  """src/Utils.py:242-253."""
+  return _pose_errors('fpb_adds_err', pred, gt, model_pts)

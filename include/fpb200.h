@@ -72,6 +72,14 @@ int fpb_register_prologue(const float* depth_in, const uint8_t* mask, int H, int
 int fpb_cluster_poses_f32(const float* poses, int N, const float* sym, int S, float angle_deg, float dist,
                           int32_t* out_keep_idx, int32_t* out_n_keep, void* stream);
 
+/* ---- pose-error metrics over a batch of B poses (row-major 4x4 float), model points [P,3]:
+ *      add_err src/Utils.py:232-240, adds_err src/Utils.py:242-253 (exhaustive nearest neighbour instead of cKDTree).
+ *      gt is one pose (gt_batched = 0) or B poses; out[B] on the device. ---- */
+int fpb_add_err(const float* pred, const float* gt, int gt_batched, const float* pts, int P, int B, float* out,
+                void* stream);
+int fpb_adds_err(const float* pred, const float* gt, int gt_batched, const float* pts, int P, int B, float* out,
+                 void* stream);
+
 /* ---- crop windows: compute_crop_window_tf_batch(method='box_3d') src/Utils.py:577-621,
  *      bbox2d_ori predict_pose_refine.py:44-45, render matrices src/Utils.py:159-181.
  *      params layout per hypothesis (FPB_CROP_STRIDE floats):

@@ -191,3 +191,21 @@ def projection_matrix_from_intrinsics(K, height, width, znear, zfar):
                    [0, 2 * K[1, 1] / h, (2 * K[1, 2] - h) / h, 0],
                    [0, 0, q, qn],
                    [0, 0, -1, 0]])
+
+
+def add_err(pred, gt, model_pts):
+  """src/Utils.py:232-240."""
+  pred, gt, pts = (np.asarray(a, dtype=np.float64) for a in (pred, gt, model_pts))
+  a = pts @ pred[:3, :3].T + pred[:3, 3]
+  b = pts @ gt[:3, :3].T + gt[:3, 3]
+  return float(np.linalg.norm(a - b, axis=-1).mean())
+
+
+def adds_err(pred, gt, model_pts):
+  """src/Utils.py:242-253 (cKDTree nearest neighbour, k=1)."""
+  from scipy.spatial import cKDTree
+  pred, gt, pts = (np.asarray(a, dtype=np.float64) for a in (pred, gt, model_pts))
+  a = pts @ pred[:3, :3].T + pred[:3, 3]
+  b = pts @ gt[:3, :3].T + gt[:3, 3]
+  d, _ = cKDTree(a).query(b, k=1)
+  return float(d.mean())
