@@ -7,12 +7,16 @@
 //   transform_batch                   learning/datasets/h5_dataset.py:79-127, 137-179
 //
 // Design: all N hypotheses in one launch per stage.
-//   1. vertex kernel   (N x V threads)  clip-space xyzw + camera xyz + diffuse term  -> L2-resident scratch
-//   2. raster kernel   (N x F threads)  1/16-px snapped integer coverage; 64-bit (z/w | face) atomicMin
-//                                       z-buffer; big triangles are re-distributed over the warp
+//   1. vertex kernel   (N x V threads)  clip-space xyzw + camera xyz + diffuse term + the 1/16-px snapped window
+//                                       position of every vertex (the two divisions happen once per vertex, not once
+//                                       per face corner)                            -> L2-resident scratch
+//   2. raster kernel   (N x F threads)  integer coverage on the snapped positions; 64-bit (z/w | face) atomicMin
+//                                       z-buffer; the float clip coordinates are only fetched by triangles that cover
+//                                       a pixel centre; big triangles are re-distributed over the warp
 //   3. shade kernel    (N x S x S)      barycentrics -> xyz / colour|texture / lighting -> normalised
 //                                       8-channel NHWC pixel, one 128-bit store (bf16) per pixel
 #include "common.cuh"
+#include <stdlib.h>
 
 struct fpb_mesh {
   int V, F, Vt, Ht, Wt;
@@ -20,6 +24,7 @@ struct fpb_mesh {
   float* vnormals;  // [V,3]
   int32_t* faces;   // [F,3]
   float* vcolor;    // [V,3] or null
+  float4* vcolor4;  // [V] rgb0 (one 128-bit load per corner in the shader) or null
   float* uv;        // [Vt,2] or null
   int32_t* uv_idx;  // [F,3] or null
   float* tex;       // [Ht,Wt,3] or null
@@ -50,9 +55,12 @@ __device__ __forceinline__ void bary_zw(const float4 c0, const float4 c1, const 
   zw = fminf(fmaxf(z / w, -1.0f), 1.0f);
 }
 
+constexpr int SNAP_INVALID = INT32_MIN;   // vertex behind the camera (w <= 0) or beyond the fixed-point range
+
 __global__ void __launch_bounds__(256) vertex_kernel(const float* __restrict__ pos, const float* __restrict__ vnormals, int V,
                                                      const float* __restrict__ poses, const float* __restrict__ params,
-                                                     float4* __restrict__ clip, float4* __restrict__ camd)
+                                                     int S, float4* __restrict__ clip, float4* __restrict__ camd,
+                                                     int2* __restrict__ snap)
 {
   const int n = blockIdx.y;
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
@@ -85,47 +93,47 @@ __global__ void __launch_bounds__(256) vertex_kernel(const float* __restrict__ p
   d = fminf(fmaxf(d, 0.0f), 1.0f);
   clip[(size_t)n * V + v] = cl;
   camd[(size_t)n * V + v] = make_float4(cam[0], cam[1], cam[2], d);
+  // window position in 1/16 pixel units (8*S sub-pixels per clip unit), snapped once per vertex
+  int2 sn = make_int2(SNAP_INVALID, 0);
+  if (cl.w > 0.0f) {
+    const float sub = (float)(8 * S);
+    const float sx = (cl.x / cl.w) * sub + sub;
+    const float sy = (cl.y / cl.w) * sub + sub;
+    if (fabsf(sx) < 1073741824.0f && fabsf(sy) < 1073741824.0f) sn = make_int2((int)rintf(sx), (int)rintf(sy));
+  }
+  snap[(size_t)n * V + v] = sn;
 }
 
 struct TriSetup {
-  long long X[3], Y[3];
+  int X[3], Y[3];     // |X|, |Y| < 2^30
   int px0, px1, py0, py1;
   int ok;
-  int small;          // every |X|, |Y| <= 16383 (within ~1000 pixels of the crop): the edge functions fit 32-bit integers
+  int small;          // every |X|, |Y| <= 16000 (within ~1000 pixels of the crop): |E| <= 2 * 32000 * 32016 < 2^31
 };
 
-__device__ __forceinline__ long long floordiv16(long long a) { return a >> 4; }
-__device__ __forceinline__ long long ceildiv16(long long a) { return -((-a) >> 4); }
+__device__ __forceinline__ int floordiv16(int a) { return a >> 4; }
+__device__ __forceinline__ int ceildiv16(int a) { return -((-a) >> 4); }
 
-__device__ __forceinline__ void tri_setup(const float4 c0, const float4 c1, const float4 c2, int S, TriSetup& t)
+__device__ __forceinline__ void tri_setup(const int2 s0, const int2 s1, const int2 s2, int S, TriSetup& t)
 {
   t.ok = 0;
   t.small = 0;
-  if (!(c0.w > 0.0f && c1.w > 0.0f && c2.w > 0.0f)) return;
-  const float sub = (float)(8 * S);
-  const float4 cc[3] = {c0, c1, c2};
-#pragma unroll
-  for (int k = 0; k < 3; k++) {
-    float sx = (cc[k].x / cc[k].w) * sub + sub;
-    float sy = (cc[k].y / cc[k].w) * sub + sub;
-    if (!(fabsf(sx) < 1073741824.0f) || !(fabsf(sy) < 1073741824.0f)) return;
-    t.X[k] = (long long)rintf(sx);
-    t.Y[k] = (long long)rintf(sy);
-  }
-  long long area = (t.X[1] - t.X[0]) * (t.Y[2] - t.Y[0]) - (t.Y[1] - t.Y[0]) * (t.X[2] - t.X[0]);
+  if (s0.x == SNAP_INVALID || s1.x == SNAP_INVALID || s2.x == SNAP_INVALID) return;
+  t.X[0] = s0.x; t.Y[0] = s0.y; t.X[1] = s1.x; t.Y[1] = s1.y; t.X[2] = s2.x; t.Y[2] = s2.y;
+  const long long area = (long long)(t.X[1] - t.X[0]) * (t.Y[2] - t.Y[0]) - (long long)(t.Y[1] - t.Y[0]) * (t.X[2] - t.X[0]);
   if (area == 0) return;
   if (area < 0) {  // orient for the coverage test only
-    long long tx = t.X[1], ty = t.Y[1];
+    int tx = t.X[1], ty = t.Y[1];
     t.X[1] = t.X[2]; t.Y[1] = t.Y[2]; t.X[2] = tx; t.Y[2] = ty;
   }
-  long long xmin = min(t.X[0], min(t.X[1], t.X[2])), xmax = max(t.X[0], max(t.X[1], t.X[2]));
-  long long ymin = min(t.Y[0], min(t.Y[1], t.Y[2])), ymax = max(t.Y[0], max(t.Y[1], t.Y[2]));
-  long long px0 = max(0LL, ceildiv16(xmin - 8)), px1 = min((long long)(S - 1), floordiv16(xmax - 8));
-  long long py0 = max(0LL, ceildiv16(ymin - 8)), py1 = min((long long)(S - 1), floordiv16(ymax - 8));
+  const int xmin = min(t.X[0], min(t.X[1], t.X[2])), xmax = max(t.X[0], max(t.X[1], t.X[2]));
+  const int ymin = min(t.Y[0], min(t.Y[1], t.Y[2])), ymax = max(t.Y[0], max(t.Y[1], t.Y[2]));
+  const int px0 = max(0, ceildiv16(xmin - 8)), px1 = min(S - 1, floordiv16(xmax - 8));
+  const int py0 = max(0, ceildiv16(ymin - 8)), py1 = min(S - 1, floordiv16(ymax - 8));
   if (px0 > px1 || py0 > py1) return;
-  t.px0 = (int)px0; t.px1 = (int)px1; t.py0 = (int)py0; t.py1 = (int)py1;
+  t.px0 = px0; t.px1 = px1; t.py0 = py0; t.py1 = py1;
   t.ok = 1;
-  t.small = xmin >= -16383 && xmax <= 16383 && ymin >= -16383 && ymax <= 16383;
+  t.small = xmin >= -16000 && xmax <= 16000 && ymin >= -16000 && ymax <= 16000;
 }
 
 __device__ __forceinline__ bool covers(const TriSetup& t, int px, int py)
@@ -134,7 +142,7 @@ __device__ __forceinline__ bool covers(const TriSetup& t, int px, int py)
 #pragma unroll
   for (int e = 0; e < 3; e++) {
     const int a = e, b = (e + 1) % 3;
-    long long dx = t.X[b] - t.X[a], dy = t.Y[b] - t.Y[a];
+    long long dx = (long long)t.X[b] - t.X[a], dy = (long long)t.Y[b] - t.Y[a];
     long long E = dx * (cy - t.Y[a]) - dy * (cx - t.X[a]);
     if (E < 0) return false;
     if (E == 0 && !(dy > 0 || (dy == 0 && dx < 0))) return false;
@@ -186,38 +194,67 @@ __device__ __forceinline__ void raster_pixel(const TriSetup& t, const float4 c0,
 
 constexpr int SMALL_TRI_PIXELS = 16;
 
-__global__ void __launch_bounds__(256, 4) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
-                                                     const float4* __restrict__ clip, int S,
-                                                     unsigned long long* __restrict__ zbuf)
+// One triangle per lane; the whole warp must call this together (the large-footprint path is warp-cooperative).
+// sn: snapped vertex positions of this hypothesis.
+__device__ __forceinline__ void raster_triangle(const int32_t* __restrict__ faces, int F, int f, const float4* __restrict__ cl,
+                                                const int2* sn, int S, unsigned long long* __restrict__ zb)
 {
-  const int n = blockIdx.y;
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
-  unsigned long long* zb = zbuf + (size_t)n * S * S;
-  const float4* cl = clip + (size_t)n * V;
   TriSetup t;
   t.ok = 0;
-  float4 c0 = make_float4(0, 0, 0, 0), c1 = c0, c2 = c0;
+  int i0 = 0, i1 = 0, i2 = 0;
   if (f < F) {
-    c0 = cl[faces[f * 3]]; c1 = cl[faces[f * 3 + 1]]; c2 = cl[faces[f * 3 + 2]];
-    tri_setup(c0, c1, c2, S, t);
+    i0 = faces[f * 3]; i1 = faces[f * 3 + 1]; i2 = faces[f * 3 + 2];
+    tri_setup(sn[i0], sn[i1], sn[i2], S, t);
   }
   int big = 0;
   if (t.ok) {
     int npx = (t.px1 - t.px0 + 1) * (t.py1 - t.py0 + 1);
     if (npx <= SMALL_TRI_PIXELS && t.small) {
-      Tri32 q;
+      // incremental 32-bit edge functions (exact integers, so identical to covers32): E_e at the first pixel centre,
+      // biased by the top-left rule so that "covered" is E_e >= 0 for all three edges, i.e. the sign bit of their OR
+      int E[3], ex[3], ey[3];
 #pragma unroll
-      for (int k = 0; k < 3; k++) { q.X[k] = (int)t.X[k]; q.Y[k] = (int)t.Y[k]; }
-      for (int py = t.py0; py <= t.py1; py++)
-        for (int px = t.px0; px <= t.px1; px++)
-          if (covers32(q, px, py)) shade_fragment(c0, c1, c2, px, py, S, (uint32_t)f, zb);
+      for (int e = 0; e < 3; e++) {
+        const int a = e, b = (e + 1) % 3;
+        const int dx = t.X[b] - t.X[a], dy = t.Y[b] - t.Y[a];
+        const int cx = 16 * t.px0 + 8, cy = 16 * t.py0 + 8;
+        const int tl = (dy > 0 || (dy == 0 && dx < 0)) ? 0 : 1;     // edges that do not own their boundary need E > 0
+        E[e] = dx * (cy - t.Y[a]) - dy * (cx - t.X[a]) - tl;
+        ex[e] = -16 * dy;                                            // one pixel to the right
+        ey[e] = 16 * dx;                                             // one pixel down
+      }
+      // pass 1 (cheap, lanes in lockstep): coverage bits of the <= 16 pixels of the bounding box, row-major
+      const int bw = t.px1 - t.px0 + 1;
+      uint32_t mask = 0, bit = 1;
+      for (int py = t.py0; py <= t.py1; py++) {
+        int r0 = E[0], r1 = E[1], r2 = E[2];
+        for (int px = t.px0; px <= t.px1; px++) {
+          if ((r0 | r1 | r2) >= 0) mask |= bit;
+          bit <<= 1;
+          r0 += ex[0]; r1 += ex[1]; r2 += ex[2];
+        }
+        E[0] += ey[0]; E[1] += ey[1]; E[2] += ey[2];
+      }
+      // pass 2: one fragment per iteration and lane, so the trip count is the largest number of COVERED pixels in the
+      // warp (1-3 for pixel-sized triangles) instead of the largest bounding box; the float clip coordinates are
+      // fetched only by triangles that cover a pixel centre
+      if (mask) {
+        const float4 c0 = cl[i0], c1 = cl[i1], c2 = cl[i2];
+        const uint32_t mdiv = (256u + (uint32_t)bw - 1u) / (uint32_t)bw;     // b / bw == (b * mdiv) >> 8 for b < 16, bw <= 16
+        do {
+          const uint32_t b = (uint32_t)__ffs(mask) - 1u;
+          mask &= mask - 1u;
+          const uint32_t dy = (b * mdiv) >> 8, dx = b - dy * (uint32_t)bw;
+          shade_fragment(c0, c1, c2, t.px0 + (int)dx, t.py0 + (int)dy, S, (uint32_t)f, zb);
+        } while (mask);
+      }
     } else {
       big = 1;       // large footprint, or coordinates beyond the 32-bit fast path: warp-cooperative 64-bit path
     }
   }
   // triangles with a large footprint: the whole warp sweeps the bounding box together
   unsigned m = __ballot_sync(0xffffffffu, big);
+  const int lane = threadIdx.x & 31;
   while (m) {
     const int src = __ffs(m) - 1;
     m &= m - 1;
@@ -229,13 +266,9 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const int32_t* __restric
     }
     s.px0 = __shfl_sync(0xffffffffu, t.px0, src); s.px1 = __shfl_sync(0xffffffffu, t.px1, src);
     s.py0 = __shfl_sync(0xffffffffu, t.py0, src); s.py1 = __shfl_sync(0xffffffffu, t.py1, src);
-    float4 d0, d1, d2;
-    d0.x = __shfl_sync(0xffffffffu, c0.x, src); d0.y = __shfl_sync(0xffffffffu, c0.y, src);
-    d0.z = __shfl_sync(0xffffffffu, c0.z, src); d0.w = __shfl_sync(0xffffffffu, c0.w, src);
-    d1.x = __shfl_sync(0xffffffffu, c1.x, src); d1.y = __shfl_sync(0xffffffffu, c1.y, src);
-    d1.z = __shfl_sync(0xffffffffu, c1.z, src); d1.w = __shfl_sync(0xffffffffu, c1.w, src);
-    d2.x = __shfl_sync(0xffffffffu, c2.x, src); d2.y = __shfl_sync(0xffffffffu, c2.y, src);
-    d2.z = __shfl_sync(0xffffffffu, c2.z, src); d2.w = __shfl_sync(0xffffffffu, c2.w, src);
+    const float4 d0 = cl[__shfl_sync(0xffffffffu, i0, src)];    // same address in every lane: one broadcast load
+    const float4 d1 = cl[__shfl_sync(0xffffffffu, i1, src)];
+    const float4 d2 = cl[__shfl_sync(0xffffffffu, i2, src)];
     const uint32_t face = (uint32_t)(f - lane + src);
     const int bw = s.px1 - s.px0 + 1, tot = bw * (s.py1 - s.py0 + 1);
     for (int i = lane; i < tot; i += 32) {
@@ -243,6 +276,29 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const int32_t* __restric
       raster_pixel(s, d0, d1, d2, px, py, S, face, zb);
     }
   }
+}
+
+// One thread per (hypothesis, face); the per-corner gathers are served by L1/L2 (a variant that staged the snapped
+// positions of one hypothesis in shared memory with bulk async copies measured no faster: the kernel is bound by
+// instruction issue in the divergent fragment loop, not by the gathers).
+__global__ void __launch_bounds__(256, 4) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
+                                                     const float4* __restrict__ clip, const int2* __restrict__ snap,
+                                                     int S, unsigned long long* __restrict__ zbuf)
+{
+  const int n = blockIdx.y;
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  raster_triangle(faces, F, f, clip + (size_t)n * V, snap + (size_t)n * V, S, zbuf + (size_t)n * S * S);
+}
+
+// a / 255.0f, correctly rounded, without the generic division sequence (range check + slow path on zero numerators):
+// q = RN(a * rc), r = a - 255 q (exact in one FMA), q' = RN(q + r * rc).  Verified exhaustively on the host against
+// IEEE a / 255.0f for every float in [0, 256] (all 1,132,462,081 bit patterns, denormals included) -- the only range used.
+__device__ __forceinline__ float div255(float a)
+{
+  const float rc = 1.0f / 255.0f;
+  const float q = a * rc;
+  const float r = fmaf(-255.0f, q, a);
+  return fmaf(r, rc, q);
 }
 
 __device__ __forceinline__ void xyz_norm(const float xyz[3], const float* T, float inv_radius, float zthr, float o[3])
@@ -282,16 +338,23 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
                                                     float* __restrict__ out_color,
                                                     float* __restrict__ out_xyz, int32_t* __restrict__ out_tri)
 {
-  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const size_t total = (size_t)N * S * S;
-  if (idx >= total) return;
-  const int n = (int)(idx / ((size_t)S * S));
-  const int rem = (int)(idx - (size_t)n * S * S);
-  const int i = rem / S, j = rem - i * S;
+  // block = 32 x 8 pixels of one crop: grid (ceil(S/32), ceil(S/8), N)
+  const int n = blockIdx.z;
+  const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y;
+  if (j >= S || i >= S) return;
+  const size_t idx = ((size_t)n * S + i) * S + j;
   const int py = S - 1 - i, px = j;  // row flip (src/Utils.py:197,216-218)
   const unsigned long long key = zbuf[(size_t)n * S * S + (size_t)py * S + px];
   float col[3] = {0.f, 0.f, 0.f}, xyz[3] = {0.f, 0.f, 0.f};
   int tri = 0;
+  if (key == ~0ull && zthr > 0.0f) {      // background: colour 0, xyz 0 -> z below the validity threshold -> the whole pixel is zero
+    if (out_color) { out_color[idx * 3] = 0.f; out_color[idx * 3 + 1] = 0.f; out_color[idx * 3 + 2] = 0.f; }
+    if (out_xyz) { out_xyz[idx * 3] = 0.f; out_xyz[idx * 3 + 1] = 0.f; out_xyz[idx * 3 + 2] = 0.f; }
+    if (out_tri) out_tri[idx] = 0;
+    const float z6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    store_px8<BF16>(outA, ((size_t)n * S + i) * out_pitch + out_xoff + j, z6);
+    return;
+  }
   if (key != ~0ull) {
     const int f = (int)(uint32_t)(key & 0xffffffffu);
     const int i0 = mesh.faces[f * 3], i1 = mesh.faces[f * 3 + 1], i2 = mesh.faces[f * 3 + 2];
@@ -327,9 +390,10 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
         c[k] = top + dv * (bot - top);
       }
     } else {
-#pragma unroll
-      for (int k = 0; k < 3; k++)
-        c[k] = (b0 * mesh.vcolor[i0 * 3 + k] + b1 * mesh.vcolor[i1 * 3 + k]) + b2 * mesh.vcolor[i2 * 3 + k];
+      const float4 k0 = mesh.vcolor4[i0], k1 = mesh.vcolor4[i1], k2 = mesh.vcolor4[i2];
+      c[0] = (b0 * k0.x + b1 * k1.x) + b2 * k2.x;
+      c[1] = (b0 * k0.y + b1 * k1.y) + b2 * k2.y;
+      c[2] = (b0 * k0.z + b1 * k1.z) + b2 * k2.z;
     }
 #pragma unroll
     for (int k = 0; k < 3; k++) {
@@ -343,7 +407,7 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
   if (out_tri) out_tri[idx] = tri;
   float v6[6];
 #pragma unroll
-  for (int k = 0; k < 3; k++) v6[k] = (col[k] * 255.0f) / 255.0f;
+  for (int k = 0; k < 3; k++) v6[k] = div255(col[k] * 255.0f);
   xyz_norm(xyz, poses + (size_t)n * 16, inv_radius, zthr, v6 + 3);
   store_px8<BF16>(outA, ((size_t)n * S + i) * out_pitch + out_xoff + j, v6);
 }
@@ -361,18 +425,15 @@ template <bool BF16, bool U8>
 __global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_, const float* __restrict__ xyz_map,
                                                    const float* __restrict__ depth, int H, int W,
                                                    const float* __restrict__ poses, const float* __restrict__ params, K9f K,
-                                                   int N, int S, float inv_radius, int mode, void* __restrict__ outB,
-                                                   int out_pitch, int out_xoff)
+                                                   int N, int S, float inv_radius, int mode, float wsc, float hsc,
+                                                   float ssc, void* __restrict__ outB, int out_pitch, int out_xoff)
 {
-  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const size_t total = (size_t)N * S * S;
-  if (idx >= total) return;
-  const int n = (int)(idx / ((size_t)S * S));
-  const int rem = (int)(idx - (size_t)n * S * S);
-  const int i = rem / S, j = rem - i * S;
+  // block = 32 x 8 pixels of one crop: grid (ceil(S/32), ceil(S/8), N); wsc = W/(W-1), hsc = H/(H-1), ssc = S/(S-1)
+  const int n = blockIdx.z;
+  const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y;
+  if (j >= S || i >= S) return;
   const float* pr = params + (size_t)n * FPB_CROP_STRIDE;
   const float i00 = pr[33], i02 = pr[34], i11 = pr[35], i12 = pr[36];
-  const float wsc = (float)W / (float)(W - 1), hsc = (float)H / (float)(H - 1), ssc = (float)S / (float)(S - 1);
   const float zthr = mode ? 0.1f : 0.001f;
   const float px = (float)j * i00 + i02, py = (float)i * i11 + i12;
   float v6[6];
@@ -383,19 +444,23 @@ __global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_
     const float wsw = (x1 - ix) * (iy - y0), wse = (ix - x0) * (iy - y0);
     const bool inx0 = x0 >= 0.0f && x0 <= (float)(W - 1), inx1 = x1 >= 0.0f && x1 <= (float)(W - 1);
     const bool iny0 = y0 >= 0.0f && y0 <= (float)(H - 1), iny1 = y1 >= 0.0f && y1 <= (float)(H - 1);
-    auto tap = [&](float yy, float xx, int k) -> float {
-      size_t o = ((size_t)(int)yy * W + (int)xx) * 3 + k;
-      if (U8) return (float)reinterpret_cast<const uint8_t*>(rgb_)[o];
+    // out-of-range taps are skipped (zero padding); their clamped offsets are never dereferenced
+    const int xi0 = inx0 ? (int)x0 : 0, xi1 = inx1 ? (int)x1 : 0, yi0 = iny0 ? (int)y0 : 0, yi1 = iny1 ? (int)y1 : 0;
+    const int o00 = (yi0 * W + xi0) * 3, o01 = (yi0 * W + xi1) * 3, o10 = (yi1 * W + xi0) * 3, o11 = (yi1 * W + xi1) * 3;
+    auto tap = [&](int o) -> float {
+      // uint8 -> float on the FMA pipe: 2^23 + b is exact, so (2^23 | b) - 2^23 == (float)b
+      if (U8) return __uint_as_float(0x4B000000u | (uint32_t)reinterpret_cast<const uint8_t*>(rgb_)[o]) - 8388608.0f;
       return reinterpret_cast<const float*>(rgb_)[o];
     };
+    const bool p00 = inx0 && iny0, p01 = inx1 && iny0, p10 = inx0 && iny1, p11 = inx1 && iny1;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
       float acc = 0.0f;
-      if (inx0 && iny0) acc += tap(y0, x0, k) * wnw;
-      if (inx1 && iny0) acc += tap(y0, x1, k) * wne;
-      if (inx0 && iny1) acc += tap(y1, x0, k) * wsw;
-      if (inx1 && iny1) acc += tap(y1, x1, k) * wse;
-      v6[k] = acc / 255.0f;
+      if (p00) acc += tap(o00 + k) * wnw;
+      if (p01) acc += tap(o01 + k) * wne;
+      if (p10) acc += tap(o10 + k) * wsw;
+      if (p11) acc += tap(o11 + k) * wse;
+      v6[k] = U8 ? div255(acc) : acc / 255.0f;     // uint8 taps: acc in [0, 255] (convex combination, up to rounding)
     }
   }
   float xyz[3] = {0.f, 0.f, 0.f};
@@ -430,6 +495,14 @@ __global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_
 // ---------------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------------
+namespace {
+__global__ void pack_color_kernel(const float* __restrict__ c3, int V, float4* __restrict__ c4)
+{
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < V) c4[v] = make_float4(c3[v * 3], c3[v * 3 + 1], c3[v * 3 + 2], 0.0f);
+}
+}  // namespace
+
 template <typename T>
 static int dev_copy(T** dst, const T* src, size_t count, cudaStream_t st)
 {
@@ -455,6 +528,14 @@ FPB_EXPORT int fpb_mesh_create(fpb_mesh** out, const float* pos, const float* vn
   if ((rc = dev_copy(&m->vnormals, vnormals, (size_t)V * 3, st))) goto fail;
   if ((rc = dev_copy(&m->faces, faces, (size_t)F * 3, st))) goto fail;
   if ((rc = dev_copy(&m->vcolor, vcolor, (size_t)V * 3, st))) goto fail;
+  if (vcolor) {
+    if (cudaMalloc((void**)&m->vcolor4, (size_t)V * sizeof(float4)) != cudaSuccess) {
+      fpb_set_error("fpb_mesh_create: cudaMalloc of the packed vertex colours failed");
+      rc = FPB_ERR_CUDA;
+      goto fail;
+    }
+    pack_color_kernel<<<fpb_cdiv(V, 256), 256, 0, st>>>(m->vcolor, V, m->vcolor4);
+  }
   if ((rc = dev_copy(&m->uv, uv, tex ? (size_t)Vt * 2 : 0, st))) goto fail;
   if ((rc = dev_copy(&m->uv_idx, uv_idx, tex ? (size_t)F * 3 : 0, st))) goto fail;
   if ((rc = dev_copy(&m->tex, tex, tex ? (size_t)Ht * Wt * 3 : 0, st))) goto fail;
@@ -469,7 +550,7 @@ fail:
 FPB_EXPORT int fpb_mesh_destroy(fpb_mesh* m)
 {
   if (!m) return FPB_OK;
-  cudaFree(m->pos); cudaFree(m->vnormals); cudaFree(m->faces); cudaFree(m->vcolor);
+  cudaFree(m->pos); cudaFree(m->vnormals); cudaFree(m->faces); cudaFree(m->vcolor); cudaFree(m->vcolor4);
   cudaFree(m->uv); cudaFree(m->uv_idx); cudaFree(m->tex);
   delete m;
   return FPB_OK;
@@ -479,7 +560,8 @@ static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 FPB_EXPORT size_t fpb_render_ws_bytes(int N, int V, int S)
 {
-  return 2 * align256((size_t)N * V * sizeof(float4)) + align256((size_t)N * S * S * sizeof(unsigned long long));
+  return 2 * align256((size_t)N * V * sizeof(float4)) + align256((size_t)N * V * sizeof(int2)) +
+         align256((size_t)N * S * S * sizeof(unsigned long long));
 }
 
 FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
@@ -493,19 +575,20 @@ FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const 
   char* w = (char*)ws;
   float4* clip = (float4*)w; w += align256((size_t)N * V * sizeof(float4));
   float4* camd = (float4*)w; w += align256((size_t)N * V * sizeof(float4));
+  int2* snap = (int2*)w; w += align256((size_t)N * V * sizeof(int2));
   unsigned long long* zbuf = (unsigned long long*)w;
   FPB_CUDA(cudaMemsetAsync(zbuf, 0xff, (size_t)N * S * S * sizeof(unsigned long long), st));
-  vertex_kernel<<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, clip, camd);
+  vertex_kernel<<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, S, clip, camd, snap);
   FPB_LAUNCH_CHECK();
-  raster_kernel<<<dim3(fpb_cdiv(F, 256), N), 256, 0, st>>>(mesh->faces, F, V, clip, S, zbuf);
+  raster_kernel<<<dim3(fpb_cdiv(F, 256), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
   FPB_LAUNCH_CHECK();
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
-  const int blocks = fpb_cdiv((long long)N * S * S, 256);
+  const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
   if (a_is_bf16)
-    shade_kernel<true><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
+    shade_kernel<true><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
                                                out_xoff, out_color, out_xyz, out_tri);
   else
-    shade_kernel<false><<<blocks, 256, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
+    shade_kernel<false><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
                                                 out_xoff, out_color, out_xyz, out_tri);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
@@ -516,17 +599,18 @@ FPB_EXPORT int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_h
                               float mesh_diameter, int mode, void* out_B, int b_is_bf16, int out_pitch, int out_xoff,
                               void* stream)
 {
-  FPB_CHECK_ARG(rgb && poses && params && K9_h && out_B && N > 0 && S > 1 && H > 1 && W > 1);
+  FPB_CHECK_ARG(rgb && poses && params && K9_h && out_B && N > 0 && N <= 65535 && S > 1 && H > 1 && W > 1);
   FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff);
   FPB_CHECK_ARG(mode == 0 ? xyz_hw3 != nullptr : depth_hw != nullptr);
   cudaStream_t st = (cudaStream_t)stream;
   K9f K;
   for (int i = 0; i < 9; i++) K.k[i] = K9_h[i];
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
-  const int blocks = fpb_cdiv((long long)N * S * S, 256);
-#define LAUNCH_WARP(BF, U8)                                                                                         \
-  warp_kernel<BF, U8><<<blocks, 256, 0, st>>>(rgb, xyz_hw3, depth_hw, H, W, poses, params, K, N, S, inv_radius, mode, \
-                                              out_B, out_pitch, out_xoff)
+  const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
+  const float wsc = (float)W / (float)(W - 1), hsc = (float)H / (float)(H - 1), ssc = (float)S / (float)(S - 1);
+#define LAUNCH_WARP(BF, U8)                                                                                           \
+  warp_kernel<BF, U8><<<blocks, threads, 0, st>>>(rgb, xyz_hw3, depth_hw, H, W, poses, params, K, N, S, inv_radius,  \
+                                                  mode, wsc, hsc, ssc, out_B, out_pitch, out_xoff)
   if (b_is_bf16) { if (rgb_is_u8) LAUNCH_WARP(true, true); else LAUNCH_WARP(true, false); }
   else           { if (rgb_is_u8) LAUNCH_WARP(false, true); else LAUNCH_WARP(false, false); }
 #undef LAUNCH_WARP
