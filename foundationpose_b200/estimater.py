@@ -212,3 +212,77 @@ class FoundationPose:
                                    get_vis=False)
     self.pose_last = pose
     return (pose @ self.get_tf_to_centered_mesh()).data.cpu().numpy().reshape(4, 4)
+
+  # ------------------------------------------------------------------------------------------------------------
+  # track_one as one CUDA graph: the video path (1 hypothesis, 2 iterations) is ~90 small launches whose device time
+  # is far below the host time needed to enqueue them, so the frame body is captured once over static buffers and
+  # replayed per frame.  Same arithmetic and same C-ABI calls as track_one (captured, not re-implemented).
+  # ------------------------------------------------------------------------------------------------------------
+  def _capture_track_graph(self, key, H, W, K, iteration, rgb_dtype):
+    dev = 'cuda'
+    g = dict(key=key)
+    g['rgb'] = torch.zeros((H, W, 3), dtype=rgb_dtype, device=dev)
+    g['depth'] = torch.zeros((H, W), dtype=torch.float, device=dev)
+    g['pose_in'] = torch.eye(4, dtype=torch.float, device=dev)
+    g['pose_out'] = torch.eye(4, dtype=torch.float, device=dev)
+    g['result'] = torch.eye(4, dtype=torch.float, device=dev)
+    g['pose_in'].copy_(self.pose_last.reshape(4, 4))
+    tf = g['tf'] = self.get_tf_to_centered_mesh()     # read by the graph at every replay: must stay alive with it
+    K32 = K.astype(np.float32).astype(np.float64)
+
+    def body():
+      d = U.erode_depth(g['depth'], radius=2, device='cuda')
+      d = U.bilateral_filter_depth(d, radius=2, device='cuda')
+      xyz_map = U.depth2xyzmap_cuda(d, K32, math_f64=False, zfar=np.inf)
+      pose, _ = self.refiner.predict(mesh=self.mesh, mesh_tensors=self.mesh_tensors, rgb=g['rgb'], depth=d, K=K,
+                                     ob_in_cams=g['pose_in'].reshape(1, 4, 4), normal_map=None, xyz_map=xyz_map,
+                                     mesh_diameter=self.diameter, glctx=self.glctx, iteration=iteration, get_vis=False)
+      g['pose_out'].copy_(pose.reshape(4, 4))
+      g['result'].copy_(pose.reshape(4, 4) @ tf)
+
+    # buffers the graph reads must belong to it: the predictor's cached input buffer / workspace may be replaced by a
+    # later register() with another batch size, so the capture allocates its own from the graph's memory pool
+    saved = (self.refiner._ab, self.refiner.model._ws)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    try:
+      with torch.cuda.stream(side):
+        for _ in range(2):          # eager warm-up on the capture stream: lazy one-time initialisation happens here
+          body()
+      torch.cuda.current_stream().wait_stream(side)
+      torch.cuda.synchronize()
+      self.refiner._ab, self.refiner.model._ws = None, None
+      graph = torch.cuda.CUDAGraph()
+      with torch.cuda.graph(graph, stream=side):
+        body()
+    finally:
+      self.refiner._ab, self.refiner.model._ws = saved
+    g['graph'] = graph
+    self._track_graph = g
+    return g
+
+  @torch.inference_mode()
+  def track_one_graphed(self, rgb, depth, K, iteration, extra={}):
+    """track_one (src/estimater.py:250-268) with the frame body replayed from a captured CUDA graph.  rgb / depth:
+    numpy, pinned or device tensors of a fixed [H,W] and dtype; the graph is re-captured when the shape, the
+    intrinsics, the iteration count or the object changes."""
+    if self.pose_last is None:
+      logging.info('Please init pose by register first')
+      raise RuntimeError
+    K = np.asarray(K, dtype=np.float64)
+    rgb_t = torch.as_tensor(rgb)
+    depth_t = torch.as_tensor(depth)
+    H, W = depth_t.shape[:2]
+    rgb_dtype = torch.uint8 if rgb_t.dtype == torch.uint8 else torch.float
+    key = (H, W, int(iteration), K.tobytes(), id(self.mesh_tensors), rgb_dtype, float(self.diameter))
+    g = getattr(self, '_track_graph', None)
+    if g is None or g['key'] != key:
+      g = self._capture_track_graph(key, H, W, K, int(iteration), rgb_dtype)
+    g['rgb'].copy_(rgb_t, non_blocking=True)
+    g['depth'].copy_(depth_t, non_blocking=True)
+    g['pose_in'].copy_(self.pose_last.reshape(4, 4), non_blocking=True)
+    g['graph'].replay()
+    out = g['result'].cpu().numpy().reshape(4, 4)          # the only synchronisation
+    self.pose_last = g['pose_out'].clone().reshape(1, 4, 4)
+    return out
+

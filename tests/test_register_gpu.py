@@ -112,3 +112,21 @@ def test_degenerate_inputs_and_track_one(scene1):
   tf = est.get_tf_to_centered_mesh().cpu().numpy()
   assert out.shape == (4, 4)
   assert _rot_err(out[:3, :3], (ref @ tf)[:3, :3]) < 2e-3 and np.abs(out[:3, 3] - (ref @ tf)[:3, 3]).max() < 2e-4
+
+
+def test_track_one_graph_replay_equals_eager(scene1):
+  """The captured CUDA graph of the frame body replays the same kernels: poses identical to eager track_one, frame
+  after frame (the pose feeds back), and still correct after a register() with another batch size in between."""
+  est, _ = _make(scene1, 'bf16')
+  sc = scene1
+  est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=1)
+  start = est.pose_last.clone()
+  eager = [est.track_one(rgb=sc['rgb'], depth=sc['depth'], K=sc['K'], iteration=2) for _ in range(3)]
+  est.pose_last = start.clone()
+  graphed = [est.track_one_graphed(rgb=sc['rgb'], depth=sc['depth'], K=sc['K'], iteration=2) for _ in range(3)]
+  for a, b in zip(eager, graphed):
+    assert np.array_equal(a, b)
+  est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=1)   # re-sizes the cached buffers
+  est.pose_last = start.clone()
+  again = est.track_one_graphed(rgb=sc['rgb'], depth=sc['depth'], K=sc['K'], iteration=2)
+  assert np.array_equal(again, eager[0])
