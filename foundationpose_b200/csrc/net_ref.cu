@@ -239,6 +239,63 @@ __global__ void __launch_bounds__(256) ln512_token_mean_kernel(const __nv_bfloat
   }
 }
 
+// Small batches (track_one: one group; 8-GPU shards: 32 groups): a cluster of 8 CTAs per group, each CTA takes an
+// eighth of the tokens and the leader sums the eight partial rows through distributed shared memory in rank order
+// (deterministic).  One block per group would leave the device idle for 400 dependent row reductions (44 us at N = 1).
+constexpr int LNM_CLUSTER = 8;
+__global__ void __cluster_dims__(LNM_CLUSTER, 1, 1) __launch_bounds__(256)
+ln512_token_mean_cluster_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                                const float* __restrict__ beta, float* __restrict__ out, int tokens, float eps)
+{
+  __shared__ float part[8][512];
+  __shared__ float row[512];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int group = blockIdx.x / LNM_CLUSTER;
+  float g[16], b[16], acc[16];
+  ln512_params(gamma, beta, lane, g, b);
+#pragma unroll
+  for (int i = 0; i < 16; i++) acc[i] = 0.0f;
+  const __nv_bfloat16* xg = x + (long long)group * tokens * 512;
+  for (int t = (int)rank * 8 + warp; t < tokens; t += 8 * LNM_CLUSTER) {
+    Ln512 r;
+    r.load(xg + (long long)t * 512, lane);
+    r.normalize(g, b, eps);
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[i] += r.v[i];
+  }
+#pragma unroll
+  for (int h = 0; h < 2; h++)
+#pragma unroll
+    for (int i = 0; i < 8; i++) part[warp][h * 256 + lane * 8 + i] = acc[h * 8 + i];
+  __syncthreads();
+  for (int c = threadIdx.x; c < 512; c += 256) {
+    float s = 0.0f;
+#pragma unroll
+    for (int w = 0; w < 8; w++) s += part[w][c];
+    row[c] = s;
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (rank == 0) {
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(row);
+    for (int c = threadIdx.x; c < 512; c += 256) {
+      float s = 0.0f;
+#pragma unroll
+      for (uint32_t r = 0; r < LNM_CLUSTER; r++) {
+        uint32_t remote;
+        float v;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(base + (uint32_t)c * 4u), "r"(r));
+        asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+        s += v;
+      }
+      out[(long long)group * 512 + c] = s / (float)tokens;
+    }
+  }
+  // peers must not exit while the leader still reads their shared memory
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // out[g][c] = mean_t x[g][t][c]; one block per (g, 64-column slab), 256 threads = 4 token lanes x 64 cols
 template <bool XBF>
 __global__ void __launch_bounds__(256) token_mean_kernel(const void* __restrict__ x_, float* __restrict__ out, int tokens,
@@ -335,7 +392,10 @@ int layernorm_token_mean_512(const void* x, const float* gamma, const float* bet
                              cudaStream_t st)
 {
   if ((uintptr_t)x & 15) { fpb_set_error("layernorm_token_mean_512: unaligned input"); return FPB_ERR_ARG; }
-  ln512_token_mean_kernel<<<groups, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
+  if (groups <= 74)      // <= 592 CTAs: two waves of clusters at most
+    ln512_token_mean_cluster_kernel<<<groups * LNM_CLUSTER, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
+  else
+    ln512_token_mean_kernel<<<groups, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }

@@ -225,6 +225,23 @@ def test_score_bf16_close_to_oracle():
   assert ef < 0.05 * np.abs(ref_feat).max() + 5e-3
 
 
+def test_small_and_large_batch_pooling_paths_agree():
+  """LayerNorm + token mean runs as 8-CTA clusters (DSMEM reduction) for <= 74 hypotheses and one block per hypothesis
+  above: same rows through both paths agree to fp32 summation-order noise."""
+  from foundationpose_b200 import nets
+  sd = nets.synthetic_state_dict(nets.REFINE)
+  n, big = 6, 78
+  AB = _inputs(n, 2).cuda().bfloat16()
+  net = nets.Net(nets.REFINE, sd, 'bf16')
+  t, r = net.refine(AB, n)
+  rep = big // n
+  ABb = torch.cat([AB[:n].repeat(rep, 1, 1, 1), AB[n:].repeat(rep, 1, 1, 1)]).contiguous()
+  tb, rb = net.refine(ABb, big)
+  for k in range(rep):
+    assert torch.allclose(tb[k * n:(k + 1) * n], t, atol=2e-6, rtol=1e-5)
+    assert torch.allclose(rb[k * n:(k + 1) * n], r, atol=2e-6, rtol=1e-5)
+
+
 def test_chunking_is_transparent(monkeypatch):
   """N larger than the hypothesis chunk gives the same result as chunk-sized calls."""
   import os, subprocess, sys, json
