@@ -37,6 +37,7 @@ _SIGS = {
   'fpb_render_crops': (ci, [vp, vp, vp, ci, ci, cf, cf, vp, vp, ci, ci, ci, vp, vp, vp, vp]),
   'fpb_warp_crops': (ci, [vp, ci, vp, vp, ci, ci, vp, vp, vp, ci, ci, cf, ci, vp, ci, ci, ci, vp]),
   'fpb_pose_update': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, vp, vp]),
+  'fpb_pose_update_ex': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, ci, ci, vp, vp, ci, vp, vp]),
   'fpb_net_create': (ci, [vp, ci, ci, vp, sz, vp]),
   'fpb_net_destroy': (ci, [vp]),
   'fpb_net_ws_bytes': (sz, [ci, ci, ci]),

@@ -96,32 +96,79 @@ __global__ void crop_params_kernel(const float* __restrict__ poses, int N, K9 K,
 
 struct F3 { float v[3]; };
 
+struct PoseUpdateArgs {
+  float radius, rot_normalizer;
+  F3 tn;
+  int normalize_xyz, trans_rep, rot_rep, S;
+  float K[9];
+};
+
 __global__ void pose_update_kernel(const float* __restrict__ poses, const float* __restrict__ trans,
-                                   const float* __restrict__ rot, int N, float radius, float rot_normalizer, F3 tn,
-                                   int normalize_xyz, float* __restrict__ out)
+                                   const float* __restrict__ rot, int N, PoseUpdateArgs a,
+                                   const float* __restrict__ crop_params, float* __restrict__ out)
 {
   int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   const float* T = poses + (size_t)n * 16;
-  float td[3], r[3];
-  for (int k = 0; k < 3; k++) {
-    float t = trans[n * 3 + k];
-    td[k] = normalize_xyz ? t * radius : tanhf(t) * tn.v[k];
-    r[k] = tanhf(rot[n * 3 + k]) * rot_normalizer;
+  float td[3];
+  if (a.trans_rep == FPB_TRANS_DEEPIM) {
+    // predict_pose_refine.py:201-215: the network predicts the shift of the projected object centre inside the
+    // crop (in units of the crop size) and the depth ratio; back-project through the inverse window and inverse K
+    const float* pr = crop_params + (size_t)n * FPB_CROP_STRIDE;
+    const float* K = a.K;
+    float uvw[3];
+    for (int i = 0; i < 3; i++) uvw[i] = (K[i * 3] * T[3] + K[i * 3 + 1] * T[7]) + K[i * 3 + 2] * T[11];
+    const float u = uvw[0] / uvw[2], v = uvw[1] / uvw[2];
+    const float uc = (pr[0] * u + pr[1] * v) + pr[2], vc = (pr[3] * u + pr[4] * v) + pr[5];      // tf_to_crop @ (u, v, 1)
+    const float z_pred = trans[n * 3 + 2] * T[11];
+    const float up = uc + trans[n * 3] * (float)a.S, vp = vc + trans[n * 3 + 1] * (float)a.S;
+    // inverse window (scale + shift): params[33..36] = (1/s_x, -t_x/s_x, 1/s_y, -t_y/s_y)
+    const float uf = pr[33] * up + pr[34], vf = pr[35] * vp + pr[36];
+    // inverse of the upper-triangular K applied to (uf, vf, 1)
+    const float yn = (vf - K[5]) / K[4];
+    const float xn = ((uf - K[2]) - K[1] * yn) / K[0];
+    td[0] = xn * z_pred - T[3]; td[1] = yn * z_pred - T[7]; td[2] = z_pred - T[11];
+    if (a.normalize_xyz)
+      for (int k = 0; k < 3; k++) td[k] *= a.radius;         // applied to every representation (:226-227)
+  } else {
+    for (int k = 0; k < 3; k++) {
+      float t = trans[n * 3 + k];
+      td[k] = a.normalize_xyz ? t * a.radius : tanhf(t) * a.tn.v[k];
+    }
   }
-  // so3_exp_map (pytorch3d, eps 1e-4), then transposed as in predict_pose_refine.py:222
-  float nrm = (r[0] * r[0] + r[1] * r[1]) + r[2] * r[2];
-  float theta = sqrtf(fmaxf(nrm, 1e-4f));
-  float f1 = sinf(theta) / theta;
-  float f2 = (1.0f - cosf(theta)) / (theta * theta);
-  float Km[9] = {0.f, -r[2], r[1], r[2], 0.f, -r[0], -r[1], r[0], 0.f};
-  float K2[9];
-  for (int i = 0; i < 3; i++)
-    for (int j = 0; j < 3; j++) K2[i * 3 + j] = (Km[i * 3] * Km[j] + Km[i * 3 + 1] * Km[3 + j]) + Km[i * 3 + 2] * Km[6 + j];
   float R[9];
-  for (int i = 0; i < 9; i++) R[i] = (f1 * Km[i] + f2 * K2[i]) + ((i % 4 == 0) ? 1.0f : 0.0f);
+  if (a.rot_rep == FPB_ROT_6D) {
+    // pytorch3d rotation_6d_to_matrix: rows b1, b2, b3 (Gram-Schmidt; F.normalize eps 1e-12)
+    const float* d6 = rot + (size_t)n * 6;
+    float b1[3], b2[3], b3[3];
+    float n1 = sqrtf((d6[0] * d6[0] + d6[1] * d6[1]) + d6[2] * d6[2]);
+    n1 = fmaxf(n1, 1e-12f);
+    for (int k = 0; k < 3; k++) b1[k] = d6[k] / n1;
+    const float dot = (b1[0] * d6[3] + b1[1] * d6[4]) + b1[2] * d6[5];
+    for (int k = 0; k < 3; k++) b2[k] = d6[3 + k] - dot * b1[k];
+    float n2 = sqrtf((b2[0] * b2[0] + b2[1] * b2[1]) + b2[2] * b2[2]);
+    n2 = fmaxf(n2, 1e-12f);
+    for (int k = 0; k < 3; k++) b2[k] = b2[k] / n2;
+    b3[0] = b1[1] * b2[2] - b1[2] * b2[1];
+    b3[1] = b1[2] * b2[0] - b1[0] * b2[2];
+    b3[2] = b1[0] * b2[1] - b1[1] * b2[0];
+    for (int k = 0; k < 3; k++) { R[k] = b1[k]; R[3 + k] = b2[k]; R[6 + k] = b3[k]; }
+  } else {
+    float r[3];
+    for (int k = 0; k < 3; k++) r[k] = tanhf(rot[n * 3 + k]) * a.rot_normalizer;
+    // so3_exp_map (pytorch3d, eps 1e-4)
+    float nrm = (r[0] * r[0] + r[1] * r[1]) + r[2] * r[2];
+    float theta = sqrtf(fmaxf(nrm, 1e-4f));
+    float f1 = sinf(theta) / theta;
+    float f2 = (1.0f - cosf(theta)) / (theta * theta);
+    float Km[9] = {0.f, -r[2], r[1], r[2], 0.f, -r[0], -r[1], r[0], 0.f};
+    float K2[9];
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) K2[i * 3 + j] = (Km[i * 3] * Km[j] + Km[i * 3 + 1] * Km[3 + j]) + Km[i * 3 + 2] * Km[6 + j];
+    for (int i = 0; i < 9; i++) R[i] = (f1 * Km[i] + f2 * K2[i]) + ((i % 4 == 0) ? 1.0f : 0.0f);
+  }
   float* o = out + (size_t)n * 16;
-  // rot_delta = R^T ; B[:3,:3] = rot_delta @ A[:3,:3]
+  // rot_delta = R^T (the .permute(0,2,1) of predict_pose_refine.py:222,224); B[:3,:3] = rot_delta @ A[:3,:3]
   for (int i = 0; i < 3; i++)
     for (int j = 0; j < 3; j++) o[i * 4 + j] = (R[0 * 3 + i] * T[0 * 4 + j] + R[1 * 3 + i] * T[1 * 4 + j]) + R[2 * 3 + i] * T[2 * 4 + j];
   o[3] = T[3] + td[0]; o[7] = T[7] + td[1]; o[11] = T[11] + td[2];
@@ -180,17 +227,30 @@ FPB_EXPORT int fpb_crop_params(const float* poses, int N, const float* K9_h, flo
   return FPB_OK;
 }
 
+FPB_EXPORT int fpb_pose_update_ex(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
+                                  float rot_normalizer, const float* tn3_h, int normalize_xyz, int trans_rep, int rot_rep,
+                                  const float* crop_params, const float* K9_h, int S, float* out_poses, void* stream)
+{
+  FPB_CHECK_ARG(poses && trans && rot && out_poses && N > 0);
+  FPB_CHECK_ARG(trans_rep == FPB_TRANS_TRACKNET || trans_rep == FPB_TRANS_DEEPIM);
+  FPB_CHECK_ARG(rot_rep == FPB_ROT_AXIS_ANGLE || rot_rep == FPB_ROT_6D);
+  FPB_CHECK_ARG(trans_rep == FPB_TRANS_DEEPIM ? (crop_params && K9_h && S > 0) : (normalize_xyz || tn3_h));
+  PoseUpdateArgs a;
+  a.radius = mesh_diameter / 2.0f;
+  a.rot_normalizer = rot_normalizer;
+  for (int i = 0; i < 3; i++) a.tn.v[i] = tn3_h ? tn3_h[i] : 0.f;
+  a.normalize_xyz = normalize_xyz; a.trans_rep = trans_rep; a.rot_rep = rot_rep; a.S = S;
+  for (int i = 0; i < 9; i++) a.K[i] = K9_h ? K9_h[i] : 0.f;
+  pose_update_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(poses, trans, rot, N, a, crop_params, out_poses);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
 FPB_EXPORT int fpb_pose_update(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
                                float rot_normalizer, const float* tn3_h, int normalize_xyz, float* out_poses, void* stream)
 {
-  FPB_CHECK_ARG(poses && trans && rot && out_poses && N > 0);
-  FPB_CHECK_ARG(normalize_xyz || tn3_h);
-  F3 tn = {{0.f, 0.f, 0.f}};
-  if (tn3_h) for (int i = 0; i < 3; i++) tn.v[i] = tn3_h[i];
-  pose_update_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(poses, trans, rot, N, mesh_diameter / 2.0f,
-                                                                       rot_normalizer, tn, normalize_xyz, out_poses);
-  FPB_LAUNCH_CHECK();
-  return FPB_OK;
+  return fpb_pose_update_ex(poses, trans, rot, N, mesh_diameter, rot_normalizer, tn3_h, normalize_xyz, FPB_TRANS_TRACKNET,
+                            FPB_ROT_AXIS_ANGLE, nullptr, nullptr, 0, out_poses, stream);
 }
 
 FPB_EXPORT int fpb_hypotheses_from_stats(const int32_t* stats_i32, const float* stats_f32, const double* Kinv9_h,

@@ -32,6 +32,7 @@ struct EncLayer { Mha att; Lin l1, l2; size_t n1g, n1b, n2g, n2b; Lin fin; };
 
 struct fpb_net {
   int kind, precision;
+  int rot_dim;        // refine: 3 (axis_angle) or 6 (rot_rep='6d', refine_network.py:61-64)
   size_t n_floats;
   float* w32;
   __nv_bfloat16* w16;
@@ -70,7 +71,7 @@ size_t layout(fpb_net* n)
       e.l1 = take_lin(c, D, D);
       e.l2 = take_lin(c, D, D);
       e.n1g = c.take(D); e.n1b = c.take(D); e.n2g = c.take(D); e.n2b = c.take(D);
-      e.fin = take_lin(c, 3, D);
+      e.fin = take_lin(c, h == 1 ? n->rot_dim : 3, D);
     }
   } else {
     n->att = take_mha(c);
@@ -293,12 +294,13 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
 // ---------------------------------------------------------------------------------------------
 FPB_EXPORT int fpb_net_create(fpb_net** out, int kind, int precision, const void* blob_h, size_t bytes, void* stream)
 {
-  FPB_CHECK_ARG(out && blob_h && (kind == FPB_NET_REFINE || kind == FPB_NET_SCORE));
+  FPB_CHECK_ARG(out && blob_h && (kind == FPB_NET_REFINE || kind == FPB_NET_SCORE || kind == FPB_NET_REFINE_6D));
   FPB_CHECK_ARG(precision == FPB_PREC_FP32 || precision == FPB_PREC_BF16);
   cudaStream_t st = (cudaStream_t)stream;
   fpb_net* n = new fpb_net();
   memset(n, 0, sizeof(*n));
-  n->kind = kind; n->precision = precision;
+  n->kind = kind == FPB_NET_REFINE_6D ? FPB_NET_REFINE : kind; n->precision = precision;
+  n->rot_dim = kind == FPB_NET_REFINE_6D ? 6 : 3;
   n->n_floats = layout(n);
   if (bytes != n->n_floats * sizeof(float)) {
     fpb_set_error("fpb_net_create: blob has %zu bytes, expected %zu", bytes, n->n_floats * sizeof(float));
@@ -341,7 +343,8 @@ FPB_EXPORT size_t fpb_net_blob_floats(int kind)
 {
   fpb_net tmp;
   memset(&tmp, 0, sizeof(tmp));
-  tmp.kind = kind;
+  tmp.kind = kind == FPB_NET_REFINE_6D ? FPB_NET_REFINE : kind;
+  tmp.rot_dim = kind == FPB_NET_REFINE_6D ? 6 : 3;
   return layout(&tmp);
 }
 
@@ -359,7 +362,7 @@ static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* o
     RET(layernorm_rows(w.y1, c.bf, c.F(e.n2g), c.F(e.n2b), w.ff, c.bf, R, D, 1e-5f, c.st));
     RET(token_mean(w.ff, c.bf, w.pooled, n, TOK, D, c.st));                            // mean commutes with Linear
   }
-  RET(small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, 3, c.st));
+  RET(small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, e.fin.N, c.st));
   return FPB_OK;
 }
 
@@ -387,7 +390,7 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
     }
     RET(run_encoders(c, in, n, w));
     RET(encoder_layer(c, net->head[0], n, w, out_trans + (size_t)b0 * 3));
-    RET(encoder_layer(c, net->head[1], n, w, out_rot + (size_t)b0 * 3));
+    RET(encoder_layer(c, net->head[1], n, w, out_rot + (size_t)b0 * net->rot_dim));
   }
   return FPB_OK;
 }

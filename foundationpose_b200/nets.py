@@ -16,6 +16,7 @@ from . import _lib
 from ._lib import lib, check, ptr, stream
 
 REFINE, SCORE = 0, 1
+REFINE_6D = 2      # fpb_net_create kind for a RefineNet whose rot head has 6 outputs (include/fpb200.h)
 PREC = {'fp32': 0, 'bf16': 1}
 D, TOK = 512, 400
 # (Cin, Cout, k, stride) of the 15 convolutions, in execution order
@@ -95,8 +96,9 @@ def pack_state_dict(kind, sd, eps=1e-5):
       for nk in ('norm1', 'norm2'):
         b.add(sd[f'{head}.0.{nk}.weight']); b.add(sd[f'{head}.0.{nk}.bias'])
       fw, fb = sd[f'{head}.1.weight'], sd[f'{head}.1.bias']
-      if fw.shape[0] != 3:
-        raise NotImplementedError("rot_rep='6d' heads are not supported (released weights use axis_angle)")
+      want = (3, 6) if head == 'rot_head' else (3,)       # rot_rep='6d' -> Linear(512, 6) (refine_network.py:61-69)
+      if fw.shape[0] not in want:
+        raise ValueError(f'{head}.1.weight has {fw.shape[0]} rows, expected one of {want}')
       b.add(fw); b.add(fb)
   else:
     b.mha(sd, 'att')
@@ -105,7 +107,7 @@ def pack_state_dict(kind, sd, eps=1e-5):
   return b.finish()
 
 
-def synthetic_state_dict(kind, seed=1234, head_gain=None, calibrate=True):
+def synthetic_state_dict(kind, seed=1234, head_gain=None, calibrate=True, rot_out_dim=3):
   """Seeded random weights with the reference's keys and shapes: He-initialised convolutions,
   randomised eval-mode BatchNorm statistics, xavier attention projections; the last Linear of each head is
   scaled so pose updates are a few mm / degrees and score logits are separated."""
@@ -151,7 +153,7 @@ def synthetic_state_dict(kind, seed=1234, head_gain=None, calibrate=True):
       for nk in ('norm1', 'norm2'):
         sd[f'{head}.0.{nk}.weight'] = 0.75 + 0.5 * rand(D)
         sd[f'{head}.0.{nk}.bias'] = randn(D) * 0.05
-      lin(f'{head}.1', 3, D, gain=hg[head], bias_std=0.0)
+      lin(f'{head}.1', rot_out_dim if head == 'rot_head' else 3, D, gain=hg[head], bias_std=0.0)
   else:
     mha('att')
     mha('att_cross', qk_gain=10.0)
@@ -222,9 +224,10 @@ class Net:
     self.kind, self.precision = kind, PREC[precision]
     self.bf16 = precision == 'bf16'
     blob = pack_state_dict(kind, state_dict)
+    self.rot_dim = int(state_dict['rot_head.1.weight'].shape[0]) if kind == REFINE else 0
     h = ctypes.c_void_p()
-    check(lib().fpb_net_create(ctypes.byref(h), kind, self.precision, blob.ctypes.data_as(ctypes.c_void_p),
-                               blob.nbytes, stream()))
+    check(lib().fpb_net_create(ctypes.byref(h), REFINE_6D if self.rot_dim == 6 else kind, self.precision,
+                               blob.ctypes.data_as(ctypes.c_void_p), blob.nbytes, stream()))
     self.handle = h
     self._ws = None
 
@@ -240,11 +243,11 @@ class Net:
     return self._ws
 
   def refine(self, AB, N):
-    """AB [2N,160,168,8] (utils.net_input_buffer layout) -> (trans [N,3], rot [N,3]) fp32"""
+    """AB [2N,160,168,8] (utils.net_input_buffer layout) -> (trans [N,3], rot [N,3] or [N,6] for rot_rep='6d') fp32"""
     AB = pad_input(AB)
     assert AB.dtype == self.act_dtype and AB.shape == (2 * N, 160, 168, 8)
     trans = torch.empty((N, 3), dtype=torch.float, device='cuda')
-    rot = torch.empty((N, 3), dtype=torch.float, device='cuda')
+    rot = torch.empty((N, self.rot_dim), dtype=torch.float, device='cuda')
     check(lib().fpb_refine_forward(self.handle, ptr(AB), N, ptr(self.workspace(N)), ptr(trans), ptr(rot), stream()))
     return trans, rot
 

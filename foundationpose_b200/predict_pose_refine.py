@@ -70,10 +70,16 @@ class PoseRefinePredictor:
         ckpt_path = cand
     if state_dict is None and ckpt_path is not None:
       state_dict = load_checkpoint_state_dict(ckpt_path)
+    if self.cfg['trans_rep'] not in U.TRANS_REPS or self.cfg['c_in'] != 6:
+      raise NotImplementedError("trans_rep must be 'tracknet' or 'deepim' and c_in must be 6")
+    if self.cfg['rot_rep'] not in U.ROT_REPS:
+      raise RuntimeError(f"unknown rot_rep {self.cfg['rot_rep']}")              # predict_pose_refine.py:225-226
+    rot_dim = 6 if self.cfg['rot_rep'] == '6d' else 3
     if state_dict is None:
-      state_dict = nets.synthetic_state_dict(nets.REFINE, seed)
-    if self.cfg['trans_rep'] != 'tracknet' or self.cfg['rot_rep'] != 'axis_angle' or self.cfg['c_in'] != 6:
-      raise NotImplementedError('only trans_rep=tracknet, rot_rep=axis_angle, c_in=6 (the released configuration)')
+      state_dict = nets.synthetic_state_dict(nets.REFINE, seed, rot_out_dim=rot_dim)
+    if int(state_dict['rot_head.1.weight'].shape[0]) != rot_dim:
+      raise ValueError(f"rot_rep={self.cfg['rot_rep']} needs a {rot_dim}-output rot head, the weights have "
+                       f"{int(state_dict['rot_head.1.weight'].shape[0])}")
     self.state_dict = state_dict
     self.precision = precision
     self.model = nets.Net(nets.REFINE, state_dict, precision)
@@ -107,11 +113,13 @@ class PoseRefinePredictor:
     tn = list(self.cfg['trans_normalizer']) if not isinstance(self.cfg['trans_normalizer'], float) else [self.cfg['trans_normalizer']] * 3
     trans = rot = None
     for _ in range(iteration):
-      make_crop_data_batch(self.cfg['input_resize'], B_in_cams, mesh, rgb_t, None, K, self.cfg['crop_ratio'], xyz_t,
-                           mesh_diameter=mesh_diameter, cfg=self.cfg, mesh_tensors=mesh_tensors, out_AB=AB)
+      _, params = make_crop_data_batch(self.cfg['input_resize'], B_in_cams, mesh, rgb_t, None, K, self.cfg['crop_ratio'],
+                                       xyz_t, mesh_diameter=mesh_diameter, cfg=self.cfg, mesh_tensors=mesh_tensors,
+                                       out_AB=AB)
       trans, rot = self.model.refine(AB, N)
       B_in_cams = U.pose_update(B_in_cams, trans, rot, mesh_diameter, self.cfg['rot_normalizer'], tn,
-                                self.cfg['normalize_xyz'])
+                                self.cfg['normalize_xyz'], trans_rep=self.cfg['trans_rep'], rot_rep=self.cfg['rot_rep'],
+                                crop_params=params, K=K, S=S)
     self.last_trans_update = trans
     self.last_rot_update = rot
     return B_in_cams, None

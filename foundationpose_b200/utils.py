@@ -396,14 +396,31 @@ def warp_crops(rgb_t, xyz_map_t, depth_t, poses, params, K, S, mesh_diameter, mo
   return out_B
 
 
-def pose_update(poses, trans, rot, mesh_diameter, rot_normalizer, trans_normalizer=None, normalize_xyz=True):
-  """predict_pose_refine.py:195-231 + egocentric_delta_pose_to_pose (src/Utils.py:848-855) in one kernel."""
+TRANS_REPS = {'tracknet': 0, 'deepim': 1}
+ROT_REPS = {'axis_angle': 0, '6d': 1}
+
+
+def pose_update(poses, trans, rot, mesh_diameter, rot_normalizer, trans_normalizer=None, normalize_xyz=True,
+                trans_rep='tracknet', rot_rep='axis_angle', crop_params=None, K=None, S=160):
+  """predict_pose_refine.py:195-231 + egocentric_delta_pose_to_pose (src/Utils.py:848-855) in one kernel.
+  trans_rep='deepim' (:201-215) needs the iteration's crop parameters, K and the crop size; rot_rep='6d' (:223-224)
+  takes rot [N,6]."""
   poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
   out = torch.empty_like(poses)
   tn = f32_host(trans_normalizer, 3) if trans_normalizer is not None else None
-  check(lib().fpb_pose_update(ptr(poses), ptr(trans.contiguous()), ptr(rot.contiguous()), len(poses),
-                              float(mesh_diameter), float(rot_normalizer), hptr(tn), 1 if normalize_xyz else 0,
-                              ptr(out), stream()))
+  if trans_rep not in TRANS_REPS or rot_rep not in ROT_REPS:
+    raise RuntimeError(f'unknown trans_rep / rot_rep: {trans_rep} / {rot_rep}')
+  rot = rot.contiguous()
+  assert rot.shape == (len(poses), 6 if rot_rep == '6d' else 3)
+  if trans_rep == 'tracknet' and rot_rep == 'axis_angle':
+    check(lib().fpb_pose_update(ptr(poses), ptr(trans.contiguous()), ptr(rot), len(poses),
+                                float(mesh_diameter), float(rot_normalizer), hptr(tn), 1 if normalize_xyz else 0,
+                                ptr(out), stream()))
+    return out
+  K9 = f32_host(torch.as_tensor(K).detach().cpu().numpy() if torch.is_tensor(K) else K, 9) if K is not None else None
+  check(lib().fpb_pose_update_ex(ptr(poses), ptr(trans.contiguous()), ptr(rot), len(poses), float(mesh_diameter),
+                                 float(rot_normalizer), hptr(tn), 1 if normalize_xyz else 0, TRANS_REPS[trans_rep],
+                                 ROT_REPS[rot_rep], ptr(crop_params), hptr(K9), int(S), ptr(out), stream()))
   return out
 
 

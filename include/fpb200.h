@@ -122,12 +122,25 @@ int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_hw3, const f
 int fpb_pose_update(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
                     float rot_normalizer, const float* tn3_h, int normalize_xyz, float* out_poses,
                     void* stream);
+/* ---- the config-gated representations of the same update (predict_pose_refine.py:201-224):
+ *      trans_rep FPB_TRANS_DEEPIM  : trans = (du, dv) in crop units + z ratio; needs the crop parameters of the
+ *                                    iteration (fpb_crop_params output), K and the crop size S (= input_resize[0]);
+ *      rot_rep   FPB_ROT_6D        : rot is [N,6], pytorch3d rotation_6d_to_matrix (Gram-Schmidt), transposed.
+ *      FPB_TRANS_TRACKNET + FPB_ROT_AXIS_ANGLE is fpb_pose_update. ---- */
+#define FPB_TRANS_TRACKNET 0
+#define FPB_TRANS_DEEPIM 1
+#define FPB_ROT_AXIS_ANGLE 0
+#define FPB_ROT_6D 1
+int fpb_pose_update_ex(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
+                       float rot_normalizer, const float* tn3_h, int normalize_xyz, int trans_rep, int rot_rep,
+                       const float* crop_params, const float* K9_h, int S, float* out_poses, void* stream);
 
 /* ---- networks: learning/models/refine_network.py:26-93, score_network.py:27-90.
  *      Weights arrive as a flat host blob produced by foundationpose_b200.nets.pack_* (BN folded). ---- */
 typedef struct fpb_net fpb_net;
 #define FPB_NET_REFINE 0
 #define FPB_NET_SCORE 1
+#define FPB_NET_REFINE_6D 2   /* RefineNet built with rot_rep='6d' (refine_network.py:61-64): out_rot is [N,6] */
 int fpb_net_create(fpb_net** out, int kind, int precision, const void* blob_h, size_t bytes, void* stream);
 int fpb_net_destroy(fpb_net* net);
 size_t fpb_net_ws_bytes(int kind, int precision, int N);

@@ -111,7 +111,7 @@ class ScoreNetMultiPair(nn.Module):
 
 def build(kind, state_dict):
   """kind in {'refine','score'}; strict load proves state_dict key compatibility."""
-  net = RefineNet() if kind == 'refine' else ScoreNetMultiPair()
+  net = RefineNet(rot_out_dim=int(state_dict['rot_head.1.weight'].shape[0])) if kind == 'refine' else ScoreNetMultiPair()
   net.load_state_dict(state_dict, strict=True)
   return net.eval()
 

@@ -127,15 +127,52 @@ def so3_exp_map(log_rot, eps=1e-4):
   return (fac1[:, None, None] * Km + fac2[:, None, None] * K2 + np.eye(3, dtype=np.float32)[None]).astype(np.float32)
 
 
-def pose_update(poses, trans, rot, mesh_diameter, rot_normalizer, trans_normalizer=None, normalize_xyz=True):
+def rotation_6d_to_matrix(d6):
+  """pytorch3d.transforms.rotation_6d_to_matrix (Zhou et al. 2019; third-party, source absent: restated)."""
+  d6 = _f32(d6)
+  a1, a2 = d6[:, :3], d6[:, 3:]
+  b1 = a1 / np.maximum(np.linalg.norm(a1, axis=-1, keepdims=True), np.float32(1e-12))
+  b2 = a2 - (b1 * a2).sum(-1, keepdims=True) * b1
+  b2 = b2 / np.maximum(np.linalg.norm(b2, axis=-1, keepdims=True), np.float32(1e-12))
+  b3 = np.cross(b1, b2)
+  return np.stack([b1, b2, b3], axis=-2).astype(np.float32)
+
+
+def pose_update(poses, trans, rot, mesh_diameter, rot_normalizer, trans_normalizer=None, normalize_xyz=True,
+                trans_rep='tracknet', rot_rep='axis_angle', tf_to_crops=None, K=None, S=160):
   """predict_pose_refine.py:195-231 + egocentric_delta_pose_to_pose (src/Utils.py:848-855)."""
   poses = _f32(poses).reshape(-1, 4, 4)
   trans = _f32(trans); rot = _f32(rot)
-  if normalize_xyz:
-    trans_delta = trans * np.float32(mesh_diameter / 2)
+  if trans_rep == 'tracknet':
+    if not normalize_xyz:
+      trans_delta = np.tanh(trans) * _f32(trans_normalizer).reshape(1, 3)
+    else:
+      trans_delta = trans.copy()
+  elif trans_rep == 'deepim':                                   # :201-215
+    K32 = _f32(K).reshape(3, 3)
+    tf = _f32(tf_to_crops).reshape(-1, 3, 3)
+    centers = poses[:, :3, 3]
+    uvs = (K32[None] @ centers.reshape(-1, 3, 1)).reshape(-1, 3)
+    uvs = uvs / uvs[:, 2:3]
+    uvA_crop = (tf @ uvs.reshape(-1, 3, 1)).reshape(-1, 3)[:, :2]
+    z_pred = trans[:, 2] * poses[:, 2, 3]
+    uv_pred_crop = uvA_crop + trans[:, :2] * np.float32(S)
+    tf_inv = np.linalg.inv(tf.astype(np.float64)).astype(np.float32)
+    uv_pred = (tf_inv[:, :2, :2] @ uv_pred_crop[..., None] + tf_inv[:, :2, 2:])[..., 0]      # transform_pts
+    center_pred = np.concatenate([uv_pred, np.ones((len(uv_pred), 1), np.float32)], -1)
+    K_inv = np.linalg.inv(K32.astype(np.float64)).astype(np.float32)
+    center_pred = (K_inv[None] @ center_pred.reshape(-1, 3, 1)).reshape(-1, 3) * z_pred.reshape(-1, 1)
+    trans_delta = center_pred - centers
   else:
-    trans_delta = np.tanh(trans) * _f32(trans_normalizer).reshape(1, 3)
-  rot_delta = so3_exp_map(np.tanh(rot) * np.float32(rot_normalizer)).transpose(0, 2, 1)
+    trans_delta = trans.copy()
+  if rot_rep == 'axis_angle':
+    rot_delta = so3_exp_map(np.tanh(rot) * np.float32(rot_normalizer)).transpose(0, 2, 1)
+  elif rot_rep == '6d':
+    rot_delta = rotation_6d_to_matrix(rot).transpose(0, 2, 1)
+  else:
+    raise RuntimeError
+  if normalize_xyz:
+    trans_delta = trans_delta * np.float32(mesh_diameter / 2)
   out = np.tile(np.eye(4, dtype=np.float32)[None], (len(poses), 1, 1))
   out[:, :3, 3] = poses[:, :3, 3] + trans_delta
   out[:, :3, :3] = rot_delta @ poses[:, :3, :3]

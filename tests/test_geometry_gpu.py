@@ -200,3 +200,28 @@ def test_pose_update_close():
     got = U.pose_update(g, torch.as_tensor(trans, device='cuda'), torch.as_tensor(rot, device='cuda'), 0.21,
                         0.3490658504, [0.02, 0.02, 0.05], nx).cpu().numpy()
     assert np.abs(got - ref).max() < 2e-6     # sinf/cosf/tanhf: device vs numpy
+
+
+@pytest.mark.parametrize('trans_rep,rot_rep', [('deepim', 'axis_angle'), ('tracknet', '6d'), ('deepim', '6d')])
+def test_pose_update_config_gated_representations(trans_rep, rot_rep, scene2):
+  """trans_rep='deepim' (predict_pose_refine.py:201-215) and rot_rep='6d' (:223-224) against the numpy restatement."""
+  from foundationpose_b200 import utils as U
+  rng = np.random.default_rng(5)
+  poses, _ = hypo_poses(scene2, n=40, jitter_seed=2)
+  K = scene2['K']
+  S = 160
+  cp = oo.crop_params(poses, K, scene2['diameter'], 1.2, S, 480, 640)
+  params = U.crop_params(poses, K, scene2['diameter'], 1.2, S, 480, 640)
+  trans = rng.normal(0, 0.05, (len(poses), 3)).astype(np.float32)
+  trans[:, 2] = 1 + rng.normal(0, 0.02, len(poses)).astype(np.float32)          # deepim: depth ratio
+  rot = rng.normal(0, 1.0, (len(poses), 6 if rot_rep == '6d' else 3)).astype(np.float32)
+  for nx in (True, False):
+    ref = oo.pose_update(poses, trans, rot, scene2['diameter'], 0.3490658504, [0.02, 0.02, 0.05], nx, trans_rep=trans_rep,
+                         rot_rep=rot_rep, tf_to_crops=cp['tf'].reshape(-1, 3, 3), K=K, S=S)
+    got = U.pose_update(poses, torch.as_tensor(trans, device='cuda'), torch.as_tensor(rot, device='cuda'),
+                        scene2['diameter'], 0.3490658504, [0.02, 0.02, 0.05], nx, trans_rep=trans_rep, rot_rep=rot_rep,
+                        crop_params=params, K=K, S=S).cpu().numpy()
+    assert np.abs(got[:, :3, :3] - ref[:, :3, :3]).max() < 3e-6
+    assert np.abs(got[:, :3, 3] - ref[:, :3, 3]).max() < 2e-5      # fp32 back-projection of ~300 px coordinates
+    R = got[:, :3, :3].astype(np.float64)
+    assert np.abs(R @ R.transpose(0, 2, 1) - np.eye(3)).max() < 1e-5

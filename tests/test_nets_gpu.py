@@ -179,6 +179,24 @@ def test_refine_fp32_matches_oracle(n, monkeypatch):
   assert np.abs(r.cpu().numpy() - ref_r).max() < 2e-4, np.abs(r.cpu().numpy() - ref_r).max()
 
 
+def test_refine_6d_rot_head_matches_oracle():
+  """rot_rep='6d': Linear(512, 6) rot head (refine_network.py:61-69) through FPB_NET_REFINE_6D."""
+  from foundationpose_b200 import nets
+  from oracle import nets as on
+  sd = nets.synthetic_state_dict(nets.REFINE, rot_out_dim=6)
+  n = 3
+  AB = _inputs(n, 6)
+  ref_t, ref_r = on.forward_chunked(on.build('refine', sd), 'refine', AB[:n, ..., :6].numpy(), AB[n:, ..., :6].numpy())
+  assert ref_r.shape == (n, 6)
+  net = nets.Net(nets.REFINE, sd, 'fp32')
+  t, r = net.refine(AB.cuda(), n)
+  assert r.shape == (n, 6)
+  assert np.abs(t.cpu().numpy() - ref_t).max() < 2e-4 and np.abs(r.cpu().numpy() - ref_r).max() < 2e-4
+  net16 = nets.Net(nets.REFINE, sd, 'bf16')
+  t16, r16 = net16.refine(AB.cuda().bfloat16(), n)
+  assert np.abs(r16.cpu().numpy() - ref_r).max() < 0.05 * np.abs(ref_r).max() + 5e-3
+
+
 def test_refine_bf16_close_to_oracle():
   from foundationpose_b200 import nets
   from oracle import nets as on

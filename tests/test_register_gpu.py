@@ -130,3 +130,33 @@ def test_track_one_graph_replay_equals_eager(scene1):
   est.pose_last = start.clone()
   again = est.track_one_graphed(rgb=sc['rgb'], depth=sc['depth'], K=sc['K'], iteration=2)
   assert np.array_equal(again, eager[0])
+
+
+def test_refiner_deepim_6d_configuration(scene1):
+  """PoseRefinePredictor with the config-gated trans_rep='deepim' / rot_rep='6d' (predict_pose_refine.py:201-224):
+  one iteration equals the oracle update applied to the CUDA network outputs; poses stay valid rigid transforms."""
+  from foundationpose_b200 import nets, utils as U
+  from foundationpose_b200.predict_pose_refine import PoseRefinePredictor
+  from oracle import ops as oo
+  from tests.helpers import centered, hypo_poses
+  sc = scene1
+  mesh, _ = centered(sc)
+  poses, d = hypo_poses(sc, n=8, jitter_seed=1)
+  ref = PoseRefinePredictor(cfg=dict(trans_rep='deepim', rot_rep='6d'), precision='fp32')
+  assert ref.model.rot_dim == 6
+  with pytest.raises(ValueError):
+    PoseRefinePredictor(cfg=dict(rot_rep='6d'), state_dict=nets.synthetic_state_dict(nets.REFINE))
+  with pytest.raises(RuntimeError):
+    PoseRefinePredictor(cfg=dict(rot_rep='quat'))
+  xyz = oo.depth2xyzmap(d, sc['K'])
+  mt = U.make_mesh_tensors(mesh)
+  out, _ = ref.predict(rgb=sc['rgb'], depth=d, K=sc['K'], ob_in_cams=poses, xyz_map=xyz, mesh=mesh, mesh_tensors=mt,
+                       mesh_diameter=sc['diameter'], iteration=1)
+  out = out.cpu().numpy()
+  cp = oo.crop_params(poses, sc['K'], sc['diameter'], 1.2, 160, 480, 640)
+  want = oo.pose_update(poses, ref.last_trans_update.cpu().numpy(), ref.last_rot_update.cpu().numpy(), sc['diameter'],
+                        ref.cfg['rot_normalizer'], ref.cfg['trans_normalizer'], True, trans_rep='deepim', rot_rep='6d',
+                        tf_to_crops=cp['tf'].reshape(-1, 3, 3), K=sc['K'], S=160)
+  assert np.abs(out - want).max() < 5e-5
+  R = out[:, :3, :3].astype(np.float64)
+  assert np.abs(R @ R.transpose(0, 2, 1) - np.eye(3)).max() < 1e-5 and np.isfinite(out).all()

@@ -33,6 +33,7 @@ def main():
   ap = argparse.ArgumentParser()
   ap.add_argument('--reps', type=int, default=50)
   ap.add_argument('--cfg', type=int, default=2)
+  ap.add_argument('--inplane', type=int, default=60, help='in-plane rotation step in degrees (15 -> 1008 hypotheses)')
   args = ap.parse_args()
   sc = synthetic.make_scene(args.cfg, n_points=300000)
   mesh = sc['mesh'].copy()
@@ -40,7 +41,7 @@ def main():
   mesh.vertices = mesh.vertices - center.reshape(1, 3)      # as FoundationPose.reset_object (src/estimater.py:44-51)
   mt = U.make_mesh_tensors(mesh)
   S, H, W = 160, sc['H'], sc['W']
-  poses = make_rotation_grid_host(40, 60).astype(np.float32)
+  poses = make_rotation_grid_host(40, args.inplane).astype(np.float32)
   poses[:, :3, 3] = (sc['gt_pose'][:3, :3] @ center + sc['gt_pose'][:3, 3]).astype(np.float32)
   N = len(poses)
   poses_t = torch.as_tensor(poses, device='cuda')
