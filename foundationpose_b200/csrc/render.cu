@@ -195,17 +195,14 @@ __device__ __forceinline__ void raster_pixel(const TriSetup& t, const float4 c0,
 constexpr int SMALL_TRI_PIXELS = 16;
 
 // One triangle per lane; the whole warp must call this together (the large-footprint path is warp-cooperative).
-// sn: snapped vertex positions of this hypothesis.
-__device__ __forceinline__ void raster_triangle(const int32_t* __restrict__ faces, int F, int f, const float4* __restrict__ cl,
-                                                const int2* sn, int S, unsigned long long* __restrict__ zb)
+// valid: this lane holds face f with corner indices i0..i2 and their snapped positions s0..s2.
+__device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i1, int i2, const int2 s0, const int2 s1,
+                                                const int2 s2, const float4* __restrict__ cl, int S,
+                                                unsigned long long* __restrict__ zb)
 {
   TriSetup t;
   t.ok = 0;
-  int i0 = 0, i1 = 0, i2 = 0;
-  if (f < F) {
-    i0 = faces[f * 3]; i1 = faces[f * 3 + 1]; i2 = faces[f * 3 + 2];
-    tri_setup(sn[i0], sn[i1], sn[i2], S, t);
-  }
+  if (valid) tri_setup(s0, s1, s2, S, t);
   int big = 0;
   if (t.ok) {
     int npx = (t.px1 - t.px0 + 1) * (t.py1 - t.py0 + 1);
@@ -278,16 +275,38 @@ __device__ __forceinline__ void raster_triangle(const int32_t* __restrict__ face
   }
 }
 
-// One thread per (hypothesis, face); the per-corner gathers are served by L1/L2 (a variant that staged the snapped
-// positions of one hypothesis in shared memory with bulk async copies measured no faster: the kernel is bound by
-// instruction issue in the divergent fragment loop, not by the gathers).
-__global__ void __launch_bounds__(256, 4) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
+// RASTER_TPT faces per thread (256 * RASTER_TPT consecutive faces per block): all corner indices are fetched first, then
+// all snapped positions, so every thread keeps 3 * RASTER_TPT independent gathers in flight -- with one face per thread
+// the kernel was bound by the latency of the two dependent loads of short-lived blocks (82 G triangles/s at 500 k faces
+// x 1008 hypotheses).  The gathers are served by L1/L2; staging the positions in shared memory (whole array or the
+// block's vertex range, by bulk async copy) measured slower at both mesh sizes.
+constexpr int RASTER_TPT = 4;
+
+__global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
                                                      const float4* __restrict__ clip, const int2* __restrict__ snap,
                                                      int S, unsigned long long* __restrict__ zbuf)
 {
   const int n = blockIdx.y;
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  raster_triangle(faces, F, f, clip + (size_t)n * V, snap + (size_t)n * V, S, zbuf + (size_t)n * S * S);
+  const int f0 = blockIdx.x * (256 * RASTER_TPT) + threadIdx.x;
+  const int2* sn = snap + (size_t)n * V;
+  int idx[RASTER_TPT][3];
+#pragma unroll
+  for (int k = 0; k < RASTER_TPT; k++) {
+    const int f = f0 + k * 256;
+#pragma unroll
+    for (int c = 0; c < 3; c++) idx[k][c] = f < F ? faces[f * 3 + c] : 0;
+  }
+  int2 sp[RASTER_TPT][3];
+#pragma unroll
+  for (int k = 0; k < RASTER_TPT; k++)
+#pragma unroll
+    for (int c = 0; c < 3; c++) sp[k][c] = sn[idx[k][c]];
+#pragma unroll
+  for (int k = 0; k < RASTER_TPT; k++) {
+    const int f = f0 + k * 256;
+    raster_triangle(f < F, f, idx[k][0], idx[k][1], idx[k][2], sp[k][0], sp[k][1], sp[k][2], clip + (size_t)n * V, S,
+                    zbuf + (size_t)n * S * S);
+  }
 }
 
 // a / 255.0f, correctly rounded, without the generic division sequence (range check + slow path on zero numerators):
@@ -580,7 +599,7 @@ FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const 
   FPB_CUDA(cudaMemsetAsync(zbuf, 0xff, (size_t)N * S * S * sizeof(unsigned long long), st));
   vertex_kernel<<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, S, clip, camd, snap);
   FPB_LAUNCH_CHECK();
-  raster_kernel<<<dim3(fpb_cdiv(F, 256), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
+  raster_kernel<<<dim3(fpb_cdiv(F, 256 * RASTER_TPT), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
   FPB_LAUNCH_CHECK();
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
   const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
