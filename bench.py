@@ -234,6 +234,37 @@ def main():
   total_hyp = n_hyp * world * args.steps
   value = total_hyp / (dev_ms / 1e3)
   e2e_value = total_hyp / (e_wall_ms / 1e3)
+  # per-stage device time: CUDA events at the boundaries of the three stages of one register(), median of 5
+  stages = None
+  if rank == 0:
+    from foundationpose_b200 import utils as U_
+    marks = []
+
+    def wrap(obj, name, tag):
+      f = getattr(obj, name)
+
+      def g(*a, **k):
+        e_in = torch.cuda.Event(enable_timing=True); e_in.record()
+        r = f(*a, **k)
+        e_out = torch.cuda.Event(enable_timing=True); e_out.record()
+        marks.append((tag, e_in, e_out))
+        return r
+      setattr(obj, name, g)
+      return f
+    saved = [(U_, 'register_prologue', wrap(U_, 'register_prologue', 'prologue')),
+             (est.refiner, 'predict', wrap(est.refiner, 'predict', 'refine')),
+             (est.scorer, 'predict', wrap(est.scorer, 'predict', 'score'))]
+    acc = {'prologue': [], 'refine': [], 'score': []}
+    for _ in range(5):
+      marks.clear()
+      est.register(K=K, rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
+      torch.cuda.synchronize()
+      for tag, a, b in marks:
+        acc[tag].append(a.elapsed_time(b))
+    for obj, name, f in saved:
+      setattr(obj, name, f)
+    stages = {k + '_ms': float(np.median(v)) for k, v in acc.items()}
+    stages['note'] = f'device time between CUDA events; refine = {ITERS} x (crop windows, render, warp, RefineNet, pose update); score = render, warp, ScoreNet, ranking'
   strong = None
   if world > 1:
     def step_strong():
@@ -272,6 +303,8 @@ def main():
               e2e=dict(value=e2e_value, unit='hypotheses/s', h2d_bytes_per_step=h2d, d2h_bytes_per_step=64 + 32,
                        register_ms_p50=float(np.median(e_per) * 1e3)),
               gpu_launches=int(launches), roofline=roof, cpu_baseline=cpu, clocks=sampler.summary())
+  if stages:
+    line['stages'] = stages
   if strong:
     line['strong'] = strong
   print(json.dumps(line), flush=True)
