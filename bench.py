@@ -152,6 +152,7 @@ def time_dominant_kernel(torch, n_rep=20):
 def main():
   ap = argparse.ArgumentParser()
   ap.add_argument('--gpus', type=int, default=1)
+  ap.add_argument('--exchange', default='auto', choices=['auto', 'p2p', 'nccl'], help='sharded register(): how features/poses are exchanged')
   ap.add_argument('--steps', type=int, default=10)
   ap.add_argument('--warmup', type=int, default=3)
   ap.add_argument('--impl', default='ours')
@@ -268,10 +269,13 @@ def main():
   strong = None
   if world > 1:
     def step_strong():
-      return fdist.register_sharded(est, K, h_rgb, h_depth, h_mask, iteration=ITERS)
+      return fdist.register_sharded(est, K, h_rgb, h_depth, h_mask, iteration=ITERS, exchange=args.exchange)
     s_dev, s_wall, s_per = timed(step_strong, args.steps, 2)
+    how = ('NCCL all_gather of features + poses' if args.exchange == 'nccl' else
+           'feature rows / poses stored into every rank\'s table by the producing kernels (peer-mapped symmetric memory over '
+           'NVLink) + one device barrier')
     strong = dict(register_ms_p50=float(np.median(s_per) * 1e3), value=n_hyp * args.steps / (s_wall / 1e3), unit='hypotheses/s',
-                  note='one object, 252 hypotheses sharded over the ranks; features + poses all-gathered (NCCL)')
+                  exchange=args.exchange, note='one object, 252 hypotheses sharded over the ranks; ' + how)
   if rank != 0:
     if world > 1:
       dist.destroy_process_group()

@@ -49,6 +49,8 @@ _SIGS = {
   'fpb_debug_attention': (ci, [vp, vp, ctypes.c_longlong, vp, vp, ci, vp]),
   'fpb_refine_forward': (ci, [vp, vp, ci, vp, vp, vp, vp]),
   'fpb_score_features': (ci, [vp, vp, ci, vp, vp, vp]),
+  'fpb_score_features_multi': (ci, [vp, vp, ci, vp, vp, ci, vp]),
+  'fpb_store_multi_f32': (ci, [vp, ctypes.c_longlong, vp, ci, vp]),
   'fpb_score_cross': (ci, [vp, vp, ci, ci, vp, vp, vp]),
 }
 

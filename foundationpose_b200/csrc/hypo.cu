@@ -265,3 +265,30 @@ FPB_EXPORT int fpb_hypotheses_from_stats(const int32_t* stats_i32, const float* 
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }
+
+// ---- small multi-destination store: the refined poses of this rank's hypotheses into every rank's pose table
+//      (peer-mapped symmetric memory), the pose half of the sharded register()'s exchange ----
+namespace {
+struct Dst8 { float* p[FPB_MAX_PEERS]; int n; };
+__global__ void store_multi_kernel(const float* __restrict__ src, long long count, Dst8 dst)
+{
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const float v = src[i];
+  for (int d = 0; d < dst.n; d++) dst.p[d][i] = v;
+}
+}  // namespace
+
+FPB_EXPORT int fpb_store_multi_f32(const float* src, long long count, float* const* dst_ptrs_h, int n_dst, void* stream)
+{
+  FPB_CHECK_ARG(src && count > 0 && dst_ptrs_h && n_dst >= 1 && n_dst <= FPB_MAX_PEERS);
+  Dst8 d;
+  d.n = n_dst;
+  for (int i = 0; i < n_dst; i++) {
+    FPB_CHECK_ARG(dst_ptrs_h[i]);
+    d.p[i] = dst_ptrs_h[i];
+  }
+  store_multi_kernel<<<fpb_cdiv(count, 256), 256, 0, (cudaStream_t)stream>>>(src, count, d);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}

@@ -395,9 +395,9 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
   return FPB_OK;
 }
 
-FPB_EXPORT int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream)
+static int score_features_impl(const fpb_net* net, const void* AB, int N, void* ws, const MultiDst& dst, void* stream)
 {
-  FPB_CHECK_ARG(net && net->kind == FPB_NET_SCORE && AB && ws && out_feat_n512 && N > 0);
+  FPB_CHECK_ARG(net && net->kind == FPB_NET_SCORE && AB && ws && N > 0);
   Ctx c{net, (cudaStream_t)stream, net->precision == FPB_PREC_BF16, (size_t)(net->precision == FPB_PREC_BF16 ? 2 : 4)};
   const int chunk = net_chunk();
   char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
@@ -417,10 +417,35 @@ FPB_EXPORT int fpb_score_features(const fpb_net* net, const void* AB, int N, voi
     const long long R = (long long)n * TOK;
     RET(run_self_attention(c, net->att, w.d0, n, w));
     RET(run_linear(c, net->att.out, w.ctx, R, w.y1, nullptr, 0, c.bf));
-    RET(token_mean(w.y1, c.bf, out_feat_n512 + (size_t)b0 * D, n, TOK, D, c.st));
+    MultiDst d = dst;
+    for (int i = 0; i < d.n; i++) d.p[i] += (size_t)b0 * D;
+    RET(token_mean_multi(w.y1, c.bf, d, n, TOK, D, c.st));
   }
   return FPB_OK;
 }
+
+FPB_EXPORT int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream)
+{
+  FPB_CHECK_ARG(out_feat_n512);
+  MultiDst d;
+  d.n = 1;
+  d.p[0] = out_feat_n512;
+  return score_features_impl(net, AB, N, ws, d, stream);
+}
+
+FPB_EXPORT int fpb_score_features_multi(const fpb_net* net, const void* AB, int N, void* ws, float* const* out_feat_ptrs_h,
+                                        int n_dst, void* stream)
+{
+  FPB_CHECK_ARG(out_feat_ptrs_h && n_dst >= 1 && n_dst <= FPB_MAX_PEERS);
+  MultiDst d;
+  d.n = n_dst;
+  for (int i = 0; i < n_dst; i++) {
+    FPB_CHECK_ARG(out_feat_ptrs_h[i]);
+    d.p[i] = out_feat_ptrs_h[i];
+  }
+  return score_features_impl(net, AB, N, ws, d, stream);
+}
+
 
 // cross-hypothesis attention + Linear(512,1): always fp32 SIMT (0.33 GMAC at L=252)
 FPB_EXPORT int fpb_score_cross(const fpb_net* net, const float* feat, int L, int bs, void* ws, float* out_logits,

@@ -83,6 +83,10 @@ int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int c
 int layernorm_rows(const void* x, int x_bf16, const float* gamma, const float* beta, void* out, int out_bf16,
                    long long rows, int cols, float eps, cudaStream_t st);
 int token_mean(const void* x, int x_bf16, float* out, int groups, int tokens, int cols, cudaStream_t st);
+// the same rows stored to up to FPB_MAX_PEERS destinations (local and peer-mapped buffers: the all-gather of the sharded
+// scorer fused into the pooling kernel, see fpb_score_features_multi)
+struct MultiDst { float* p[FPB_MAX_PEERS]; int n; };
+int token_mean_multi(const void* x, int x_bf16, const MultiDst& out, int groups, int tokens, int cols, cudaStream_t st);
 int layernorm_token_mean_512(const void* x, const float* gamma, const float* beta, float* out, int groups, int tokens, float eps,
                              cudaStream_t st);                        // bf16 rows of 512: mean over tokens of LayerNorm(x), fused
 int small_linear(const float* x, const float* W, const float* b, float* out, int rows, int K, int N,

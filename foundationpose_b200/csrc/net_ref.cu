@@ -298,8 +298,7 @@ ln512_token_mean_cluster_kernel(const __nv_bfloat16* __restrict__ x, const float
 
 // out[g][c] = mean_t x[g][t][c]; one block per (g, 64-column slab), 256 threads = 4 token lanes x 64 cols
 template <bool XBF>
-__global__ void __launch_bounds__(256) token_mean_kernel(const void* __restrict__ x_, float* __restrict__ out, int tokens,
-                                                         int cols)
+__global__ void __launch_bounds__(256) token_mean_kernel(const void* __restrict__ x_, const MultiDst out, int tokens, int cols)
 {
   __shared__ float part[4][64];
   const int g = blockIdx.x, c = blockIdx.y * 64 + (threadIdx.x & 63), tl = threadIdx.x >> 6;
@@ -311,8 +310,10 @@ __global__ void __launch_bounds__(256) token_mean_kernel(const void* __restrict_
     }
   part[tl][threadIdx.x & 63] = s;
   __syncthreads();
-  if (tl == 0 && c < cols)
-    out[(long long)g * cols + c] = (((part[0][threadIdx.x] + part[1][threadIdx.x]) + part[2][threadIdx.x]) + part[3][threadIdx.x]) / (float)tokens;
+  if (tl == 0 && c < cols) {
+    const float v = (((part[0][threadIdx.x] + part[1][threadIdx.x]) + part[2][threadIdx.x]) + part[3][threadIdx.x]) / (float)tokens;
+    for (int d = 0; d < out.n; d++) out.p[d][(long long)g * cols + c] = v;      // peer destinations: stores over NVLink
+  }
 }
 
 // one warp per output element
@@ -401,6 +402,14 @@ int layernorm_token_mean_512(const void* x, const float* gamma, const float* bet
 }
 
 int token_mean(const void* x, int x_bf16, float* out, int groups, int tokens, int cols, cudaStream_t st)
+{
+  MultiDst d;
+  d.n = 1;
+  d.p[0] = out;
+  return token_mean_multi(x, x_bf16, d, groups, tokens, cols, st);
+}
+
+int token_mean_multi(const void* x, int x_bf16, const MultiDst& out, int groups, int tokens, int cols, cudaStream_t st)
 {
   dim3 grid(groups, fpb_cdiv(cols, 64));
   if (x_bf16) token_mean_kernel<true><<<grid, 256, 0, st>>>(x, out, tokens, cols);

@@ -258,6 +258,14 @@ class Net:
     check(lib().fpb_score_features(self.handle, ptr(AB), N, ptr(self.workspace(N)), ptr(feat), stream()))
     return feat
 
+  def score_features_multi(self, AB, N, dst_ptrs):
+    """score_features with the pooled [N,512] rows stored to every address of dst_ptrs (ints: local / peer-mapped
+    device addresses already offset to this rank's first row) -- the fused all-gather of dist.register_sharded."""
+    AB = pad_input(AB)
+    assert AB.dtype == self.act_dtype and AB.shape == (2 * N, 160, 168, 8)
+    arr = (ctypes.c_void_p * len(dst_ptrs))(*[int(p) for p in dst_ptrs])
+    check(lib().fpb_score_features_multi(self.handle, ptr(AB), N, ptr(self.workspace(N)), arr, len(dst_ptrs), stream()))
+
   def score_cross(self, feat, L, bs=1):
     """feat [bs*L,512] fp32 -> logits [bs,L]"""
     need = lib().fpb_score_cross_ws_bytes(L, bs)

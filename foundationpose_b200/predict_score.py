@@ -67,8 +67,10 @@ class ScorePredictor:
     return self._ab
 
   @torch.inference_mode()
-  def extract_features(self, rgb, depth, K, ob_in_cams, mesh=None, mesh_tensors=None, mesh_diameter=None):
-    """Per-hypothesis 512-d features (score_network.py:60-77); shardable across ranks."""
+  def extract_features(self, rgb, depth, K, ob_in_cams, mesh=None, mesh_tensors=None, mesh_diameter=None, dst_ptrs=None):
+    """Per-hypothesis 512-d features (score_network.py:60-77); shardable across ranks.  With dst_ptrs (device
+    addresses, e.g. every rank's feature table at this rank's row offset) the rows are stored there by the pooling
+    kernel itself and nothing is returned."""
     poses = torch.as_tensor(ob_in_cams, dtype=torch.float, device='cuda').reshape(-1, 4, 4).contiguous()
     N = len(poses)
     rgb_t = torch.as_tensor(rgb, device='cuda')
@@ -80,6 +82,8 @@ class ScorePredictor:
     AB = self._ab_buffer(N, S)
     make_crop_data_batch(self.cfg['input_resize'], poses, mesh, rgb_t, depth_t, K, self.cfg['crop_ratio'],
                          mesh_diameter=mesh_diameter, mesh_tensors=mesh_tensors, cfg=self.cfg, out_AB=AB)
+    if dst_ptrs is not None:
+      return self.model.score_features_multi(AB, N, dst_ptrs)
     return self.model.score_features(AB, N)
 
   @torch.inference_mode()

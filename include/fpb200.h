@@ -153,6 +153,17 @@ size_t fpb_score_cross_ws_bytes(int L, int bs);
 int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
                        void* stream);
 int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream);
+/* ---- multi-GPU (new; the reference has no distributed code): hypotheses sharded over the GPUs of one box.
+ *      ScoreNet's cross-hypothesis attention (score_network.py:86) needs all N feature rows on every rank, so the
+ *      pooling kernel that produces a rank's [N_r,512] rows stores them straight into every rank's feature table
+ *      (peer-mapped symmetric memory, stores travel over NVLink / NVSwitch): the all-gather is fused into the
+ *      producing kernel.  out_feat_ptrs_h[i] = destination i already offset to this rank's first row (host array
+ *      of n_dst <= FPB_MAX_PEERS device pointers; entry 0 is normally the local table).  fpb_store_multi_f32 does
+ *      the same for the [N_r,16] refined poses.  The caller orders the exchange with a device barrier. ---- */
+#define FPB_MAX_PEERS 8
+int fpb_score_features_multi(const fpb_net* net, const void* AB, int N, void* ws, float* const* out_feat_ptrs_h,
+                             int n_dst, void* stream);
+int fpb_store_multi_f32(const float* src, long long count, float* const* dst_ptrs_h, int n_dst, void* stream);
 int fpb_score_cross(const fpb_net* net, const float* feat, int L, int bs, void* ws, float* out_logits,
                     void* stream);
 
