@@ -18,4 +18,4 @@ def test_p2p_exchange_equals_nccl_on_two_gpus():
          '--master-port', '29541', os.path.join(ROOT, 'tools', 'p2p_check.py')]
   r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
   assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-  assert r.stdout.count('p2p == nccl: True') == 2, r.stdout[-2000:]
+  assert 'p2p_equals_nccl=False' not in r.stdout and r.stdout.count('p2p_equals_nccl=True') == 2, r.stdout[-2000:]

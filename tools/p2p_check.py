@@ -19,6 +19,8 @@ ok = True
 for mode, lst in outs.items():
   for p, s, P in lst:
     ok &= np.array_equal(p, ref[0]) and np.array_equal(s, ref[1]) and np.array_equal(P, ref[2])
-print(rank, 'p2p == nccl:', ok, 'best score', float(ref[1][0]), flush=True)
+sys.stdout.write(f'rank{rank}:p2p_equals_nccl={bool(ok)}:best_score={float(ref[1][0]):.4f}\n')
+sys.stdout.flush()
 dist.barrier()
 dist.destroy_process_group()
+sys.exit(0 if ok else 1)
