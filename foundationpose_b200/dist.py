@@ -122,22 +122,20 @@ def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, excha
   depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
   rgb_t = torch.as_tensor(rgb, device='cuda').contiguous()
   mask_t = (torch.as_tensor(ob_mask, device='cuda') > 0).to(torch.uint8).contiguous()
-  depth_t = U.erode_depth(depth_t, radius=2, device='cuda')
-  depth_t = U.bilateral_filter_depth(depth_t, radius=2, device='cuda')
-  stats = U.mask_depth_stats(depth_t, mask_t)
-  center = _center_from_stats(stats, K)
-  if stats[5] < 4:
-    pose = np.eye(4)
-    pose[:3, 3] = center
-    return pose
+  # one-call prologue without a host round trip (as FoundationPose.register): stencils, translation guess and all N
+  # hypotheses on the device; the "too few valid pixels" early exit (src/estimater.py:176-180) is evaluated after the
+  # single synchronisation at the end -- every rank takes the same branch, so the exchange below stays collective
+  depth_t, xyz_map, poses_all, si, sf, _ = U.register_prologue(depth_t, mask_t, K, est.rot_grid, min_valid=4)
+  if getattr(est, '_stats_host', None) is None:
+    est._stats_host = (torch.empty(6, dtype=torch.int32, pin_memory=True), torch.empty(2, dtype=torch.float, pin_memory=True))
+  est._stats_host[0].copy_(si, non_blocking=True)
+  est._stats_host[1].copy_(sf, non_blocking=True)
   n_total = len(est.rot_grid)
   if exchange == 'auto':
     exchange = 'p2p' if (world > 1 and world <= MAX_PEERS and dist.get_backend(group) == 'nccl') else 'nccl'
   px = peer_exchange(n_total, group) if (exchange == 'p2p' and world > 1) else None
   lo, hi = shard_bounds(n_total, rank, world)
-  poses = est.rot_grid[lo:hi].clone()
-  poses[:, :3, 3] = torch.as_tensor(center.reshape(1, 3), device='cuda', dtype=torch.float)
-  xyz_map = U.depth2xyzmap_cuda(depth_t, K, math_f64=True)
+  poses = poses_all[lo:hi].contiguous()
   if hi > lo:
     poses, _ = est.refiner.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=rgb_t, depth=depth_t, K=K,
                                    ob_in_cams=poses, xyz_map=xyz_map, mesh_diameter=est.diameter, iteration=iteration)
@@ -158,9 +156,16 @@ def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, excha
     poses = all_gather_ragged(poses.reshape(-1, 16), n_total, world, group).reshape(-1, 4, 4)
   scores = est.scorer.score_from_features(feats)
   ids = scores.argsort(descending=True)
+  best = (poses[ids[0]] @ est.get_tf_to_centered_mesh()).data.cpu().numpy()          # the only synchronisation
+  oi, of = est._stats_host[0].numpy(), est._stats_host[1].numpy()
+  stats = (int(oi[0]), int(oi[1]), int(oi[2]), int(oi[3]), int(oi[4]), int(oi[5]), of[0], of[1])
+  if stats[5] < 4:
+    pose = np.eye(4)
+    pose[:3, 3] = _center_from_stats(stats, K)
+    return pose
   est.poses, est.scores = poses[ids], scores[ids]
   est.pose_last, est.best_id = est.poses[0], ids[0]
-  return (est.poses[0] @ est.get_tf_to_centered_mesh()).data.cpu().numpy()
+  return best
 
 
 def gather_best(pose, score, group=None):

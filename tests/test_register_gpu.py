@@ -160,3 +160,18 @@ def test_refiner_deepim_6d_configuration(scene1):
   assert np.abs(out - want).max() < 5e-5
   R = out[:, :3, :3].astype(np.float64)
   assert np.abs(R @ R.transpose(0, 2, 1) - np.eye(3)).max() < 1e-5 and np.isfinite(out).all()
+
+
+def test_register_sharded_single_rank_equals_register(scene1):
+  """dist.register_sharded without a process group (world 1) runs the same kernels on the same batch as register()."""
+  from foundationpose_b200 import dist as fdist
+  est, _ = _make(scene1, 'bf16')
+  sc = scene1
+  a = est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=2)
+  sa, pa = est.scores.cpu().numpy().copy(), est.poses.cpu().numpy().copy()
+  b = fdist.register_sharded(est, sc['K'], sc['rgb'], sc['depth'], sc['mask'], iteration=2)
+  assert np.array_equal(a, b)
+  assert np.array_equal(sa, est.scores.cpu().numpy()) and np.array_equal(pa, est.poses.cpu().numpy())
+  tiny = np.zeros_like(sc['mask']); ys, xs = np.nonzero(sc['mask']); tiny[ys[0], xs[0]] = 1
+  p = fdist.register_sharded(est, sc['K'], sc['rgb'], sc['depth'], tiny, iteration=1)
+  assert np.array_equal(p[:3, :3], np.eye(3))            # < 4 valid pixels: src/estimater.py:176-180

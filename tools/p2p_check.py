@@ -16,6 +16,10 @@ for mode in ('nccl', 'p2p', 'p2p', 'nccl', 'p2p'):
   outs.setdefault(mode, []).append((pose.copy(), est.scores.cpu().numpy().copy(), est.poses.cpu().numpy().copy()))
 ref = outs['nccl'][0]
 ok = True
+# the sharded result against the unsharded register() of the same estimator (per-hypothesis arithmetic does not depend
+# on the batch, up to the fp32 summation order of the pooling kernels)
+full = est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=2)
+ok &= bool(np.abs(full - ref[0]).max() < 1e-4) and bool(np.abs(est.scores.cpu().numpy() - ref[1]).max() < 1e-3)
 for mode, lst in outs.items():
   for p, s, P in lst:
     ok &= np.array_equal(p, ref[0]) and np.array_equal(s, ref[1]) and np.array_equal(P, ref[2])
