@@ -271,6 +271,8 @@ def main():
     def step_strong():
       return fdist.register_sharded(est, K, h_rgb, h_depth, h_mask, iteration=ITERS, exchange=args.exchange)
     s_dev, s_wall, s_per = timed(step_strong, args.steps, 2)
+    if args.exchange == 'auto':
+      args.exchange = 'p2p' if world <= fdist.MAX_PEERS else 'nccl'      # what register_sharded resolves 'auto' to on NCCL
     how = ('NCCL all_gather of features + poses' if args.exchange == 'nccl' else
            'feature rows / poses stored into every rank\'s table by the producing kernels (peer-mapped symmetric memory over '
            'NVLink) + one device barrier')
