@@ -137,3 +137,28 @@ def test_so3_exp_and_pose_update():
   out = oo.pose_update(poses, np.ones((3, 3), np.float32) * 0.1, np.zeros((3, 3), np.float32), 0.2, 0.349)
   assert np.allclose(out[:, :3, 3], 0.01, atol=1e-7)
   assert np.allclose(out[:, :3, :3], np.eye(3)[None], atol=1e-6)
+
+
+def test_pose_update_deepim_and_6d_known_answers():
+  """Config-gated representations (predict_pose_refine.py:201-224): a zero image-plane shift with depth ratio 1 leaves
+  the translation unchanged; the 6-D rotation of (e1, e2) is the identity; Gram-Schmidt output is a rotation."""
+  g = og.make_rotation_grid()[:16].copy()
+  g[:, :3, 3] = np.array([0.03, -0.02, 0.6], np.float32)
+  K = np.array([[600, 0, 320], [0, 600, 240], [0, 0, 1.0]])
+  cp = oo.crop_params(g, K, 0.2, 1.2, 160, 480, 640)
+  tf = cp['tf'].reshape(-1, 3, 3)
+  trans = np.zeros((16, 3), np.float32); trans[:, 2] = 1.0
+  rot6 = np.tile(np.array([1, 0, 0, 0, 1, 0], np.float32), (16, 1))
+  out = oo.pose_update(g, trans, rot6, 0.2, 0.349, [0.02, 0.02, 0.05], False, trans_rep='deepim', rot_rep='6d',
+                       tf_to_crops=tf, K=K, S=160)
+  assert np.abs(out - g).max() < 2e-6
+  # a pure depth change moves the object along its viewing ray
+  trans[:, 2] = 1.1
+  out = oo.pose_update(g, trans, rot6, 0.2, 0.349, [0.02, 0.02, 0.05], False, trans_rep='deepim', rot_rep='6d',
+                       tf_to_crops=tf, K=K, S=160)
+  assert np.allclose(out[:, :3, 3], g[:, :3, 3] * 1.1, atol=1e-5)
+  rng = np.random.default_rng(0)
+  R = oo.rotation_6d_to_matrix(rng.normal(size=(64, 6)).astype(np.float32)).astype(np.float64)
+  assert np.abs(R @ R.transpose(0, 2, 1) - np.eye(3)).max() < 1e-5 and np.allclose(np.linalg.det(R), 1, atol=1e-5)
+  with pytest.raises(RuntimeError):
+    oo.pose_update(g, trans, rot6, 0.2, 0.349, None, True, rot_rep='quat')
