@@ -98,8 +98,10 @@ size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
 struct Ws {
   char *c0, *c1, *c2, *c3, *ab0, *ab1, *ab2, *d0, *d1, *d2, *qkv, *P, *vt, *ctx, *y1, *y, *ff;
   float *scores, *pooled;
+  char* splitk;       // split-K scratch of the persistent GEMM kernel (small batches only)
   size_t total;
 };
+constexpr size_t SPLITK_BYTES = 16u << 20;
 
 Ws carve(char* base, int n, size_t esz)
 {
@@ -125,6 +127,7 @@ Ws carve(char* base, int n, size_t esz)
   w.ff = take((size_t)n * TOK * D * esz);
   w.scores = (float*)take((size_t)n * HEADS * TOK * TOKP * sizeof(float));
   w.pooled = (float*)take((size_t)n * D * sizeof(float));
+  w.splitk = take(SPLITK_BYTES);
   w.total = o;
   return w;
 }
@@ -134,11 +137,15 @@ struct Ctx {
   cudaStream_t st;
   bool bf;
   size_t esz;
+  void* splitk = nullptr;     // set per chunk from the workspace (Ws::splitk)
   const void* W(size_t off) const { return bf ? (const void*)(net->w16 + off) : (const void*)(net->w32 + off); }
   const float* F(size_t off) const { return net->w32 + off; }
-  int gemm(const GemmProblem& p) const
+  int gemm(const GemmProblem& p_in) const
   {
-    if (!bf) return ref_gemm(p, st);
+    if (!bf) return ref_gemm(p_in, st);
+    GemmProblem p = p_in;
+    p.splitk_ws = splitk;
+    p.splitk_ws_bytes = splitk ? (long long)SPLITK_BYTES : 0;
     int rc = tc3_gemm(p, st, 0);                          // narrow layers (Cout 64 / 128): operand-swapped kernel
     if (rc == FPB_ERR_UNSUPPORTED) rc = tc2_gemm(p, st);  // persistent TMA kernel
     return rc == FPB_ERR_UNSUPPORTED ? tc_gemm(p, st) : rc;  // batched / odd shapes: cp.async kernel
@@ -378,6 +385,8 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
   for (int b0 = 0; b0 < N; b0 += chunk) {
     const int n = (N - b0) < chunk ? (N - b0) : chunk;
     Ws w = carve(base, n, c.esz);
+    c.splitk = N == 1 ? w.splitk : nullptr;   // split-K only for single-hypothesis calls (track_one): every larger batch keeps
+                                              // per-hypothesis results independent of the batch it is evaluated in
     const void* in = AB;
     if (!(b0 == 0 && n == N)) {
       // reuse c3/c2 region? keep it simple: stage the chunk's [A;B] pairs at the start of c1 (dead until conv1 runs)
@@ -405,6 +414,8 @@ static int score_features_impl(const fpb_net* net, const void* AB, int N, void* 
   for (int b0 = 0; b0 < N; b0 += chunk) {
     const int n = (N - b0) < chunk ? (N - b0) : chunk;
     Ws w = carve(base, n, c.esz);
+    c.splitk = N == 1 ? w.splitk : nullptr;   // split-K only for single-hypothesis calls (track_one): every larger batch keeps
+                                              // per-hypothesis results independent of the batch it is evaluated in
     const void* in = AB;
     if (!(b0 == 0 && n == N)) {
       char* stage = w.c1;

@@ -45,6 +45,11 @@ struct GemmProblem {
   int c_transposed;   // tc3 kernel only: out[n * ldc + m] (bf16), i.e. the product is stored transposed
   const float* row_shift;   // optional per-ROW additive term (after scale/shift; tc2 kernel only): v += row_shift[m]
   int row_remap;      // output rows: 0 as computed, 1 dense pixel index -> position, 2 position -> dense (borders skipped)
+  // optional scratch for split-K (tc2 kernel only): with few output tiles (single-hypothesis batches: track_one) the K
+  // loop is divided over ksplit CTAs per tile, fp32 partial tiles land here ([ksplit][M][N]) and a second kernel sums
+  // them in a fixed order and applies the epilogue
+  void* splitk_ws;
+  long long splitk_ws_bytes;
 };
 
 static inline GemmProblem gemm_problem_default()

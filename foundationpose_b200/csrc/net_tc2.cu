@@ -36,6 +36,8 @@ struct Tc2Params {
   int m_tiles, n_tiles;  // tiles of (TM*CG) x BN
   int halo, Wp, IS, hrows, na, nb, tps;   // halo mode: position pitch, image stride, A box rows, A / W ring depths, taps per W stage
   int fast_epi;          // 1: smem-transposed, fully coalesced bf16 epilogue (ncols % 64 == 0)
+  int ksplit;            // split-K factor (1 = off): work item t -> output tile t / ksplit, K slice t % ksplit (nk % ksplit == 0)
+  long long c_split_stride;   // elements between the fp32 partial outputs of consecutive K slices
   int dbg;               // FPB_TC2_DBG experiment bits: 1 no stores, 2 no scale/shift, 4 no residual, 8 no MMA
 };
 
@@ -82,8 +84,9 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
   const int cluster_id = blockIdx.x / CG, n_clusters = gridDim.x / CG;
-  const int total_tiles = q.m_tiles * q.n_tiles;
-  const int nk = p.K / KC;
+  const int ksp = q.ksplit;
+  const int total_tiles = q.m_tiles * q.n_tiles * ksp;       // work items: (output tile, K slice)
+  const int nk = p.K / KC / ksp;                              // K stages per work item
   pdl_launch_dependents();
 
   if (threadIdx.x == 0) {
@@ -161,7 +164,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         int s = 0;
         uint32_t ph = 1;
         for (int t = cluster_id; t < total_tiles; t += n_clusters) {
-          const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
+          const int tile = ksp == 1 ? t : t / ksp, ks = t - tile * ksp;
+          const int mt = tile / q.n_tiles, nt = tile - mt * q.n_tiles;
           const int m0 = (mt * CG + (int)rank) * TM;
           const int nrow0 = nt * BN + (int)rank * C::B_ROWS;
           int cw = 0, ch = 0, img = 0;
@@ -173,6 +177,12 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             ch = oy * p.stride + q.lower_h;
           }
           int k0 = 0, c0 = 0, kx = 0, ky = 0;                  // K walks (ky, kx, c) with c fastest
+          if (ks) {                                            // split-K: this item starts at K stage ks * nk
+            k0 = ks * nk * KC;
+            const int tap = k0 / p.Cin;
+            c0 = k0 - tap * p.Cin;
+            ky = tap / p.KW; kx = tap - ky * p.KW;
+          }
           for (int kc = 0; kc < nk; kc++, k0 += KC) {
             mbar_wait(&ctl->empty[s], ph);
             const uint32_t sa = s0 + s * C::STAGE_BYTES;
@@ -296,7 +306,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       load_res(mw0, n00 + ehalf * 64);
     }
     for (int t = cluster_id; t < total_tiles; t += n_clusters, tc++) {
-      const int mt = t / q.n_tiles, nt = t - mt * q.n_tiles;
+      const int tile = ksp == 1 ? t : t / ksp, ks = t - tile * ksp;
+      const int mt = tile / q.n_tiles, nt = tile - mt * q.n_tiles;
       const int m = (mt * CG + (int)rank) * TM + row;
       const int n0 = nt * BN;
       const uint32_t acc = tc & 1u;
@@ -475,7 +486,8 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         continue;
       }
       const bool m_ok = m < p.M;
-      const long long orow = m_ok ? (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off : 0;
+      const long long orow = (m_ok ? (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off : 0) +
+                             (long long)ks * q.c_split_stride;
       const float* pe_row = (p.pe && m_ok) ? p.pe + (long long)(m % p.pe_rows) * p.pe_ld : nullptr;
       const __nv_bfloat16* res_row = (p.residual && m_ok) ? (const __nv_bfloat16*)p.residual + (long long)m * p.ldr : nullptr;
 #pragma unroll 1
@@ -694,7 +706,7 @@ int launch_tc2(const CUtensorMap& mA, const CUtensorMap& mB, const Tc2Params& q_
     FPB_CUDA(cudaFuncSetAttribute(tc2_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
     configured = true;
   }
-  const int total = q.m_tiles * q.n_tiles;
+  const int total = q.m_tiles * q.n_tiles * q.ksplit;
   int clusters = g_num_sms / CG;
   if (clusters > total) clusters = total;
   cudaLaunchConfig_t cfg;
@@ -716,6 +728,57 @@ int launch_tc2(const CUtensorMap& mA, const CUtensorMap& mB, const Tc2Params& q_
 }
 
 int g_force_cg = 0;
+
+// Second half of a split-K GEMM: out = epilogue(sum over K slices of the fp32 partial tiles), slices added in index order
+// (deterministic).  One thread per (row, 4 columns); same operation order as the kernel's epilogue.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(GemmProblem p, const float* __restrict__ part, int ksplit,
+                                                            long long stride, int ld, int nst)
+{
+  const int n4 = nst >> 2;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)p.M * n4) return;
+  const int m = (int)(i / n4), n = (int)(i - (long long)m * n4) * 4;
+  float4 a = *reinterpret_cast<const float4*>(part + (long long)m * ld + n);
+  for (int k = 1; k < ksplit; k++) {
+    const float4 b = *reinterpret_cast<const float4*>(part + k * stride + (long long)m * ld + n);
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+  }
+  float v[4] = {a.x * p.alpha, a.y * p.alpha, a.z * p.alpha, a.w * p.alpha};
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    if (p.scale) v[j] = v[j] * p.scale[n + j] + (p.shift ? p.shift[n + j] : 0.0f);
+    else if (p.shift) v[j] += p.shift[n + j];
+    if (p.row_shift) v[j] += p.row_shift[m];
+    if (p.residual) v[j] += __bfloat162float(((const __nv_bfloat16*)p.residual)[(long long)m * p.ldr + n + j]);
+    if (p.relu) v[j] = fmaxf(v[j], 0.0f);
+    if (p.pe) v[j] += p.pe[(long long)(m % p.pe_rows) * p.pe_ld + n + j];
+  }
+  const long long o = (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off + n;
+  if (p.out_bf16) {
+    __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
+    *reinterpret_cast<uint2*>((__nv_bfloat16*)p.C + o) = pk;
+  } else {
+    *reinterpret_cast<float4*>((float*)p.C + o) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
+// split-K factor for a problem with `tiles` output tiles on `clusters` CTAs / CTA pairs: the largest divisor s of the
+// nk K stages that keeps >= 4 stages per slice, fits the scratch buffer and does not exceed one wave
+int choose_ksplit(const GemmProblem& p, int tiles, int clusters, int nk, int ncols)
+{
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("FPB_SPLITK"); enabled = e ? atoi(e) : 1; }
+  if (!enabled || !p.splitk_ws || p.halo || p.row_remap || tiles * 2 > clusters || nk < 8) return 1;
+  if (ncols % 4 || p.ldc % 4 || p.split_col_off % 4 || (p.residual && p.ldr % 2)) return 1;
+  const long long per = (long long)p.M * ncols * 4;
+  int smax = clusters / tiles;
+  if (smax > nk / 4) smax = nk / 4;
+  for (int s = smax; s >= 2; s--)
+    if (nk % s == 0 && per * s <= p.splitk_ws_bytes) return s;
+  return 1;
+}
 
 
 int tc2_cta_group()
@@ -797,6 +860,16 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
   }
   q.m_tiles = fpb_cdiv(p.M, TM * CG);
   q.n_tiles = fpb_cdiv(ncols, BN);
+  q.ksplit = choose_ksplit(p, q.m_tiles * q.n_tiles, g_num_sms / CG, p.K / KC, ncols);
+  q.c_split_stride = 0;
+  if (q.ksplit > 1) {
+    // first kernel: raw fp32 partial tiles [ksplit][M][ncols] into the scratch buffer, no epilogue math
+    GemmProblem& s = q.p;
+    s.C = p.splitk_ws; s.out_bf16 = 0; s.alpha = 1.0f; s.scale = nullptr; s.shift = nullptr; s.row_shift = nullptr;
+    s.residual = nullptr; s.relu = 0; s.pe = nullptr; s.ldc = ncols; s.m_split = 0x7fffffff; s.split_col_off = 0;
+    q.fast_epi = 0;
+    q.c_split_stride = (long long)p.M * ncols;
+  }
   CUtensorMap mA, mB;
   if (p.halo) {
     rc = get_tiled_map(p.A, p.M, p.Cin, p.pix_pitch, q.hrows, &mA);       // [positions][C], box = halo rows x 64 channels
@@ -809,13 +882,13 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
   if (rc) return rc;
   rc = get_tiled_map(p.W, p.N, p.K, p.ldw, BN / CG, &mB);
   if (rc) return rc;
-#define TC2_LAUNCH(BN_, CG_) return launch_tc2<BN_, CG_>(mA, mB, q, st)
-  if (CG == 2) {
-    if (BN == 256) TC2_LAUNCH(256, 2);
-    TC2_LAUNCH(128, 2);
-  }
-  if (BN == 256) TC2_LAUNCH(256, 1);
-  if (BN == 128) TC2_LAUNCH(128, 1);
-  TC2_LAUNCH(64, 1);
-#undef TC2_LAUNCH
+  if (CG == 2) rc = BN == 256 ? launch_tc2<256, 2>(mA, mB, q, st) : launch_tc2<128, 2>(mA, mB, q, st);
+  else if (BN == 256) rc = launch_tc2<256, 1>(mA, mB, q, st);
+  else if (BN == 128) rc = launch_tc2<128, 1>(mA, mB, q, st);
+  else rc = launch_tc2<64, 1>(mA, mB, q, st);
+  if (rc || q.ksplit == 1) return rc;
+  const long long work = (long long)p.M * (ncols / 4);
+  splitk_reduce_kernel<<<fpb_cdiv(work, 256), 256, 0, st>>>(p, (const float*)p.splitk_ws, q.ksplit, q.c_split_stride, ncols, ncols);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
 }

@@ -274,6 +274,27 @@ def test_chunking_is_transparent(monkeypatch):
   assert np.abs(outs[0] - outs[1]).max() < 1e-6
 
 
+def test_split_k_is_transparent():
+  """Single-hypothesis batches (track_one) run the >= 256-channel convolutions split-K (K slices on separate CTAs, fp32 partial
+  tiles summed by a second kernel): same outputs as the unsplit kernel up to fp32 summation order."""
+  import os, subprocess, sys, json
+  code = ("import torch,sys;sys.path.insert(0,'.');from foundationpose_b200 import nets;from tests.test_nets_gpu import _inputs;"
+          "from foundationpose_b200._lib import lib;import json;"
+          "sd=nets.synthetic_state_dict(0);out=[]\n"
+          "for n in (1,):\n"
+          "  AB=_inputs(n,1).cuda().bfloat16();net=nets.Net(0,sd,'bf16');lib().fpb_launch_count(1);t,r=net.refine(AB,n);"
+          "out.append(torch.cat([t,r]).cpu().numpy().tolist());out.append(int(lib().fpb_launch_count(0)))\n"
+          "print(json.dumps(out))")
+  res = []
+  for flag in ('0', '1'):
+    env = dict(os.environ, FPB_SPLITK=flag)
+    o = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, env=env, check=True).stdout
+    res.append(json.loads(o.strip().splitlines()[-1]))
+  a, b = np.array(res[0][0]), np.array(res[1][0])
+  assert np.abs(a - b).max() < 2e-3 * max(1.0, np.abs(a).max()), (a, b)
+  assert res[1][1] > res[0][1]          # the split path really ran (extra reduce launches)
+
+
 def _golden_inputs(seed, n):
   from foundationpose_b200.nets import _calibration_batch
   x = _calibration_batch(torch.Generator().manual_seed(seed), n)            # [2n,6,160,160]
