@@ -278,8 +278,11 @@ __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i
 // RASTER_TPT faces per thread (256 * RASTER_TPT consecutive faces per block): all corner indices are fetched first, then
 // all snapped positions, so every thread keeps 3 * RASTER_TPT independent gathers in flight -- with one face per thread
 // the kernel was bound by the latency of the two dependent loads of short-lived blocks (82 G triangles/s at 500 k faces
-// x 1008 hypotheses).  The gathers are served by L1/L2; staging the positions in shared memory (whole array or the
-// block's vertex range, by bulk async copy) measured slower at both mesh sizes.
+// x 1008 hypotheses).  The gathers are served by L1/L2.  Staging the positions in shared memory by bulk async copy
+// (cp.async.bulk + mbarrier) was implemented three ways -- the whole array of a hypothesis for small meshes, the vertex
+// range of each 256-face block, and the range of each 1024-face block with the copy issued ahead of the index loads --
+// and measured equal or slower at both mesh sizes (cfg 4: 7.99 -> 8.15 ms per pass): the kernel is bound by the
+// latency chain of short-lived blocks (indices -> positions -> set-up), not by L2 sector traffic.
 constexpr int RASTER_TPT = 4;
 
 __global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
