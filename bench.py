@@ -230,7 +230,7 @@ def main():
   lib().fpb_launch_count(1)
   dev_ms, wall_ms, per = timed(step_device, args.steps, max(args.warmup, 3))
   launches = lib().fpb_launch_count(0)
-  e_dev_ms, e_wall_ms, e_per = timed(step_host, args.steps, 1)
+  e_dev_ms, e_wall_ms, e_per = timed(step_host, args.steps, max(args.warmup, 3))
   sampler.stop_flag = True
   total_hyp = n_hyp * world * args.steps
   value = total_hyp / (dev_ms / 1e3)

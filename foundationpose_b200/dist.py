@@ -19,7 +19,7 @@ import torch.distributed as dist
 
 from . import utils as U
 from ._lib import lib, check, ptr, stream
-from .estimater import _center_from_stats
+from .estimater import _center_from_stats, _h2d
 
 MAX_PEERS = 8      # FPB_MAX_PEERS (include/fpb200.h)
 
@@ -119,9 +119,11 @@ def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, excha
   rank = dist.get_rank(group) if dist.is_initialized() else 0
   U.set_seed(0)
   K = np.asarray(K, dtype=np.float64)
-  depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
-  rgb_t = torch.as_tensor(rgb, device='cuda').contiguous()
-  mask_t = (torch.as_tensor(ob_mask, device='cuda') > 0).to(torch.uint8).contiguous()
+  depth_t = _h2d(depth, torch.float)
+  rgb_t = _h2d(rgb)
+  mask_t = _h2d(ob_mask)
+  mask_t = (mask_t.view(torch.uint8) if mask_t.dtype == torch.bool else
+            mask_t if mask_t.dtype == torch.uint8 else (mask_t > 0).to(torch.uint8)).contiguous()
   # one-call prologue without a host round trip (as FoundationPose.register): stencils, translation guess and all N
   # hypotheses on the device; the "too few valid pixels" early exit (src/estimater.py:176-180) is evaluated after the
   # single synchronisation at the end -- every rank takes the same branch, so the exchange below stays collective

@@ -50,6 +50,18 @@ def _center_from_stats(stats, K):
   return center.reshape(3)
 
 
+def _h2d(x, dtype=None):
+  """Frame buffer -> cuda tensor.  Page-locked host memory is copied asynchronously on the current stream (the kernels
+  that read it are enqueued behind the copy and register() / track_one() end with a synchronisation, so the caller's
+  buffer is free again when they return); pageable memory takes torch's synchronous path."""
+  t = torch.as_tensor(x)
+  if not t.is_cuda:
+    t = t.to('cuda', non_blocking=t.is_pinned())
+  if dtype is not None and t.dtype != dtype:
+    t = t.to(dtype)
+  return t.contiguous()
+
+
 class FoundationPose:
   def __init__(self, model_pts, model_normals, symmetry_tfs=None, mesh=None, scorer: ScorePredictor = None,
                refiner: PoseRefinePredictor = None, glctx=None, debug=0, debug_dir='/tmp/fpb200_debug/',
@@ -152,10 +164,14 @@ class FoundationPose:
     """src/estimater.py:159-240 -> np.ndarray [4,4] float32 (object pose in camera, un-centred mesh frame)."""
     U.set_seed(0)
     K = np.asarray(K, dtype=np.float64)
-    depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
-    rgb_t = torch.as_tensor(rgb, device='cuda').contiguous()
-    mask_t = torch.as_tensor(ob_mask, device='cuda')
-    mask_t = (mask_t if mask_t.dtype == torch.uint8 else (mask_t > 0).to(torch.uint8)).contiguous()
+    depth_t = _h2d(depth, torch.float)
+    rgb_t = _h2d(rgb)
+    mask_t = _h2d(ob_mask)
+    if mask_t.dtype == torch.bool:
+      mask_t = mask_t.view(torch.uint8)          # bool is one byte holding 0 / 1: reinterpret, no kernel
+    elif mask_t.dtype != torch.uint8:
+      mask_t = (mask_t > 0).to(torch.uint8)
+    mask_t = mask_t.contiguous()
     # The whole call is enqueued without a host round trip (the reference crosses the bus ~10 times): the translation
     # guess and the hypotheses are produced on the device, the mask statistics travel to pinned host memory
     # asynchronously and the "too few valid pixels" early exit (src/estimater.py:176-180) is evaluated after the one
@@ -202,11 +218,11 @@ class FoundationPose:
       logging.info('Please init pose by register first')
       raise RuntimeError
     K = np.asarray(K, dtype=np.float64)
-    depth_t = torch.as_tensor(depth, device='cuda', dtype=torch.float).contiguous()
+    depth_t = _h2d(depth, torch.float)
     depth_t = U.erode_depth(depth_t, radius=2, device='cuda')
     depth_t = U.bilateral_filter_depth(depth_t, radius=2, device='cuda')
     xyz_map = U.depth2xyzmap_cuda(depth_t, K.astype(np.float32).astype(np.float64), math_f64=False, zfar=np.inf)
-    pose, _ = self.refiner.predict(mesh=self.mesh, mesh_tensors=self.mesh_tensors, rgb=torch.as_tensor(rgb, device='cuda'),
+    pose, _ = self.refiner.predict(mesh=self.mesh, mesh_tensors=self.mesh_tensors, rgb=_h2d(rgb),
                                    depth=depth_t, K=K, ob_in_cams=self.pose_last.reshape(1, 4, 4), normal_map=None,
                                    xyz_map=xyz_map, mesh_diameter=self.diameter, glctx=self.glctx, iteration=iteration,
                                    get_vis=False)
