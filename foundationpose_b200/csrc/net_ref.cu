@@ -3,6 +3,7 @@
 //   ConvBNReLU / ResnetBasicBlock   learning/models/network_modules.py:37-50, 73-111
 //   TransformerEncoderLayer / MHA   learning/models/refine_network.py:56-70, score_network.py:53-54
 #include "net_kernels.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -393,7 +394,9 @@ int layernorm_token_mean_512(const void* x, const float* gamma, const float* bet
                              cudaStream_t st)
 {
   if ((uintptr_t)x & 15) { fpb_set_error("layernorm_token_mean_512: unaligned input"); return FPB_ERR_ARG; }
-  if (groups <= 74)      // <= 592 CTAs: two waves of clusters at most
+  static int cluster_max = -1;
+  if (cluster_max < 0) { const char* e = getenv("FPB_LNM_CLUSTER_MAX"); cluster_max = e ? atoi(e) : 74; }
+  if (groups <= cluster_max)      // default 74: <= 592 CTAs, two waves of clusters at most
     ln512_token_mean_cluster_kernel<<<groups * LNM_CLUSTER, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
   else
     ln512_token_mean_kernel<<<groups, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
