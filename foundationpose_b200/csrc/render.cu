@@ -266,7 +266,7 @@ __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i
     const float4 d0 = cl[__shfl_sync(0xffffffffu, i0, src)];    // same address in every lane: one broadcast load
     const float4 d1 = cl[__shfl_sync(0xffffffffu, i1, src)];
     const float4 d2 = cl[__shfl_sync(0xffffffffu, i2, src)];
-    const uint32_t face = (uint32_t)(f - lane + src);
+    const uint32_t face = (uint32_t)__shfl_sync(0xffffffffu, f, src);     // lanes hold arbitrary faces (compacted queue)
     const int bw = s.px1 - s.px0 + 1, tot = bw * (s.py1 - s.py0 + 1);
     for (int i = lane; i < tot; i += 32) {
       int py = s.py0 + i / bw, px = s.px0 + i % bw;
@@ -275,22 +275,85 @@ __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i
   }
 }
 
-// RASTER_TPT faces per thread (256 * RASTER_TPT consecutive faces per block): all corner indices are fetched first, then
-// all snapped positions, so every thread keeps 3 * RASTER_TPT independent gathers in flight -- with one face per thread
-// the kernel was bound by the latency of the two dependent loads of short-lived blocks (82 G triangles/s at 500 k faces
-// x 1008 hypotheses).  The gathers are served by L1/L2.  Staging the positions in shared memory by bulk async copy
-// (cp.async.bulk + mbarrier) was implemented three ways -- the whole array of a hypothesis for small meshes, the vertex
-// range of each 256-face block, and the range of each 1024-face block with the copy issued ahead of the index loads --
-// and measured equal or slower at both mesh sizes (cfg 4: 7.99 -> 8.15 ms per pass): the kernel is bound by the
-// latency chain of short-lived blocks (indices -> positions -> set-up), not by L2 sector traffic.
+// Two phases per block of RASTER_FACES = 1024 consecutive faces (4 per thread):
+//   1. cull (all lanes busy): all corner indices are fetched first, then all snapped positions (12 independent gathers
+//      in flight per thread), then the integer set-up decides whether the triangle's pixel-centre bounding box inside
+//      the crop is non-empty.  Survivors are appended to a shared-memory queue (warp-aggregated atomics).
+//   2. rasterise (dense): the queue is walked with one surviving triangle per lane.
+// ncu on cfg 4 (1008 hypotheses x 500 k faces, ~40 triangles per pixel) showed the one-phase kernel issue-bound at
+// 16.6 active threads per instruction: 45 % of its instructions ran in the coverage / fragment code with 1-3 active
+// lanes, because a warp executes that path as soon as ONE of its 32 triangles survives the cull.  (Staging the positions
+// in shared memory by bulk async copy -- whole array, per-block vertex range, with or without overlap with the index
+// loads -- and a persistent variant with next-chunk prefetch all measured equal or slower: latency and L2 sector
+// traffic are not what bounds this kernel.)
 constexpr int RASTER_TPT = 4;
+constexpr int RASTER_FACES = 256 * RASTER_TPT;
 
+__global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __restrict__ faces, int F, int V,
+                                                          const float4* __restrict__ clip, const int2* __restrict__ snap,
+                                                          int S, unsigned long long* __restrict__ zbuf)
+{
+  __shared__ int q_f[RASTER_FACES];
+  __shared__ int q_i[3][RASTER_FACES];
+  __shared__ int2 q_s[3][RASTER_FACES];
+  __shared__ int q_count;
+  const int n = blockIdx.y;
+  const int f0 = blockIdx.x * RASTER_FACES + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int2* sn = snap + (size_t)n * V;
+  if (threadIdx.x == 0) q_count = 0;
+  int idx[RASTER_TPT][3];
+#pragma unroll
+  for (int k = 0; k < RASTER_TPT; k++) {
+    const int f = f0 + k * 256;
+#pragma unroll
+    for (int c = 0; c < 3; c++) idx[k][c] = f < F ? faces[f * 3 + c] : 0;
+  }
+  int2 sp[RASTER_TPT][3];
+#pragma unroll
+  for (int k = 0; k < RASTER_TPT; k++)
+#pragma unroll
+    for (int c = 0; c < 3; c++) sp[k][c] = sn[idx[k][c]];
+  __syncthreads();                                   // q_count = 0 is visible
+#pragma unroll
+  for (int k = 0; k < RASTER_TPT; k++) {
+    const int f = f0 + k * 256;
+    TriSetup t;
+    t.ok = 0;
+    if (f < F) tri_setup(sp[k][0], sp[k][1], sp[k][2], S, t);
+    const unsigned m = __ballot_sync(0xffffffffu, t.ok);
+    if (m) {
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&q_count, __popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (t.ok) {
+        const int e = base + __popc(m & ((1u << lane) - 1u));
+        q_f[e] = f;
+#pragma unroll
+        for (int c = 0; c < 3; c++) { q_i[c][e] = idx[k][c]; q_s[c][e] = sp[k][c]; }
+      }
+    }
+  }
+  __syncthreads();
+  const int count = q_count;
+  const float4* cl = clip + (size_t)n * V;
+  unsigned long long* zb = zbuf + (size_t)n * S * S;
+  for (int base = 0; base < count; base += 256) {    // warp-uniform trip count
+    const int e = base + (int)threadIdx.x;
+    const bool valid = e < count;
+    const int ee = valid ? e : 0;
+    raster_triangle(valid, q_f[ee], q_i[0][ee], q_i[1][ee], q_i[2][ee], q_s[0][ee], q_s[1][ee], q_s[2][ee], cl, S, zb);
+  }
+}
+
+// One-phase variant for meshes with few triangles per pixel (most triangles survive the cull, so the queue only adds
+// overhead: cfg 2, 20 k faces on ~15 k covered pixels, 234 vs 245 us per pass): same loads, triangles rasterised in place.
 __global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
                                                      const float4* __restrict__ clip, const int2* __restrict__ snap,
                                                      int S, unsigned long long* __restrict__ zbuf)
 {
   const int n = blockIdx.y;
-  const int f0 = blockIdx.x * (256 * RASTER_TPT) + threadIdx.x;
+  const int f0 = blockIdx.x * RASTER_FACES + threadIdx.x;
   const int2* sn = snap + (size_t)n * V;
   int idx[RASTER_TPT][3];
 #pragma unroll
@@ -602,7 +665,13 @@ FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const 
   FPB_CUDA(cudaMemsetAsync(zbuf, 0xff, (size_t)N * S * S * sizeof(unsigned long long), st));
   vertex_kernel<<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, S, clip, camd, snap);
   FPB_LAUNCH_CHECK();
-  raster_kernel<<<dim3(fpb_cdiv(F, 256 * RASTER_TPT), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
+  // dense meshes (several triangles per crop pixel): cull first, rasterise the survivors densely
+  static int cull_min = -1;
+  if (cull_min < 0) { const char* e = getenv("FPB_RASTER_CULL_MIN"); cull_min = e ? atoi(e) : 4; }
+  if ((long long)F >= (long long)cull_min * S * S)
+    raster_cull_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
+  else
+    raster_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
   FPB_LAUNCH_CHECK();
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
   const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
