@@ -40,9 +40,11 @@ __global__ void __launch_bounds__(256) ref_gemm_kernel(GemmProblem p)
 #pragma unroll
     for (int j = 0; j < 4; j++) acc[i][j] = 0.0f;
 
-  for (int k0 = 0; k0 < p.K; k0 += BK) {
+  // operand tile of K step k0 into registers (zero outside the image / the matrix)
+  auto fetch = [&](int k0, float4& av, float4& wv) {
     const int k = k0 + lk;
-    float4 av = make_float4(0.f, 0.f, 0.f, 0.f), wv = av;
+    av = make_float4(0.f, 0.f, 0.f, 0.f);
+    wv = av;
     if (mrow_ok && k < p.K) {
       const int tap = k / p.Cin, c = k - tap * p.Cin;
       const int ky = tap / p.KW, kx = tap - ky * p.KW;
@@ -51,9 +53,15 @@ __global__ void __launch_bounds__(256) ref_gemm_kernel(GemmProblem p)
         av = *reinterpret_cast<const float4*>(A + ((long long)(img * p.Hin + iy) * (p.row_pitch > 0 ? p.row_pitch : p.Win) + ix) * p.pix_pitch + c);
     }
     if (wrow_ok && k < p.K) wv = *reinterpret_cast<const float4*>(W + (long long)wn * p.ldw + k);
+  };
+  // the loads of step k0 + BK are issued before the FMAs of step k0 (the loop was bound by one global round trip per step)
+  float4 av, wv;
+  fetch(0, av, wv);
+  for (int k0 = 0; k0 < p.K; k0 += BK) {
     As[lk + 0][lr] = av.x; As[lk + 1][lr] = av.y; As[lk + 2][lr] = av.z; As[lk + 3][lr] = av.w;
     Bs[lk + 0][lr] = wv.x; Bs[lk + 1][lr] = wv.y; Bs[lk + 2][lr] = wv.z; Bs[lk + 3][lr] = wv.w;
     __syncthreads();
+    if (k0 + BK < p.K) fetch(k0 + BK, av, wv);
 #pragma unroll
     for (int kk = 0; kk < BK; kk++) {
       float a[4], w[4];
