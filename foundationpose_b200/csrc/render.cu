@@ -57,6 +57,53 @@ __device__ __forceinline__ void bary_zw(const float4 c0, const float4 c1, const 
 
 constexpr int SNAP_INVALID = INT32_MIN;   // vertex behind the camera (w <= 0) or beyond the fixed-point range
 
+// Clip-space position of one vertex (P * glcam * pose, then the crop zoom): the ONE instruction sequence used by the
+// vertex pass and, in lean mode, by the rasteriser and the shader when they recompute a corner (bit-identical values).
+__device__ __forceinline__ float4 vertex_clip(float x, float y, float z, const float* M, const float* R)
+{
+  float c[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) c[j] = ((M[j * 4] * x + M[j * 4 + 1] * y) + M[j * 4 + 2] * z) + M[j * 4 + 3];
+  float4 cl;
+  cl.x = c[0] * R[0] + c[3] * R[2];
+  cl.y = c[1] * R[1] + c[3] * R[3];
+  cl.z = c[2];
+  cl.w = c[3];
+  return cl;
+}
+
+// camera-frame position + diffuse term (headlight: -normal_z clamped) of one vertex
+__device__ __forceinline__ float4 vertex_camd(float x, float y, float z, float nx, float ny, float nz, const float* T)
+{
+  float cam[3], cn[3];
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    cam[j] = ((T[j * 4] * x + T[j * 4 + 1] * y) + T[j * 4 + 2] * z) + T[j * 4 + 3];
+    cn[j] = (T[j * 4] * nx + T[j * 4 + 1] * ny) + T[j * 4 + 2] * nz;
+  }
+  float nrm = sqrtf((cn[0] * cn[0] + cn[1] * cn[1]) + cn[2] * cn[2]);
+  float d = -(cn[2] / fmaxf(nrm, 1e-12f));
+  d = fminf(fmaxf(d, 0.0f), 1.0f);
+  return make_float4(cam[0], cam[1], cam[2], d);
+}
+
+// Where the rasteriser / shader get the float clip coordinates of a corner from: the array written by the vertex pass,
+// or (lean mode: large meshes, where that array is 16 B x V x N of HBM writes for a few thousand visible corners)
+// recomputed from the mesh position with the per-hypothesis matrices.
+struct ClipSrc {
+  const float4* cl;      // [V] of this hypothesis, or null in lean mode
+  const float* pos;      // [V,3]
+  const float* M;        // 16 floats (params + 13)
+  const float* R;        // 4 floats (params + 29)
+  __device__ __forceinline__ float4 get(int i) const
+  {
+    if (cl) return cl[i];
+    return vertex_clip(pos[i * 3], pos[i * 3 + 1], pos[i * 3 + 2], M, R);
+  }
+};
+
+// LEAN: only the snapped window positions are written (8 B per vertex instead of 40)
+template <bool LEAN>
 __global__ void __launch_bounds__(256) vertex_kernel(const float* __restrict__ pos, const float* __restrict__ vnormals, int V,
                                                      const float* __restrict__ poses, const float* __restrict__ params,
                                                      int S, float4* __restrict__ clip, float4* __restrict__ camd,
@@ -73,26 +120,11 @@ __global__ void __launch_bounds__(256) vertex_kernel(const float* __restrict__ p
   __syncthreads();
   if (v >= V) return;
   const float x = pos[v * 3], y = pos[v * 3 + 1], z = pos[v * 3 + 2];
-  float c[4];
-#pragma unroll
-  for (int j = 0; j < 4; j++) c[j] = ((sM[j * 4] * x + sM[j * 4 + 1] * y) + sM[j * 4 + 2] * z) + sM[j * 4 + 3];
-  float4 cl;
-  cl.x = c[0] * sR[0] + c[3] * sR[2];
-  cl.y = c[1] * sR[1] + c[3] * sR[3];
-  cl.z = c[2];
-  cl.w = c[3];
-  float cam[3], cn[3];
-  const float nx = vnormals[v * 3], ny = vnormals[v * 3 + 1], nz = vnormals[v * 3 + 2];
-#pragma unroll
-  for (int j = 0; j < 3; j++) {
-    cam[j] = ((sT[j * 4] * x + sT[j * 4 + 1] * y) + sT[j * 4 + 2] * z) + sT[j * 4 + 3];
-    cn[j] = (sT[j * 4] * nx + sT[j * 4 + 1] * ny) + sT[j * 4 + 2] * nz;
+  const float4 cl = vertex_clip(x, y, z, sM, sR);
+  if (!LEAN) {
+    clip[(size_t)n * V + v] = cl;
+    camd[(size_t)n * V + v] = vertex_camd(x, y, z, vnormals[v * 3], vnormals[v * 3 + 1], vnormals[v * 3 + 2], sT);
   }
-  float nrm = sqrtf((cn[0] * cn[0] + cn[1] * cn[1]) + cn[2] * cn[2]);
-  float d = -(cn[2] / fmaxf(nrm, 1e-12f));
-  d = fminf(fmaxf(d, 0.0f), 1.0f);
-  clip[(size_t)n * V + v] = cl;
-  camd[(size_t)n * V + v] = make_float4(cam[0], cam[1], cam[2], d);
   // window position in 1/16 pixel units (8*S sub-pixels per clip unit), snapped once per vertex
   int2 sn = make_int2(SNAP_INVALID, 0);
   if (cl.w > 0.0f) {
@@ -197,7 +229,7 @@ constexpr int SMALL_TRI_PIXELS = 16;
 // One triangle per lane; the whole warp must call this together (the large-footprint path is warp-cooperative).
 // valid: this lane holds face f with corner indices i0..i2 and their snapped positions s0..s2.
 __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i1, int i2, const int2 s0, const int2 s1,
-                                                const int2 s2, const float4* __restrict__ cl, int S,
+                                                const int2 s2, const ClipSrc cl, int S,
                                                 unsigned long long* __restrict__ zb)
 {
   TriSetup t;
@@ -236,7 +268,7 @@ __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i
       // warp (1-3 for pixel-sized triangles) instead of the largest bounding box; the float clip coordinates are
       // fetched only by triangles that cover a pixel centre
       if (mask) {
-        const float4 c0 = cl[i0], c1 = cl[i1], c2 = cl[i2];
+        const float4 c0 = cl.get(i0), c1 = cl.get(i1), c2 = cl.get(i2);
         const uint32_t mdiv = (256u + (uint32_t)bw - 1u) / (uint32_t)bw;     // b / bw == (b * mdiv) >> 8 for b < 16, bw <= 16
         do {
           const uint32_t b = (uint32_t)__ffs(mask) - 1u;
@@ -263,9 +295,9 @@ __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i
     }
     s.px0 = __shfl_sync(0xffffffffu, t.px0, src); s.px1 = __shfl_sync(0xffffffffu, t.px1, src);
     s.py0 = __shfl_sync(0xffffffffu, t.py0, src); s.py1 = __shfl_sync(0xffffffffu, t.py1, src);
-    const float4 d0 = cl[__shfl_sync(0xffffffffu, i0, src)];    // same address in every lane: one broadcast load
-    const float4 d1 = cl[__shfl_sync(0xffffffffu, i1, src)];
-    const float4 d2 = cl[__shfl_sync(0xffffffffu, i2, src)];
+    const float4 d0 = cl.get(__shfl_sync(0xffffffffu, i0, src));    // same address in every lane: one broadcast load
+    const float4 d1 = cl.get(__shfl_sync(0xffffffffu, i1, src));
+    const float4 d2 = cl.get(__shfl_sync(0xffffffffu, i2, src));
     const uint32_t face = (uint32_t)__shfl_sync(0xffffffffu, f, src);     // lanes hold arbitrary faces (compacted queue)
     const int bw = s.px1 - s.px0 + 1, tot = bw * (s.py1 - s.py0 + 1);
     for (int i = lane; i < tot; i += 32) {
@@ -291,6 +323,7 @@ constexpr int RASTER_FACES = 256 * RASTER_TPT;
 
 __global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __restrict__ faces, int F, int V,
                                                           const float4* __restrict__ clip, const int2* __restrict__ snap,
+                                                          const float* __restrict__ pos, const float* __restrict__ params,
                                                           int S, unsigned long long* __restrict__ zbuf)
 {
   __shared__ int q_f[RASTER_FACES];
@@ -336,7 +369,8 @@ __global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __re
   }
   __syncthreads();
   const int count = q_count;
-  const float4* cl = clip + (size_t)n * V;
+  const ClipSrc cl = {clip ? clip + (size_t)n * V : nullptr, pos, params + (size_t)n * FPB_CROP_STRIDE + 13,
+                      params + (size_t)n * FPB_CROP_STRIDE + 29};
   unsigned long long* zb = zbuf + (size_t)n * S * S;
   for (int base = 0; base < count; base += 256) {    // warp-uniform trip count
     const int e = base + (int)threadIdx.x;
@@ -350,6 +384,7 @@ __global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __re
 // overhead: cfg 2, 20 k faces on ~15 k covered pixels, 234 vs 245 us per pass): same loads, triangles rasterised in place.
 __global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
                                                      const float4* __restrict__ clip, const int2* __restrict__ snap,
+                                                     const float* __restrict__ pos, const float* __restrict__ params,
                                                      int S, unsigned long long* __restrict__ zbuf)
 {
   const int n = blockIdx.y;
@@ -370,7 +405,9 @@ __global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restric
 #pragma unroll
   for (int k = 0; k < RASTER_TPT; k++) {
     const int f = f0 + k * 256;
-    raster_triangle(f < F, f, idx[k][0], idx[k][1], idx[k][2], sp[k][0], sp[k][1], sp[k][2], clip + (size_t)n * V, S,
+    const ClipSrc cl = {clip ? clip + (size_t)n * V : nullptr, pos, params + (size_t)n * FPB_CROP_STRIDE + 13,
+                        params + (size_t)n * FPB_CROP_STRIDE + 29};
+    raster_triangle(f < F, f, idx[k][0], idx[k][1], idx[k][2], sp[k][0], sp[k][1], sp[k][2], cl, S,
                     zbuf + (size_t)n * S * S);
   }
 }
@@ -414,11 +451,12 @@ __device__ __forceinline__ void store_px8(void* base, size_t pix, const float v[
   }
 }
 
-template <bool BF16>
+template <bool BF16, bool LEAN>
 __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4* __restrict__ clip,
                                                     const float4* __restrict__ camd,
                                                     const unsigned long long* __restrict__ zbuf,
-                                                    const float* __restrict__ poses, int N, int S, float inv_radius,
+                                                    const float* __restrict__ poses, const float* __restrict__ params,
+                                                    int N, int S, float inv_radius,
                                                     float zthr, void* __restrict__ outA, int out_pitch, int out_xoff,
                                                     float* __restrict__ out_color,
                                                     float* __restrict__ out_xyz, int32_t* __restrict__ out_tri)
@@ -443,14 +481,32 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
   if (key != ~0ull) {
     const int f = (int)(uint32_t)(key & 0xffffffffu);
     const int i0 = mesh.faces[f * 3], i1 = mesh.faces[f * 3 + 1], i2 = mesh.faces[f * 3 + 2];
-    const float4* cl = clip + (size_t)n * mesh.V;
-    const float4* cd = camd + (size_t)n * mesh.V;
     const float xs = 2.0f / (float)S, xo = 1.0f / (float)S - 1.0f;
     float fx = (float)px * xs + xo, fy = (float)py * xs + xo;
     float b0, b1, zw;
-    bary_zw(cl[i0], cl[i1], cl[i2], fx, fy, b0, b1, zw);
+    float4 q0, q1, q2;
+    if (!LEAN) {
+      const float4* cl = clip + (size_t)n * mesh.V;
+      const float4* cd = camd + (size_t)n * mesh.V;
+      bary_zw(cl[i0], cl[i1], cl[i2], fx, fy, b0, b1, zw);
+      q0 = cd[i0]; q1 = cd[i1]; q2 = cd[i2];
+    } else {
+      // lean mode: the three corners of the visible triangle are recomputed (same instruction sequence as the vertex pass)
+      const float* T = poses + (size_t)n * 16;
+      const float* M = params + (size_t)n * FPB_CROP_STRIDE + 13;
+      const float* R = params + (size_t)n * FPB_CROP_STRIDE + 29;
+      const int iv[3] = {i0, i1, i2};
+      float4 cc[3], qq[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const float x = mesh.pos[iv[k] * 3], y = mesh.pos[iv[k] * 3 + 1], z = mesh.pos[iv[k] * 3 + 2];
+        cc[k] = vertex_clip(x, y, z, M, R);
+        qq[k] = vertex_camd(x, y, z, mesh.vnormals[iv[k] * 3], mesh.vnormals[iv[k] * 3 + 1], mesh.vnormals[iv[k] * 3 + 2], T);
+      }
+      bary_zw(cc[0], cc[1], cc[2], fx, fy, b0, b1, zw);
+      q0 = qq[0]; q1 = qq[1]; q2 = qq[2];
+    }
     const float b2 = (1.0f - b0) - b1;
-    const float4 q0 = cd[i0], q1 = cd[i1], q2 = cd[i2];
     xyz[0] = (b0 * q0.x + b1 * q1.x) + b2 * q2.x;
     xyz[1] = (b0 * q0.y + b1 * q1.y) + b2 * q2.y;
     xyz[2] = (b0 * q0.z + b1 * q1.z) + b2 * q2.z;
@@ -663,24 +719,36 @@ FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const 
   int2* snap = (int2*)w; w += align256((size_t)N * V * sizeof(int2));
   unsigned long long* zbuf = (unsigned long long*)w;
   FPB_CUDA(cudaMemsetAsync(zbuf, 0xff, (size_t)N * S * S * sizeof(unsigned long long), st));
-  vertex_kernel<<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, S, clip, camd, snap);
+  // lean mode: for large meshes the float clip / camera arrays (32 B x V x N, written once and read for a few thousand
+  // visible corners) are not materialised; rasteriser and shader recompute the corners they need.  FPB_RENDER_LEAN:
+  // 1 forces it (tests), 0 disables it; default: when those arrays would exceed 512 MB
+  static int lean_env = -2;
+  if (lean_env == -2) { const char* e = getenv("FPB_RENDER_LEAN"); lean_env = e ? atoi(e) : -1; }
+  const bool lean = lean_env >= 0 ? lean_env != 0 : (size_t)N * V * 32 > ((size_t)512 << 20);
+  if (lean) {
+    vertex_kernel<true><<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, S, clip, camd, snap);
+    clip = nullptr;
+    camd = nullptr;
+  } else {
+    vertex_kernel<false><<<dim3(fpb_cdiv(V, 256), N), 256, 0, st>>>(mesh->pos, mesh->vnormals, V, poses, params, S, clip, camd, snap);
+  }
   FPB_LAUNCH_CHECK();
   // dense meshes (several triangles per crop pixel): cull first, rasterise the survivors densely
   static int cull_min = -1;
   if (cull_min < 0) { const char* e = getenv("FPB_RASTER_CULL_MIN"); cull_min = e ? atoi(e) : 4; }
   if ((long long)F >= (long long)cull_min * S * S)
-    raster_cull_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
+    raster_cull_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, mesh->pos, params, S, zbuf);
   else
-    raster_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, S, zbuf);
+    raster_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, mesh->pos, params, S, zbuf);
   FPB_LAUNCH_CHECK();
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
   const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
-  if (a_is_bf16)
-    shade_kernel<true><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
-                                               out_xoff, out_color, out_xyz, out_tri);
-  else
-    shade_kernel<false><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, N, S, inv_radius, zthr, out_A, out_pitch,
-                                                out_xoff, out_color, out_xyz, out_tri);
+#define LAUNCH_SHADE(BF, LN)                                                                                          \
+  shade_kernel<BF, LN><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, params, N, S, inv_radius, zthr, out_A, \
+                                                   out_pitch, out_xoff, out_color, out_xyz, out_tri)
+  if (a_is_bf16) { if (lean) LAUNCH_SHADE(true, true); else LAUNCH_SHADE(true, false); }
+  else           { if (lean) LAUNCH_SHADE(false, true); else LAUNCH_SHADE(false, false); }
+#undef LAUNCH_SHADE
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }

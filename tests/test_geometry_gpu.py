@@ -227,13 +227,15 @@ def test_pose_update_config_gated_representations(trans_rep, rot_rep, scene2):
     assert np.abs(R @ R.transpose(0, 2, 1) - np.eye(3)).max() < 1e-5
 
 
-def test_render_bit_exact_two_phase_rasteriser():
-  """Dense meshes take the cull-then-rasterise kernel (raster_cull_kernel); force it for every mesh
-  (FPB_RASTER_CULL_MIN=0, read once per process) and repeat the bit-exact render comparison against the oracle."""
+@pytest.mark.parametrize('env', [dict(FPB_RASTER_CULL_MIN='0'), dict(FPB_RENDER_LEAN='1'),
+                                 dict(FPB_RASTER_CULL_MIN='0', FPB_RENDER_LEAN='1')])
+def test_render_bit_exact_dense_mesh_paths(env):
+  """Large / dense meshes take other kernels: cull-then-rasterise (raster_cull_kernel) and the lean vertex pass (only
+  snapped positions are stored, rasteriser and shader recompute the corners they need).  Force them for every mesh (the
+  switches are read once per process) and repeat the bit-exact render comparison against the oracle."""
   import os, subprocess, sys
   root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-  env = dict(os.environ, FPB_RASTER_CULL_MIN='0')
   r = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(root, 'tests', 'test_geometry_gpu.py'), '-m', 'gpu', '-q', '-x',
-                      '-k', 'test_render_bit_exact and not two_phase'], capture_output=True, text=True, env=env, cwd=root,
-                     timeout=900)
+                      '-k', 'test_render_bit_exact and not dense_mesh_paths'], capture_output=True, text=True,
+                     env=dict(os.environ, **env), cwd=root, timeout=900)
   assert r.returncode == 0 and '2 passed' in r.stdout, r.stdout[-1500:] + r.stderr[-500:]
