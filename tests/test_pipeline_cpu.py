@@ -79,3 +79,19 @@ def test_obj_reader_and_euler(tmp_path):
   T = np.eye(4); T[:3, :3] = Rz; T[:3, 3] = [1, 2, 3]
   x, y, z, roll, pitch, yaw = P.pose_to_6d(T)
   assert (x, y, z) == (1, 2, 3) and abs(yaw - a) < 1e-12 and abs(roll) < 1e-12 and abs(pitch) < 1e-12
+
+
+def test_bench_reference_arm_prints_one_json_line():
+  """bench.py contract: exactly ONE JSON line on stdout (library chatter goes to stderr); the reference arm times the CPU
+  port on a bounded sample and carries impl / cpu_baseline / e2e."""
+  import json, os, subprocess, sys
+  root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+  r = subprocess.run([sys.executable, os.path.join(root, 'bench.py'), '--impl', 'reference', '--steps', '1', '--warmup', '0',
+                      '--ref-hyps', '2'], capture_output=True, text=True, cwd=root, timeout=600)
+  assert r.returncode == 0, r.stderr[-1500:]
+  lines = [l for l in r.stdout.splitlines() if l.strip()]
+  assert len(lines) == 1
+  d = json.loads(lines[0])
+  assert d['impl'] == 'reference' and d['unit'] == 'hypotheses/s' and d['higher_is_better'] is True and d['value'] > 0
+  assert d['cpu_baseline']['kind'] == 'port' and d['cpu_baseline']['cores'] >= 1 and d['cpu_baseline']['value'] == d['value']
+  assert d['e2e']['value'] == d['value'] and d['e2e']['h2d_bytes_per_step'] == 0 and d['e2e']['d2h_bytes_per_step'] == 0
