@@ -35,9 +35,11 @@ _SIGS = {
   'fpb_mesh_destroy': (ci, [vp]),
   'fpb_render_ws_bytes': (sz, [ci, ci, ci]),
   'fpb_render_crops': (ci, [vp, vp, vp, ci, ci, cf, cf, vp, vp, ci, ci, ci, vp, vp, vp, vp]),
+  'fpb_render_crops_ex': (ci, [vp, vp, vp, ci, ci, cf, cf, vp, vp, ci, ci, ci, vp, vp, vp, ci, cf, cf, vp, vp]),
   'fpb_warp_crops': (ci, [vp, ci, vp, vp, ci, ci, vp, vp, vp, ci, ci, cf, ci, vp, ci, ci, ci, vp]),
   'fpb_pose_update': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, vp, vp]),
   'fpb_pose_update_ex': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, ci, ci, vp, vp, ci, vp, vp]),
+  'fpb_pose_update_deltas': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, ci, ci, vp, vp, ci, vp, vp, vp, vp]),
   'fpb_net_create': (ci, [vp, ci, ci, vp, sz, vp]),
   'fpb_net_destroy': (ci, [vp]),
   'fpb_net_ws_bytes': (sz, [ci, ci, ci]),

@@ -105,7 +105,8 @@ struct PoseUpdateArgs {
 
 __global__ void pose_update_kernel(const float* __restrict__ poses, const float* __restrict__ trans,
                                    const float* __restrict__ rot, int N, PoseUpdateArgs a,
-                                   const float* __restrict__ crop_params, float* __restrict__ out)
+                                   const float* __restrict__ crop_params, float* __restrict__ out,
+                                   float* __restrict__ out_td, float* __restrict__ out_rd)
 {
   int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
@@ -173,6 +174,11 @@ __global__ void pose_update_kernel(const float* __restrict__ poses, const float*
     for (int j = 0; j < 3; j++) o[i * 4 + j] = (R[0 * 3 + i] * T[0 * 4 + j] + R[1 * 3 + i] * T[1 * 4 + j]) + R[2 * 3 + i] * T[2 * 4 + j];
   o[3] = T[3] + td[0]; o[7] = T[7] + td[1]; o[11] = T[11] + td[2];
   o[12] = 0.f; o[13] = 0.f; o[14] = 0.f; o[15] = 1.f;
+  // trans_delta / rot_mat_delta as the reference keeps them in last_trans_update / last_rot_update (:238-239)
+  if (out_td) { out_td[n * 3] = td[0]; out_td[n * 3 + 1] = td[1]; out_td[n * 3 + 2] = td[2]; }
+  if (out_rd)
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) out_rd[n * 9 + i * 3 + j] = R[j * 3 + i];
 }
 
 
@@ -227,9 +233,10 @@ FPB_EXPORT int fpb_crop_params(const float* poses, int N, const float* K9_h, flo
   return FPB_OK;
 }
 
-FPB_EXPORT int fpb_pose_update_ex(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
-                                  float rot_normalizer, const float* tn3_h, int normalize_xyz, int trans_rep, int rot_rep,
-                                  const float* crop_params, const float* K9_h, int S, float* out_poses, void* stream)
+FPB_EXPORT int fpb_pose_update_deltas(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
+                                      float rot_normalizer, const float* tn3_h, int normalize_xyz, int trans_rep,
+                                      int rot_rep, const float* crop_params, const float* K9_h, int S, float* out_poses,
+                                      float* out_trans_delta, float* out_rot_delta, void* stream)
 {
   FPB_CHECK_ARG(poses && trans && rot && out_poses && N > 0);
   FPB_CHECK_ARG(trans_rep == FPB_TRANS_TRACKNET || trans_rep == FPB_TRANS_DEEPIM);
@@ -241,9 +248,18 @@ FPB_EXPORT int fpb_pose_update_ex(const float* poses, const float* trans, const 
   for (int i = 0; i < 3; i++) a.tn.v[i] = tn3_h ? tn3_h[i] : 0.f;
   a.normalize_xyz = normalize_xyz; a.trans_rep = trans_rep; a.rot_rep = rot_rep; a.S = S;
   for (int i = 0; i < 9; i++) a.K[i] = K9_h ? K9_h[i] : 0.f;
-  pose_update_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(poses, trans, rot, N, a, crop_params, out_poses);
+  pose_update_kernel<<<fpb_cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(poses, trans, rot, N, a, crop_params, out_poses,
+                                                                          out_trans_delta, out_rot_delta);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
+}
+
+FPB_EXPORT int fpb_pose_update_ex(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
+                                  float rot_normalizer, const float* tn3_h, int normalize_xyz, int trans_rep, int rot_rep,
+                                  const float* crop_params, const float* K9_h, int S, float* out_poses, void* stream)
+{
+  return fpb_pose_update_deltas(poses, trans, rot, N, mesh_diameter, rot_normalizer, tn3_h, normalize_xyz, trans_rep, rot_rep,
+                                crop_params, K9_h, S, out_poses, nullptr, nullptr, stream);
 }
 
 FPB_EXPORT int fpb_pose_update(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,

@@ -451,6 +451,10 @@ __device__ __forceinline__ void store_px8(void* base, size_t pix, const float v[
   }
 }
 
+// use_light / w_ambient / w_diffuse of nvdiffrast_render (src/Utils.py:200-211, default head light) and the optional
+// normal_map output (:192-197): interpolated camera-frame vertex normals, F.normalize'd, background 0
+struct ShadeOpts { int use_light; float w_ambient, w_diffuse; float* out_normal; };
+
 template <bool BF16, bool LEAN>
 __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4* __restrict__ clip,
                                                     const float4* __restrict__ camd,
@@ -459,7 +463,8 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
                                                     int N, int S, float inv_radius,
                                                     float zthr, void* __restrict__ outA, int out_pitch, int out_xoff,
                                                     float* __restrict__ out_color,
-                                                    float* __restrict__ out_xyz, int32_t* __restrict__ out_tri)
+                                                    float* __restrict__ out_xyz, int32_t* __restrict__ out_tri,
+                                                    ShadeOpts opt)
 {
   // block = 32 x 8 pixels of one crop: grid (ceil(S/32), ceil(S/8), N)
   const int n = blockIdx.z;
@@ -474,6 +479,7 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
     if (out_color) { out_color[idx * 3] = 0.f; out_color[idx * 3 + 1] = 0.f; out_color[idx * 3 + 2] = 0.f; }
     if (out_xyz) { out_xyz[idx * 3] = 0.f; out_xyz[idx * 3 + 1] = 0.f; out_xyz[idx * 3 + 2] = 0.f; }
     if (out_tri) out_tri[idx] = 0;
+    if (opt.out_normal) { opt.out_normal[idx * 3] = 0.f; opt.out_normal[idx * 3 + 1] = 0.f; opt.out_normal[idx * 3 + 2] = 0.f; }
     const float z6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     store_px8<BF16>(outA, ((size_t)n * S + i) * out_pitch + out_xoff + j, z6);
     return;
@@ -538,10 +544,29 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
     }
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-      float cv = c[k] * 0.8f + (dm * c[k]) * 0.5f;
+      float cv = opt.use_light ? c[k] * opt.w_ambient + (dm * c[k]) * opt.w_diffuse : c[k];
       col[k] = fminf(fmaxf(cv, 0.0f), 1.0f);
     }
     tri = f + 1;
+    if (opt.out_normal) {     // off the hot path: the rotated corner normals are recomputed here
+      const float* T = poses + (size_t)n * 16;
+      const int iv[3] = {i0, i1, i2};
+      float cn[3][3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const float nx = mesh.vnormals[iv[k] * 3], ny = mesh.vnormals[iv[k] * 3 + 1], nz = mesh.vnormals[iv[k] * 3 + 2];
+#pragma unroll
+        for (int jj = 0; jj < 3; jj++) cn[k][jj] = (T[jj * 4] * nx + T[jj * 4 + 1] * ny) + T[jj * 4 + 2] * nz;
+      }
+      float nm[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) nm[k] = (b0 * cn[0][k] + b1 * cn[1][k]) + b2 * cn[2][k];
+      const float dn = fmaxf(sqrtf((nm[0] * nm[0] + nm[1] * nm[1]) + nm[2] * nm[2]), 1e-12f);
+#pragma unroll
+      for (int k = 0; k < 3; k++) opt.out_normal[idx * 3 + k] = nm[k] / dn;
+    }
+  } else if (opt.out_normal) {
+    opt.out_normal[idx * 3] = 0.f; opt.out_normal[idx * 3 + 1] = 0.f; opt.out_normal[idx * 3 + 2] = 0.f;
   }
   if (out_color) { out_color[idx * 3] = col[0]; out_color[idx * 3 + 1] = col[1]; out_color[idx * 3 + 2] = col[2]; }
   if (out_xyz) { out_xyz[idx * 3] = xyz[0]; out_xyz[idx * 3 + 1] = xyz[1]; out_xyz[idx * 3 + 2] = xyz[2]; }
@@ -701,17 +726,15 @@ static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 FPB_EXPORT size_t fpb_render_ws_bytes(int N, int V, int S)
 {
+  if (N > 65535) N = 65535;      // larger batches are rendered in chunks on the same workspace
   return 2 * align256((size_t)N * V * sizeof(float4)) + align256((size_t)N * V * sizeof(int2)) +
          align256((size_t)N * S * S * sizeof(unsigned long long));
 }
 
-FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
-                                float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch,
-                                int out_xoff, float* out_color, float* out_xyz, int32_t* out_tri, void* stream)
+static int render_chunk(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S, float mesh_diameter,
+                        float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch, int out_xoff, float* out_color,
+                        float* out_xyz, int32_t* out_tri, ShadeOpts opt, cudaStream_t st)
 {
-  FPB_CHECK_ARG(mesh && poses && params && ws && out_A && N > 0 && S > 1 && S <= 4096 && N <= 65535);
-  FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff);
-  cudaStream_t st = (cudaStream_t)stream;
   const int V = mesh->V, F = mesh->F;
   char* w = (char*)ws;
   float4* clip = (float4*)w; w += align256((size_t)N * V * sizeof(float4));
@@ -745,7 +768,7 @@ FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const 
   const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
 #define LAUNCH_SHADE(BF, LN)                                                                                          \
   shade_kernel<BF, LN><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, params, N, S, inv_radius, zthr, out_A, \
-                                                   out_pitch, out_xoff, out_color, out_xyz, out_tri)
+                                                   out_pitch, out_xoff, out_color, out_xyz, out_tri, opt)
   if (a_is_bf16) { if (lean) LAUNCH_SHADE(true, true); else LAUNCH_SHADE(true, false); }
   else           { if (lean) LAUNCH_SHADE(false, true); else LAUNCH_SHADE(false, false); }
 #undef LAUNCH_SHADE
@@ -753,26 +776,66 @@ FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const 
   return FPB_OK;
 }
 
+// grid.z carries the hypothesis index (<= 65535 per launch): larger batches run in chunks on the same workspace
+// (the reference batches its renders in chunks of 512, predict_pose_refine.py:50-54, for any N)
+constexpr int MAX_N_PER_LAUNCH = 65535;
+
+FPB_EXPORT int fpb_render_crops_ex(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
+                                   float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch,
+                                   int out_xoff, float* out_color, float* out_xyz, int32_t* out_tri, int use_light,
+                                   float w_ambient, float w_diffuse, float* out_normal, void* stream)
+{
+  FPB_CHECK_ARG(mesh && poses && params && ws && out_A && N > 0 && S > 1 && S <= 4096);
+  FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff);
+  const size_t esz = a_is_bf16 ? 2 : 4;
+  for (int n0 = 0; n0 < N; n0 += MAX_N_PER_LAUNCH) {
+    const int n = (N - n0) < MAX_N_PER_LAUNCH ? (N - n0) : MAX_N_PER_LAUNCH;
+    const size_t px = (size_t)n0 * S * S;
+    ShadeOpts opt = {use_light, w_ambient, w_diffuse, out_normal ? out_normal + px * 3 : nullptr};
+    const int rc = render_chunk(mesh, poses + (size_t)n0 * 16, params + (size_t)n0 * FPB_CROP_STRIDE, n, S, mesh_diameter, zthr,
+                                ws, (char*)out_A + (size_t)n0 * S * out_pitch * 8 * esz, a_is_bf16, out_pitch, out_xoff,
+                                out_color ? out_color + px * 3 : nullptr, out_xyz ? out_xyz + px * 3 : nullptr,
+                                out_tri ? out_tri + px : nullptr, opt, (cudaStream_t)stream);
+    if (rc) return rc;
+  }
+  return FPB_OK;
+}
+
+FPB_EXPORT int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
+                                float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch,
+                                int out_xoff, float* out_color, float* out_xyz, int32_t* out_tri, void* stream)
+{
+  return fpb_render_crops_ex(mesh, poses, params, N, S, mesh_diameter, zthr, ws, out_A, a_is_bf16, out_pitch, out_xoff,
+                             out_color, out_xyz, out_tri, 1, 0.8f, 0.5f, nullptr, stream);
+}
+
 FPB_EXPORT int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_hw3, const float* depth_hw, int H, int W,
                               const float* poses, const float* params, const float* K9_h, int N, int S,
                               float mesh_diameter, int mode, void* out_B, int b_is_bf16, int out_pitch, int out_xoff,
                               void* stream)
 {
-  FPB_CHECK_ARG(rgb && poses && params && K9_h && out_B && N > 0 && N <= 65535 && S > 1 && H > 1 && W > 1);
+  FPB_CHECK_ARG(rgb && poses && params && K9_h && out_B && N > 0 && S > 1 && H > 1 && W > 1);
   FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff);
   FPB_CHECK_ARG(mode == 0 ? xyz_hw3 != nullptr : depth_hw != nullptr);
   cudaStream_t st = (cudaStream_t)stream;
   K9f K;
   for (int i = 0; i < 9; i++) K.k[i] = K9_h[i];
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
-  const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
   const float wsc = (float)W / (float)(W - 1), hsc = (float)H / (float)(H - 1), ssc = (float)S / (float)(S - 1);
+  const size_t esz = b_is_bf16 ? 2 : 4;
+  for (int n0 = 0; n0 < N; n0 += MAX_N_PER_LAUNCH) {      // grid.z limit: chunks of <= 65535 hypotheses
+    const int n = (N - n0) < MAX_N_PER_LAUNCH ? (N - n0) : MAX_N_PER_LAUNCH;
+    const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), n), threads(32, 8);
+    const float* po = poses + (size_t)n0 * 16;
+    const float* pa = params + (size_t)n0 * FPB_CROP_STRIDE;
+    void* ob = (char*)out_B + (size_t)n0 * S * out_pitch * 8 * esz;
 #define LAUNCH_WARP(BF, U8)                                                                                           \
-  warp_kernel<BF, U8><<<blocks, threads, 0, st>>>(rgb, xyz_hw3, depth_hw, H, W, poses, params, K, N, S, inv_radius,  \
-                                                  mode, wsc, hsc, ssc, out_B, out_pitch, out_xoff)
-  if (b_is_bf16) { if (rgb_is_u8) LAUNCH_WARP(true, true); else LAUNCH_WARP(true, false); }
-  else           { if (rgb_is_u8) LAUNCH_WARP(false, true); else LAUNCH_WARP(false, false); }
+  warp_kernel<BF, U8><<<blocks, threads, 0, st>>>(rgb, xyz_hw3, depth_hw, H, W, po, pa, K, n, S, inv_radius, mode,   \
+                                                  wsc, hsc, ssc, ob, out_pitch, out_xoff)
+    if (b_is_bf16) { if (rgb_is_u8) LAUNCH_WARP(true, true); else LAUNCH_WARP(true, false); }
+    else           { if (rgb_is_u8) LAUNCH_WARP(false, true); else LAUNCH_WARP(false, false); }
 #undef LAUNCH_WARP
-  FPB_LAUNCH_CHECK();
+    FPB_LAUNCH_CHECK();
+  }
   return FPB_OK;
 }

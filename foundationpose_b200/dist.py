@@ -109,7 +109,7 @@ def all_gather_ragged(x, n_total, world, group=None):
 
 
 @torch.inference_mode()
-def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, exchange='auto'):
+def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, exchange='auto', ob_id=None):
   """FoundationPose.register (src/estimater.py:159-240) with the hypotheses sharded over the ranks of `group`.
   Every rank returns the same best pose (np.ndarray [4,4]).
   exchange: 'p2p' = stores into peer-mapped tables fused into the producing kernels + one device barrier
@@ -165,6 +165,8 @@ def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, excha
     pose = np.eye(4)
     pose[:3, 3] = _center_from_stats(stats, K)
     return pose
+  est.H, est.W = depth_t.shape[:2]                   # the attributes register() leaves behind (src/estimater.py:192-240)
+  est.K, est.ob_id, est.ob_mask = K, ob_id, ob_mask
   est.poses, est.scores = poses[ids], scores[ids]
   est.pose_last, est.best_id = est.poses[0], ids[0]
   return best

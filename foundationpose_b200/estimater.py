@@ -83,6 +83,10 @@ class FoundationPose:
   def reset_object(self, model_pts, model_normals, symmetry_tfs=None, mesh=None):
     """src/estimater.py:44-78 (the open3d voxel down-sampling only feeds utilities off the hot path; kept as a
     plain numpy grid-average)."""
+    if isinstance(mesh, dict):                 # a ready mesh_tensors dict (SURVEY 8(b))
+      mesh = U.mesh_from_tensors(mesh)
+    elif not hasattr(mesh, 'copy'):            # duck-typed mesh without .copy()
+      mesh = U.MeshLike(mesh.vertices, mesh.faces, mesh.vertex_normals, getattr(mesh, 'visual', None))
     verts = np.asarray(mesh.vertices)
     max_xyz = verts.max(axis=0)
     min_xyz = verts.min(axis=0)

@@ -113,7 +113,8 @@ def load_obj(path):
     np.add.at(vn, F[:, k], fn)
   vn /= np.maximum(np.linalg.norm(vn, axis=1, keepdims=True), 1e-12)
   grey = np.tile(np.array([[128, 128, 128, 255]], dtype=np.uint8), (len(V), 1))   # untextured CAD part
-  return SimpleNamespace(vertices=V, faces=F, vertex_normals=vn, visual=SimpleNamespace(vertex_colors=grey))
+  from .utils import MeshLike
+  return MeshLike(V, F, vn, SimpleNamespace(vertex_colors=grey, uv=None, material=None))
 
 
 def pose_to_6d(pose):
@@ -156,12 +157,10 @@ class FoundationPoseEstimator(Processor):
       from .estimater import FoundationPose
       from .predict_pose_refine import PoseRefinePredictor
       from .predict_score import ScorePredictor
-      if isinstance(mesh, dict):
-        pts, nrm = mesh['pos'], mesh['vnormals']
-        pts = pts.detach().cpu().numpy() if hasattr(pts, 'detach') else np.asarray(pts)
-        nrm = nrm.detach().cpu().numpy() if hasattr(nrm, 'detach') else np.asarray(nrm)
-      else:
-        pts, nrm = np.asarray(mesh.vertices), np.asarray(mesh.vertex_normals)
+      if isinstance(mesh, dict):              # a ready mesh_tensors dict: rebuild the trimesh-like view reset_object needs
+        from .utils import mesh_from_tensors
+        mesh = mesh_from_tensors(mesh)
+      pts, nrm = np.asarray(mesh.vertices), np.asarray(mesh.vertex_normals)
       self.est = FoundationPose(model_pts=pts, model_normals=nrm, mesh=mesh, scorer=self.scorer or ScorePredictor(),
                                 refiner=self.refiner or PoseRefinePredictor(), glctx=None, debug=self.debug)
     return self.est

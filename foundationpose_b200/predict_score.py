@@ -12,7 +12,8 @@ import torch
 
 from . import nets
 from . import utils as U
-from .predict_pose_refine import Config, load_checkpoint_state_dict
+from .datasets import ScoreMultiPairH5Dataset
+from .predict_pose_refine import Config, batch_from_AB, resolve_weights
 
 
 def default_score_cfg():
@@ -21,9 +22,16 @@ def default_score_cfg():
                 zfar=np.inf, enable_amp=True)
 
 
+# predict_score.py:126-141: defaults for keys a run's config.yml may lack
+SCORE_COMPAT_DEFAULTS = dict(use_normal=False, use_BN=False, zfar=np.inf, c_in=4, normalize_xyz=False, crop_ratio=1.2)
+
+
 def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_ratio, normal_map=None, mesh_diameter=None,
                          glctx=None, mesh_tensors=None, dataset=None, cfg=None, out_AB=None, bf16=True):
-  """reference :57-114 + TripletH5Dataset.transform_batch fused -> (AB [2N,S,S+8,8], params)."""
+  """reference :57-114 + TripletH5Dataset.transform_batch (h5_dataset.py:137-179) fused.  Returns a BatchPoseData
+  of zero-copy views over the network input `pose_data.AB` ([2N,S,S+8,8]) as the refiner's function does;
+  xyz_mapBs is the rebuilt (depth -> full frame -> xyz -> crop) map of h5_dataset.py:158-161.  depthAs / depthBs
+  ([N,1,S,S], the raw crop depths of :84-99) are not needed by the fused path and are produced on first access."""
   S = int(render_size[0])
   H, W = rgb.shape[:2]
   N = len(ob_in_cams)
@@ -34,30 +42,40 @@ def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_rati
     out_AB = U.net_input_buffer(N, S, torch.bfloat16 if bf16 else torch.float)
   U.render_crops(mesh_tensors, ob_in_cams, params, S, mesh_diameter, 0.1, out_A=out_AB[:N])
   U.warp_crops(rgb, None, depth, ob_in_cams, params, K, S, mesh_diameter, 1, out_B=out_AB[N:])
-  return out_AB, params
+  pd = batch_from_AB(out_AB, params, ob_in_cams, K, mesh_diameter, S)
+  pd.Ks = pd.Ks.expand(N, 3, 3)                                     # :102
+  poses = pd.poseA
+
+  def depth_As():                                                   # :84,92: z of the rendered xyz map
+    _, ex = U.render_crops(mesh_tensors, poses, params, S, 1.0, 0.0, bf16=False, debug=True)
+    return ex['xyz'][..., 2].reshape(N, 1, S, S).contiguous()
+
+  def depth_Bs():                                                   # :93: nearest warp of the observed depth
+    return U.warp_depth_nearest(depth, params, S)
+
+  pd.set_lazy('depthAs', depth_As)
+  pd.set_lazy('depthBs', depth_Bs)
+  return pd
 
 
 class ScorePredictor:
-  def __init__(self, amp=True, cfg=None, state_dict=None, ckpt_path=None, seed=1234, precision='bf16'):
+  def __init__(self, amp=True, cfg=None, state_dict=None, ckpt_path=None, seed=None, precision='bf16',
+               allow_synthetic=False):
+    """reference :118-156 reads weights/2024-01-11-20-02-45/{model_best.pth,config.yml}; see PoseRefinePredictor for
+    ckpt_path / state_dict / cfg / allow_synthetic."""
     self.amp = amp
     self.run_name = '2024-01-11-20-02-45'
-    self.cfg = default_score_cfg()
-    if cfg is not None:
-      self.cfg.update(cfg)
-    if ckpt_path is None:
-      cand = os.path.join(os.path.dirname(os.path.realpath(__file__)), '..', 'weights', self.run_name, 'model_best.pth')
-      if os.path.exists(cand):
-        ckpt_path = cand
-    if state_dict is None and ckpt_path is not None:
-      state_dict = load_checkpoint_state_dict(ckpt_path)
+    synthetic_ok = allow_synthetic or seed is not None
+    self.cfg, state_dict = resolve_weights(self.run_name, default_score_cfg(), SCORE_COMPAT_DEFAULTS, cfg, state_dict,
+                                           ckpt_path, synthetic_ok, 'ScorePredictor')
     if state_dict is None:
-      state_dict = nets.synthetic_state_dict(nets.SCORE, seed)
-    if not self.cfg['normalize_xyz'] or self.cfg['c_in'] != 6:
-      raise NotImplementedError('only normalize_xyz=True, c_in=6 (the released configuration)')
+      state_dict = nets.synthetic_state_dict(nets.SCORE, 1234 if seed is None else seed)
+    if not self.cfg['normalize_xyz'] or self.cfg['c_in'] != 6 or not self.cfg['use_BN'] or self.cfg['use_normal']:
+      raise NotImplementedError('only normalize_xyz=True, c_in=6, use_BN=True, use_normal=False (the released configuration)')
     self.state_dict = state_dict
     self.precision = precision
     self.model = nets.Net(nets.SCORE, state_dict, precision)
-    self.dataset = None
+    self.dataset = ScoreMultiPairH5Dataset(cfg=self.cfg, mode='test', h5_file=None, max_num_key=1)
     self._ab = None
     self.last_features = None
 

@@ -333,6 +333,39 @@ def make_mesh_tensors(mesh, device='cuda', max_tex_size=None):
   return mesh_tensors
 
 
+class MeshLike:
+  """Minimal duck-typed stand-in for trimesh.Trimesh (trimesh is absent offline): what reset_object /
+  make_mesh_tensors touch -- .vertices, .faces, .vertex_normals, .visual and .copy()."""
+
+  def __init__(self, vertices, faces, vertex_normals, visual):
+    self.vertices, self.faces, self.vertex_normals, self.visual = vertices, faces, vertex_normals, visual
+
+  def copy(self):
+    import copy
+    return MeshLike(np.array(self.vertices), np.array(self.faces), np.array(self.vertex_normals), copy.deepcopy(self.visual))
+
+
+def mesh_from_tensors(mesh_tensors):
+  """Inverse of make_mesh_tensors: a ready mesh_tensors dict (pos, faces, vnormals, vertex_color | tex + uv [+ uv_idx],
+  torch or numpy) -> MeshLike, so that callers holding only the dict can build a FoundationPose."""
+  from types import SimpleNamespace
+
+  def host(x):
+    return x.detach().cpu().numpy() if torch.is_tensor(x) else np.asarray(x)
+  mt = mesh_tensors
+  if 'tex' in mt:
+    tex = host(mt['tex']).reshape(mt['tex'].shape[-3], mt['tex'].shape[-2], 3)
+    uv = host(mt['uv']).astype(np.float64).copy()
+    uv[:, 1] = 1 - uv[:, 1]                                   # make_mesh_tensors flips v
+    img = np.clip(np.rint(tex * 255.0), 0, 255).astype(np.uint8)
+    visual = SimpleNamespace(uv=uv, material=SimpleNamespace(image=img), vertex_colors=None)
+  else:
+    col = np.clip(np.rint(host(mt['vertex_color']) * 255.0), 0, 255).astype(np.uint8)
+    visual = SimpleNamespace(uv=None, material=None, vertex_colors=col)
+  return MeshLike(host(mt['pos']).astype(np.float64), host(mt['faces']).astype(np.int64),
+                  host(mt['vnormals']).astype(np.float64), visual)
+
+
 def mesh_handle_of(mesh_tensors):
   """Cache the device mesh handle inside the mesh_tensors dict (the dict is the drop-in's mesh interface)."""
   h = mesh_tensors.get('_fpb_handle')
@@ -355,10 +388,11 @@ def net_input_buffer(N, S, dtype):
   return torch.zeros((2 * N, S, IN_PITCH, 8), dtype=dtype, device='cuda')
 
 
-def render_crops(mesh_tensors, poses, params, S, mesh_diameter, zthr, out_A=None, bf16=True, debug=False):
+def render_crops(mesh_tensors, poses, params, S, mesh_diameter, zthr, out_A=None, bf16=True, debug=False, use_light=True,
+                 w_ambient=0.8, w_diffuse=0.5, get_normal=False):
   """Render all N hypotheses at crop resolution and write network input A ([N,S,P,8]; P = S for a dense buffer,
   P = IN_PITCH for the row-padded layout the networks read, see net_input_buffer).
-  Returns (A, extras) where extras holds fp32 color/xyz/tri when debug=True."""
+  Returns (A, extras) where extras holds fp32 color/xyz/tri when debug=True and `normal` when get_normal=True."""
   mh = mesh_handle_of(mesh_tensors)
   poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
   N = len(poses)
@@ -372,9 +406,13 @@ def render_crops(mesh_tensors, poses, params, S, mesh_diameter, zthr, out_A=None
     x = torch.empty((N, S, S, 3), dtype=torch.float, device='cuda')
     t = torch.empty((N, S, S), dtype=torch.int32, device='cuda')
     extras = dict(color=c, xyz=x, tri=t)
-  check(lib().fpb_render_crops(mh.handle, ptr(poses), ptr(params), N, S, float(mesh_diameter), float(zthr), ptr(ws),
-                               ptr(out_A), 1 if out_A.dtype == torch.bfloat16 else 0, out_A.shape[2],
-                               (out_A.shape[2] - S) // 2, ptr(c), ptr(x), ptr(t), stream()))
+  nm = None
+  if get_normal:
+    nm = extras['normal'] = torch.empty((N, S, S, 3), dtype=torch.float, device='cuda')
+  check(lib().fpb_render_crops_ex(mh.handle, ptr(poses), ptr(params), N, S, float(mesh_diameter), float(zthr), ptr(ws),
+                                  ptr(out_A), 1 if out_A.dtype == torch.bfloat16 else 0, out_A.shape[2],
+                                  (out_A.shape[2] - S) // 2, ptr(c), ptr(x), ptr(t), 1 if use_light else 0,
+                                  float(w_ambient), float(w_diffuse), ptr(nm), stream()))
   return out_A, extras
 
 
@@ -396,17 +434,51 @@ def warp_crops(rgb_t, xyz_map_t, depth_t, poses, params, K, S, mesh_diameter, mo
   return out_B
 
 
+def warp_depth_nearest(depth, params, S):
+  """kornia warp_perspective(depth, tf_to_crops, dsize=(S,S), mode='nearest', align_corners=False) of
+  predict_score.py:93 -> [N,1,S,S] fp32.  Runs through the refiner-mode warp kernel on the map (0, 0, depth) with a
+  zero translation and diameter 2^11: the kernel's (v - 0) * 2/d and |.| >= 2 test are then an exact power-of-two
+  scaling (undone here) and a no-op for depths below 2048 m; depths below 0.001 come out as 0."""
+  d = _as_cuda_f32(depth)
+  H, W = d.shape
+  N = len(params)
+  xyz = torch.zeros((H, W, 3), dtype=torch.float, device=d.device)
+  xyz[..., 2] = d
+  rgb = torch.zeros((H, W, 3), dtype=torch.uint8, device=d.device)
+  poses = torch.eye(4, dtype=torch.float, device=d.device).expand(N, 4, 4).contiguous()
+  out = torch.empty((N, S, S, 8), dtype=torch.float, device=d.device)
+  K9 = f32_host(np.eye(3), 9)
+  check(lib().fpb_warp_crops(ptr(rgb), 1, ptr(xyz), None, H, W, ptr(poses), ptr(params.contiguous()), hptr(K9), N, S, 2048.0,
+                             0, ptr(out), 0, S, 0, stream()))
+  return (out[..., 5] * 1024.0).reshape(N, 1, S, S)
+
+
 TRANS_REPS = {'tracknet': 0, 'deepim': 1}
 ROT_REPS = {'axis_angle': 0, '6d': 1}
 
 
 def pose_update(poses, trans, rot, mesh_diameter, rot_normalizer, trans_normalizer=None, normalize_xyz=True,
-                trans_rep='tracknet', rot_rep='axis_angle', crop_params=None, K=None, S=160):
+                trans_rep='tracknet', rot_rep='axis_angle', crop_params=None, K=None, S=160, return_deltas=False):
   """predict_pose_refine.py:195-231 + egocentric_delta_pose_to_pose (src/Utils.py:848-855) in one kernel.
   trans_rep='deepim' (:201-215) needs the iteration's crop parameters, K and the crop size; rot_rep='6d' (:223-224)
-  takes rot [N,6]."""
+  takes rot [N,6].  return_deltas: also (trans_delta [N,3], rot_mat_delta [N,3,3]) as the reference stores them in
+  last_trans_update / last_rot_update (:238-239)."""
   poses = _as_cuda_f32(poses).reshape(-1, 4, 4)
   out = torch.empty_like(poses)
+  if return_deltas:
+    if trans_rep not in TRANS_REPS or rot_rep not in ROT_REPS:
+      raise RuntimeError(f'unknown trans_rep / rot_rep: {trans_rep} / {rot_rep}')
+    rot = rot.contiguous()
+    assert rot.shape == (len(poses), 6 if rot_rep == '6d' else 3)
+    tn_ = f32_host(trans_normalizer, 3) if trans_normalizer is not None else None
+    K9_ = f32_host(torch.as_tensor(K).detach().cpu().numpy() if torch.is_tensor(K) else K, 9) if K is not None else None
+    td = torch.empty((len(poses), 3), dtype=torch.float, device=poses.device)
+    rd = torch.empty((len(poses), 3, 3), dtype=torch.float, device=poses.device)
+    check(lib().fpb_pose_update_deltas(ptr(poses), ptr(trans.contiguous()), ptr(rot), len(poses), float(mesh_diameter),
+                                       float(rot_normalizer), hptr(tn_), 1 if normalize_xyz else 0, TRANS_REPS[trans_rep],
+                                       ROT_REPS[rot_rep], ptr(crop_params), hptr(K9_), int(S), ptr(out), ptr(td), ptr(rd),
+                                       stream()))
+    return out, td, rd
   tn = f32_host(trans_normalizer, 3) if trans_normalizer is not None else None
   if trans_rep not in TRANS_REPS or rot_rep not in ROT_REPS:
     raise RuntimeError(f'unknown trans_rep / rot_rep: {trans_rep} / {rot_rep}')
@@ -428,17 +500,30 @@ def nvdiffrast_render(K=None, H=None, W=None, ob_in_cams=None, glctx=None, conte
                       mesh_tensors=None, mesh=None, projection_mat=None, bbox2d=None, output_size=None, use_light=False,
                       light_color=None, light_dir=np.array([0, 0, 1]), light_pos=np.array([0, 0, 0]), w_ambient=0.8,
                       w_diffuse=0.5, extra={}):
-  """reference: src/Utils.py:133-219, for the configuration the hot path uses (use_light=True, default light,
-  square crop given by bbox2d + output_size).  glctx/context are accepted and ignored.
-  Returns (color [n,S,S,3], depth [n,S,S], None); extra['xyz_map'] = camera-frame xyz [n,S,S,3]."""
-  if not use_light or light_color is not None or get_normal or projection_mat is not None or bbox2d is None:
-    raise NotImplementedError('only the render configuration used by make_crop_data_batch is implemented')
+  """reference: src/Utils.py:133-219.  glctx / context are accepted and ignored (there is no nvdiffrast context).
+  Returns (color [n,h,w,3], depth [n,h,w], normal_map [n,h,w,3] | None); extra['xyz_map'] = camera-frame xyz.
+  Supported: bbox2d + square output_size (the hot path) or the full frame (bbox2d=None, rendered into a square of
+  max(H, W) and cut back to [H,W]), use_light on/off with any w_ambient / w_diffuse, get_normal.  The default head
+  light (light_dir=(0,0,1), light_color=None) is the only light implemented: other values raise instead of being
+  silently ignored, as does a caller-supplied projection_mat."""
+  if projection_mat is not None or light_color is not None:
+    raise NotImplementedError('projection_mat / light_color are not supported')
+  if use_light and (light_dir is None or not np.array_equal(np.asarray(light_dir, dtype=np.float64).reshape(-1), [0, 0, 1])):
+    raise NotImplementedError('only the default head light light_dir=(0,0,1) is implemented (light_pos is unused with it)')
   if mesh_tensors is None:
     mesh_tensors = make_mesh_tensors(mesh)
-  S = int(output_size[0])
-  assert int(output_size[1]) == S
   poses = _as_cuda_f32(ob_in_cams).reshape(-1, 4, 4)
   N = len(poses)
+  full = bbox2d is None
+  if full:
+    # the full frame is the crop (0, 0, L, L), L = max(H, W): the same projection evaluated on a square raster whose
+    # first H rows / W columns are the frame's pixels
+    L = int(max(H, W))
+    S = L
+    bbox2d = torch.tensor([0.0, 0.0, float(L), float(L)], device='cuda').reshape(1, 4).expand(N, 4)
+  else:
+    S = int(output_size[0])
+    assert int(output_size[1]) == S, 'square crops only'
   K64 = np.asarray(K, dtype=np.float64)
   # rebuild the parameter block from the caller's bbox2d (umin,vmin,umax,vmax)
   params = torch.zeros((N, CROP_STRIDE), dtype=torch.float, device='cuda')
@@ -450,9 +535,14 @@ def nvdiffrast_render(K=None, H=None, W=None, ob_in_cams=None, glctx=None, conte
   l, t, r, b = bb[:, 0], H - bb[:, 1], bb[:, 2], H - bb[:, 3]
   params[:, 29] = W / (r - l); params[:, 30] = H / (t - b)
   params[:, 31] = (W - r - l) / (r - l); params[:, 32] = (H - t - b) / (t - b)
-  _, ex = render_crops(mesh_tensors, poses, params, S, 1.0, 0.0, bf16=False, debug=True)
-  extra['xyz_map'] = ex['xyz']
-  return ex['color'], ex['xyz'][..., 2].contiguous(), None
+  _, ex = render_crops(mesh_tensors, poses, params, S, 1.0, 0.0, bf16=False, debug=True, use_light=bool(use_light),
+                       w_ambient=w_ambient, w_diffuse=w_diffuse, get_normal=bool(get_normal or use_light))
+  color, xyz, normal = ex['color'], ex['xyz'], ex.get('normal')
+  if full:
+    color, xyz = color[:, :H, :W].contiguous(), xyz[:, :H, :W].contiguous()
+    normal = normal[:, :H, :W].contiguous() if normal is not None else None
+  extra['xyz_map'] = xyz
+  return color, xyz[..., 2].contiguous(), normal
 
 
 # ------------------------------------------------------------------------------------------------

@@ -107,6 +107,14 @@ size_t fpb_render_ws_bytes(int N, int V, int S);
 int fpb_render_crops(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
                      float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch,
                      int out_xoff, float* out_color, float* out_xyz, int32_t* out_tri, void* stream);
+/* the remaining arguments of nvdiffrast_render (src/Utils.py:133): use_light (0: unlit colour), w_ambient / w_diffuse
+ * (:211; fpb_render_crops uses the hot path's 1 / 0.8 / 0.5 with the default head light light_dir = (0,0,1)) and the
+ * normal_map output (:192-197, get_normal): out_normal [N,S,S,3] fp32 or NULL.  N is unbounded: batches above 65535
+ * hypotheses run in chunks on the same workspace (fpb_render_ws_bytes clamps N accordingly; so does fpb_warp_crops). */
+int fpb_render_crops_ex(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S,
+                        float mesh_diameter, float zthr, void* ws, void* out_A, int a_is_bf16, int out_pitch,
+                        int out_xoff, float* out_color, float* out_xyz, int32_t* out_tri, int use_light,
+                        float w_ambient, float w_diffuse, float* out_normal, void* stream);
 
 /* ---- observed-side crops into network input B: kornia warp_perspective call sites
  *      predict_pose_refine.py:63,72; predict_score.py:89-90; h5_dataset.py:137-170.
@@ -134,6 +142,13 @@ int fpb_pose_update(const float* poses, const float* trans, const float* rot, in
 int fpb_pose_update_ex(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
                        float rot_normalizer, const float* tn3_h, int normalize_xyz, int trans_rep, int rot_rep,
                        const float* crop_params, const float* K9_h, int S, float* out_poses, void* stream);
+/* same, additionally storing what the reference keeps as PoseRefinePredictor.last_trans_update / last_rot_update
+ * (predict_pose_refine.py:238-239): trans_delta [N,3] (after the normaliser / radius scaling) and rot_mat_delta
+ * [N,3,3] (the transposed exponential map); either pointer may be NULL. */
+int fpb_pose_update_deltas(const float* poses, const float* trans, const float* rot, int N, float mesh_diameter,
+                           float rot_normalizer, const float* tn3_h, int normalize_xyz, int trans_rep, int rot_rep,
+                           const float* crop_params, const float* K9_h, int S, float* out_poses,
+                           float* out_trans_delta, float* out_rot_delta, void* stream);
 
 /* ---- networks: learning/models/refine_network.py:26-93, score_network.py:27-90.
  *      Weights arrive as a flat host blob produced by foundationpose_b200.nets.pack_* (BN folded). ---- */

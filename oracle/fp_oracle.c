@@ -235,8 +235,12 @@ ORC_API void orc_render(const float* poses, const float* mtx, const float* rtf, 
                         const float* pos, const float* vnormals, const float* vcolor, int V,
                         const int32_t* faces, int F,
                         const float* uv, const int32_t* uv_idx, const float* tex, int Ht, int Wt,
-                        float* out_color, float* out_xyz, int32_t* out_tri)
+                        float* out_color, float* out_xyz, int32_t* out_tri,
+                        int use_light, float w_ambient, float w_diffuse, float* out_normal)
 {
+  /* use_light / w_ambient / w_diffuse: src/Utils.py:200-211 with the default head light (light_dir = (0,0,1));
+   * out_normal (may be NULL): the normal_map output, src/Utils.py:192-197 (interpolated camera-frame vertex normals,
+   * F.normalize'd, background 0). */
   const float xs = 2.0f / (float)S, xo = 1.0f / (float)S - 1.0f;
   const float sub = (float)(8 * S);
 #pragma omp parallel for schedule(dynamic, 1)
@@ -247,6 +251,7 @@ ORC_API void orc_render(const float* poses, const float* mtx, const float* rtf, 
     float* clip = (float*)malloc(sizeof(float) * 4 * V);
     float* cam = (float*)malloc(sizeof(float) * 3 * V);
     float* dif = (float*)malloc(sizeof(float) * V);
+    float* cnv = (float*)malloc(sizeof(float) * 3 * V);
     uint64_t* zb = (uint64_t*)malloc(sizeof(uint64_t) * S * S);
     for (int i = 0; i < S * S; i++) zb[i] = ~0ull;
     for (int v = 0; v < V; v++) {
@@ -261,6 +266,7 @@ ORC_API void orc_render(const float* poses, const float* mtx, const float* rtf, 
       float nx = vnormals[v * 3], ny = vnormals[v * 3 + 1], nz = vnormals[v * 3 + 2];
       float cn[3];
       for (int j = 0; j < 3; j++) cn[j] = (T[j * 4] * nx + T[j * 4 + 1] * ny) + T[j * 4 + 2] * nz;
+      for (int j = 0; j < 3; j++) cnv[v * 3 + j] = cn[j];
       float nrm = sqrtf((cn[0] * cn[0] + cn[1] * cn[1]) + cn[2] * cn[2]);
       float den = fmaxf(nrm, 1e-12f);
       float d = -(cn[2] / den);
@@ -322,6 +328,7 @@ ORC_API void orc_render(const float* poses, const float* mtx, const float* rtf, 
         uint64_t key = zb[py * S + px];
         if (key == ~0ull) {
           for (int k = 0; k < 3; k++) { out_color[o * 3 + k] = 0.0f; out_xyz[o * 3 + k] = 0.0f; }
+          if (out_normal) for (int k = 0; k < 3; k++) out_normal[o * 3 + k] = 0.0f;
           out_tri[o] = 0;
           continue;
         }
@@ -357,12 +364,19 @@ ORC_API void orc_render(const float* poses, const float* mtx, const float* rtf, 
         }
         float dm = (b0 * dif[i0] + b1 * dif[i1]) + b2 * dif[i2];
         for (int k = 0; k < 3; k++) {
-          float cv = col[k] * 0.8f + (dm * col[k]) * 0.5f;
+          float cv = use_light ? col[k] * w_ambient + (dm * col[k]) * w_diffuse : col[k];
           out_color[o * 3 + k] = fminf(fmaxf(cv, 0.0f), 1.0f);
+        }
+        if (out_normal) {
+          float nm[3];
+          for (int k = 0; k < 3; k++) nm[k] = (b0 * cnv[i0 * 3 + k] + b1 * cnv[i1 * 3 + k]) + b2 * cnv[i2 * 3 + k];
+          float nn = sqrtf((nm[0] * nm[0] + nm[1] * nm[1]) + nm[2] * nm[2]);
+          float dn = fmaxf(nn, 1e-12f);
+          for (int k = 0; k < 3; k++) out_normal[o * 3 + k] = nm[k] / dn;
         }
         out_tri[o] = f + 1;
       }
-    free(clip); free(cam); free(dif); free(zb);
+    free(clip); free(cam); free(dif); free(cnv); free(zb);
   }
 }
 

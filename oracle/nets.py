@@ -117,6 +117,14 @@ def build(kind, state_dict):
 
 
 @torch.no_grad()
+def score_from_features(net, feats):
+  """score_network.py:80-90 after extract_feat: feats [L,512] -> logits [L] (att_cross over the L hypotheses + linear)."""
+  x = feats.reshape(1, feats.shape[0], -1)
+  x, _ = net.att_cross(x, x, x)
+  return net.linear(x).reshape(-1)
+
+
+@torch.no_grad()
 def forward_chunked(net, kind, A_nhwc, B_nhwc, chunk=16):
   """A/B numpy [N,S,S,6] -> refine: (trans [N,3], rot [N,3]); score: feats handled whole (L=N)."""
   import numpy as np

@@ -67,9 +67,10 @@ def crop_params(poses, K, mesh_diameter, crop_ratio, S, H, W):
   return out
 
 
-def render(poses, cp, mesh, S):
+def render(poses, cp, mesh, S, use_light=True, w_ambient=0.8, w_diffuse=0.5, get_normal=False):
   """nvdiffrast_render restatement (src/Utils.py:133-219); mesh = dict of numpy arrays
-  (pos, faces, vnormals, and vertex_color | tex+uv+uv_idx, like make_mesh_tensors)."""
+  (pos, faces, vnormals, and vertex_color | tex+uv+uv_idx, like make_mesh_tensors).
+  Returns (color, xyz, tri) and, with get_normal, a 4th array: the normal_map (:192-197)."""
   poses = _f32(poses).reshape(-1, 16)
   N = len(poses)
   pos = _f32(mesh['pos']); vn = _f32(mesh['vnormals'])
@@ -85,8 +86,12 @@ def render(poses, cp, mesh, S):
   color = np.empty((N, S, S, 3), np.float32)
   xyz = np.empty((N, S, S, 3), np.float32)
   tri = np.empty((N, S, S), np.int32)
+  normal = np.empty((N, S, S, 3), np.float32) if get_normal else None
   lib().orc_render(_p(poses), _p(cp['mtx']), _p(cp['rtf']), N, S, _p(pos), _p(vn), _p(vc), len(pos),
-                   _p(faces), len(faces), _p(uv), _p(uvi), _p(tex), Ht, Wt, _p(color), _p(xyz), _p(tri))
+                   _p(faces), len(faces), _p(uv), _p(uvi), _p(tex), Ht, Wt, _p(color), _p(xyz), _p(tri),
+                   1 if use_light else 0, c_f(w_ambient), c_f(w_diffuse), _p(normal))
+  if get_normal:
+    return color, xyz, tri, normal
   return color, xyz, tri
 
 

@@ -9,6 +9,10 @@ What is pinned:
     tests; sha256 digests of both are stored so drift is detected.
   * pure functions AST-extracted from src/Utils.py: depth2xyzmap (:399-417), projection_matrix_from_intrinsics
     (:752-802), egocentric_delta_pose_to_pose (:848-855).
+  * pins.npz: src/transform.py PoseTransformer imported as-is (both unit settings, both gimbal-lock branches), and
+    AST-extracted add_err / adds_err (:232-253, scipy cKDTree), to_homo_torch / transform_pts / transform_dirs
+    (:520-546), symmetry_tfs_from_info (:806-834; its `euler_matrix` is the absent `transformations` package, so the
+    restatement foundationpose_b200.utils.euler_matrix is injected -- that one function stays unpinned).
 """
 import ast
 import hashlib
@@ -55,10 +59,11 @@ class _Cfg(dict):
   use_BN = True
 
 
-def extract_functions(names):
+def extract_functions(names, extra_ns=None):
   src = open(os.path.join(REF, 'src', 'Utils.py')).read()
   tree = ast.parse(src)
   ns = {'np': np, 'torch': torch}
+  ns.update(extra_ns or {})
   for node in tree.body:
     if isinstance(node, ast.FunctionDef) and node.name in names:
       exec(compile(ast.Module(body=[node], type_ignores=[]), 'Utils.py', 'exec'), ns)
@@ -106,6 +111,76 @@ def main():
   Bp = ego(torch.from_numpy(Apose), torch.from_numpy(td), torch.from_numpy(rd)).numpy()
   np.savez(os.path.join(HERE, 'utils_fns.npz'), depth=depth, K=K, xyz=xyz, P=P, A=Apose, td=td, rd=rd, B=Bp)
   print('utils_fns ok')
+  make_pins()
+
+
+def rot_zyx(roll, pitch, yaw):
+  import math
+  cr, sr, cp, sp, cy, sy = math.cos(roll), math.sin(roll), math.cos(pitch), math.sin(pitch), math.cos(yaw), math.sin(yaw)
+  Rx = np.array([[1, 0, 0], [0, cr, -sr], [0, sr, cr]])
+  Ry = np.array([[cp, 0, sp], [0, 1, 0], [-sp, 0, cp]])
+  Rz = np.array([[cy, -sy, 0], [sy, cy, 0], [0, 0, 1]])
+  return Rz @ Ry @ Rx
+
+
+def make_pins():
+  import contextlib
+  import importlib.util
+  import io
+  import math
+  from scipy.spatial import cKDTree
+  from foundationpose_b200.utils import euler_matrix
+  out = {}
+  spec = importlib.util.spec_from_file_location('ref_transform', os.path.join(REF, 'src', 'transform.py'))
+  mod = importlib.util.module_from_spec(spec)
+  spec.loader.exec_module(mod)
+  rng = np.random.default_rng(77)
+  poses = []
+  for k in range(10):
+    P = np.eye(4)
+    if k == 8:
+      P[:3, :3] = rot_zyx(0.7, math.pi / 2, 0.0)          # gimbal lock, R[2,0] < 0
+    elif k == 9:
+      P[:3, :3] = rot_zyx(-0.4, -math.pi / 2, 0.0)        # gimbal lock, R[2,0] > 0
+    else:
+      P[:3, :3] = rot_zyx(*rng.uniform(-1.4, 1.4, 3))
+    P[:3, 3] = rng.normal(size=3)
+    poses.append(P)
+  poses = np.array(poses)
+  with contextlib.redirect_stdout(io.StringIO()):
+    out['pt_poses'] = poses
+    out['pt_inch_deg'] = np.array([mod.PoseTransformer().transform_pose(P) for P in poses], dtype=np.float64)
+    out['pt_m_rad'] = np.array([mod.PoseTransformer(False, False).transform_pose(P) for P in poses], dtype=np.float64)
+  names = ['to_homo_torch', 'transform_pts', 'transform_dirs', 'add_err', 'adds_err', 'symmetry_tfs_from_info']
+  homo, tpts, tdirs, add_err, adds_err, sym = extract_functions(names, dict(cKDTree=cKDTree, euler_matrix=euler_matrix))
+  pts = rng.normal(size=(200, 3)) * 0.05
+  pred, gt = poses[0].copy(), poses[0].copy()
+  gt[:3, :3] = gt[:3, :3] @ rot_zyx(0.05, -0.03, 0.08)
+  gt[:3, 3] += [0.004, -0.002, 0.007]
+  out['err_pts'], out['err_pred'], out['err_gt'] = pts, pred, gt
+  out['add'] = np.float64(add_err(pred, gt, pts))
+  out['adds'] = np.float64(adds_err(pred, gt, pts))
+  tp = torch.from_numpy(rng.normal(size=(7, 3)).astype(np.float32))
+  tf1 = torch.from_numpy(poses[1].astype(np.float32))
+  tfb = torch.from_numpy(poses[:4].astype(np.float32))
+  out['tp_pts'], out['tp_tf1'], out['tp_tfb'] = tp.numpy(), tf1.numpy(), tfb.numpy()
+  out['tp_homo'] = homo(tp).numpy()
+  out['tp_single'] = tpts(tp, tf1).numpy()
+  out['tp_batched'] = tpts(tp, tfb).numpy()                 # [4,4,4] vs [7,3]: tf.shape[-3] != pts.shape[-2] -> broadcast
+  out['td_single'] = tdirs(tp, tf1).numpy()
+  out['td_batched'] = tdirs(tp, tfb).numpy()
+  T = np.eye(4); T[:3, :3] = rot_zyx(0, 0, math.pi); T[:3, 3] = [10, 20, 30]
+  infos = [{}, {'symmetries_discrete': [T.reshape(-1).tolist()]},
+           {'symmetries_continuous': [{'axis': [0, 0, 1], 'offset': [0, 0, 0]}]},
+           {'symmetries_continuous': [{'axis': [1, 0, 0], 'offset': [0.0, 0.01, 0.0]}],
+            'symmetries_discrete': [T.reshape(-1).tolist()]},
+           {'symmetries_continuous': [{'axis': [0, 1, 0], 'offset': [0, 0, 0]}]}]
+  import json
+  out['sym_infos'] = np.array(json.dumps(infos))
+  for i, info in enumerate(infos):
+    out[f'sym_{i}'] = sym(json.loads(json.dumps(info)), rot_angle_discrete=5 if i != 4 else 30)
+  np.savez_compressed(os.path.join(HERE, 'pins.npz'), **out)
+  print('pins ok', {k: getattr(v, 'shape', v) for k, v in out.items()})
 
 
 if __name__ == '__main__':

@@ -47,8 +47,8 @@ def test_register_fp32_matches_oracle(scene1):
   for step in orc.trace['refine']:
     got, _ = est.refiner.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=sc['rgb'], depth=d, K=sc['K'],
                                  ob_in_cams=step['poses_in'], xyz_map=xyz_map, mesh_diameter=est.diameter, iteration=1)
-    assert np.abs(est.refiner.last_trans_update.cpu().numpy() - step['trans']).max() < 2e-4
-    assert np.abs(est.refiner.last_rot_update.cpu().numpy() - step['rot']).max() < 2e-4
+    assert np.abs(est.refiner.last_trans_raw.cpu().numpy() - step['trans']).max() < 2e-4
+    assert np.abs(est.refiner.last_rot_raw.cpu().numpy() - step['rot']).max() < 2e-4
     assert np.abs(got.cpu().numpy() - step['poses_out']).max() < 1e-4
   tr = orc.trace['score']
   got_s, _ = est.scorer.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=sc['rgb'], depth=d, K=sc['K'],
@@ -81,18 +81,20 @@ def test_refine_iteration_bf16_within_north_star_bounds(scene1):
   assert rot < 1e-3 and trn < 1e-4
 
 
-def test_register_bf16_ranking_agrees(scene1):
+def test_register_bf16_scores_track_the_oracle(scene1):
+  """Scores of the GPU's refined poses vs the oracle scorer on the same poses (12 cube hypotheses): bounded absolute
+  deviation and the oracle's best hypothesis inside the GPU's top 2.  The top-1 agreement RATE over many ranking
+  problems is measured in tests/test_register_cfg2_gpu.py."""
   est, orc = _make(scene1, 'bf16')
   sc = scene1
   est.register(K=sc['K'], rgb=sc['rgb'], depth=sc['depth'], ob_mask=sc['mask'], iteration=2)
-  # score the GPU's refined poses with the oracle scorer: top-1 must agree
   poses = est.poses.cpu().numpy()
   d = orc.preprocess(sc['depth'])
   ref_scores, _ = orc.score_predict(sc['rgb'], d, poses, sc['K'])
   got = est.scores.cpu().numpy()
-  margin = np.sort(ref_scores)[-1] - np.sort(ref_scores)[-2]
-  print('score margin', margin, 'max |diff|', np.abs(got - ref_scores).max())
-  assert int(np.argmax(ref_scores)) == 0 or margin < 2 * np.abs(got - ref_scores).max()
+  print('score spread', np.ptp(ref_scores), 'max |diff|', np.abs(got - ref_scores).max())
+  assert np.abs(got - ref_scores).max() < 0.25 * max(np.ptp(ref_scores), 0.2)
+  assert int(np.argmax(ref_scores)) in (0, 1)            # est.poses are sorted by the GPU's scores
 
 
 def test_degenerate_inputs_and_track_one(scene1):
@@ -142,19 +144,19 @@ def test_refiner_deepim_6d_configuration(scene1):
   sc = scene1
   mesh, _ = centered(sc)
   poses, d = hypo_poses(sc, n=8, jitter_seed=1)
-  ref = PoseRefinePredictor(cfg=dict(trans_rep='deepim', rot_rep='6d'), precision='fp32')
+  ref = PoseRefinePredictor(cfg=dict(trans_rep='deepim', rot_rep='6d'), precision='fp32', allow_synthetic=True)
   assert ref.model.rot_dim == 6
   with pytest.raises(ValueError):
     PoseRefinePredictor(cfg=dict(rot_rep='6d'), state_dict=nets.synthetic_state_dict(nets.REFINE))
   with pytest.raises(RuntimeError):
-    PoseRefinePredictor(cfg=dict(rot_rep='quat'))
+    PoseRefinePredictor(cfg=dict(rot_rep='quat'), allow_synthetic=True)
   xyz = oo.depth2xyzmap(d, sc['K'])
   mt = U.make_mesh_tensors(mesh)
   out, _ = ref.predict(rgb=sc['rgb'], depth=d, K=sc['K'], ob_in_cams=poses, xyz_map=xyz, mesh=mesh, mesh_tensors=mt,
                        mesh_diameter=sc['diameter'], iteration=1)
   out = out.cpu().numpy()
   cp = oo.crop_params(poses, sc['K'], sc['diameter'], 1.2, 160, 480, 640)
-  want = oo.pose_update(poses, ref.last_trans_update.cpu().numpy(), ref.last_rot_update.cpu().numpy(), sc['diameter'],
+  want = oo.pose_update(poses, ref.last_trans_raw.cpu().numpy(), ref.last_rot_raw.cpu().numpy(), sc['diameter'],
                         ref.cfg['rot_normalizer'], ref.cfg['trans_normalizer'], True, trans_rep='deepim', rot_rep='6d',
                         tf_to_crops=cp['tf'].reshape(-1, 3, 3), K=sc['K'], S=160)
   assert np.abs(out - want).max() < 5e-5
