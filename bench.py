@@ -1,16 +1,21 @@
 #!/usr/bin/env python
 """bench.py -- hypotheses/sec of the render-and-compare path (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2]
-  torchrun --nproc-per-node N bench.py --gpus N ...        (one rank per GPU; hypotheses sharded, weak=false)
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision fp16|bf16]
+  torchrun --nproc-per-node N bench.py --gpus N ...        (one rank per GPU)
 
 A step = one full FoundationPose.register(): depth stencils, hypothesis generation, `iteration` x
 [crop windows, batched render, crop/warp, RefineNet, pose update], scorer render/warp, ScoreNet, ranking.
 Workload = BASELINE config 2: synthetic 20,480-face mesh, 640x480 RGB-D, 252 hypotheses, 5 refine iterations,
-160x160 crops, seeded random-init networks, bf16 tensor-core path.
-  value : hypotheses/s with the frame already resident in HBM (device tensors passed to register()).
-  e2e   : same call with HOST numpy buffers (pinned), H2D copies + the D2H read of the pose inside the timed region.
---impl reference times the CPU restatement of the reference path (oracle/) on the host cores: a bounded sample.
+160x160 crops, seeded random-init networks, tcgen05 tensor-core path (fp16 operands -- the reference's autocast dtype
+-- by default, fp32 accumulation; --precision bf16 selects bf16 operands, same kernels and speed).
+  N = 1 : value = hypotheses/s with the frame already resident in HBM (device tensors passed to register());
+          e2e = the same call with HOST numpy buffers (pinned), H2D copies + the D2H read of the pose inside the timed region.
+  N > 1 : the north-star partition -- ONE object, its 252 hypotheses sharded over the N ranks (dist.register_sharded;
+          "scaling": "strong", 252 hypotheses per step whatever N); value / e2e as above.  The result is checked
+          against the unsharded register() on every rank (`matches_unsharded`).  Extras: `replicas` (one full
+          register() per rank = BASELINE config 5, 8 distinct meshes sharded by object, only best pose + score gathered).
+--impl reference times the CPU restatement of the reference path (oracle/) on the host cores (full 252-hypothesis steps).
 """
 import argparse
 import json
@@ -28,6 +33,8 @@ sys.path.insert(0, ROOT)
 N_HYP, ITERS, S = 252, 5, 160
 FLOP_REFINE, FLOP_SCORE = 23.946e9, 21.938e9       # per hypothesis(-iteration), SURVEY 8(d)
 METRIC = 'hypotheses/sec (render+crop+refine+score)'
+WORKLOAD = ('cfg2: synthetic 20480-face mesh, 640x480 RGB-D, 252 hyps (42 views x 6 in-plane), est_refine_iter=5, '
+            '160x160 crops, full register()')
 
 
 _STDOUT = sys.stdout
@@ -113,17 +120,18 @@ def run_reference(args):
   from foundationpose_b200 import synthetic, nets
   scene = synthetic.make_scene(2)
   sd_r, sd_s = nets.synthetic_state_dict(nets.REFINE), nets.synthetic_state_dict(nets.SCORE)
-  n_hyp = args.ref_hyps
+  n_hyp = args.ref_hyps                 # default: all 252 hypotheses = the same workload as the GPU arm (~1 min per step)
   for _ in range(min(args.warmup, 1)):
     cpu_sample(scene, sd_r, sd_s, 2, 1)
   vals = []
-  for _ in range(min(args.steps, 3)):
+  for _ in range(max(1, min(args.steps, 2))):
     vals.append(cpu_sample(scene, sd_r, sd_s, n_hyp, ITERS))
   best = sorted(vals, key=lambda d: d['seconds'])[len(vals) // 2]
   line = dict(metric=METRIC, value=best['value'], unit='hypotheses/s', n_gpus=args.gpus, steps=len(vals),
               warmup=min(args.warmup, 1), ms_per_step=best['seconds'] * 1e3, higher_is_better=True, scaling='weak',
               vs_baseline=None, dtype='f32', data='synthetic', impl='reference',
-              config=dict(workload=f'cfg2 sample: {n_hyp} of {N_HYP} hypotheses, 20480-face mesh, 640x480, {ITERS} iters'),
+              config=dict(workload=WORKLOAD if n_hyp == N_HYP else f'cfg2 sample: {n_hyp} of {N_HYP} hypotheses, 20480-face mesh, '
+                                   f'640x480, {ITERS} iters', hypotheses=n_hyp, iterations=ITERS, precision='fp32'),
               cpu_baseline=dict(value=best['value'], unit='hypotheses/s', cores=best['cores'], kind='port', sample=best['sample']),
               e2e=dict(value=best['value'], unit='hypotheses/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0))
   emit(line)
@@ -167,10 +175,10 @@ def main():
   ap.add_argument('--steps', type=int, default=10)
   ap.add_argument('--warmup', type=int, default=3)
   ap.add_argument('--impl', default='ours')
-  ap.add_argument('--ref-hyps', type=int, default=24)
-  ap.add_argument('--cpu-hyps', type=int, default=12)
+  ap.add_argument('--ref-hyps', type=int, default=N_HYP)
+  ap.add_argument('--cpu-hyps', type=int, default=24)
   ap.add_argument('--no-cpu-baseline', action='store_true')
-  ap.add_argument('--precision', default='bf16')
+  ap.add_argument('--precision', default='fp16', choices=['fp16', 'bf16'])
   args = ap.parse_args()
   if args.impl == 'reference':
     return run_reference(args)
@@ -201,10 +209,12 @@ def main():
       dist.barrier()
     torch.cuda.synchronize()
 
-  def timed(fn, steps, warmup):
+  def timed(fn, steps, warmup, count_launches=False):
     for _ in range(warmup):
       fn()
     barrier()
+    if count_launches:
+      lib().fpb_launch_count(1)                  # reset AFTER the warm-up: gpu_launches counts the timed region only
     per = []
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
@@ -222,33 +232,68 @@ def main():
       dist.all_reduce(tot, op=dist.ReduceOp.MAX)
     return float(tot[0]), float(tot[1]), per
 
-  # weak scaling: every rank registers its own object (same synthetic frame) -> N * 252 hypotheses per step
-  def step_device():
-    pose = est.register(K=K, rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
-    if world > 1:
-      fdist.gather_best(pose, est.scores[0])
-    return pose
+  # N = 1: the full register(); N > 1: the same object, hypotheses sharded over the ranks (north-star partition)
+  if world == 1:
+    def step_device():
+      return est.register(K=K, rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
 
-  def step_host():
-    pose = est.register(K=K, rgb=h_rgb, depth=h_depth, ob_mask=h_mask, iteration=ITERS)
-    if world > 1:
-      fdist.gather_best(pose, est.scores[0])
-    return pose
+    def step_host():
+      return est.register(K=K, rgb=h_rgb, depth=h_depth, ob_mask=h_mask, iteration=ITERS)
+  else:
+    def step_device():
+      return fdist.register_sharded(est, K, d_rgb, d_depth, d_mask, iteration=ITERS, exchange=args.exchange)
+
+    def step_host():
+      return fdist.register_sharded(est, K, h_rgb, h_depth, h_mask, iteration=ITERS, exchange=args.exchange)
 
   sampler = ClockSampler(local)
   if rank == 0:
     sampler.start()
-  lib().fpb_launch_count(1)
-  dev_ms, wall_ms, per = timed(step_device, args.steps, max(args.warmup, 3))
+  dev_ms, wall_ms, per = timed(step_device, args.steps, max(args.warmup, 3), count_launches=True)
   launches = lib().fpb_launch_count(0)
   e_dev_ms, e_wall_ms, e_per = timed(step_host, args.steps, max(args.warmup, 3))
   sampler.stop_flag = True
-  total_hyp = n_hyp * world * args.steps
+  total_hyp = n_hyp * args.steps                 # strong scaling: 252 hypotheses per step whatever the number of ranks
   value = total_hyp / (dev_ms / 1e3)
   e2e_value = total_hyp / (e_wall_ms / 1e3)
+
+  # ---- N > 1: correctness of the sharded result on every rank + the replica (object-sharded, cfg 5) number ----
+  multi = None
+  if world > 1:
+    pose_s = step_host()
+    best_s, top_s = int(est.best_id), est.poses[0].clone()
+    pose_u = est.register(K=K, rgb=h_rgb, depth=h_depth, ob_mask=h_mask, iteration=ITERS)
+    ok = float(np.abs(pose_s - pose_u).max()) <= 1e-4 and best_s == int(est.best_id)
+    flag = torch.tensor([1.0 if ok else 0.0, float(np.abs(pose_s - pose_u).max())], device='cuda', dtype=torch.float64)
+    mn = flag.clone(); dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+    mx = flag.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    # cfg 5: 8 distinct meshes (seeds 50..57), one object per rank, only best pose + score all-gathered
+    obj_mesh = synthetic.blob_mesh(seed=50 + rank, coef=(0.15 + 0.01 * rank, 3.0 + 0.25 * rank, 2.0 - 0.1 * rank, 0.1))
+    oc = (obj_mesh.vertices.min(0) + obj_mesh.vertices.max(0)) / 2
+    obj_est, _, _ = make_estimator(dict(scene, mesh=obj_mesh, diameter=float(2 * np.linalg.norm(obj_mesh.vertices - oc, axis=1).max())),
+                                   args.precision)
+
+    def step_replica():
+      pose = obj_est.register(K=K, rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)
+      return fdist.gather_best(pose, obj_est.scores[0])
+    r_dev, r_wall, r_per = timed(step_replica, max(3, args.steps // 2), 2)
+    r_steps = max(3, args.steps // 2)
+    exch = args.exchange
+    if exch == 'auto':
+      exch = 'p2p' if world <= fdist.MAX_PEERS else 'nccl'      # what register_sharded resolves 'auto' to on NCCL
+    how = ('NCCL all_gather of features + poses' if exch == 'nccl' else
+           'feature rows / poses stored into every rank\'s table by the producing kernels (peer-mapped symmetric memory over '
+           'NVLink) + one device barrier')
+    multi = dict(matches_unsharded=bool(mn[0] > 0.5), max_pose_diff_vs_unsharded=float(mx[1]), exchange=exch, exchange_how=how,
+                 replicas=dict(value=n_hyp * world * r_steps / (r_dev / 1e3), unit='hypotheses/s', scaling='weak',
+                               register_ms_p50=float(np.median(r_per) * 1e3),
+                               note='BASELINE cfg 5: one distinct mesh (blob seeds 50..57) per rank, full 252-hypothesis register() '
+                                    'each, all_gather of the best pose + score only'))
+
   # per-stage device time: CUDA events at the boundaries of the three stages of one register(), median of 5
   stages = None
-  if rank == 0:
+  extras = {}
+  if rank == 0 and world == 1:
     from foundationpose_b200 import utils as U_
     marks = []
 
@@ -277,18 +322,28 @@ def main():
       setattr(obj, name, f)
     stages = {k + '_ms': float(np.median(v)) for k, v in acc.items()}
     stages['note'] = f'device time between CUDA events; refine = {ITERS} x (crop windows, render, warp, RefineNet, pose update); score = render, warp, ScoreNet, ranking'
-  strong = None
-  if world > 1:
-    def step_strong():
-      return fdist.register_sharded(est, K, h_rgb, h_depth, h_mask, iteration=ITERS, exchange=args.exchange)
-    s_dev, s_wall, s_per = timed(step_strong, args.steps, 2)
-    if args.exchange == 'auto':
-      args.exchange = 'p2p' if world <= fdist.MAX_PEERS else 'nccl'      # what register_sharded resolves 'auto' to on NCCL
-    how = ('NCCL all_gather of features + poses' if args.exchange == 'nccl' else
-           'feature rows / poses stored into every rank\'s table by the producing kernels (peer-mapped symmetric memory over '
-           'NVLink) + one device barrier')
-    strong = dict(register_ms_p50=float(np.median(s_per) * 1e3), value=n_hyp * args.steps / (s_wall / 1e3), unit='hypotheses/s',
-                  exchange=args.exchange, note='one object, 252 hypotheses sharded over the ranks; ' + how)
+    # cfg 3 (track_one video path: 1 hypothesis, 2 refine iterations, host frames) as a driver-visible number
+    lat = []
+    for _ in range(60):
+      s0 = time.perf_counter()
+      est.track_one_graphed(rgb=h_rgb, depth=h_depth, K=K, iteration=2)
+      lat.append(time.perf_counter() - s0)
+    extras['track_ms_p50'] = float(np.median(lat[10:]) * 1e3)
+    extras['track_note'] = 'cfg 3: track_one_graphed (CUDA-graph replay), 1 hypothesis x 2 iterations, pinned host frame in, pose out'
+    # the other operand type on the same kernels
+    other = 'bf16' if args.precision == 'fp16' else 'fp16'
+    est_o, _, _ = make_estimator(scene, other)
+    o_dev, _, o_per = timed(lambda: est_o.register(K=K, rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS), 5, 2)
+    extras['other_precision'] = dict(dtype=other, ms_per_step=o_dev / 5, register_ms_p50=float(np.median(o_per) * 1e3))
+    del est_o
+    # cfg 1 (12-face textured cube, 252 hypotheses, 1 iteration): the large-triangle regime of the rasteriser
+    sc1 = synthetic.make_scene(1)
+    est1, _, _ = make_estimator(sc1, args.precision)
+    d1 = [torch.as_tensor(sc1[k]).cuda() for k in ('rgb', 'depth', 'mask')]
+    c_dev, _, c_per = timed(lambda: est1.register(K=sc1['K'], rgb=d1[0], depth=d1[1], ob_mask=d1[2], iteration=1), 5, 2)
+    extras['cfg1'] = dict(ms_per_step=c_dev / 5, register_ms_p50=float(np.median(c_per) * 1e3),
+                          note='BASELINE cfg 1: textured cube (12 faces), 252 hypotheses, 1 refine iteration + scoring')
+    del est1
   if rank != 0:
     if world > 1:
       dist.destroy_process_group()
@@ -296,24 +351,26 @@ def main():
   pk = peaks()
   dom = time_dominant_kernel(torch)
   step_flops = n_hyp * (ITERS * FLOP_REFINE + FLOP_SCORE)
-  traffic = None
-  prof = os.path.join(ROOT, 'profiles', 'ncu_conv6_r01.json')      # dram__bytes_read+write of this kernel, one ncu --set full capture
-  if os.path.exists(prof):
-    traffic = json.load(open(prof)).get('traffic_bytes_per_launch')
+  traffic = traffic_from = None
+  for name in ('ncu_conv6_r02.json', 'ncu_conv6_r01.json'):      # dram__bytes_read+write of this kernel, one ncu --set full capture
+    prof = os.path.join(ROOT, 'profiles', name)
+    if os.path.exists(prof):
+      pj = json.load(open(prof))
+      traffic, traffic_from = pj.get('traffic_bytes_per_launch'), f"{name} (ncu --set full capture of build {pj.get('build', 'r01j')}, not of this run)"
+      break
   roof = dict(bound='tensor', achieved=dom['tflops'], peak=pk['tf_burst'], unit='TFLOP/s', frac=dom['tflops'] / pk['tf_burst'],
-              traffic=traffic, kernel=dom['kernel'], ms_per_launch=dom['ms'], flops_per_launch=dom['flops'], peak_source=pk['src'],
-              step_tflops=step_flops * world * args.steps / (dev_ms / 1e3) / 1e12 / world,
-              step_frac_of_sustained=step_flops * args.steps / (dev_ms / 1e3) / 1e12 / pk['tf_sust'])
+              traffic=traffic, traffic_source=traffic_from, kernel=dom['kernel'], ms_per_launch=dom['ms'], flops_per_launch=dom['flops'], peak_source=pk['src'],
+              step_tflops=step_flops * args.steps / (dev_ms / 1e3) / 1e12 / world,
+              step_frac_of_sustained=step_flops * args.steps / (dev_ms / 1e3) / 1e12 / world / pk['tf_sust'])
   cpu = None
-  if not args.no_cpu_baseline:
+  if not args.no_cpu_baseline and world == 1:
     cpu = cpu_sample(scene, sd_r, sd_s, args.cpu_hyps, ITERS)
     cpu.pop('seconds')
   h2d = int(rgb.nbytes + depth.nbytes + mask.nbytes)
   line = dict(metric=METRIC, value=value, unit='hypotheses/s', n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
-              ms_per_step=dev_ms / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='bf16',
-              data='synthetic',
-              config=dict(workload='cfg2: synthetic 20480-face mesh, 640x480 RGB-D, 252 hyps (42 views x 6 in-plane), '
-                                   'est_refine_iter=5, 160x160 crops, full register(); N>1: one object per GPU',
+              ms_per_step=dev_ms / args.steps, higher_is_better=True, scaling='weak' if world == 1 else 'strong', vs_baseline=None,
+              dtype=args.precision, data='synthetic',
+              config=dict(workload=WORKLOAD + ('' if world == 1 else f'; ONE object, its 252 hypotheses sharded over {world} GPUs'),
                           hypotheses=n_hyp, iterations=ITERS, precision=args.precision,
                           l2='no flush needed: ~4 GB of activations stream through per step (>> 126 MB L2)'),
               register_ms_p50=float(np.median(per) * 1e3), register_ms_p95=float(np.percentile(per, 95) * 1e3),
@@ -322,8 +379,9 @@ def main():
               gpu_launches=int(launches), roofline=roof, cpu_baseline=cpu, clocks=sampler.summary())
   if stages:
     line['stages'] = stages
-  if strong:
-    line['strong'] = strong
+  line.update(extras)
+  if multi:
+    line.update(multi)
   emit(line)
   if world > 1:
     dist.destroy_process_group()

@@ -16,19 +16,17 @@ OBJ = os.path.join(HERE, 'build')
 
 ARCH = ['-gencode', 'arch=compute_100a,code=sm_100a']
 COMMON = ['-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC,-fvisibility=hidden', '--expt-relaxed-constexpr']
+# (source, extra flags, object suffix).  The network kernel units are compiled twice: bf16 operands (namespace bf16) and,
+# with -DFPB_ACT_FP16, IEEE fp16 operands (namespace f16) -- csrc/act_type.cuh.
+NET_UNITS = ['net_ref.cu', 'net_tc.cu', 'net_tc2.cu', 'net_tc3.cu', 'net_stem.cu', 'net_attn.cu']
 UNITS = [
-  ('api.cu', []),
-  ('depth.cu', ['-fmad=false']),
-  ('hypo.cu', ['-fmad=false']),
-  ('render.cu', ['-fmad=false']),
-  ('metrics.cu', ['-fmad=false']),
-  ('net_ref.cu', []),
-  ('net_tc.cu', []),
-  ('net_tc2.cu', []),
-  ('net_tc3.cu', []),
-  ('net_stem.cu', []),
-  ('net_attn.cu', []),
-  ('net.cu', []),
+  ('api.cu', [], ''),
+  ('depth.cu', ['-fmad=false'], ''),
+  ('hypo.cu', ['-fmad=false'], ''),
+  ('render.cu', ['-fmad=false'], ''),
+  ('metrics.cu', ['-fmad=false'], ''),
+] + [(u, [], '') for u in NET_UNITS] + [(u, ['-DFPB_ACT_FP16'], '_f16') for u in NET_UNITS] + [
+  ('net.cu', [], ''),
 ]
 
 
@@ -56,15 +54,23 @@ def build(force=False, verbose=False):
   rebuilt = False
   env = dict(os.environ)
   env.pop('CC', None); env.pop('CXX', None)
-  for name, flags in UNITS:
+  jobs = []
+  for name, flags, suffix in UNITS:
     src = os.path.join(CSRC, name)
     if not os.path.exists(src):
       continue
-    obj = os.path.join(OBJ, name.replace('.cu', '.o'))
+    obj = os.path.join(OBJ, name.replace('.cu', suffix + '.o'))
     stamp = obj + '.sha'
     dig = _digest([src] + headers, flags + COMMON + ARCH)
     if force or not os.path.exists(obj) or not os.path.exists(stamp) or open(stamp).read() != dig:
       cmd = [nvcc] + ARCH + COMMON + flags + ['-ccbin', '/usr/bin/g++', '-c', src, '-o', obj]
+      jobs.append((name + suffix, cmd, stamp, dig))
+    objs.append(obj)
+  if jobs:                                    # independent translation units: compile them in parallel
+    from concurrent.futures import ThreadPoolExecutor
+
+    def run(job):
+      name, cmd, stamp, dig = job
       if verbose:
         print(' '.join(cmd), flush=True)
       r = subprocess.run(cmd, capture_output=True, text=True, env=env)
@@ -72,8 +78,9 @@ def build(force=False, verbose=False):
         raise RuntimeError(f'nvcc failed for {name}:\n{r.stdout}\n{r.stderr}')
       with open(stamp, 'w') as f:
         f.write(dig)
-      rebuilt = True
-    objs.append(obj)
+    with ThreadPoolExecutor(max_workers=min(len(jobs), max(1, (os.cpu_count() or 2) - 1))) as ex:
+      list(ex.map(run, jobs))
+    rebuilt = True
   if rebuilt or force or not os.path.exists(OUT):
     cmd = [nvcc] + ARCH + ['-shared', '-ccbin', '/usr/bin/g++', '-o', OUT] + objs + ['-cudart', 'static']
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)

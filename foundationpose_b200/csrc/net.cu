@@ -35,8 +35,8 @@ struct fpb_net {
   int rot_dim;        // refine: 3 (axis_angle) or 6 (rot_rep='6d', refine_network.py:61-64)
   size_t n_floats;
   float* w32;
-  __nv_bfloat16* w16;
-  __nv_bfloat16* w_stem;   // stem weights stacked for net_stem.cu ([9][128][64], bf16 mode only)
+  uint16_t* w16;           // 16-bit shadow of the blob in the operand type of `precision` (bf16 or fp16)
+  uint16_t* w_stem;        // stem weights stacked for net_stem.cu ([9][128][64], 16-bit modes only)
   Conv conv[15];
   size_t pe;
   EncLayer head[2];   // refine: trans, rot
@@ -132,23 +132,28 @@ Ws carve(char* base, int n, size_t esz)
   return w;
 }
 
+const NetKernels kKernelsBf16 = FPB_NET_KERNEL_TABLE(bf16), kKernelsF16 = FPB_NET_KERNEL_TABLE(f16);
+inline const NetKernels* kernels_of(int precision) { return precision == FPB_PREC_FP16 ? &kKernelsF16 : &kKernelsBf16; }
+inline bool is16(int precision) { return precision == FPB_PREC_BF16 || precision == FPB_PREC_FP16; }
+
 struct Ctx {
   const fpb_net* net;
   cudaStream_t st;
-  bool bf;
+  bool bf;                    // 16-bit tensor-core mode (bf16 or fp16 operands); false = fp32 SIMT parity mode
   size_t esz;
+  const NetKernels* k;        // kernels of the operand type (fp32 mode: either table, the SIMT kernels are the same)
   void* splitk = nullptr;     // set per chunk from the workspace (Ws::splitk)
   const void* W(size_t off) const { return bf ? (const void*)(net->w16 + off) : (const void*)(net->w32 + off); }
   const float* F(size_t off) const { return net->w32 + off; }
   int gemm(const GemmProblem& p_in) const
   {
-    if (!bf) return ref_gemm(p_in, st);
+    if (!bf) return k->ref_gemm(p_in, st);
     GemmProblem p = p_in;
     p.splitk_ws = splitk;
     p.splitk_ws_bytes = splitk ? (long long)SPLITK_BYTES : 0;
-    int rc = tc3_gemm(p, st, 0);                          // narrow layers (Cout 64 / 128): operand-swapped kernel
-    if (rc == FPB_ERR_UNSUPPORTED) rc = tc2_gemm(p, st);  // persistent TMA kernel
-    return rc == FPB_ERR_UNSUPPORTED ? tc_gemm(p, st) : rc;  // batched / odd shapes: cp.async kernel
+    int rc = k->tc3_gemm(p, st, 0);                          // narrow layers (Cout 64 / 128): operand-swapped kernel
+    if (rc == FPB_ERR_UNSUPPORTED) rc = k->tc2_gemm(p, st);  // persistent TMA kernel
+    return rc == FPB_ERR_UNSUPPORTED ? k->tc_gemm(p, st) : rc;  // batched / odd shapes: cp.async kernel
   }
 };
 
@@ -207,7 +212,7 @@ int run_encoders(const Ctx& c, const void* AB, int n, Ws& w)
 {
   int rc0 = FPB_ERR_UNSUPPORTED;
   if (c.bf && c.net->w_stem)      // dedicated stem kernel: input rows loaded once, two output rows stacked in the MMA M dimension
-    rc0 = stem_conv(AB, 2 * n, c.net->w_stem, c.F(c.net->conv[0].scale), c.F(c.net->conv[0].shift), 1, w.c0, c.st, 0);
+    rc0 = c.k->stem_conv(AB, 2 * n, c.net->w_stem, c.F(c.net->conv[0].scale), c.F(c.net->conv[0].shift), 1, w.c0, c.st, 0);
   if (rc0 == FPB_ERR_UNSUPPORTED) rc0 = run_conv(c, 0, AB, 2 * n, w.c0, nullptr, 1, false, 0, 0, 0);
   RET(rc0);
   // optional (FPB_HALO=1): 3x3 stride-1 blocks in the zero-bordered position layout (one TMA box per 64 channels feeds all
@@ -236,7 +241,7 @@ int run_attention_core(const Ctx& c, const void* qkv, int g, int tokens, int tok
                        void* ctx, bool bf)
 {
   const size_t esz = bf ? 2 : 4;
-  RET(transpose_v(qkv, vt, bf, g, tokens, HEADS, DH, 3 * D, 2 * D, tokp, c.st));
+  RET(c.k->transpose_v(qkv, vt, bf, g, tokens, HEADS, DH, 3 * D, 2 * D, tokp, c.st));
   GemmProblem p = gemm_problem_default();
   p.A = qkv; p.W = (const char*)qkv + (size_t)D * esz; p.C = scores;
   p.M = tokens; p.N = tokens; p.K = DH; p.Cin = DH; p.pix_pitch = 3 * D; p.ldw = 3 * D;
@@ -245,8 +250,8 @@ int run_attention_core(const Ctx& c, const void* qkv, int g, int tokens, int tok
   p.C_outer = (long long)HEADS * tokens * tokp; p.C_inner = (long long)tokens * tokp; p.ldc = tokp;
   p.alpha = 0.08838834764831845f;   // 1/sqrt(128)
   p.n_valid = tokens; p.out_bf16 = 0;
-  RET(bf ? tc_gemm(p, c.st) : ref_gemm(p, c.st));
-  RET(softmax_rows(scores, P, bf, (long long)g * HEADS * tokens, tokens, tokp, tokp, c.st));
+  RET(bf ? c.k->tc_gemm(p, c.st) : c.k->ref_gemm(p, c.st));
+  RET(c.k->softmax_rows(scores, P, bf, (long long)g * HEADS * tokens, tokens, tokp, tokp, c.st));
   GemmProblem q = gemm_problem_default();
   q.A = P; q.W = vt; q.C = ctx;
   q.M = tokens; q.N = DH; q.K = tokp; q.Cin = tokp; q.pix_pitch = tokp; q.ldw = tokp;
@@ -254,7 +259,7 @@ int run_attention_core(const Ctx& c, const void* qkv, int g, int tokens, int tok
   q.A_outer = (long long)HEADS * tokens * tokp; q.A_inner = (long long)tokens * tokp;
   q.W_outer = (long long)HEADS * DH * tokp; q.W_inner = (long long)DH * tokp;
   q.C_outer = (long long)tokens * D; q.C_inner = DH; q.ldc = D; q.out_bf16 = bf;
-  RET(bf ? tc_gemm(q, c.st) : ref_gemm(q, c.st));
+  RET(bf ? c.k->tc_gemm(q, c.st) : c.k->ref_gemm(q, c.st));
   return FPB_OK;
 }
 
@@ -269,8 +274,8 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
   // bf16: Q|K projection [R,1024]; V is produced already transposed, V^T = Wv . X^T  ([512, R], tokens contiguous),
   // by swapping the GEMM operands, so the fused attention kernel can TMA it as a K-major B operand; the V bias is a
   // per-row term of that transposed product (row_shift).
-  __nv_bfloat16* qk = (__nv_bfloat16*)w.qkv;
-  __nv_bfloat16* vt = qk + R * 2 * D;
+  uint16_t* qk = (uint16_t*)w.qkv;
+  uint16_t* vt = qk + R * 2 * D;
   Lin lqk = m.in; lqk.N = 2 * D;
   RET(run_linear(c, lqk, x, R, qk, nullptr, 0, 1));
   {
@@ -280,10 +285,10 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
     t.A = x; t.W = c.W(m.in.w + (size_t)2 * D * D); t.C = vt;
     t.M = (int)R; t.N = D; t.K = D; t.Cin = D; t.pix_pitch = D; t.ldw = D; t.ldc = (int)R; t.out_bf16 = 1;
     t.shift = c.F(m.in.b + 2 * D); t.c_transposed = 1;
-    const int rc3 = tc3_gemm(t, c.st, 0);
+    const int rc3 = c.k->tc3_gemm(t, c.st, 0);
     if (rc3 != FPB_ERR_UNSUPPORTED) {
       RET(rc3);
-      return tc_attention(qk, vt, R, nullptr, w.ctx, n, c.st);
+      return c.k->tc_attention(qk, vt, R, nullptr, w.ctx, n, c.st);
     }
   }
   GemmProblem p = gemm_problem_default();
@@ -291,7 +296,7 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
   p.M = D; p.N = (int)R; p.K = D; p.Cin = D; p.pix_pitch = D; p.ldw = D; p.ldc = (int)R; p.out_bf16 = 1;
   p.row_shift = c.F(m.in.b + 2 * D);
   RET(c.gemm(p));
-  return tc_attention(qk, vt, R, nullptr, w.ctx, n, c.st);
+  return c.k->tc_attention(qk, vt, R, nullptr, w.ctx, n, c.st);
 }
 
 }  // namespace
@@ -302,7 +307,7 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
 FPB_EXPORT int fpb_net_create(fpb_net** out, int kind, int precision, const void* blob_h, size_t bytes, void* stream)
 {
   FPB_CHECK_ARG(out && blob_h && (kind == FPB_NET_REFINE || kind == FPB_NET_SCORE || kind == FPB_NET_REFINE_6D));
-  FPB_CHECK_ARG(precision == FPB_PREC_FP32 || precision == FPB_PREC_BF16);
+  FPB_CHECK_ARG(precision == FPB_PREC_FP32 || precision == FPB_PREC_BF16 || precision == FPB_PREC_FP16);
   cudaStream_t st = (cudaStream_t)stream;
   fpb_net* n = new fpb_net();
   memset(n, 0, sizeof(*n));
@@ -316,12 +321,13 @@ FPB_EXPORT int fpb_net_create(fpb_net** out, int kind, int precision, const void
   }
   FPB_CUDA(cudaMalloc((void**)&n->w32, bytes));
   FPB_CUDA(cudaMemcpyAsync(n->w32, blob_h, bytes, cudaMemcpyHostToDevice, st));
-  if (precision == FPB_PREC_BF16) {
-    FPB_CUDA(cudaMalloc((void**)&n->w16, n->n_floats * sizeof(__nv_bfloat16)));
-    int rc = f32_to_bf16(n->w32, n->w16, (long long)n->n_floats, st);
+  if (is16(precision)) {
+    const NetKernels* k = kernels_of(precision);
+    FPB_CUDA(cudaMalloc((void**)&n->w16, n->n_floats * sizeof(uint16_t)));
+    int rc = k->f32_to_act(n->w32, n->w16, (long long)n->n_floats, st);
     if (rc) return rc;
-    FPB_CUDA(cudaMalloc((void**)&n->w_stem, (size_t)9 * 128 * 64 * sizeof(__nv_bfloat16)));
-    rc = stem_pack_weights(n->w32 + n->conv[0].w, 0, n->w_stem, st);
+    FPB_CUDA(cudaMalloc((void**)&n->w_stem, (size_t)9 * 128 * 64 * sizeof(uint16_t)));
+    rc = k->stem_pack_weights(n->w32 + n->conv[0].w, 0, n->w_stem, st);
     if (rc) return rc;
   }
   FPB_CUDA(cudaStreamSynchronize(st));
@@ -343,7 +349,7 @@ FPB_EXPORT size_t fpb_net_ws_bytes(int kind, int precision, int N)
 {
   (void)kind;
   const int n = N < net_chunk() ? N : net_chunk();
-  return carve(nullptr, n, precision == FPB_PREC_BF16 ? 2 : 4).total + 1024;
+  return carve(nullptr, n, is16(precision) ? 2 : 4).total + 1024;
 }
 
 FPB_EXPORT size_t fpb_net_blob_floats(int kind)
@@ -360,16 +366,16 @@ static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* o
   const long long R = (long long)n * TOK;
   RET(run_self_attention(c, e.att, w.d0, n, w));
   RET(run_linear(c, e.att.out, w.ctx, R, w.y1, w.d0, 0, c.bf));                       // x + SA(x)
-  RET(layernorm_rows(w.y1, c.bf, c.F(e.n1g), c.F(e.n1b), w.y, c.bf, R, D, 1e-5f, c.st));
+  RET(c.k->layernorm_rows(w.y1, c.bf, c.F(e.n1g), c.F(e.n1b), w.y, c.bf, R, D, 1e-5f, c.st));
   RET(run_linear(c, e.l1, w.y, R, w.ff, nullptr, 1, c.bf));
   RET(run_linear(c, e.l2, w.ff, R, w.y1, w.y, 0, c.bf));                               // y + FF(y)
   if (c.bf && D == 512) {                                                              // LayerNorm + token mean in one pass
-    RET(layernorm_token_mean_512(w.y1, c.F(e.n2g), c.F(e.n2b), w.pooled, n, TOK, 1e-5f, c.st));
+    RET(c.k->layernorm_token_mean_512(w.y1, c.F(e.n2g), c.F(e.n2b), w.pooled, n, TOK, 1e-5f, c.st));
   } else {
-    RET(layernorm_rows(w.y1, c.bf, c.F(e.n2g), c.F(e.n2b), w.ff, c.bf, R, D, 1e-5f, c.st));
-    RET(token_mean(w.ff, c.bf, w.pooled, n, TOK, D, c.st));                            // mean commutes with Linear
+    RET(c.k->layernorm_rows(w.y1, c.bf, c.F(e.n2g), c.F(e.n2b), w.ff, c.bf, R, D, 1e-5f, c.st));
+    RET(c.k->token_mean(w.ff, c.bf, w.pooled, n, TOK, D, c.st));                            // mean commutes with Linear
   }
-  RET(small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, e.fin.N, c.st));
+  RET(c.k->small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, e.fin.N, c.st));
   return FPB_OK;
 }
 
@@ -377,7 +383,7 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
                                   void* stream)
 {
   FPB_CHECK_ARG(net && net->kind == FPB_NET_REFINE && AB && ws && out_trans && out_rot && N > 0);
-  Ctx c{net, (cudaStream_t)stream, net->precision == FPB_PREC_BF16, (size_t)(net->precision == FPB_PREC_BF16 ? 2 : 4)};
+  Ctx c{net, (cudaStream_t)stream, is16(net->precision), (size_t)(is16(net->precision) ? 2 : 4), kernels_of(net->precision)};
   const int chunk = net_chunk();
   char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
   const size_t img = (size_t)IN_S * IN_PITCH * IN_C * c.esz;
@@ -407,7 +413,7 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
 static int score_features_impl(const fpb_net* net, const void* AB, int N, void* ws, const MultiDst& dst, void* stream)
 {
   FPB_CHECK_ARG(net && net->kind == FPB_NET_SCORE && AB && ws && N > 0);
-  Ctx c{net, (cudaStream_t)stream, net->precision == FPB_PREC_BF16, (size_t)(net->precision == FPB_PREC_BF16 ? 2 : 4)};
+  Ctx c{net, (cudaStream_t)stream, is16(net->precision), (size_t)(is16(net->precision) ? 2 : 4), kernels_of(net->precision)};
   const int chunk = net_chunk();
   char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
   const size_t img = (size_t)IN_S * IN_PITCH * IN_C * c.esz;
@@ -430,7 +436,7 @@ static int score_features_impl(const fpb_net* net, const void* AB, int N, void* 
     RET(run_linear(c, net->att.out, w.ctx, R, w.y1, nullptr, 0, c.bf));
     MultiDst d = dst;
     for (int i = 0; i < d.n; i++) d.p[i] += (size_t)b0 * D;
-    RET(token_mean_multi(w.y1, c.bf, d, n, TOK, D, c.st));
+    RET(c.k->token_mean_multi(w.y1, c.bf, d, n, TOK, D, c.st));
   }
   return FPB_OK;
 }
@@ -464,7 +470,7 @@ FPB_EXPORT int fpb_score_cross(const fpb_net* net, const float* feat, int L, int
 {
   FPB_CHECK_ARG(net && net->kind == FPB_NET_SCORE && feat && ws && out_logits && L > 0 && bs > 0);
   cudaStream_t st = (cudaStream_t)stream;
-  Ctx c{net, st, false, 4};
+  Ctx c{net, st, false, 4, kernels_of(net->precision)};
   const int Lp = (L + 3) & ~3;
   const long long R = (long long)bs * L;
   char* base = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
@@ -479,7 +485,7 @@ FPB_EXPORT int fpb_score_cross(const fpb_net* net, const float* feat, int L, int
   RET(run_linear(c, net->att_cross.in, feat, R, qkv, nullptr, 0, 0));
   RET(run_attention_core(c, qkv, bs, L, Lp, scores, P, vt, ctx, false));
   RET(run_linear(c, net->att_cross.out, ctx, R, y, nullptr, 0, 0));
-  RET(small_linear(y, c.F(net->lin.w), c.F(net->lin.b), out_logits, (int)R, D, 1, st));
+  RET(c.k->small_linear(y, c.F(net->lin.w), c.F(net->lin.b), out_logits, (int)R, D, 1, st));
   return FPB_OK;
 }
 
@@ -488,6 +494,16 @@ FPB_EXPORT size_t fpb_score_cross_ws_bytes(int L, int bs)
   const size_t Lp = (L + 3) & ~3, R = (size_t)bs * L;
   return al(R * 3 * D * 4) + 2 * al((size_t)bs * HEADS * L * Lp * 4) + al((size_t)bs * HEADS * DH * Lp * 4) + 2 * al(R * D * 4) + 1024;
 }
+
+// operand type the debug / unit-test entries below run in: FPB_PREC_BF16 (default) or FPB_PREC_FP16
+static int g_debug_precision = FPB_PREC_BF16;
+FPB_EXPORT int fpb_debug_set_precision(int precision)
+{
+  FPB_CHECK_ARG(precision == FPB_PREC_BF16 || precision == FPB_PREC_FP16);
+  g_debug_precision = precision;
+  return FPB_OK;
+}
+#define DK (kernels_of(g_debug_precision))
 
 // Debug / unit-test entry: one implicit GEMM through one kernel family (see GemmProblem).
 //   mode 0: fp32 operands (SIMT); 1: bf16 tcgen05 with cp.async producers; 2 / 3: bf16 tcgen05 persistent TMA
@@ -508,12 +524,12 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
   if (out_bf16 == 2) { p.c_transposed = 1; p.ldc = M; }      // bf16 output stored transposed: C[n][m] (mode 4 only)
   cudaStream_t st = (cudaStream_t)stream;
   switch (mode) {
-    case 0: return ref_gemm(p, st);
-    case 1: return tc_gemm(p, st);
-    case 2: tc2_force_cta_group(1); break;
-    case 3: tc2_force_cta_group(2); break;
+    case 0: return DK->ref_gemm(p, st);
+    case 1: return DK->tc_gemm(p, st);
+    case 2: DK->tc2_force_cta_group(1); break;
+    case 3: DK->tc2_force_cta_group(2); break;
     case 4: {
-      const int rc3 = tc3_gemm(p, st, 1);
+      const int rc3 = DK->tc3_gemm(p, st, 1);
       if (rc3 == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_igemm: shape not supported by the operand-swapped kernel");
       return rc3;
     }
@@ -524,14 +540,14 @@ FPB_EXPORT int fpb_debug_igemm_ex(int mode, const void* A, const void* W, void* 
       }
       static void* ws = nullptr;                   // debug entry only: never freed, re-packed on every call
       if (!ws) FPB_CUDA(cudaMalloc(&ws, (size_t)9 * 128 * 64 * 2));
-      int rc5 = stem_pack_weights(W, 1, ws, st);
-      if (!rc5) rc5 = stem_conv(A, M / 6400, ws, scale, shift, relu, C, st, 1);
+      int rc5 = DK->stem_pack_weights(W, 1, ws, st);
+      if (!rc5) rc5 = DK->stem_conv(A, M / 6400, ws, scale, shift, relu, C, st, 1);
       return rc5;
     }
     default: fpb_set_error("fpb_debug_igemm: unknown mode %d", mode); return FPB_ERR_ARG;
   }
-  const int rc = tc2_gemm(p, st);
-  tc2_force_cta_group(0);
+  const int rc = DK->tc2_gemm(p, st);
+  DK->tc2_force_cta_group(0);
   if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_igemm: shape not supported by the TMA kernel");
   return rc;
 }
@@ -550,13 +566,13 @@ FPB_EXPORT int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* 
   p.M = halo ? nimg * (H + 1) * (Wd + 1) : nimg * H * Wd;
   p.scale = scale; p.shift = shift; p.residual = residual; p.ldr = Cout; p.relu = relu; p.ldc = Cout; p.out_bf16 = 1;
   if (cta_group == 3) {                              // operand-swapped kernel (net_tc3.cu)
-    const int rc3 = tc3_gemm(p, (cudaStream_t)stream, 1);
+    const int rc3 = DK->tc3_gemm(p, (cudaStream_t)stream, 1);
     if (rc3 == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_conv3x3_halo: shape not supported by the operand-swapped kernel");
     return rc3;
   }
-  tc2_force_cta_group(cta_group);
-  const int rc = tc2_gemm(p, (cudaStream_t)stream);
-  tc2_force_cta_group(0);
+  DK->tc2_force_cta_group(cta_group);
+  const int rc = DK->tc2_gemm(p, (cudaStream_t)stream);
+  DK->tc2_force_cta_group(0);
   if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_conv3x3_halo: shape not supported");
   return rc;
 }
@@ -565,7 +581,7 @@ FPB_EXPORT int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* 
 FPB_EXPORT int fpb_debug_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups,
                                    void* stream)
 {
-  return tc_attention(qk, vt, vt_pitch, bv, ctx, groups, (cudaStream_t)stream);
+  return DK->tc_attention(qk, vt, vt_pitch, bv, ctx, groups, (cudaStream_t)stream);
 }
 
 FPB_EXPORT int fpb_debug_igemm(int precision, const void* A, const void* W, void* C, int M, int N, int K, int Hin, int Win,

@@ -17,8 +17,11 @@
 // Measured: with 4 softmax warps (one per scheduler) every tcgen05.wait / mbarrier wait was exposed and the kernel
 // ran at 272 us per call with all MMAs and exps disabled it still took 168 us; see DESIGN.md 4.3.
 #include "net_kernels.cuh"
+#include "act_type.cuh"
 #include <cuda.h>
 #include <stdlib.h>
+
+namespace FPB_ACT_NS {
 
 namespace {
 
@@ -83,7 +86,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr)      // K-major, S
 }
 __host__ __device__ constexpr uint32_t make_idesc(int n)
 {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  return (1u << 4) | (ACT_IDESC_FMT << 7) | (ACT_IDESC_FMT << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum)
 {
@@ -172,7 +175,7 @@ static_assert(SMEM_TOTAL <= 227 * 1024, "attention shared memory budget");
 template <int DBG>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapK,
-            const __grid_constant__ CUtensorMap mapV, const float* __restrict__ bv, __nv_bfloat16* __restrict__ ctx,
+            const __grid_constant__ CUtensorMap mapV, const float* __restrict__ bv, act_t* __restrict__ ctx,
             float c1)
 {
   extern __shared__ uint8_t smem_raw[];
@@ -199,7 +202,7 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
   for (int i = threadIdx.x; i < NV * 128; i += NTHREADS) {
     // the 16 constant rows behind each V^T stage: row 128 = ones (its dot product with P is the row sum), the rest 0
     const int s = i >> 7, o = (i & 127) * 16;
-    const uint32_t w = o < 128 ? 0x3F803F80u : 0u;
+    const uint32_t w = o < 128 ? ACT_ONE_X2 : 0u;
     *reinterpret_cast<uint4*>(sV + s * V_STAGE + T16 + o) = make_uint4(w, w, w, w);
   }
   fence_proxy_async();
@@ -376,7 +379,7 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
             for (int e = 0; e < 4; e++) {
               float p0 = fmaf(__uint_as_float(r2[jj * 8 + e * 2]), c1, off), p1 = fmaf(__uint_as_float(r2[jj * 8 + e * 2 + 1]), c1, off);
               if (!(DBG & 2)) { p0 = ex2(p0); p1 = ex2(p1); }
-              __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+              act2_t hh = f2act2(p0, p1);
               pk[e] = *reinterpret_cast<uint32_t*>(&hh);
             }
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sp + (uint32_t)((jj ^ (row & 7)) << 4)), "r"(pk[0]),
@@ -415,7 +418,7 @@ attn_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CU
             const int d = half * 32 + q8 * 8 + e * 2;
             float a = __uint_as_float(o[d]) * inv, b = __uint_as_float(o[d + 1]) * inv;
             if (bv) { a += __ldg(bv + h * DH + set * 64 + d); b += __ldg(bv + h * DH + set * 64 + d + 1); }
-            __nv_bfloat162 hh = __floats2bfloat162_rn(a, b);
+            act2_t hh = f2act2(a, b);
             pw[e] = *reinterpret_cast<uint32_t*>(&hh);
           }
           asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + (uint32_t)(lane * 64 + ((q8 ^ ((lane >> 1) & 3)) << 4))), "r"(pw[0]),
@@ -453,9 +456,9 @@ int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float
   const long long R = (long long)groups * TOK;
   CUtensorMap mQ, mK, mV;
   int rc;
-  if ((rc = fpb_tiled_map_bf16(qk, R, 2 * DM, 2 * DM, 128, &mQ, nullptr))) return rc;
-  if ((rc = fpb_tiled_map_bf16(qk, R, 2 * DM, 2 * DM, 200, &mK, nullptr))) return rc;
-  if ((rc = fpb_tiled_map_bf16(vt, DM, R, vt_pitch, 128, &mV, nullptr))) return rc;
+  if ((rc = fpb_tiled_map_act(qk, R, 2 * DM, 2 * DM, 128, &mQ, nullptr))) return rc;
+  if ((rc = fpb_tiled_map_act(qk, R, 2 * DM, 2 * DM, 200, &mK, nullptr))) return rc;
+  if ((rc = fpb_tiled_map_act(vt, DM, R, vt_pitch, 128, &mV, nullptr))) return rc;
   static int dbg = -1;
   if (dbg < 0) { const char* e = getenv("FPB_ATTN_DBG"); dbg = e ? atoi(e) : 0; }
   const float c1 = 0.08838834764831845f * 1.4426950408889634f;   // 1/sqrt(128) * log2(e)
@@ -477,7 +480,7 @@ int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float
     attr[0].val.programmaticStreamSerializationAllowed = 1;                                                        \
     cfg.attrs = attr;                                                                                              \
     cfg.numAttrs = fpb_pdl_enabled() ? 1 : 0;                                                                      \
-    FPB_CUDA(cudaLaunchKernelEx(&cfg, attn_kernel<D>, mQ, mK, mV, bv, (__nv_bfloat16*)ctx, c1));                    \
+    FPB_CUDA(cudaLaunchKernelEx(&cfg, attn_kernel<D>, mQ, mK, mV, bv, (act_t*)ctx, c1));                    \
   } while (0)
   switch (dbg) {
     case 0: ATTN_LAUNCH(0); break;
@@ -495,3 +498,5 @@ int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }
+
+}  // namespace FPB_ACT_NS

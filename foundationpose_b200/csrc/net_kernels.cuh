@@ -63,39 +63,71 @@ static inline GemmProblem gemm_problem_default()
   return p;
 }
 
-// 1 unless FPB_PDL=0: launch the tcgen05 kernels with programmatic stream serialization (see tc_ptx.cuh)
-int fpb_pdl_enabled();
-
-int ref_gemm(const GemmProblem& p, cudaStream_t st);   // fp32 SIMT
-int tc_gemm(const GemmProblem& p, cudaStream_t st);    // bf16 tcgen05, fp32 accumulate (cp.async producers)
-int tc2_gemm(const GemmProblem& p, cudaStream_t st);   // bf16 tcgen05, persistent TMA kernel; FPB_ERR_UNSUPPORTED -> use tc_gemm
-int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force);   // bf16 tcgen05, operand-swapped (Cout 64 / 128); FPB_ERR_UNSUPPORTED -> tc2_gemm
-// dedicated 7x7 stride-2 stem kernel (net_stem.cu): row-padded input [nimg,160,168,8] bf16 -> [nimg*6400,64] bf16
-int stem_pack_weights(const void* w_packed, int is_bf16, void* w_stacked, cudaStream_t st);   // [64][7][8][8] -> [9][128][64] bf16
-int stem_conv(const void* in, int nimg, const void* w_stacked, const float* scale, const float* shift, int relu, void* out,
-              cudaStream_t st, int force);
-void tc2_force_cta_group(int cg);                      // tests: 0 = default, 1 / 2 = force
-
-int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms);
-int fpb_im2col_map_bf16(const GemmProblem& p, int nimg, void* out_map);   // 128 output pixels x 64 channels per request
-// fused multi-head self-attention (bf16, tcgen05): qk [R][1024] (Q | K, head h at +128h), vt [512][vt_pitch]
-// (V transposed: row = h*128+d, column = token row), bv [512] fp32 V bias -> ctx [R][512];  R = groups * 400
-int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups, cudaStream_t st);
-
-// small ops (fp32 math; io dtype flags)
-int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int cols, int ld_in, int ld_out,
-                 cudaStream_t st);                                     // pad columns [cols, ld_out) written as 0
-int layernorm_rows(const void* x, int x_bf16, const float* gamma, const float* beta, void* out, int out_bf16,
-                   long long rows, int cols, float eps, cudaStream_t st);
-int token_mean(const void* x, int x_bf16, float* out, int groups, int tokens, int cols, cudaStream_t st);
-// the same rows stored to up to FPB_MAX_PEERS destinations (local and peer-mapped buffers: the all-gather of the sharded
-// scorer fused into the pooling kernel, see fpb_score_features_multi)
 struct MultiDst { float* p[FPB_MAX_PEERS]; int n; };
-int token_mean_multi(const void* x, int x_bf16, const MultiDst& out, int groups, int tokens, int cols, cudaStream_t st);
-int layernorm_token_mean_512(const void* x, const float* gamma, const float* beta, float* out, int groups, int tokens, float eps,
-                             cudaStream_t st);                        // bf16 rows of 512: mean over tokens of LayerNorm(x), fused
-int small_linear(const float* x, const float* W, const float* b, float* out, int rows, int K, int N,
-                 cudaStream_t st);                                     // out[r][n] = x[r].W[n] + b[n]
-int transpose_v(const void* qkv, void* vt, int is_bf16, int groups, int tokens, int heads, int dh, int ld_qkv, int v_off,
-                int ld_vt, cudaStream_t st);                           // vt[(g*heads+h)][d][t]
-int f32_to_bf16(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st);
+
+// Everything below exists twice: the network translation units are compiled once with bf16 operands (namespace bf16)
+// and once with fp16 operands (namespace f16), see act_type.cuh.  "bf16" in the flag names below (out_bf16, x_bf16,
+// is_bf16) means "the 16-bit activation type of this namespace" as opposed to fp32.
+#define FPB_NET_KERNEL_DECLS \
+/* 1 unless FPB_PDL=0: launch the tcgen05 kernels with programmatic stream serialization (see tc_ptx.cuh) */ \
+int fpb_pdl_enabled(); \
+ \
+int ref_gemm(const GemmProblem& p, cudaStream_t st); /* fp32 SIMT */ \
+int tc_gemm(const GemmProblem& p, cudaStream_t st); /* bf16 tcgen05, fp32 accumulate (cp.async producers) */ \
+int tc2_gemm(const GemmProblem& p, cudaStream_t st); /* bf16 tcgen05, persistent TMA kernel; FPB_ERR_UNSUPPORTED -> use tc_gemm */ \
+int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force); /* bf16 tcgen05, operand-swapped (Cout 64 / 128); FPB_ERR_UNSUPPORTED -> tc2_gemm */ \
+/* dedicated 7x7 stride-2 stem kernel (net_stem.cu): row-padded input [nimg,160,168,8] bf16 -> [nimg*6400,64] bf16 */ \
+int stem_pack_weights(const void* w_packed, int is_bf16, void* w_stacked, cudaStream_t st); /* [64][7][8][8] -> [9][128][64] bf16 */ \
+int stem_conv(const void* in, int nimg, const void* w_stacked, const float* scale, const float* shift, int relu, void* out, \
+              cudaStream_t st, int force); \
+void tc2_force_cta_group(int cg); /* tests: 0 = default, 1 / 2 = force */ \
+ \
+int fpb_tiled_map_act(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms); \
+int fpb_im2col_map_act(const GemmProblem& p, int nimg, void* out_map); /* 128 output pixels x 64 channels per request */ \
+/* fused multi-head self-attention (bf16, tcgen05): qk [R][1024] (Q | K, head h at +128h), vt [512][vt_pitch] */ \
+/* (V transposed: row = h*128+d, column = token row), bv [512] fp32 V bias -> ctx [R][512];  R = groups * 400 */ \
+int tc_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups, cudaStream_t st); \
+ \
+/* small ops (fp32 math; io dtype flags) */ \
+int softmax_rows(const float* in, void* out, int out_bf16, long long rows, int cols, int ld_in, int ld_out, \
+                 cudaStream_t st); /* pad columns [cols, ld_out) written as 0 */ \
+int layernorm_rows(const void* x, int x_bf16, const float* gamma, const float* beta, void* out, int out_bf16, \
+                   long long rows, int cols, float eps, cudaStream_t st); \
+int token_mean(const void* x, int x_bf16, float* out, int groups, int tokens, int cols, cudaStream_t st); \
+/* the same rows stored to up to FPB_MAX_PEERS destinations (local and peer-mapped buffers: the all-gather of the sharded */ \
+/* scorer fused into the pooling kernel, see fpb_score_features_multi) */ \
+int token_mean_multi(const void* x, int x_bf16, const MultiDst& out, int groups, int tokens, int cols, cudaStream_t st); \
+int layernorm_token_mean_512(const void* x, const float* gamma, const float* beta, float* out, int groups, int tokens, float eps, \
+                             cudaStream_t st); /* bf16 rows of 512: mean over tokens of LayerNorm(x), fused */ \
+int small_linear(const float* x, const float* W, const float* b, float* out, int rows, int K, int N, \
+                 cudaStream_t st); /* out[r][n] = x[r].W[n] + b[n] */ \
+int transpose_v(const void* qkv, void* vt, int is_bf16, int groups, int tokens, int heads, int dh, int ld_qkv, int v_off, \
+                int ld_vt, cudaStream_t st); /* vt[(g*heads+h)][d][t] */ \
+int f32_to_act(const float* in, void* out, long long n, cudaStream_t st); /* fp32 -> act_t (bf16 / fp16) */ \
+
+namespace bf16 { FPB_NET_KERNEL_DECLS }
+namespace f16 { FPB_NET_KERNEL_DECLS }
+
+// function table of one namespace, so that net.cu can pick the operand type at run time (fpb_net::precision)
+struct NetKernels {
+  decltype(&bf16::ref_gemm) ref_gemm;
+  decltype(&bf16::tc_gemm) tc_gemm;
+  decltype(&bf16::tc2_gemm) tc2_gemm;
+  decltype(&bf16::tc3_gemm) tc3_gemm;
+  decltype(&bf16::stem_pack_weights) stem_pack_weights;
+  decltype(&bf16::stem_conv) stem_conv;
+  decltype(&bf16::tc2_force_cta_group) tc2_force_cta_group;
+  decltype(&bf16::tc_attention) tc_attention;
+  decltype(&bf16::softmax_rows) softmax_rows;
+  decltype(&bf16::layernorm_rows) layernorm_rows;
+  decltype(&bf16::token_mean) token_mean;
+  decltype(&bf16::token_mean_multi) token_mean_multi;
+  decltype(&bf16::layernorm_token_mean_512) layernorm_token_mean_512;
+  decltype(&bf16::small_linear) small_linear;
+  decltype(&bf16::transpose_v) transpose_v;
+  decltype(&bf16::f32_to_act) f32_to_act;
+};
+#define FPB_NET_KERNEL_TABLE(ns)                                                                                        \
+  {ns::ref_gemm, ns::tc_gemm, ns::tc2_gemm, ns::tc3_gemm, ns::stem_pack_weights, ns::stem_conv, ns::tc2_force_cta_group, \
+   ns::tc_attention, ns::softmax_rows, ns::layernorm_rows, ns::token_mean, ns::token_mean_multi,                        \
+   ns::layernorm_token_mean_512, ns::small_linear, ns::transpose_v, ns::f32_to_act}

@@ -3,7 +3,10 @@
 //   ConvBNReLU / ResnetBasicBlock   learning/models/network_modules.py:37-50, 73-111
 //   TransformerEncoderLayer / MHA   learning/models/refine_network.py:56-70, score_network.py:53-54
 #include "net_kernels.cuh"
+#include "act_type.cuh"
 #include <stdlib.h>
+
+namespace FPB_ACT_NS {
 
 namespace {
 
@@ -90,7 +93,7 @@ __global__ void __launch_bounds__(256) ref_gemm_kernel(GemmProblem p)
       if (p.residual) v += ((const float*)p.residual)[(long long)mm * p.ldr + nn];
       if (p.relu) v = fmaxf(v, 0.0f);
       if (p.pe) v += p.pe[(long long)(mm % p.pe_rows) * p.pe_ld + nn];
-      if (p.out_bf16) ((__nv_bfloat16*)p.C)[orow + nn] = __float2bfloat16(v);
+      if (p.out_bf16) ((act_t*)p.C)[orow + nn] = f2act(v);
       else ((float*)p.C)[orow + nn] = v;
     }
   }
@@ -126,7 +129,7 @@ __global__ void __launch_bounds__(256) softmax_kernel(const float* __restrict__ 
   const float inv = 1.0f / s;
   for (int c = lane; c < ld_out; c += 32) {
     float v = c < cols ? __expf(x[c] - mx) * inv : 0.0f;
-    if (out_bf16) ((__nv_bfloat16*)out)[row * ld_out + c] = __float2bfloat16(v);
+    if (out_bf16) ((act_t*)out)[row * ld_out + c] = f2act(v);
     else ((float*)out)[row * ld_out + c] = v;
   }
 }
@@ -140,7 +143,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
   auto ld = [&](int c) -> float {
-    if (XBF) return __bfloat162float(((const __nv_bfloat16*)x_)[row * cols + c]);
+    if (XBF) return act2f(((const act_t*)x_)[row * cols + c]);
     return ((const float*)x_)[row * cols + c];
   };
   float s = 0.0f;
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__
   const float rstd = rsqrtf(warp_sum(v) / (float)cols + eps);
   for (int c = lane; c < cols; c += 32) {
     float y = (ld(c) - mean) * rstd * gamma[c] + beta[c];
-    if (out_bf16) ((__nv_bfloat16*)out)[row * cols + c] = __float2bfloat16(y);
+    if (out_bf16) ((act_t*)out)[row * cols + c] = f2act(y);
     else ((float*)out)[row * cols + c] = y;
   }
 }
@@ -161,12 +164,12 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__
 //      (lane l holds columns 8l..8l+7 and 256+8l..256+8l+7: two 16-byte loads, 512 contiguous bytes per warp each)
 struct Ln512 {
   float v[16];
-  __device__ __forceinline__ void load(const __nv_bfloat16* row, int lane)
+  __device__ __forceinline__ void load(const act_t* row, int lane)
   {
     const uint4 a = __ldg(reinterpret_cast<const uint4*>(row) + lane), b = __ldg(reinterpret_cast<const uint4*>(row) + 32 + lane);
     const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 #pragma unroll
-    for (int i = 0; i < 8; i++) { v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+    for (int i = 0; i < 8; i++) { v[2 * i] = actbits2f((unsigned short)(w[i] & 0xffffu)); v[2 * i + 1] = actbits2f((unsigned short)(w[i] >> 16)); }
   }
   // (x - mean) * rstd * gamma + beta, in place
   __device__ __forceinline__ void normalize(const float (&g)[16], const float (&b)[16], float eps)
@@ -191,8 +194,8 @@ __device__ __forceinline__ void ln512_params(const float* gamma, const float* be
     for (int i = 0; i < 8; i++) { g[h * 8 + i] = __ldg(gamma + h * 256 + lane * 8 + i); b[h * 8 + i] = __ldg(beta + h * 256 + lane * 8 + i); }
 }
 
-__global__ void __launch_bounds__(256) ln512_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
-                                                    const float* __restrict__ beta, __nv_bfloat16* __restrict__ out,
+__global__ void __launch_bounds__(256) ln512_kernel(const act_t* __restrict__ x, const float* __restrict__ gamma,
+                                                    const float* __restrict__ beta, act_t* __restrict__ out,
                                                     long long rows, float eps)
 {
   const int lane = threadIdx.x & 31;
@@ -206,7 +209,7 @@ __global__ void __launch_bounds__(256) ln512_kernel(const __nv_bfloat16* __restr
     uint32_t w[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-      const __nv_bfloat162 h = __floats2bfloat162_rn(r.v[2 * i], r.v[2 * i + 1]);
+      const act2_t h = f2act2(r.v[2 * i], r.v[2 * i + 1]);
       w[i] = *reinterpret_cast<const uint32_t*>(&h);
     }
     uint4* o = reinterpret_cast<uint4*>(out + row * 512);
@@ -217,7 +220,7 @@ __global__ void __launch_bounds__(256) ln512_kernel(const __nv_bfloat16* __restr
 
 // LayerNorm followed by the mean over a group's tokens (the normalised rows are never written): one block per group,
 // 8 warps stride over the tokens, fixed-order reduction over warps in shared memory (deterministic).
-__global__ void __launch_bounds__(256) ln512_token_mean_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+__global__ void __launch_bounds__(256) ln512_token_mean_kernel(const act_t* __restrict__ x, const float* __restrict__ gamma,
                                                                const float* __restrict__ beta, float* __restrict__ out,
                                                                int tokens, float eps)
 {
@@ -227,7 +230,7 @@ __global__ void __launch_bounds__(256) ln512_token_mean_kernel(const __nv_bfloat
   ln512_params(gamma, beta, lane, g, b);
 #pragma unroll
   for (int i = 0; i < 16; i++) acc[i] = 0.0f;
-  const __nv_bfloat16* xg = x + (long long)blockIdx.x * tokens * 512;
+  const act_t* xg = x + (long long)blockIdx.x * tokens * 512;
   for (int t = warp; t < tokens; t += 8) {
     Ln512 r;
     r.load(xg + (long long)t * 512, lane);
@@ -253,7 +256,7 @@ __global__ void __launch_bounds__(256) ln512_token_mean_kernel(const __nv_bfloat
 // (deterministic).  One block per group would leave the device idle for 400 dependent row reductions (44 us at N = 1).
 constexpr int LNM_CLUSTER = 8;
 __global__ void __cluster_dims__(LNM_CLUSTER, 1, 1) __launch_bounds__(256)
-ln512_token_mean_cluster_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+ln512_token_mean_cluster_kernel(const act_t* __restrict__ x, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, float* __restrict__ out, int tokens, float eps)
 {
   __shared__ float part[8][512];
@@ -266,7 +269,7 @@ ln512_token_mean_cluster_kernel(const __nv_bfloat16* __restrict__ x, const float
   ln512_params(gamma, beta, lane, g, b);
 #pragma unroll
   for (int i = 0; i < 16; i++) acc[i] = 0.0f;
-  const __nv_bfloat16* xg = x + (long long)group * tokens * 512;
+  const act_t* xg = x + (long long)group * tokens * 512;
   for (int t = (int)rank * 8 + warp; t < tokens; t += 8 * LNM_CLUSTER) {
     Ln512 r;
     r.load(xg + (long long)t * 512, lane);
@@ -315,7 +318,7 @@ __global__ void __launch_bounds__(256) token_mean_kernel(const void* __restrict_
   if (c < cols)
     for (int t = tl; t < tokens; t += 4) {
       const long long i = ((long long)g * tokens + t) * cols + c;
-      s += XBF ? __bfloat162float(((const __nv_bfloat16*)x_)[i]) : ((const float*)x_)[i];
+      s += XBF ? act2f(((const act_t*)x_)[i]) : ((const float*)x_)[i];
     }
   part[tl][threadIdx.x & 63] = s;
   __syncthreads();
@@ -361,10 +364,10 @@ __global__ void __launch_bounds__(256) transpose_v_kernel(const T* __restrict__ 
   }
 }
 
-__global__ void f32_to_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n)
+__global__ void f32_to_act_kernel(const float* __restrict__ in, act_t* __restrict__ out, long long n)
 {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = __float2bfloat16(in[i]);
+  if (i < n) out[i] = f2act(in[i]);
 }
 
 }  // namespace
@@ -390,7 +393,7 @@ int layernorm_rows(const void* x, int x_bf16, const float* gamma, const float* b
 {
   if (x_bf16 && out_bf16 && cols == 512 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0) {
     const long long blocks = fpb_cdiv(rows, 8);
-    ln512_kernel<<<(unsigned)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)out, rows, eps);
+    ln512_kernel<<<(unsigned)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, st>>>((const act_t*)x, gamma, beta, (act_t*)out, rows, eps);
   } else if (x_bf16) layernorm_kernel<true><<<fpb_cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, out, out_bf16, rows, cols, eps);
   else layernorm_kernel<false><<<fpb_cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, out, out_bf16, rows, cols, eps);
   FPB_LAUNCH_CHECK();
@@ -405,9 +408,9 @@ int layernorm_token_mean_512(const void* x, const float* gamma, const float* bet
   static int cluster_max = -1;
   if (cluster_max < 0) { const char* e = getenv("FPB_LNM_CLUSTER_MAX"); cluster_max = e ? atoi(e) : 74; }
   if (groups <= cluster_max)      // default 74: <= 592 CTAs, two waves of clusters at most
-    ln512_token_mean_cluster_kernel<<<groups * LNM_CLUSTER, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
+    ln512_token_mean_cluster_kernel<<<groups * LNM_CLUSTER, 256, 0, st>>>((const act_t*)x, gamma, beta, out, tokens, eps);
   else
-    ln512_token_mean_kernel<<<groups, 256, 0, st>>>((const __nv_bfloat16*)x, gamma, beta, out, tokens, eps);
+    ln512_token_mean_kernel<<<groups, 256, 0, st>>>((const act_t*)x, gamma, beta, out, tokens, eps);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }
@@ -441,7 +444,7 @@ int transpose_v(const void* qkv, void* vt, int is_bf16, int groups, int tokens, 
 {
   dim3 grid(fpb_cdiv(ld_vt, 32), fpb_cdiv(dh, 32), groups * heads);
   if (is_bf16)
-    transpose_v_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)qkv, (__nv_bfloat16*)vt, tokens, heads,
+    transpose_v_kernel<act_t><<<grid, 256, 0, st>>>((const act_t*)qkv, (act_t*)vt, tokens, heads,
                                                              dh, ld_qkv, v_off, ld_vt);
   else
     transpose_v_kernel<float><<<grid, 256, 0, st>>>((const float*)qkv, (float*)vt, tokens, heads, dh, ld_qkv, v_off, ld_vt);
@@ -449,9 +452,11 @@ int transpose_v(const void* qkv, void* vt, int is_bf16, int groups, int tokens, 
   return FPB_OK;
 }
 
-int f32_to_bf16(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st)
+int f32_to_act(const float* in, void* out, long long n, cudaStream_t st)
 {
-  f32_to_bf16_kernel<<<fpb_cdiv(n, 256), 256, 0, st>>>(in, out, n);
+  f32_to_act_kernel<<<fpb_cdiv(n, 256), 256, 0, st>>>(in, (act_t*)out, n);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }
+
+}  // namespace FPB_ACT_NS

@@ -24,6 +24,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+namespace FPB_ACT_NS {
+
 namespace {
 
 constexpr int ST_NT = 320;                         // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
@@ -53,7 +55,7 @@ static_assert(ST_SMEM <= 227 * 1024, "stem shared memory budget");
 struct StemParams {
   const float* scale;      // [64] folded BatchNorm
   const float* shift;
-  __nv_bfloat16* out;      // [nimg][80][80][64]
+  act_t* out;      // [nimg][80][80][64]
   int nimg, relu;
   int dbg;                 // FPB_STEM_DBG bits: 1 no stores, 8 no MMA, 128 no input loads (timing experiments)
 };
@@ -187,7 +189,7 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX4, const __grid_constant__ C
       mbar_wait(&ctl->tmem_full[acc], (tc >> 1) & 1u);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256 + (uint32_t)(half * 128);
-      __nv_bfloat16* obase = q.out + (long long)img * (ST_OUT * ST_OUT * ST_CH) + ch0 + (lane & ~1);
+      act_t* obase = q.out + (long long)img * (ST_OUT * ST_OUT * ST_CH) + ch0 + (lane & ~1);
 #pragma unroll 1
       for (int g = 0; g < 4; g++) {
         uint32_t r[32];
@@ -207,7 +209,7 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX4, const __grid_constant__ C
         for (int jj = 0; jj < 16; jj++) {
           const float mine_keep = odd ? v[2 * jj + 1] : v[2 * jj];
           const float other = __shfl_xor_sync(0xffffffffu, odd ? v[2 * jj] : v[2 * jj + 1], 1);
-          const __nv_bfloat162 h2 = odd ? __floats2bfloat162_rn(other, mine_keep) : __floats2bfloat162_rn(mine_keep, other);
+          const act2_t h2 = odd ? f2act2(other, mine_keep) : f2act2(mine_keep, other);
           hh[jj] = *reinterpret_cast<const uint32_t*>(&h2);
         }
         // The 32 pixels of a group cross at most one row end.  Pixel 2jj + odd of this lane sits at ox = oxm + 2jj: it is
@@ -246,7 +248,7 @@ stem_kernel(const __grid_constant__ CUtensorMap mapX4, const __grid_constant__ C
 // stacked weights [9 ky'][128 rows][4 pairs][2 px][8 ch] from the packed stem weights [64][7][8 taps][8 ch]
 // (tap j of the packed layout = kernel column j; here pixel 2t+h of the window is kernel column 2t+h-1)
 template <typename T>
-__global__ void stem_pack_kernel(const T* __restrict__ w, __nv_bfloat16* __restrict__ out)
+__global__ void stem_pack_kernel(const T* __restrict__ w, act_t* __restrict__ out)
 {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= 9 * 128 * 64) return;
@@ -255,7 +257,7 @@ __global__ void stem_pack_kernel(const T* __restrict__ w, __nv_bfloat16* __restr
   const int kx = (col >> 3) - 1, c = col & 7;
   float v = 0.0f;
   if (ky >= 0 && ky < 7 && kx >= 0 && kx < 7) v = (float)w[((co * 7 + ky) * 8 + kx) * 8 + c];
-  out[idx] = __float2bfloat16(v);
+  out[idx] = f2act(v);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -278,8 +280,8 @@ int stem_enabled()
 int stem_pack_weights(const void* w_packed, int is_bf16, void* w_stacked, cudaStream_t st)
 {
   const int n = 9 * 128 * 64;
-  if (is_bf16) stem_pack_kernel<__nv_bfloat16><<<(n + 255) / 256, 256, 0, st>>>((const __nv_bfloat16*)w_packed, (__nv_bfloat16*)w_stacked);
-  else stem_pack_kernel<float><<<(n + 255) / 256, 256, 0, st>>>((const float*)w_packed, (__nv_bfloat16*)w_stacked);
+  if (is_bf16) stem_pack_kernel<act_t><<<(n + 255) / 256, 256, 0, st>>>((const act_t*)w_packed, (act_t*)w_stacked);
+  else stem_pack_kernel<float><<<(n + 255) / 256, 256, 0, st>>>((const float*)w_packed, (act_t*)w_stacked);
   FPB_CUDA(cudaGetLastError());
   return FPB_OK;
 }
@@ -315,17 +317,17 @@ int stem_conv(const void* in, int nimg, const void* w_stacked, const float* scal
     cuuint64_t strides[4] = {32, row_b, 4 * row_b, (cuuint64_t)ST_IMG * row_b};
     cuuint32_t box[5] = {16, (cuuint32_t)ST_PAIRS, 1, (cuuint32_t)(4 + bi), 1};
     cuuint32_t es[5] = {1, 1, 1, 1, 1};
-    CUresult r = g_encode(&mX[bi], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, (void*)in, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    CUresult r = g_encode(&mX[bi], ACT_TMAP_DTYPE, 5, (void*)in, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                           CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { fpb_set_error("stem_conv: cuTensorMapEncodeTiled (input) failed (%d)", (int)r); return FPB_ERR_CUDA; }
     if (g_xmaps.size() > 256) g_xmaps.clear();
     g_xmaps[key] = mX[bi];
   }
   int sms = 0;
-  int rc = fpb_tiled_map_bf16(w_stacked, 9 * 128, 64, 64, 128, &mW, &sms);
+  int rc = fpb_tiled_map_act(w_stacked, 9 * 128, 64, 64, 128, &mW, &sms);
   if (rc) return rc;
   StemParams q;
-  q.scale = scale; q.shift = shift; q.out = (__nv_bfloat16*)out; q.nimg = nimg; q.relu = relu;
+  q.scale = scale; q.shift = shift; q.out = (act_t*)out; q.nimg = nimg; q.relu = relu;
   { const char* e = getenv("FPB_STEM_DBG"); q.dbg = e ? atoi(e) : 0; }
   const int tiles = nimg * ST_TILES_PER_IMG;
   cudaLaunchConfig_t cfg;
@@ -343,3 +345,5 @@ int stem_conv(const void* in, int nimg, const void* w_stacked, const float* scal
   fpb_count_launch();
   return FPB_OK;
 }
+
+}  // namespace FPB_ACT_NS

@@ -11,6 +11,9 @@
 // (128 lanes x BN columns) and the epilogue applies folded BN / bias, residual, ReLU, positional embedding and
 // writes bf16 (or fp32) rows with 16-byte stores.
 #include "net_kernels.cuh"
+#include "act_type.cuh"
+
+namespace FPB_ACT_NS {
 
 namespace {
 
@@ -69,7 +72,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr)
 // N>>3 at [17,23), M>>4 at [24,29)
 __host__ __device__ constexpr uint32_t make_idesc(int n)
 {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+  return (1u << 4) | (ACT_IDESC_FMT << 7) | (ACT_IDESC_FMT << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 }
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum)
@@ -143,8 +146,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
   if (warp >= 4 && warp < 8) {
     // ------------------------------------------------------------------ producers
     const int pt = threadIdx.x - 128;            // 0..127 : A row of the tile
-    const __nv_bfloat16* A = (const __nv_bfloat16*)p.A + a_off;
-    const __nv_bfloat16* W = (const __nv_bfloat16*)p.W + w_off;
+    const act_t* A = (const act_t*)p.A + a_off;
+    const act_t* W = (const act_t*)p.W + w_off;
     const int m = m0 + pt;
     const bool m_ok = m < p.M;
     int img = 0, oy = 0, ox = 0;
@@ -170,7 +173,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
           const int ky = tap / p.KW, kx = tap - ky * p.KW;
           const int iy = iy0 + ky, ix = ix0 + kx;
           const bool ok = m_ok && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win;
-          const __nv_bfloat16* src = ok ? A + (img_base + (long long)iy * rp + ix) * p.pix_pitch + c : A;
+          const act_t* src = ok ? A + (img_base + (long long)iy * rp + ix) * p.pix_pitch + c : A;
 #pragma unroll
           for (int j = 0; j < 8; j++) cp_async16(sa + ((j ^ sw) << 4), src + (ok ? j * 8 : 0), ok ? 16u : 0u);
         } else {
@@ -181,7 +184,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
             const int ky = tap / p.KW, kx = tap - ky * p.KW;
             const int iy = iy0 + ky, ix = ix0 + kx;
             const bool ok = m_ok && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win;
-            const __nv_bfloat16* src = ok ? A + (img_base + (long long)iy * rp + ix) * p.pix_pitch + c : A;
+            const act_t* src = ok ? A + (img_base + (long long)iy * rp + ix) * p.pix_pitch + c : A;
             cp_async16(sa + ((j ^ sw) << 4), src, ok ? 16u : 0u);
           }
         }
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
           if (row < BN) {
             const int n = n0 + row;
             const bool ok = n < p.N;
-            const __nv_bfloat16* src = ok ? W + (long long)n * p.ldw + k0 : W;
+            const act_t* src = ok ? W + (long long)n * p.ldw + k0 : W;
             const uint32_t dst = sb + row * 128;
             const uint32_t swb = (uint32_t)(row & 7);
 #pragma unroll
@@ -235,7 +238,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
     const int nst = p.n_valid > 0 ? p.n_valid : p.N;
     const long long orow = m_ok ? (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off + c_off : 0;
     const float* pe_row = (p.pe && m_ok) ? p.pe + (long long)(m % p.pe_rows) * p.pe_ld : nullptr;
-    const __nv_bfloat16* res_row = (p.residual && m_ok) ? (const __nv_bfloat16*)p.residual + (long long)m * p.ldr : nullptr;
+    const act_t* res_row = (p.residual && m_ok) ? (const act_t*)p.residual + (long long)m * p.ldr : nullptr;
 #pragma unroll 1
     for (int ch = 0; ch < BN / 32; ch++) {
       uint32_t r[32];
@@ -260,15 +263,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             const uint4 rv = *reinterpret_cast<const uint4*>(res_row + nb + q * 8);
-            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rv);
+            const act2_t* h = reinterpret_cast<const act2_t*>(&rv);
 #pragma unroll
             for (int e = 0; e < 4; e++) {
-              const float2 f = __bfloat1622float2(h[e]);
+              const float2 f = act22f2(h[e]);
               v[q * 8 + e * 2] += f.x; v[q * 8 + e * 2 + 1] += f.y;
             }
           }
         } else {
-          for (int i = 0; i < 32 && nb + i < nst; i++) v[i] += __bfloat162float(res_row[nb + i]);
+          for (int i = 0; i < 32 && nb + i < nst; i++) v[i] += act2f(res_row[nb + i]);
         }
       }
       if (p.relu) {
@@ -281,19 +284,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) tc_gemm_kernel(GemmProblem p)
           if (full || nb + i < nst) v[i] += __ldg(pe_row + nb + i);
       }
       if (p.out_bf16) {
-        __nv_bfloat16* o = (__nv_bfloat16*)p.C + orow + nb;
+        act_t* o = (act_t*)p.C + orow + nb;
         if (full) {
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             uint4 pk;
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[q * 8 + 0], v[q * 8 + 1]), h1 = __floats2bfloat162_rn(v[q * 8 + 2], v[q * 8 + 3]);
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[q * 8 + 4], v[q * 8 + 5]), h3 = __floats2bfloat162_rn(v[q * 8 + 6], v[q * 8 + 7]);
+            act2_t h0 = f2act2(v[q * 8 + 0], v[q * 8 + 1]), h1 = f2act2(v[q * 8 + 2], v[q * 8 + 3]);
+            act2_t h2 = f2act2(v[q * 8 + 4], v[q * 8 + 5]), h3 = f2act2(v[q * 8 + 6], v[q * 8 + 7]);
             pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
             pk.z = *reinterpret_cast<uint32_t*>(&h2); pk.w = *reinterpret_cast<uint32_t*>(&h3);
             *reinterpret_cast<uint4*>(o + q * 8) = pk;
           }
         } else {
-          for (int i = 0; i < 32 && nb + i < nst; i++) o[i] = __float2bfloat16(v[i]);
+          for (int i = 0; i < 32 && nb + i < nst; i++) o[i] = f2act(v[i]);
         }
       } else {
         float* o = (float*)p.C + orow + nb;
@@ -343,3 +346,5 @@ int tc_gemm(const GemmProblem& p, cudaStream_t st)
   if (ncols > 64) return launch_tc<128, 4>(p, st);
   return launch_tc<64, 4>(p, st);
 }
+
+}  // namespace FPB_ACT_NS

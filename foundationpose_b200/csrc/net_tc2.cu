@@ -21,6 +21,8 @@
 #include <mutex>
 #include <vector>
 
+namespace FPB_ACT_NS {
+
 namespace {
 
 constexpr int TM = 128;
@@ -290,7 +292,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
       for (int i = 0; i < 8; i++) {
         const int mr = mw_ + 4 * i + (lane >> 3);
-        rr[i] = mr < p.M ? __ldg(reinterpret_cast<const uint4*>((const __nv_bfloat16*)p.residual + (long long)mr * p.ldr + nb_) + (lane & 7))
+        rr[i] = mr < p.M ? __ldg(reinterpret_cast<const uint4*>((const act_t*)p.residual + (long long)mr * p.ldr + nb_) + (lane & 7))
                          : make_uint4(0u, 0u, 0u, 0u);
       }
     };
@@ -328,7 +330,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         if (use_res && t + n_clusters < total_tiles) tile_mw(t + n_clusters, mw_next, n0_next);
         // a warp's 32 rows never straddle m_split (host guarantees m_split % 32 == 0 or m_split >= M)
         const int seg = p.m_split >= p.M ? 0 : m_w / p.m_split;
-        __nv_bfloat16* out_w = (__nv_bfloat16*)p.C + (long long)(m_w - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
+        act_t* out_w = (act_t*)p.C + (long long)(m_w - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
         const int pe_r0 = p.pe ? m_w % p.pe_rows : 0;
         bool interior = true;                                   // halo mode: border positions produce zeros
         if (q.halo) {
@@ -336,18 +338,18 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           interior = yy >= 1 && r_ - yy * q.Wp < p.img_w;
         }
         // global address of output row mr (nullptr: not stored)
-        auto row_ptr = [&](int mr) -> __nv_bfloat16* {
+        auto row_ptr = [&](int mr) -> act_t* {
           if (mr >= p.M) return nullptr;
           if (p.row_remap == 0) return out_w + (long long)(mr - m_w) * p.ldc;
           const int hw = p.img_h * p.img_w;
           if (p.row_remap == 1) {                               // dense pixel index -> zero-bordered position
             const int img = mr / hw, r_ = mr - img * hw, y = r_ / p.img_w;
-            return (__nv_bfloat16*)p.C + ((long long)img * q.IS + (long long)(y + 1) * q.Wp + (r_ - y * p.img_w)) * p.ldc;
+            return (act_t*)p.C + ((long long)img * q.IS + (long long)(y + 1) * q.Wp + (r_ - y * p.img_w)) * p.ldc;
           }
           const int img = mr / q.IS, r_ = mr - img * q.IS, yy = r_ / q.Wp, xx = r_ - yy * q.Wp;   // position -> dense
           if (yy < 1 || xx >= p.img_w) return nullptr;
           const int md = img * hw + (yy - 1) * p.img_w + xx;
-          return (__nv_bfloat16*)p.C + (long long)(md % p.m_split) * p.ldc + (long long)(md / p.m_split) * p.split_col_off;
+          return (act_t*)p.C + (long long)(md % p.m_split) * p.ldc + (long long)(md / p.m_split) * p.split_col_off;
         };
         // the epilogue warps fill the table of this tile together; one named barrier per tile orders it (the table is
         // double buffered, and passing the barrier of tile i+1 implies every warp has finished tile i)
@@ -408,10 +410,10 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             for (int j = 0; j < 8; j++) {
               uint4 rv;
               asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(rv.x), "=r"(rv.y), "=r"(rv.z), "=r"(rv.w) : "r"(s_res + stg_off(lane, j)) : "memory");
-              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rv);
+              const act2_t* h = reinterpret_cast<const act2_t*>(&rv);
 #pragma unroll
               for (int e = 0; e < 4; e++) {
-                const float2 f = __bfloat1622float2(h[e]);
+                const float2 f = act22f2(h[e]);
                 v[j * 8 + e * 2] += f.x; v[j * 8 + e * 2 + 1] += f.y;
               }
             }
@@ -448,11 +450,11 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           }
           if ((q.dbg & 1) && v[0] != 123456.0f) { prefetch_next(); continue; }
           __syncwarp();                                         // staging tile: residual / pe reads done before it is reused
-          const __nv_bfloat162 zero2 = __floats2bfloat162_rn(0.0f, 0.0f);
+          const act2_t zero2 = f2act2(0.0f, 0.0f);
 #pragma unroll
           for (int j = 0; j < 8; j++) {
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j * 8 + 0], v[j * 8 + 1]), h1 = __floats2bfloat162_rn(v[j * 8 + 2], v[j * 8 + 3]);
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j * 8 + 4], v[j * 8 + 5]), h3 = __floats2bfloat162_rn(v[j * 8 + 6], v[j * 8 + 7]);
+            act2_t h0 = f2act2(v[j * 8 + 0], v[j * 8 + 1]), h1 = f2act2(v[j * 8 + 2], v[j * 8 + 3]);
+            act2_t h2 = f2act2(v[j * 8 + 4], v[j * 8 + 5]), h3 = f2act2(v[j * 8 + 6], v[j * 8 + 7]);
             if (relu_packed) { h0 = __hmax2(h0, zero2); h1 = __hmax2(h1, zero2); h2 = __hmax2(h2, zero2); h3 = __hmax2(h3, zero2); }
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(s_out + stg_off(lane, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
                          "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
@@ -476,7 +478,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               const int mr = m_w + 4 * i + sub;
               uint4 ov;
               asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + stg_off(4 * i + sub, cj)) : "memory");
-              __nv_bfloat16* op = row_ptr(mr);
+              act_t* op = row_ptr(mr);
               if (op && !(q.dbg & 2048)) *(reinterpret_cast<uint4*>(op + nb) + cj) = ov;
             }
           }
@@ -489,7 +491,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       const long long orow = (m_ok ? (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off : 0) +
                              (long long)ks * q.c_split_stride;
       const float* pe_row = (p.pe && m_ok) ? p.pe + (long long)(m % p.pe_rows) * p.pe_ld : nullptr;
-      const __nv_bfloat16* res_row = (p.residual && m_ok) ? (const __nv_bfloat16*)p.residual + (long long)m * p.ldr : nullptr;
+      const act_t* res_row = (p.residual && m_ok) ? (const act_t*)p.residual + (long long)m * p.ldr : nullptr;
 #pragma unroll 1
       for (int chn = ehalf; chn < BN / 32; chn += GSTEP) {
         uint32_t r[32];
@@ -519,15 +521,15 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
             for (int qq = 0; qq < 4; qq++) {
               const uint4 rv = *reinterpret_cast<const uint4*>(res_row + nb + qq * 8);
-              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rv);
+              const act2_t* h = reinterpret_cast<const act2_t*>(&rv);
 #pragma unroll
               for (int e = 0; e < 4; e++) {
-                const float2 f = __bfloat1622float2(h[e]);
+                const float2 f = act22f2(h[e]);
                 v[qq * 8 + e * 2] += f.x; v[qq * 8 + e * 2 + 1] += f.y;
               }
             }
           } else {
-            for (int i = 0; i < 32 && nb + i < nst; i++) v[i] += __bfloat162float(res_row[nb + i]);
+            for (int i = 0; i < 32 && nb + i < nst; i++) v[i] += act2f(res_row[nb + i]);
           }
         }
         if (p.relu) {
@@ -541,19 +543,19 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         }
         if ((q.dbg & 1) && v[0] != 123456.0f) continue;
         if (p.out_bf16) {
-          __nv_bfloat16* o = (__nv_bfloat16*)p.C + orow + nb;
+          act_t* o = (act_t*)p.C + orow + nb;
           if (full) {
 #pragma unroll
             for (int qq = 0; qq < 4; qq++) {
               uint4 pk;
-              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[qq * 8 + 0], v[qq * 8 + 1]), h1 = __floats2bfloat162_rn(v[qq * 8 + 2], v[qq * 8 + 3]);
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[qq * 8 + 4], v[qq * 8 + 5]), h3 = __floats2bfloat162_rn(v[qq * 8 + 6], v[qq * 8 + 7]);
+              act2_t h0 = f2act2(v[qq * 8 + 0], v[qq * 8 + 1]), h1 = f2act2(v[qq * 8 + 2], v[qq * 8 + 3]);
+              act2_t h2 = f2act2(v[qq * 8 + 4], v[qq * 8 + 5]), h3 = f2act2(v[qq * 8 + 6], v[qq * 8 + 7]);
               pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
               pk.z = *reinterpret_cast<uint32_t*>(&h2); pk.w = *reinterpret_cast<uint32_t*>(&h3);
               *reinterpret_cast<uint4*>(o + qq * 8) = pk;
             }
           } else {
-            for (int i = 0; i < 32 && nb + i < nst; i++) o[i] = __float2bfloat16(v[i]);
+            for (int i = 0; i < 32 && nb + i < nst; i++) o[i] = f2act(v[i]);
           }
         } else {
           float* o = (float*)p.C + orow + nb;
@@ -643,7 +645,7 @@ int get_tiled_map(const void* ptr, long long rows, long long cols, long long pit
   cuuint32_t box[2] = {(cuuint32_t)KC, (cuuint32_t)box_rows};
   cuuint32_t es[2] = {1, 1};
   CUtensorMap m;
-  CUresult r = g_tiled(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)ptr, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  CUresult r = g_tiled(&m, ACT_TMAP_DTYPE, 2, (void*)ptr, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     fpb_set_error("cuTensorMapEncodeTiled failed (%d): rows=%lld cols=%lld pitch=%lld box_rows=%d", (int)r, rows, cols, pitch, box_rows);
@@ -674,7 +676,7 @@ int get_im2col_map(const GemmProblem& p, int nimg, CUtensorMap* out)
   int upper[2] = {(p.Wo - 1) * p.stride - p.pad_w - (p.Win - 1), (p.Ho - 1) * p.stride - p.pad - (p.Hin - 1)};
   cuuint32_t es[4] = {1, (cuuint32_t)p.stride, (cuuint32_t)p.stride, 1};
   CUtensorMap m;
-  CUresult r = g_im2col(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, (void*)p.A, dims, strides, lower, upper, (cuuint32_t)KC,
+  CUresult r = g_im2col(&m, ACT_TMAP_DTYPE, 4, (void*)p.A, dims, strides, lower, upper, (cuuint32_t)KC,
                         (cuuint32_t)TM, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -749,16 +751,16 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(GemmProblem p, const
     if (p.scale) v[j] = v[j] * p.scale[n + j] + (p.shift ? p.shift[n + j] : 0.0f);
     else if (p.shift) v[j] += p.shift[n + j];
     if (p.row_shift) v[j] += p.row_shift[m];
-    if (p.residual) v[j] += __bfloat162float(((const __nv_bfloat16*)p.residual)[(long long)m * p.ldr + n + j]);
+    if (p.residual) v[j] += act2f(((const act_t*)p.residual)[(long long)m * p.ldr + n + j]);
     if (p.relu) v[j] = fmaxf(v[j], 0.0f);
     if (p.pe) v[j] += p.pe[(long long)(m % p.pe_rows) * p.pe_ld + n + j];
   }
   const long long o = (long long)(m % p.m_split) * p.ldc + (long long)(m / p.m_split) * p.split_col_off + n;
   if (p.out_bf16) {
-    __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+    act2_t h0 = f2act2(v[0], v[1]), h1 = f2act2(v[2], v[3]);
     uint2 pk;
     pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
-    *reinterpret_cast<uint2*>((__nv_bfloat16*)p.C + o) = pk;
+    *reinterpret_cast<uint2*>((act_t*)p.C + o) = pk;
   } else {
     *reinterpret_cast<float4*>((float*)p.C + o) = make_float4(v[0], v[1], v[2], v[3]);
   }
@@ -808,7 +810,7 @@ int fpb_pdl_enabled()
 }
 
 // shared with net_attn.cu: cached tiled 2-D bf16 tensor map (box = 64 columns x box_rows rows, 128B swizzle)
-int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms)
+int fpb_tiled_map_act(const void* ptr, long long rows, long long cols, long long pitch, int box_rows, void* out_map, int* num_sms)
 {
   int rc = resolve_driver();
   if (rc) return rc;
@@ -816,7 +818,7 @@ int fpb_tiled_map_bf16(const void* ptr, long long rows, long long cols, long lon
   return get_tiled_map(ptr, rows, cols, pitch, box_rows, (CUtensorMap*)out_map);
 }
 
-int fpb_im2col_map_bf16(const GemmProblem& p, int nimg, void* out_map)
+int fpb_im2col_map_act(const GemmProblem& p, int nimg, void* out_map)
 {
   int rc = resolve_driver();
   if (rc) return rc;
@@ -892,3 +894,5 @@ int tc2_gemm(const GemmProblem& p, cudaStream_t st)
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }
+
+}  // namespace FPB_ACT_NS

@@ -21,6 +21,8 @@
 #include "tc_ptx.cuh"
 #include <stdlib.h>
 
+namespace FPB_ACT_NS {
+
 namespace {
 
 constexpr int TP = 256;                       // pixels per tile (MMA N)
@@ -330,22 +332,22 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     const bool use_res = active && p.residual && !(q.dbg & 4);
     const int hw = p.img_h * p.img_w;
     // global address of the 64 channels-bytes this lane stores for pixel row mr (nullptr: not stored)
-    auto row_ptr = [&](int mr) -> __nv_bfloat16* {
+    auto row_ptr = [&](int mr) -> act_t* {
       if (mr >= p.M) return nullptr;
       if (p.row_remap == 0) {
-        if (p.m_split >= p.M) return (__nv_bfloat16*)p.C + (long long)mr * p.ldc;
+        if (p.m_split >= p.M) return (act_t*)p.C + (long long)mr * p.ldc;
         const int seg = mr / p.m_split;
-        return (__nv_bfloat16*)p.C + (long long)(mr - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
+        return (act_t*)p.C + (long long)(mr - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
       }
       if (p.row_remap == 1) {                               // dense pixel index -> zero-bordered position
         const int img = mr / hw, r_ = mr - img * hw, y = r_ / p.img_w;
-        return (__nv_bfloat16*)p.C + ((long long)img * q.IS + (long long)(y + 1) * q.Wp + (r_ - y * p.img_w)) * p.ldc;
+        return (act_t*)p.C + ((long long)img * q.IS + (long long)(y + 1) * q.Wp + (r_ - y * p.img_w)) * p.ldc;
       }
       const int img = mr / q.IS, r_ = mr - img * q.IS, yy = r_ / q.Wp, xx = r_ - yy * q.Wp;   // position -> dense
       if (yy < 1 || xx >= p.img_w) return nullptr;
       const int md = img * hw + (yy - 1) * p.img_w + xx;
       const int seg = md / p.m_split;
-      return (__nv_bfloat16*)p.C + (long long)(md - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
+      return (act_t*)p.C + (long long)(md - seg * p.m_split) * p.ldc + (long long)seg * p.split_col_off;
     };
     // Direct path (dense output rows): lane = channel, so one warp instruction moves the 32 channels x 2 B = 64
     // contiguous bytes (two full sectors) of one pixel; no transposition, no staging, ~4x fewer instructions than
@@ -371,7 +373,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
       for (int i = 0; i < 4; i++) {
         const int mr = mbase + 8 * i + spx;
-        rr[i] = mr < p.M ? __ldg(reinterpret_cast<const uint4*>((const __nv_bfloat16*)p.residual + (long long)mr * p.ldr + ch0) + scj)
+        rr[i] = mr < p.M ? __ldg(reinterpret_cast<const uint4*>((const act_t*)p.residual + (long long)mr * p.ldr + ch0) + scj)
                          : make_uint4(0u, 0u, 0u, 0u);
       }
     };
@@ -406,7 +408,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         if (direct) {
           if (use_res) {
 #pragma unroll
-            for (int j = 0; j < 32; j++) v[j] += __uint_as_float((uint32_t)rq[j] << 16);
+            for (int j = 0; j < 32; j++) v[j] += actbits2f(rq[j]);
             if (g < 3) load_res_direct(mg + 32);
             else if (t + t_step < q.tiles) load_res_direct((t + t_step) * TP + half * 128);
           }
@@ -417,7 +419,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           if ((q.dbg & 1) && v[0] != 123456.0f) continue;
           if (p.c_transposed) {
             // out[channel][pixel]: the accumulator layout itself; 32 pixels of this lane's channel = 64 contiguous bytes
-            __nv_bfloat16* ot = (__nv_bfloat16*)p.C + (long long)(ch0 + lane) * p.ldc + mg;
+            act_t* ot = (act_t*)p.C + (long long)(ch0 + lane) * p.ldc + mg;
             if (mg + 32 <= p.M) {
 #pragma unroll
               for (int j4 = 0; j4 < 4; j4++) {
@@ -425,7 +427,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                 uint32_t* pw = reinterpret_cast<uint32_t*>(&pk);
 #pragma unroll
                 for (int e = 0; e < 4; e++) {
-                  __nv_bfloat162 hh = __floats2bfloat162_rn(v[j4 * 8 + e * 2], v[j4 * 8 + e * 2 + 1]);
+                  act2_t hh = f2act2(v[j4 * 8 + e * 2], v[j4 * 8 + e * 2 + 1]);
                   pw[e] = *reinterpret_cast<uint32_t*>(&hh);
                 }
                 reinterpret_cast<uint4*>(ot)[j4] = pk;
@@ -433,7 +435,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             } else {
 #pragma unroll
               for (int j = 0; j < 32; j++)
-                if (mg + j < p.M) ot[j] = __float2bfloat16(v[j]);
+                if (mg + j < p.M) ot[j] = f2act(v[j]);
             }
             continue;
           }
@@ -443,7 +445,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           // layers), so neighbouring lanes swap one value per pixel pair and every lane stores a bf16x2: even lanes
           // write channels (c, c+1) of pixel j, odd lanes channels (c-1, c) of pixel j+1 -- 16 four-byte stores.
           const int odd = lane & 1;
-          char* op = (char*)((__nv_bfloat16*)p.C + (long long)(mg - seg * p.m_split + odd) * p.ldc + (long long)seg * p.split_col_off + ch0 + (lane & ~1));
+          char* op = (char*)((act_t*)p.C + (long long)(mg - seg * p.m_split + odd) * p.ldc + (long long)seg * p.split_col_off + ch0 + (lane & ~1));
           uint32_t pitch2 = (uint32_t)p.ldc * 4u;            // two pixel rows, in bytes
           asm volatile("" : "+r"(pitch2));
           const int left = p.M - mg - odd;                   // pixel j + odd is stored iff j < left
@@ -451,8 +453,8 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           for (int jj = 0; jj < 16; jj++) {
             const float mine_keep = odd ? v[2 * jj + 1] : v[2 * jj];
             const float other = __shfl_xor_sync(0xffffffffu, odd ? v[2 * jj] : v[2 * jj + 1], 1);
-            const __nv_bfloat162 hh = odd ? __floats2bfloat162_rn(other, mine_keep) : __floats2bfloat162_rn(mine_keep, other);
-            if (2 * jj < left && !(q.dbg & 2048)) *(__nv_bfloat162*)(op + (unsigned long long)jj * pitch2) = hh;
+            const act2_t hh = odd ? f2act2(other, mine_keep) : f2act2(mine_keep, other);
+            if (2 * jj < left && !(q.dbg & 2048)) *(act2_t*)(op + (unsigned long long)jj * pitch2) = hh;
           }
           continue;
         }
@@ -465,7 +467,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           for (int j = 0; j < 32; j++) {
             uint16_t hv;
             asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hv) : "r"(s_res + (uint32_t)(j * 64 + lane * 2)) : "memory");
-            v[j] += __uint_as_float((uint32_t)hv << 16);
+            v[j] += actbits2f(hv);
           }
           // prefetch the residual of the next 32 pixels (next group, or the first group of the next tile)
           if (g < 3) load_res(mg + 32);
@@ -479,7 +481,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         if (!(q.dbg & 1024))
 #pragma unroll
         for (int j = 0; j < 32; j++) {
-          const __nv_bfloat16 hb = __float2bfloat16(v[j]);
+          const act_t hb = f2act(v[j]);
           asm volatile("st.shared.u16 [%0], %1;" ::"r"(s_out + (uint32_t)(j * 64 + lane * 2)), "h"(*reinterpret_cast<const uint16_t*>(&hb)) : "memory");
         }
         __syncwarp();
@@ -488,7 +490,7 @@ tc3_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           const int mr = mg + 8 * i + spx;
           uint4 ov;
           asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_out + (uint32_t)((8 * i + spx) * 64 + scj * 16)) : "memory");
-          __nv_bfloat16* op = row_ptr(mr);
+          act_t* op = row_ptr(mr);
           if (halo && p.row_remap == 0 && op) {     // border positions of the halo layout are written as zeros
             const int r_ = mr % q.IS, yy = r_ / q.Wp;
             if (yy < 1 || r_ - yy * q.Wp >= p.img_w) ov = make_uint4(0u, 0u, 0u, 0u);
@@ -567,17 +569,17 @@ int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force)
   CUtensorMap mA, mA2, mW;
   int rc;
   if (p.halo) {
-    rc = fpb_tiled_map_bf16(p.A, p.M, p.Cin, p.pix_pitch, TP, &mA, &num_sms);
-    if (!rc) rc = fpb_tiled_map_bf16(p.A, p.M, p.Cin, p.pix_pitch, q.hrows - TP, &mA2, &num_sms);
+    rc = fpb_tiled_map_act(p.A, p.M, p.Cin, p.pix_pitch, TP, &mA, &num_sms);
+    if (!rc) rc = fpb_tiled_map_act(p.A, p.M, p.Cin, p.pix_pitch, q.hrows - TP, &mA2, &num_sms);
   } else if (plain) {
-    rc = fpb_tiled_map_bf16(p.A, p.M, p.K, p.pix_pitch, TP / CGn, &mA, &num_sms);
+    rc = fpb_tiled_map_act(p.A, p.M, p.K, p.pix_pitch, TP / CGn, &mA, &num_sms);
     mA2 = mA;
   } else {
-    rc = fpb_im2col_map_bf16(p, fpb_cdiv(p.M, p.Ho * p.Wo), &mA);
+    rc = fpb_im2col_map_act(p, fpb_cdiv(p.M, p.Ho * p.Wo), &mA);
     mA2 = mA;
   }
   if (rc) return rc;
-  rc = fpb_tiled_map_bf16(p.W, p.N, p.K, p.ldw, wres ? 128 : ncols, &mW, &num_sms);
+  rc = fpb_tiled_map_act(p.W, p.N, p.K, p.ldw, wres ? 128 : ncols, &mW, &num_sms);
   if (rc) return rc;
   static bool configured = false;
   if (!configured) {
@@ -611,3 +613,5 @@ int tc3_gemm(const GemmProblem& p, cudaStream_t st, int force)
   fpb_count_launch();
   return FPB_OK;
 }
+
+}  // namespace FPB_ACT_NS

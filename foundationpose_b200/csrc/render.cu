@@ -16,6 +16,7 @@
 //   3. shade kernel    (N x S x S)      barycentrics -> xyz / colour|texture / lighting -> normalised
 //                                       8-channel NHWC pixel, one 128-bit store (bf16) per pixel
 #include "common.cuh"
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 struct fpb_mesh {
@@ -412,16 +413,11 @@ __global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restric
   }
 }
 
-// a / 255.0f, correctly rounded, without the generic division sequence (range check + slow path on zero numerators):
-// q = RN(a * rc), r = a - 255 q (exact in one FMA), q' = RN(q + r * rc).  Verified exhaustively on the host against
-// IEEE a / 255.0f for every float in [0, 256] (all 1,132,462,081 bit patterns, denormals included) -- the only range used.
-__device__ __forceinline__ float div255(float a)
-{
-  const float rc = 1.0f / 255.0f;
-  const float q = a * rc;
-  const float r = fmaf(-255.0f, q, a);
-  return fmaf(r, rc, q);
-}
+// transform_batch's `rgb.cuda().float() / 255.0` (h5_dataset.py:123-124): on CUDA tensors ATen evaluates a division by
+// a Python scalar as a multiplication with the fp32 reciprocal ("a * reciprocal(b)", BinaryDivTrueKernel.cu), and the
+// reference only runs on CUDA, so x * (1.0f / 255.0f) IS the reference value (it differs from the correctly rounded
+// quotient by one ulp on about a quarter of the inputs).  make_mesh_tensors' `/ 255.0` is the same torch op.
+__device__ __forceinline__ float div255(float a) { return a * (1.0f / 255.0f); }
 
 __device__ __forceinline__ void xyz_norm(const float xyz[3], const float* T, float inv_radius, float zthr, float o[3])
 {
@@ -434,12 +430,19 @@ __device__ __forceinline__ void xyz_norm(const float xyz[3], const float* T, flo
   }
 }
 
-template <bool BF16>
+// DT: element type of the network input buffer -- 0 fp32, 1 bf16, 2 fp16 (FPB_PREC_*)
+template <int DT>
 __device__ __forceinline__ void store_px8(void* base, size_t pix, const float v[6])
 {
-  if (BF16) {
+  if (DT == 1) {
     __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]),
                    c = __floats2bfloat162_rn(v[4], v[5]);
+    uint4 q;
+    q.x = *reinterpret_cast<uint32_t*>(&a); q.y = *reinterpret_cast<uint32_t*>(&b);
+    q.z = *reinterpret_cast<uint32_t*>(&c); q.w = 0u;
+    reinterpret_cast<uint4*>(base)[pix] = q;
+  } else if (DT == 2) {
+    __half2 a = __floats2half2_rn(v[0], v[1]), b = __floats2half2_rn(v[2], v[3]), c = __floats2half2_rn(v[4], v[5]);
     uint4 q;
     q.x = *reinterpret_cast<uint32_t*>(&a); q.y = *reinterpret_cast<uint32_t*>(&b);
     q.z = *reinterpret_cast<uint32_t*>(&c); q.w = 0u;
@@ -455,7 +458,7 @@ __device__ __forceinline__ void store_px8(void* base, size_t pix, const float v[
 // normal_map output (:192-197): interpolated camera-frame vertex normals, F.normalize'd, background 0
 struct ShadeOpts { int use_light; float w_ambient, w_diffuse; float* out_normal; };
 
-template <bool BF16, bool LEAN>
+template <int BF16, bool LEAN>
 __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4* __restrict__ clip,
                                                     const float4* __restrict__ camd,
                                                     const unsigned long long* __restrict__ zbuf,
@@ -587,7 +590,7 @@ __device__ __forceinline__ int nearest_src(float p, float scale, int size)
 
 struct K9f { float k[9]; };
 
-template <bool BF16, bool U8>
+template <int BF16, bool U8>
 __global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_, const float* __restrict__ xyz_map,
                                                    const float* __restrict__ depth, int H, int W,
                                                    const float* __restrict__ poses, const float* __restrict__ params, K9f K,
@@ -626,7 +629,7 @@ __global__ void __launch_bounds__(256) warp_kernel(const void* __restrict__ rgb_
       if (p01) acc += tap(o01 + k) * wne;
       if (p10) acc += tap(o10 + k) * wsw;
       if (p11) acc += tap(o11 + k) * wse;
-      v6[k] = U8 ? div255(acc) : acc / 255.0f;     // uint8 taps: acc in [0, 255] (convex combination, up to rounding)
+      v6[k] = div255(acc);
     }
   }
   float xyz[3] = {0.f, 0.f, 0.f};
@@ -769,8 +772,9 @@ static int render_chunk(const fpb_mesh* mesh, const float* poses, const float* p
 #define LAUNCH_SHADE(BF, LN)                                                                                          \
   shade_kernel<BF, LN><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, params, N, S, inv_radius, zthr, out_A, \
                                                    out_pitch, out_xoff, out_color, out_xyz, out_tri, opt)
-  if (a_is_bf16) { if (lean) LAUNCH_SHADE(true, true); else LAUNCH_SHADE(true, false); }
-  else           { if (lean) LAUNCH_SHADE(false, true); else LAUNCH_SHADE(false, false); }
+  if (a_is_bf16 == 1)      { if (lean) LAUNCH_SHADE(1, true); else LAUNCH_SHADE(1, false); }
+  else if (a_is_bf16 == 2) { if (lean) LAUNCH_SHADE(2, true); else LAUNCH_SHADE(2, false); }
+  else                     { if (lean) LAUNCH_SHADE(0, true); else LAUNCH_SHADE(0, false); }
 #undef LAUNCH_SHADE
   FPB_LAUNCH_CHECK();
   return FPB_OK;
@@ -786,7 +790,7 @@ FPB_EXPORT int fpb_render_crops_ex(const fpb_mesh* mesh, const float* poses, con
                                    float w_ambient, float w_diffuse, float* out_normal, void* stream)
 {
   FPB_CHECK_ARG(mesh && poses && params && ws && out_A && N > 0 && S > 1 && S <= 4096);
-  FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff);
+  FPB_CHECK_ARG(out_xoff >= 0 && out_pitch >= S + out_xoff && a_is_bf16 >= 0 && a_is_bf16 <= 2);
   const size_t esz = a_is_bf16 ? 2 : 4;
   for (int n0 = 0; n0 < N; n0 += MAX_N_PER_LAUNCH) {
     const int n = (N - n0) < MAX_N_PER_LAUNCH ? (N - n0) : MAX_N_PER_LAUNCH;
@@ -832,8 +836,9 @@ FPB_EXPORT int fpb_warp_crops(const void* rgb, int rgb_is_u8, const float* xyz_h
 #define LAUNCH_WARP(BF, U8)                                                                                           \
   warp_kernel<BF, U8><<<blocks, threads, 0, st>>>(rgb, xyz_hw3, depth_hw, H, W, po, pa, K, n, S, inv_radius, mode,   \
                                                   wsc, hsc, ssc, ob, out_pitch, out_xoff)
-    if (b_is_bf16) { if (rgb_is_u8) LAUNCH_WARP(true, true); else LAUNCH_WARP(true, false); }
-    else           { if (rgb_is_u8) LAUNCH_WARP(false, true); else LAUNCH_WARP(false, false); }
+    if (b_is_bf16 == 1)      { if (rgb_is_u8) LAUNCH_WARP(1, true); else LAUNCH_WARP(1, false); }
+    else if (b_is_bf16 == 2) { if (rgb_is_u8) LAUNCH_WARP(2, true); else LAUNCH_WARP(2, false); }
+    else                     { if (rgb_is_u8) LAUNCH_WARP(0, true); else LAUNCH_WARP(0, false); }
 #undef LAUNCH_WARP
     FPB_LAUNCH_CHECK();
   }

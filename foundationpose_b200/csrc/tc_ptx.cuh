@@ -2,7 +2,7 @@
 // UMMA descriptors, tcgen05.mma / commit / ld, TMA tiled + im2col loads.
 #pragma once
 #include <cuda.h>
-#include <cuda_bf16.h>
+#include "act_type.cuh"
 #include <stdint.h>
 
 namespace {
@@ -91,7 +91,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr)
 }
 __host__ __device__ constexpr uint32_t make_idesc(int m, int n)
 {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+  return (1u << 4) | (ACT_IDESC_FMT << 7) | (ACT_IDESC_FMT << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 template <int CG>

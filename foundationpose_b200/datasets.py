@@ -79,9 +79,11 @@ class BatchPoseData:
     """pose_dataset.py:129-134: gathers every non-None field (the result owns copies, not views of AB)."""
     out = BatchPoseData()
     ids = torch.as_tensor(ids)
+    n = len(self.poseA) if torch.is_tensor(self.poseA) else None
     for k in self._tensor_fields():
       v = self.__dict__[k]
-      out.__dict__[k] = v[ids.to(v.device)]
+      # broadcast fields (the refiner's Ks is [1,3,3], predict_pose_refine.py:54) are shared, not gathered
+      out.__dict__[k] = v if (n is not None and v.shape[0] == 1 and n != 1) else v[ids.to(v.device)]
     return out
 
 

@@ -17,7 +17,8 @@ from ._lib import lib, check, ptr, stream
 
 REFINE, SCORE = 0, 1
 REFINE_6D = 2      # fpb_net_create kind for a RefineNet whose rot head has 6 outputs (include/fpb200.h)
-PREC = {'fp32': 0, 'bf16': 1}
+PREC = {'fp32': 0, 'bf16': 1, 'fp16': 2}     # FPB_PREC_* (include/fpb200.h)
+ACT_DTYPE = {'fp32': torch.float, 'bf16': torch.bfloat16, 'fp16': torch.float16}
 D, TOK = 512, 400
 # (Cin, Cout, k, stride) of the 15 convolutions, in execution order
 _CONVS = [(6, 64, 7, 2), (64, 128, 3, 2)] + [(128, 128, 3, 1)] * 4 + [(256, 256, 3, 1)] * 4 + [(256, 512, 3, 2)] + \
@@ -219,10 +220,11 @@ def pad_input(AB):
 class Net:
   """Device-side network handle (fpb_net) plus its workspace."""
 
-  def __init__(self, kind, state_dict, precision='bf16'):
+  def __init__(self, kind, state_dict, precision='fp16'):
     _lib.require_cuda()
     self.kind, self.precision = kind, PREC[precision]
     self.bf16 = precision == 'bf16'
+    self.precision_name = precision
     blob = pack_state_dict(kind, state_dict)
     self.rot_dim = int(state_dict['rot_head.1.weight'].shape[0]) if kind == REFINE else 0
     h = ctypes.c_void_p()
@@ -233,7 +235,7 @@ class Net:
 
   @property
   def act_dtype(self):
-    return torch.bfloat16 if self.bf16 else torch.float
+    return ACT_DTYPE[self.precision_name]
 
   def workspace(self, N):
     need = lib().fpb_net_ws_bytes(self.kind, self.precision, N)

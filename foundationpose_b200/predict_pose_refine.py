@@ -116,16 +116,17 @@ def batch_from_AB(AB, params, ob_in_cams, K, mesh_diameter, S):
   N = len(ob_in_cams)
   rgbAs, xyzAs, rgbBs, xyzBs = views_of_AB(AB, N, S, U.IN_XOFF)
   poseA = torch.as_tensor(ob_in_cams, dtype=torch.float, device='cuda').reshape(-1, 4, 4)
-  Ks = torch.as_tensor(np.asarray(K, dtype=np.float32), device='cuda').reshape(1, 3, 3)
   pd = BatchPoseData(rgbAs=rgbAs, rgbBs=rgbBs, xyz_mapAs=xyzAs, xyz_mapBs=xyzBs, poseA=poseA,
-                     tf_to_crops=params[:, :9].reshape(N, 3, 3), Ks=Ks,
-                     mesh_diameters=torch.full((N,), float(mesh_diameter), dtype=torch.float, device='cuda'))
+                     tf_to_crops=params[:, :9].reshape(N, 3, 3))
+  # Ks / mesh_diameters cost a host-to-device copy / a fill launch: built on first access, not in the refine loop
+  pd.set_lazy('Ks', lambda: torch.as_tensor(np.asarray(K, dtype=np.float32), device='cuda').reshape(1, 3, 3))
+  pd.set_lazy('mesh_diameters', lambda: torch.full((N,), float(mesh_diameter), dtype=torch.float, device='cuda'))
   pd.AB, pd.params, pd.transformed = AB, params, True
   return pd
 
 
 class PoseRefinePredictor:
-  def __init__(self, cfg=None, state_dict=None, ckpt_path=None, seed=None, precision='bf16', allow_synthetic=False):
+  def __init__(self, cfg=None, state_dict=None, ckpt_path=None, seed=None, precision='fp16', allow_synthetic=False):
     """The reference ctor takes no argument and reads weights/2023-10-28-18-33-37/{model_best.pth,config.yml}
     (:94-143).  Same here when that directory exists next to the package; `ckpt_path` / `state_dict` name other
     weights, `cfg` overrides single keys.  Without any weights the ctor raises, unless allow_synthetic=True (or an

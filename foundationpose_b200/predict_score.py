@@ -43,7 +43,7 @@ def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_rati
   U.render_crops(mesh_tensors, ob_in_cams, params, S, mesh_diameter, 0.1, out_A=out_AB[:N])
   U.warp_crops(rgb, None, depth, ob_in_cams, params, K, S, mesh_diameter, 1, out_B=out_AB[N:])
   pd = batch_from_AB(out_AB, params, ob_in_cams, K, mesh_diameter, S)
-  pd.Ks = pd.Ks.expand(N, 3, 3)                                     # :102
+  pd.set_lazy('Ks', lambda: torch.as_tensor(np.asarray(K, dtype=np.float32), device='cuda').reshape(1, 3, 3).expand(N, 3, 3))   # :102
   poses = pd.poseA
 
   def depth_As():                                                   # :84,92: z of the rendered xyz map
@@ -59,7 +59,7 @@ def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_rati
 
 
 class ScorePredictor:
-  def __init__(self, amp=True, cfg=None, state_dict=None, ckpt_path=None, seed=None, precision='bf16',
+  def __init__(self, amp=True, cfg=None, state_dict=None, ckpt_path=None, seed=None, precision='fp16',
                allow_synthetic=False):
     """reference :118-156 reads weights/2024-01-11-20-02-45/{model_best.pth,config.yml}; see PoseRefinePredictor for
     ckpt_path / state_dict / cfg / allow_synthetic."""

@@ -379,6 +379,7 @@ def mesh_handle_of(mesh_tensors):
 # render / warp / pose update
 # ------------------------------------------------------------------------------------------------
 IN_PITCH, IN_XOFF = 168, 4      # FPB_IN_PITCH / FPB_IN_XOFF of include/fpb200.h (S = 160)
+_DT_CODE = {torch.float: 0, torch.bfloat16: 1, torch.float16: 2}     # a_is_bf16 / b_is_bf16 of fpb_render_crops / fpb_warp_crops
 
 
 def net_input_buffer(N, S, dtype):
@@ -410,7 +411,7 @@ def render_crops(mesh_tensors, poses, params, S, mesh_diameter, zthr, out_A=None
   if get_normal:
     nm = extras['normal'] = torch.empty((N, S, S, 3), dtype=torch.float, device='cuda')
   check(lib().fpb_render_crops_ex(mh.handle, ptr(poses), ptr(params), N, S, float(mesh_diameter), float(zthr), ptr(ws),
-                                  ptr(out_A), 1 if out_A.dtype == torch.bfloat16 else 0, out_A.shape[2],
+                                  ptr(out_A), _DT_CODE[out_A.dtype], out_A.shape[2],
                                   (out_A.shape[2] - S) // 2, ptr(c), ptr(x), ptr(t), 1 if use_light else 0,
                                   float(w_ambient), float(w_diffuse), ptr(nm), stream()))
   return out_A, extras
@@ -429,7 +430,7 @@ def warp_crops(rgb_t, xyz_map_t, depth_t, poses, params, K, S, mesh_diameter, mo
     rgb_t = rgb_t.float().contiguous()
   check(lib().fpb_warp_crops(ptr(rgb_t), 1 if is_u8 else 0, ptr(xyz_map_t), ptr(depth_t), H, W, ptr(poses), ptr(params),
                              hptr(K9), N, S, float(mesh_diameter), mode, ptr(out_B),
-                             1 if out_B.dtype == torch.bfloat16 else 0, out_B.shape[2], (out_B.shape[2] - S) // 2,
+                             _DT_CODE[out_B.dtype], out_B.shape[2], (out_B.shape[2] - S) // 2,
                              stream()))
   return out_B
 

@@ -29,6 +29,11 @@ extern "C" {
 /* precision modes of the network path */
 #define FPB_PREC_FP32 0   /* SIMT fp32 parity mode */
 #define FPB_PREC_BF16 1   /* tcgen05 bf16 operands, fp32 accumulation */
+#define FPB_PREC_FP16 2   /* tcgen05 IEEE fp16 operands, fp32 accumulation: the dtype of the reference's autocast path
+                             (predict_pose_refine.py:190, predict_score.py:193); same instruction, same speed, 3 more
+                             mantissa bits than bf16 */
+/* element type of 16-bit image / activation buffers handed to fpb_render_crops / fpb_warp_crops (a_is_bf16 /
+ * b_is_bf16 arguments): 0 fp32, 1 bf16, 2 fp16 (= the FPB_PREC_* value of the network that will read them) */
 
 const char* fpb_last_error(void);
 int fpb_version(void);
@@ -205,6 +210,9 @@ int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* W, void* C,
  * ctx [R][512] out;  R = groups*400.  Replaces nn.MultiheadAttention's core (refine_network.py:56-70). */
 int fpb_debug_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups,
                         void* stream);
+
+/* operand type (FPB_PREC_BF16 default, or FPB_PREC_FP16) the fpb_debug_* unit-test entries run in */
+int fpb_debug_set_precision(int precision);
 
 /* number of kernels this library launched on the calling thread since the last reset */
 long long fpb_launch_count(int reset);

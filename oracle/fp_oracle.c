@@ -401,11 +401,15 @@ ORC_API void orc_make_A(const float* color, const float* xyz, const float* poses
 {
   const float radius = mesh_diameter / 2.0f;
   const float inv_radius = 1.0f / radius;
+  /* transform_batch's `rgb.cuda().float()/255.0` (h5_dataset.py:123-124): on a CUDA tensor ATen divides by a Python
+   * scalar as a multiplication with the fp32 reciprocal (BinaryDivTrueKernel.cu, "a * reciprocal(b)"), and the
+   * reference only runs on CUDA -- so the faithful value is x * (1.0f/255.0f), not the correctly rounded quotient */
+  const float inv255 = 1.0f / 255.0f;
 #pragma omp parallel for schedule(static)
   for (int n = 0; n < N; n++)
     for (int p = 0; p < S * S; p++) {
       size_t o = (size_t)n * S * S + p;
-      for (int k = 0; k < 3; k++) A[o * 6 + k] = (color[o * 3 + k] * 255.0f) / 255.0f;
+      for (int k = 0; k < 3; k++) A[o * 6 + k] = (color[o * 3 + k] * 255.0f) * inv255;
       xyz_norm(xyz + o * 3, poses + n * 16, inv_radius, zthr, A + o * 6 + 3);
     }
 }
@@ -439,6 +443,7 @@ ORC_API void orc_make_B(const float* rgb, const float* xyz_map, const float* dep
   const float wsc = (float)W / (float)(W - 1), hsc = (float)H / (float)(H - 1);
   const float ssc = (float)S / (float)(S - 1);
   const float zthr = mode ? 0.1f : 0.001f;
+  const float inv255 = 1.0f / 255.0f;
 #pragma omp parallel for schedule(static)
   for (int n = 0; n < N; n++) {
     const float* iv = inv4 + n * 4;
@@ -461,7 +466,7 @@ ORC_API void orc_make_B(const float* rgb, const float* xyz_map, const float* dep
           if (inx1 && iny0) acc += rgb[((size_t)(int)y0 * W + (int)x1) * 3 + k] * wne;
           if (inx0 && iny1) acc += rgb[((size_t)(int)y1 * W + (int)x0) * 3 + k] * wsw;
           if (inx1 && iny1) acc += rgb[((size_t)(int)y1 * W + (int)x1) * 3 + k] * wse;
-          o[k] = acc / 255.0f;
+          o[k] = acc * inv255;      /* see orc_make_A */
         }
         /* nearest xyz */
         float xyz[3] = {0.0f, 0.0f, 0.0f};

@@ -125,9 +125,16 @@ def score_from_features(net, feats):
 
 
 @torch.no_grad()
-def forward_chunked(net, kind, A_nhwc, B_nhwc, chunk=16):
-  """A/B numpy [N,S,S,6] -> refine: (trans [N,3], rot [N,3]); score: feats handled whole (L=N)."""
+def forward_chunked(net, kind, A_nhwc, B_nhwc, chunk=16, autocast=None):
+  """A/B numpy [N,S,S,6] -> refine: (trans [N,3], rot [N,3]); score: feats handled whole (L=N).
+  autocast: None (fp32) or a torch dtype -- the model call runs under torch.autocast('cpu', dtype) and the outputs are
+  cast back to fp32, as the reference does on CUDA (predict_pose_refine.py:190-193, predict_score.py:193-195)."""
+  import contextlib
   import numpy as np
+  if autocast is not None:
+    with torch.autocast('cpu', dtype=autocast):
+      out = forward_chunked(net, kind, A_nhwc, B_nhwc, chunk, None)
+    return tuple(np.asarray(o, dtype=np.float32) for o in out)
   A = torch.from_numpy(np.ascontiguousarray(A_nhwc)).permute(0, 3, 1, 2).contiguous()
   B = torch.from_numpy(np.ascontiguousarray(B_nhwc)).permute(0, 3, 1, 2).contiguous()
   N = len(A)
@@ -136,8 +143,8 @@ def forward_chunked(net, kind, A_nhwc, B_nhwc, chunk=16):
     for b in range(0, N, chunk):
       o = net(A[b:b + chunk], B[b:b + chunk])
       tr.append(o['trans']); ro.append(o['rot'])
-    return torch.cat(tr).numpy(), torch.cat(ro).numpy()
+    return torch.cat(tr).float().numpy(), torch.cat(ro).float().numpy()
   feats = torch.cat([net.extract_feat(A[b:b + chunk], B[b:b + chunk]) for b in range(0, N, chunk)])
   x = feats.reshape(1, N, -1)
   x, _ = net.att_cross(x, x, x)
-  return net.linear(x).reshape(N).numpy(), feats.numpy()
+  return net.linear(x).reshape(N).float().numpy(), feats.float().numpy()

@@ -11,6 +11,8 @@ ScoreNetMultiPair (tests/golden/make_golden.py).  Contents:
   pool_poses / pool_feats                       a second set of 252 scorer evaluations (the poses after iteration 1):
                                                 together with score_* a pool of 504 (pose, feature) pairs for the
                                                 top-1-agreement trials
+  it{k}_trans_ac16 / _rot_ac16, *_feats_ac16    the same modules under torch.autocast('cpu', fp16) on the same inputs: the
+                                                reference's own fp16 deviation from fp32, for context
   sha_scene / sha_refine / sha_score            digests of the scene arrays and both state dicts (drift detection)
 """
 import hashlib
@@ -63,6 +65,21 @@ def main():
   pool = out['it0_poses_out']
   _, feats = orc.score_predict(sc['rgb'], d, pool, sc['K'])
   out['pool_poses'], out['pool_feats'] = pool, feats
+  # The reference's OWN reduced-precision behaviour, for context: the same modules under torch.autocast fp16 (what
+  # predict_pose_refine.py:190 / predict_score.py:193 do on CUDA), on the fp32 trajectory's inputs.
+  from oracle import nets as on
+  from oracle import ops as oo
+  xyz_map = oo.depth2xyzmap(d, sc['K'])
+  for k in range(5):
+    A, B, _ = orc.refine_inputs(sc['rgb'], xyz_map, out[f'it{k}_poses_in'], sc['K'])
+    t16, r16 = on.forward_chunked(orc.refine, 'refine', A, B, orc.net_chunk, autocast=torch.float16)
+    out[f'it{k}_trans_ac16'], out[f'it{k}_rot_ac16'] = t16, r16
+    print('autocast fp16 refine iter', k, np.abs(t16 - out[f'it{k}_trans']).max(), np.abs(r16 - out[f'it{k}_rot']).max(), flush=True)
+  for name, poses in (('score', tr['poses']), ('pool', pool)):
+    A, B, _ = orc.score_inputs(sc['rgb'], d, poses, sc['K'])
+    _, f16 = on.forward_chunked(orc.score, 'score', A, B, orc.net_chunk, autocast=torch.float16)
+    out[f'{name}_feats_ac16'] = f16
+    print('autocast fp16 feats', name, np.abs(f16 - out[f'{name}_feats']).max(), np.abs(f16 - out[f'{name}_feats']).mean(), flush=True)
   out['sha_scene'], out['sha_refine'], out['sha_score'] = scene_digest(sc), state_digest(sd_r), state_digest(sd_s)
   np.savez_compressed(os.path.join(HERE, 'trace_cfg2.npz'), **out)
   print('done', time.time() - t0, 's', {k: getattr(v, 'shape', v) for k, v in out.items()})

@@ -1,6 +1,9 @@
 """Shared helpers for the parity tests (oracle = checker only)."""
 import numpy as np
 
+# make_mesh_tensors divides by 255.0 on a CUDA tensor (src/Utils.py:112,121): ATen multiplies by the fp32 reciprocal
+INV255 = np.float32(1.0) / np.float32(255.0)
+
 
 def mesh_np(mesh):
   """SimpleMesh -> dict of numpy arrays in make_mesh_tensors layout (src/Utils.py:104-130)."""
@@ -9,13 +12,13 @@ def mesh_np(mesh):
   vis = mesh.visual
   if vis.uv is not None and vis.material is not None:
     img = np.asarray(vis.material.image)[..., :3]
-    d['tex'] = (img.astype(np.float32) / np.float32(255.0))[None]
+    d['tex'] = (img.astype(np.float32) * INV255)[None]
     uv = np.asarray(vis.uv, np.float32).copy()
     uv[:, 1] = 1 - uv[:, 1]
     d['uv'] = uv
     d['uv_idx'] = d['faces']
   else:
-    d['vertex_color'] = np.asarray(vis.vertex_colors)[..., :3].astype(np.float32) / np.float32(255.0)
+    d['vertex_color'] = np.asarray(vis.vertex_colors)[..., :3].astype(np.float32) * INV255
   return d
 
 

@@ -162,7 +162,7 @@ def test_nvdiffrast_render_api(scene1):
   # matrices come from torch matmul here (not the fused crop kernel): compare with a tolerance
   assert (np.abs(c.cpu().numpy() - color) > 1e-3).mean() < 2e-3
   assert (np.abs(extra['xyz_map'].cpu().numpy() - xyz) > 1e-4).mean() < 2e-3
-  assert nrm is None and d.shape == (6, S, S)
+  assert nrm.shape == (6, S, S, 3) and d.shape == (6, S, S)      # use_light implies get_normal (src/Utils.py:190-191)
 
 
 @pytest.mark.parametrize('cfg', [1, 2])

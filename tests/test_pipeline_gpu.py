@@ -7,7 +7,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _estimator(scene, precision='bf16'):
+def _estimator(scene, precision='fp16'):
   from foundationpose_b200 import nets
   from foundationpose_b200.estimater import FoundationPose
   from foundationpose_b200.predict_pose_refine import PoseRefinePredictor
