@@ -226,12 +226,32 @@ __device__ __forceinline__ void raster_pixel(const TriSetup& t, const float4 c0,
 }
 
 constexpr int SMALL_TRI_PIXELS = 16;
+// Triangles whose pixel bounding box exceeds SMALL_TRI_PIXELS (low-poly / CAD-like meshes: the 12-face cube of BASELINE
+// cfg 1 covers ~10^4 pixels per face) are not rasterised here: their face index goes to a per-hypothesis queue and the
+// shading kernel resolves them TILE-PARALLEL -- the raster kernel queues the finished set-up record (snapped corners, pixel box,
+// clip coordinates), every 32 x 8 pixel block of shade_kernel copies the records to shared memory, skips those whose
+// box misses the tile, and each pixel thread z-tests the rest in registers
+// against the z-buffer value the small-triangle path left (same integer edge functions, same (z/w | face) key: bit-
+// identical images, no atomics).  The first version swept each big triangle's box with ONE warp, serially: 686 us per
+// launch for 12 hypotheses x 12 faces.  BIG_CAP bounds the queue; overflow falls back to that warp sweep.
+constexpr int BIG_CAP = 256;
+constexpr int BIG_CHUNK = 64;
+// one queued big triangle: the raster kernel's set-up + clip coordinates, 96 bytes (six 16-byte words)
+struct __align__(16) BigTri {
+  int X[3], Y[3];
+  int px0, px1, py0, py1;
+  int small;
+  uint32_t face;
+  float4 c0, c1, c2;
+};
+static_assert(sizeof(BigTri) == 96, "BigTri record");
 
 // One triangle per lane; the whole warp must call this together (the large-footprint path is warp-cooperative).
 // valid: this lane holds face f with corner indices i0..i2 and their snapped positions s0..s2.
 __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i1, int i2, const int2 s0, const int2 s1,
                                                 const int2 s2, const ClipSrc cl, int S,
-                                                unsigned long long* __restrict__ zb)
+                                                unsigned long long* __restrict__ zb, uint32_t* __restrict__ bigcnt,
+                                                BigTri* __restrict__ bigq)
 {
   TriSetup t;
   t.ok = 0;
@@ -279,7 +299,22 @@ __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i
         } while (mask);
       }
     } else {
-      big = 1;       // large footprint, or coordinates beyond the 32-bit fast path: warp-cooperative 64-bit path
+      // large footprint, or coordinates beyond the 32-bit fast path: queue it for the tile-parallel resolve in the shading
+      // kernel (the counter starts at 0xffffffff: one memset initialises it together with the z-buffer)
+      const uint32_t slot = atomicAdd(bigcnt, 1u) + 1u;
+      if (slot < (uint32_t)BIG_CAP) {
+        BigTri r;
+#pragma unroll
+        for (int e = 0; e < 3; e++) { r.X[e] = t.X[e]; r.Y[e] = t.Y[e]; }
+        r.px0 = t.px0; r.px1 = t.px1; r.py0 = t.py0; r.py1 = t.py1; r.small = t.small; r.face = (uint32_t)f;
+        r.c0 = cl.get(i0); r.c1 = cl.get(i1); r.c2 = cl.get(i2);
+        const uint4* src = reinterpret_cast<const uint4*>(&r);
+        uint4* dst = reinterpret_cast<uint4*>(bigq + slot);
+#pragma unroll
+        for (int e = 0; e < 6; e++) dst[e] = src[e];
+      } else {
+        big = 1;     // queue full: warp-cooperative 64-bit sweep below
+      }
     }
   }
   // triangles with a large footprint: the whole warp sweeps the bounding box together
@@ -325,7 +360,8 @@ constexpr int RASTER_FACES = 256 * RASTER_TPT;
 __global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __restrict__ faces, int F, int V,
                                                           const float4* __restrict__ clip, const int2* __restrict__ snap,
                                                           const float* __restrict__ pos, const float* __restrict__ params,
-                                                          int S, unsigned long long* __restrict__ zbuf)
+                                                          int S, unsigned long long* __restrict__ zbuf,
+                                                          uint32_t* __restrict__ bigcnt, BigTri* __restrict__ bigq)
 {
   __shared__ int q_f[RASTER_FACES];
   __shared__ int q_i[3][RASTER_FACES];
@@ -377,7 +413,8 @@ __global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __re
     const int e = base + (int)threadIdx.x;
     const bool valid = e < count;
     const int ee = valid ? e : 0;
-    raster_triangle(valid, q_f[ee], q_i[0][ee], q_i[1][ee], q_i[2][ee], q_s[0][ee], q_s[1][ee], q_s[2][ee], cl, S, zb);
+    raster_triangle(valid, q_f[ee], q_i[0][ee], q_i[1][ee], q_i[2][ee], q_s[0][ee], q_s[1][ee], q_s[2][ee], cl, S, zb,
+                    bigcnt + n, bigq + (size_t)n * BIG_CAP);
   }
 }
 
@@ -386,7 +423,8 @@ __global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __re
 __global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restrict__ faces, int F, int V,
                                                      const float4* __restrict__ clip, const int2* __restrict__ snap,
                                                      const float* __restrict__ pos, const float* __restrict__ params,
-                                                     int S, unsigned long long* __restrict__ zbuf)
+                                                     int S, unsigned long long* __restrict__ zbuf,
+                                                     uint32_t* __restrict__ bigcnt, BigTri* __restrict__ bigq)
 {
   const int n = blockIdx.y;
   const int f0 = blockIdx.x * RASTER_FACES + threadIdx.x;
@@ -409,7 +447,7 @@ __global__ void __launch_bounds__(256, 3) raster_kernel(const int32_t* __restric
     const ClipSrc cl = {clip ? clip + (size_t)n * V : nullptr, pos, params + (size_t)n * FPB_CROP_STRIDE + 13,
                         params + (size_t)n * FPB_CROP_STRIDE + 29};
     raster_triangle(f < F, f, idx[k][0], idx[k][1], idx[k][2], sp[k][0], sp[k][1], sp[k][2], cl, S,
-                    zbuf + (size_t)n * S * S);
+                    zbuf + (size_t)n * S * S, bigcnt + n, bigq + (size_t)n * BIG_CAP);
   }
 }
 
@@ -454,12 +492,63 @@ __device__ __forceinline__ void store_px8(void* base, size_t pix, const float v[
   }
 }
 
+// Tile-parallel resolve of the queued big triangles of one hypothesis for the 32 x 8 pixel block of the caller: returns
+// min(key, keys of the queued triangles covering raster pixel (px, py)).  Block-cooperative (every thread of the block
+// must call it; `inb` = this thread owns a pixel inside the crop).  rx0..ry1: the block's raster-space pixel rectangle.
+__device__ __noinline__ unsigned long long resolve_big_triangles(unsigned long long key, bool inb, int px, int py, int rx0,
+                                                                 int rx1, int ry0, int ry1, int S, int nbig,
+                                                                 const BigTri* __restrict__ bigq, BigTri* sh)
+{
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  const float xs = 2.0f / (float)S, xo = 1.0f / (float)S - 1.0f;
+  const float fx = (float)px * xs + xo, fy = (float)py * xs + xo;
+  for (int base = 0; base < nbig; base += BIG_CHUNK) {
+    const int cnt = min(BIG_CHUNK, nbig - base);
+    __syncthreads();                                   // the previous chunk has been consumed
+    for (int w = tid; w < cnt * 6; w += 256)
+      reinterpret_cast<uint4*>(sh)[w] = __ldg(reinterpret_cast<const uint4*>(bigq + base) + w);
+    __syncthreads();
+    if (inb) {
+      for (int k = 0; k < cnt; k++) {
+        const BigTri& b = sh[k];
+        if (b.px1 < rx0 || b.px0 > rx1 || b.py1 < ry0 || b.py0 > ry1) continue;     // misses this tile (block-uniform)
+        if (px < b.px0 || px > b.px1 || py < b.py0 || py > b.py1) continue;
+        bool in;
+        if (b.small) {
+          Tri32 q;
+#pragma unroll
+          for (int e = 0; e < 3; e++) { q.X[e] = b.X[e]; q.Y[e] = b.Y[e]; }
+          in = covers32(q, px, py);
+        } else {
+          TriSetup t;
+#pragma unroll
+          for (int e = 0; e < 3; e++) { t.X[e] = b.X[e]; t.Y[e] = b.Y[e]; }
+          in = covers(t, px, py);
+        }
+        if (!in) continue;
+        float b0, b1, zw;
+        bary_zw(b.c0, b.c1, b.c2, fx, fy, b0, b1, zw);
+        if (zw != zw) continue;
+        const unsigned long long kk = ((unsigned long long)f2ord(zw) << 32) | b.face;
+        key = kk < key ? kk : key;
+      }
+    }
+  }
+  return key;
+}
+
 // use_light / w_ambient / w_diffuse of nvdiffrast_render (src/Utils.py:200-211, default head light) and the optional
 // normal_map output (:192-197): interpolated camera-frame vertex normals, F.normalize'd, background 0
-struct ShadeOpts { int use_light; float w_ambient, w_diffuse; float* out_normal; };
+struct ShadeOpts {
+  int use_light; float w_ambient, w_diffuse; float* out_normal;
+  const uint32_t* bigcnt; const BigTri* bigq;      // queue of big triangles (written by the raster kernels)
+};
 
-template <int BF16, bool LEAN>
-__global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4* __restrict__ clip,
+// FULL: the off-hot-path arguments of nvdiffrast_render (normal_map output, non-default light) are compiled in; the hot
+// path instantiates FULL = false so that they do not cost it registers (62 vs 40 per thread: half the occupancy of a
+// latency-bound kernel)
+template <int BF16, bool LEAN, bool FULL>
+__global__ void __launch_bounds__(256, (FULL || LEAN) ? 1 : 6) shade_kernel(fpb_mesh mesh, const float4* __restrict__ clip,
                                                     const float4* __restrict__ camd,
                                                     const unsigned long long* __restrict__ zbuf,
                                                     const float* __restrict__ poses, const float* __restrict__ params,
@@ -472,17 +561,26 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
   // block = 32 x 8 pixels of one crop: grid (ceil(S/32), ceil(S/8), N)
   const int n = blockIdx.z;
   const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y;
-  if (j >= S || i >= S) return;
-  const size_t idx = ((size_t)n * S + i) * S + j;
+  const bool inb = j < S && i < S;
   const int py = S - 1 - i, px = j;  // row flip (src/Utils.py:197,216-218)
-  const unsigned long long key = zbuf[(size_t)n * S * S + (size_t)py * S + px];
+  unsigned long long key = inb ? zbuf[(size_t)n * S * S + (size_t)py * S + px] : ~0ull;
+  // big triangles queued by the raster kernel (none for dense meshes: one load, no barrier)
+  const uint32_t stored = opt.bigcnt[n] + 1u;          // counter starts at 0xffffffff
+  if (stored != 0u) {
+    __shared__ BigTri sh_big[BIG_CHUNK];
+    const int nbig = (int)(stored < (uint32_t)BIG_CAP ? stored : (uint32_t)BIG_CAP);
+    const int rx0 = blockIdx.x * 32, rx1 = rx0 + 31, ry1 = S - 1 - (int)blockIdx.y * 8, ry0 = ry1 - 7;
+    key = resolve_big_triangles(key, inb, px, py, rx0, rx1, ry0, ry1, S, nbig, opt.bigq + (size_t)n * BIG_CAP, sh_big);
+  }
+  if (!inb) return;
+  const size_t idx = ((size_t)n * S + i) * S + j;
   float col[3] = {0.f, 0.f, 0.f}, xyz[3] = {0.f, 0.f, 0.f};
   int tri = 0;
   if (key == ~0ull && zthr > 0.0f) {      // background: colour 0, xyz 0 -> z below the validity threshold -> the whole pixel is zero
     if (out_color) { out_color[idx * 3] = 0.f; out_color[idx * 3 + 1] = 0.f; out_color[idx * 3 + 2] = 0.f; }
     if (out_xyz) { out_xyz[idx * 3] = 0.f; out_xyz[idx * 3 + 1] = 0.f; out_xyz[idx * 3 + 2] = 0.f; }
     if (out_tri) out_tri[idx] = 0;
-    if (opt.out_normal) { opt.out_normal[idx * 3] = 0.f; opt.out_normal[idx * 3 + 1] = 0.f; opt.out_normal[idx * 3 + 2] = 0.f; }
+    if (FULL && opt.out_normal) { opt.out_normal[idx * 3] = 0.f; opt.out_normal[idx * 3 + 1] = 0.f; opt.out_normal[idx * 3 + 2] = 0.f; }
     const float z6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     store_px8<BF16>(outA, ((size_t)n * S + i) * out_pitch + out_xoff + j, z6);
     return;
@@ -547,11 +645,11 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
     }
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-      float cv = opt.use_light ? c[k] * opt.w_ambient + (dm * c[k]) * opt.w_diffuse : c[k];
+      float cv = FULL ? (opt.use_light ? c[k] * opt.w_ambient + (dm * c[k]) * opt.w_diffuse : c[k]) : c[k] * 0.8f + (dm * c[k]) * 0.5f;
       col[k] = fminf(fmaxf(cv, 0.0f), 1.0f);
     }
     tri = f + 1;
-    if (opt.out_normal) {     // off the hot path: the rotated corner normals are recomputed here
+    if (FULL && opt.out_normal) {     // off the hot path: the rotated corner normals are recomputed here
       const float* T = poses + (size_t)n * 16;
       const int iv[3] = {i0, i1, i2};
       float cn[3][3];
@@ -568,7 +666,7 @@ __global__ void __launch_bounds__(256) shade_kernel(fpb_mesh mesh, const float4*
 #pragma unroll
       for (int k = 0; k < 3; k++) opt.out_normal[idx * 3 + k] = nm[k] / dn;
     }
-  } else if (opt.out_normal) {
+  } else if (FULL && opt.out_normal) {
     opt.out_normal[idx * 3] = 0.f; opt.out_normal[idx * 3 + 1] = 0.f; opt.out_normal[idx * 3 + 2] = 0.f;
   }
   if (out_color) { out_color[idx * 3] = col[0]; out_color[idx * 3 + 1] = col[1]; out_color[idx * 3 + 2] = col[2]; }
@@ -731,7 +829,8 @@ FPB_EXPORT size_t fpb_render_ws_bytes(int N, int V, int S)
 {
   if (N > 65535) N = 65535;      // larger batches are rendered in chunks on the same workspace
   return 2 * align256((size_t)N * V * sizeof(float4)) + align256((size_t)N * V * sizeof(int2)) +
-         align256((size_t)N * S * S * sizeof(unsigned long long));
+         align256((size_t)N * S * S * sizeof(unsigned long long) + (size_t)N * sizeof(uint32_t)) +
+         align256((size_t)N * BIG_CAP * sizeof(BigTri));
 }
 
 static int render_chunk(const fpb_mesh* mesh, const float* poses, const float* params, int N, int S, float mesh_diameter,
@@ -744,7 +843,11 @@ static int render_chunk(const fpb_mesh* mesh, const float* poses, const float* p
   float4* camd = (float4*)w; w += align256((size_t)N * V * sizeof(float4));
   int2* snap = (int2*)w; w += align256((size_t)N * V * sizeof(int2));
   unsigned long long* zbuf = (unsigned long long*)w;
-  FPB_CUDA(cudaMemsetAsync(zbuf, 0xff, (size_t)N * S * S * sizeof(unsigned long long), st));
+  uint32_t* bigcnt = (uint32_t*)(zbuf + (size_t)N * S * S);     // directly behind the z-buffer: one memset initialises both
+  w += align256((size_t)N * S * S * sizeof(unsigned long long) + (size_t)N * sizeof(uint32_t));
+  BigTri* bigq = (BigTri*)w;
+  FPB_CUDA(cudaMemsetAsync(zbuf, 0xff, (size_t)N * S * S * sizeof(unsigned long long) + (size_t)N * sizeof(uint32_t), st));
+  opt.bigcnt = bigcnt; opt.bigq = bigq;
   // lean mode: for large meshes the float clip / camera arrays (32 B x V x N, written once and read for a few thousand
   // visible corners) are not materialised; rasteriser and shader recompute the corners they need.  FPB_RENDER_LEAN:
   // 1 forces it (tests), 0 disables it; default: when those arrays would exceed 512 MB
@@ -763,15 +866,20 @@ static int render_chunk(const fpb_mesh* mesh, const float* poses, const float* p
   static int cull_min = -1;
   if (cull_min < 0) { const char* e = getenv("FPB_RASTER_CULL_MIN"); cull_min = e ? atoi(e) : 4; }
   if ((long long)F >= (long long)cull_min * S * S)
-    raster_cull_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, mesh->pos, params, S, zbuf);
+    raster_cull_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, mesh->pos, params, S, zbuf, bigcnt, bigq);
   else
-    raster_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, mesh->pos, params, S, zbuf);
+    raster_kernel<<<dim3(fpb_cdiv(F, RASTER_FACES), N), 256, 0, st>>>(mesh->faces, F, V, clip, snap, mesh->pos, params, S, zbuf, bigcnt, bigq);
   FPB_LAUNCH_CHECK();
   const float radius = mesh_diameter / 2.0f, inv_radius = 1.0f / radius;
   const dim3 blocks(fpb_cdiv(S, 32), fpb_cdiv(S, 8), N), threads(32, 8);
+  const bool full = opt.out_normal || !opt.use_light || opt.w_ambient != 0.8f || opt.w_diffuse != 0.5f;
 #define LAUNCH_SHADE(BF, LN)                                                                                          \
-  shade_kernel<BF, LN><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, params, N, S, inv_radius, zthr, out_A, \
-                                                   out_pitch, out_xoff, out_color, out_xyz, out_tri, opt)
+  do {                                                                                                                \
+    if (full) shade_kernel<BF, LN, true><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, params, N, S, inv_radius, zthr, \
+                                                                     out_A, out_pitch, out_xoff, out_color, out_xyz, out_tri, opt); \
+    else shade_kernel<BF, LN, false><<<blocks, threads, 0, st>>>(*mesh, clip, camd, zbuf, poses, params, N, S, inv_radius, zthr, \
+                                                                 out_A, out_pitch, out_xoff, out_color, out_xyz, out_tri, opt); \
+  } while (0)
   if (a_is_bf16 == 1)      { if (lean) LAUNCH_SHADE(1, true); else LAUNCH_SHADE(1, false); }
   else if (a_is_bf16 == 2) { if (lean) LAUNCH_SHADE(2, true); else LAUNCH_SHADE(2, false); }
   else                     { if (lean) LAUNCH_SHADE(0, true); else LAUNCH_SHADE(0, false); }
@@ -795,7 +903,7 @@ FPB_EXPORT int fpb_render_crops_ex(const fpb_mesh* mesh, const float* poses, con
   for (int n0 = 0; n0 < N; n0 += MAX_N_PER_LAUNCH) {
     const int n = (N - n0) < MAX_N_PER_LAUNCH ? (N - n0) : MAX_N_PER_LAUNCH;
     const size_t px = (size_t)n0 * S * S;
-    ShadeOpts opt = {use_light, w_ambient, w_diffuse, out_normal ? out_normal + px * 3 : nullptr};
+    ShadeOpts opt = {use_light, w_ambient, w_diffuse, out_normal ? out_normal + px * 3 : nullptr, nullptr, nullptr};
     const int rc = render_chunk(mesh, poses + (size_t)n0 * 16, params + (size_t)n0 * FPB_CROP_STRIDE, n, S, mesh_diameter, zthr,
                                 ws, (char*)out_A + (size_t)n0 * S * out_pitch * 8 * esz, a_is_bf16, out_pitch, out_xoff,
                                 out_color ? out_color + px * 3 : nullptr, out_xyz ? out_xyz + px * 3 : nullptr,
