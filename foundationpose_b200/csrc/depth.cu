@@ -6,6 +6,9 @@
 //   depth2xyzmap / _batch          src/Utils.py:399-438
 //   guess_translation              src/estimater.py:137-156
 #include "common.cuh"
+#include <cooperative_groups.h>
+#include <stdlib.h>
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -222,6 +225,137 @@ __global__ void __launch_bounds__(ST) mask_stats_kernel(const float* __restrict_
   }
 }
 
+// ---- the same statistics on a thread-block cluster of 8 CTAs (8192 threads) ----
+// The one-CTA kernel above took 79 us at 640 x 480 -- rank-redundant fixed cost of every register(), 1.2 % of the 8-GPU
+// step.  Here the mask scan and every radix pass are spread over the cluster: each CTA counts its slice into its own
+// shared-memory histogram, the non-empty bins are added to CTA 0's histogram through distributed shared memory, CTA 0
+// picks the digit and the other CTAs read it back from its shared memory.  Integer counts: the result is identical.
+constexpr int MS_CL = 8;
+
+__device__ uint32_t radix_select_cluster(cg::cluster_group& cluster, const float* depth, const uint8_t* mask, int W, int u0,
+                                         int v0, int bw, int bh, uint32_t rank, uint32_t* hist, uint32_t* hist0, uint32_t* sh,
+                                         const uint32_t* sh0)
+{
+  const unsigned crank = cluster.block_rank();
+  uint32_t prefix = 0, pmask = 0;
+  const int n = bw * bh;
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    for (int i = threadIdx.x; i < 256; i += ST) hist[i] = 0;
+    cluster.sync();                                            // CTA 0's histogram is clear (and sh of the last pass consumed)
+    __shared__ uint32_t local[256];
+    for (int i = threadIdx.x; i < 256; i += ST) local[i] = 0;
+    __syncthreads();
+    for (int i = crank * ST + threadIdx.x; i < n; i += MS_CL * ST) {
+      const int r = i / bw;
+      float d;
+      if (px_valid(depth, mask, (v0 + r) * W + u0 + (i - r * bw), d)) {
+        uint32_t b = __float_as_uint(d);
+        if ((b & pmask) == prefix) atomicAdd(&local[(b >> shift) & 255u], 1u);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < 256 && local[threadIdx.x]) atomicAdd(hist0 + threadIdx.x, local[threadIdx.x]);   // DSMEM (CTA 0: its own)
+    cluster.sync();
+    if (crank == 0 && threadIdx.x < 32) {                       // warp 0 of CTA 0: first bin whose inclusive prefix count exceeds the rank
+      const int lane = threadIdx.x;
+      uint32_t c[8], tot = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) { c[k] = hist[lane * 8 + k]; tot += c[k]; }
+      uint32_t incl = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      const uint32_t excl = incl - tot;
+      if (excl <= rank && rank < incl) {
+        uint32_t a = excl;
+        int k = 0;
+        for (; k < 8; k++) {
+          if (a + c[k] > rank) break;
+          a += c[k];
+        }
+        sh[0] = (uint32_t)(lane * 8 + k);
+        sh[1] = rank - a;
+      }
+    }
+    cluster.sync();
+    prefix |= sh0[0] << shift;
+    pmask |= 255u << shift;
+    rank = sh0[1];
+  }
+  cluster.sync();                                              // nobody still reads CTA 0's sh when the next select starts
+  return prefix;
+}
+
+__global__ void __cluster_dims__(MS_CL, 1, 1) __launch_bounds__(ST)
+mask_stats_cluster_kernel(const float* __restrict__ depth, const uint8_t* __restrict__ mask, int H, int W, int32_t* out_i,
+                          float* out_f)
+{
+  cg::cluster_group cluster = cg::this_cluster();
+  __shared__ uint32_t hist[256];
+  __shared__ uint32_t sh[2];
+  __shared__ int s_box[6];                                     // umin, umax, vmin, vmax, nmask, nvalid
+  const unsigned crank = cluster.block_rank();
+  uint32_t* hist0 = cluster.map_shared_rank(hist, 0);
+  const uint32_t* sh0 = cluster.map_shared_rank(sh, 0);
+  int* box0 = cluster.map_shared_rank(s_box, 0);
+  const int n = H * W;
+  if (threadIdx.x == 0) { s_box[0] = W; s_box[1] = -1; s_box[2] = H; s_box[3] = -1; s_box[4] = 0; s_box[5] = 0; }
+  cluster.sync();
+  int umin = W, umax = -1, vmin = H, vmax = -1, nm = 0, nv = 0;
+  auto visit = [&](int i) {
+    const int v = i / W, u = i - v * W;
+    umin = min(umin, u); umax = max(umax, u); vmin = min(vmin, v); vmax = max(vmax, v);
+    nm++;
+    if (depth[i] >= 0.001f) nv++;
+  };
+  const int gt = crank * ST + threadIdx.x, gs = MS_CL * ST;
+  const int head = min(n, (int)((16 - ((uintptr_t)mask & 15)) & 15));       // bytes before the first 16-byte boundary
+  const int nvec = (n - head) / 16;
+  for (int i = gt; i < head; i += gs)
+    if (mask[i]) visit(i);
+  const uint4* mv = reinterpret_cast<const uint4*>(mask + head);
+  for (int q = gt; q < nvec; q += gs) {
+    const uint4 m = __ldg(mv + q);
+    if ((m.x | m.y | m.z | m.w) == 0u) continue;
+    const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if ((w[k >> 2] >> ((k & 3) * 8)) & 255u) visit(head + q * 16 + k);
+  }
+  for (int i = head + nvec * 16 + gt; i < n; i += gs)
+    if (mask[i]) visit(i);
+  // warp-level reduction first, then one set of DSMEM atomics per warp
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    umin = min(umin, __shfl_xor_sync(0xffffffffu, umin, o)); umax = max(umax, __shfl_xor_sync(0xffffffffu, umax, o));
+    vmin = min(vmin, __shfl_xor_sync(0xffffffffu, vmin, o)); vmax = max(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    nm += __shfl_xor_sync(0xffffffffu, nm, o); nv += __shfl_xor_sync(0xffffffffu, nv, o);
+  }
+  if ((threadIdx.x & 31) == 0 && nm > 0) {
+    atomicMin(box0 + 0, umin); atomicMax(box0 + 1, umax); atomicMin(box0 + 2, vmin); atomicMax(box0 + 3, vmax);
+    atomicAdd(box0 + 4, nm); atomicAdd(box0 + 5, nv);
+  }
+  cluster.sync();
+  const int b_umin = box0[0], b_umax = box0[1], b_vmin = box0[2], b_vmax = box0[3], nmask = box0[4], nvalid = box0[5];
+  float m0 = 0.0f, m1 = 0.0f;
+  if (nvalid > 0) {                                            // cluster-uniform
+    const int bw = b_umax - b_umin + 1, bh = b_vmax - b_vmin + 1;
+    uint32_t a = radix_select_cluster(cluster, depth, mask, W, b_umin, b_vmin, bw, bh, (uint32_t)((nvalid - 1) / 2), hist, hist0, sh, sh0);
+    uint32_t b = (nvalid & 1) ? a
+                              : radix_select_cluster(cluster, depth, mask, W, b_umin, b_vmin, bw, bh, (uint32_t)(nvalid / 2), hist, hist0, sh, sh0);
+    m0 = __uint_as_float(a);
+    m1 = __uint_as_float(b);
+  }
+  if (crank == 0 && threadIdx.x == 0) {
+    out_i[0] = b_umin; out_i[1] = b_umax; out_i[2] = b_vmin; out_i[3] = b_vmax;
+    out_i[4] = nmask; out_i[5] = nvalid;
+    out_f[0] = m0; out_f[1] = m1;
+  }
+  cluster.sync();                                              // CTA 0's shared memory stays alive until every CTA has read it
+}
+
 }  // namespace
 
 FPB_EXPORT int fpb_erode_depth_f32(const float* in, float* out, int H, int W, int radius, float diff_thres,
@@ -258,7 +392,10 @@ FPB_EXPORT int fpb_mask_depth_stats(const float* depth, const uint8_t* mask, int
                                     float* out_f32, void* stream)
 {
   FPB_CHECK_ARG(depth && mask && out_i32 && out_f32 && H > 0 && W > 0);
-  mask_stats_kernel<<<1, ST, 0, (cudaStream_t)stream>>>(depth, mask, H, W, out_i32, out_f32);
+  static int one_cta = -1;        // FPB_MASK_STATS_1CTA=1: the one-block kernel (kept as the reference for the cluster version)
+  if (one_cta < 0) { const char* e = getenv("FPB_MASK_STATS_1CTA"); one_cta = e ? atoi(e) : 0; }
+  if (one_cta) mask_stats_kernel<<<1, ST, 0, (cudaStream_t)stream>>>(depth, mask, H, W, out_i32, out_f32);
+  else mask_stats_cluster_kernel<<<MS_CL, ST, 0, (cudaStream_t)stream>>>(depth, mask, H, W, out_i32, out_f32);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }

@@ -370,11 +370,89 @@ __global__ void f32_to_act_kernel(const float* __restrict__ in, act_t* __restric
   if (i < n) out[i] = f2act(in[i]);
 }
 
+// Plain fp32 GEMMs with few rows (ScoreNet's cross-hypothesis attention: 252 x 512 x 1536 and smaller, score_network.py:86):
+// the 64 x 64 x 16 kernel above puts 4 x 24 blocks on 148 SMs and walks 32 dependent global round trips.  32 x 64 tiles
+// with 32-deep K steps double the blocks and halve the trips; every output is still one sequential fmaf chain over k,
+// i.e. bit-identical to ref_gemm_kernel.  (160 -> ~40 us for the whole att_cross block at L = 252.)
+constexpr int SM_ = 32, SN_ = 64, SK_ = 32;
+__global__ void __launch_bounds__(256) small_gemm_kernel(GemmProblem p)
+{
+  __shared__ float As[SK_][SM_ + 4];
+  __shared__ float Bs[SK_][SN_ + 4];
+  const int b = blockIdx.z;
+  const float* A = (const float*)p.A + (long long)(b / p.b_inner) * p.A_outer + (long long)(b % p.b_inner) * p.A_inner;
+  const float* W = (const float*)p.W + (long long)(b / p.b_inner) * p.W_outer + (long long)(b % p.b_inner) * p.W_inner;
+  const long long c_off = (long long)(b / p.b_inner) * p.C_outer + (long long)(b % p.b_inner) * p.C_inner;
+  const int m0 = blockIdx.x * SM_, n0 = blockIdx.y * SN_;
+  const int tid = threadIdx.x;
+  const int ar = tid >> 3, ak = (tid & 7) * 4;          // A loader: row 0..31, k offset 0..28
+  const int wr = tid >> 3, wk = (tid & 7) * 4;          // W loader: rows wr and wr + 32
+  const int ty = tid >> 4, tx = tid & 15;               // outputs: rows ty*2 + {0,1}, columns tx*4 + {0..3}
+  float acc[2][4];
+#pragma unroll
+  for (int i = 0; i < 2; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j] = 0.0f;
+  auto fetch = [&](int k0, float4& av, float4& w0, float4& w1) {
+    av = make_float4(0.f, 0.f, 0.f, 0.f); w0 = av; w1 = av;
+    if (m0 + ar < p.M && k0 + ak < p.K) av = *reinterpret_cast<const float4*>(A + (long long)(m0 + ar) * p.pix_pitch + k0 + ak);
+    if (k0 + wk < p.K) {
+      if (n0 + wr < p.N) w0 = *reinterpret_cast<const float4*>(W + (long long)(n0 + wr) * p.ldw + k0 + wk);
+      if (n0 + wr + 32 < p.N) w1 = *reinterpret_cast<const float4*>(W + (long long)(n0 + wr + 32) * p.ldw + k0 + wk);
+    }
+  };
+  float4 av, w0, w1;
+  fetch(0, av, w0, w1);
+  for (int k0 = 0; k0 < p.K; k0 += SK_) {
+    As[ak + 0][ar] = av.x; As[ak + 1][ar] = av.y; As[ak + 2][ar] = av.z; As[ak + 3][ar] = av.w;
+    Bs[wk + 0][wr] = w0.x; Bs[wk + 1][wr] = w0.y; Bs[wk + 2][wr] = w0.z; Bs[wk + 3][wr] = w0.w;
+    Bs[wk + 0][wr + 32] = w1.x; Bs[wk + 1][wr + 32] = w1.y; Bs[wk + 2][wr + 32] = w1.z; Bs[wk + 3][wr + 32] = w1.w;
+    __syncthreads();
+    if (k0 + SK_ < p.K) fetch(k0 + SK_, av, w0, w1);
+#pragma unroll
+    for (int kk = 0; kk < SK_; kk++) {
+      const float a0 = As[kk][ty * 2], a1 = As[kk][ty * 2 + 1];
+      const float4 w = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      acc[0][0] = fmaf(a0, w.x, acc[0][0]); acc[0][1] = fmaf(a0, w.y, acc[0][1]);
+      acc[0][2] = fmaf(a0, w.z, acc[0][2]); acc[0][3] = fmaf(a0, w.w, acc[0][3]);
+      acc[1][0] = fmaf(a1, w.x, acc[1][0]); acc[1][1] = fmaf(a1, w.y, acc[1][1]);
+      acc[1][2] = fmaf(a1, w.z, acc[1][2]); acc[1][3] = fmaf(a1, w.w, acc[1][3]);
+    }
+    __syncthreads();
+  }
+  const int nst = p.n_valid > 0 ? p.n_valid : p.N;
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const int mm = m0 + ty * 2 + i;
+    if (mm >= p.M) continue;
+    const long long orow = (long long)mm * p.ldc + c_off;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int nn = n0 + tx * 4 + j;
+      if (nn >= nst) continue;
+      float v = acc[i][j] * p.alpha;
+      if (p.scale) v = v * p.scale[nn] + (p.shift ? p.shift[nn] : 0.0f);
+      else if (p.shift) v += p.shift[nn];
+      if (p.residual) v += ((const float*)p.residual)[(long long)mm * p.ldr + nn];
+      if (p.relu) v = fmaxf(v, 0.0f);
+      ((float*)p.C)[orow + nn] = v;
+    }
+  }
+}
+
 }  // namespace
 
 int ref_gemm(const GemmProblem& p, cudaStream_t st)
 {
   FPB_CHECK_ARG(p.A && p.W && p.C && p.M > 0 && p.N > 0 && p.K > 0 && p.K % 4 == 0 && p.Cin % 4 == 0 && !p.row_shift && !p.c_transposed);
+  const bool plain = p.KH == 1 && p.KW == 1 && p.Hin == 1 && p.Win == 1 && p.Ho == 1 && p.Wo == 1 && p.stride == 1 && p.pad == 0 &&
+                     p.pad_w == 0 && p.Cin == p.K && !p.pe && !p.out_bf16 && p.m_split >= p.M && p.pix_pitch % 4 == 0 && p.ldw % 4 == 0;
+  if (plain && p.M <= 2048) {
+    dim3 g(fpb_cdiv(p.M, SM_), fpb_cdiv(p.N, SN_), p.batch);
+    small_gemm_kernel<<<g, 256, 0, st>>>(p);
+    FPB_LAUNCH_CHECK();
+    return FPB_OK;
+  }
   dim3 grid(fpb_cdiv(p.M, BM), fpb_cdiv(p.N, BN), p.batch);
   ref_gemm_kernel<<<grid, 256, 0, st>>>(p);
   FPB_LAUNCH_CHECK();

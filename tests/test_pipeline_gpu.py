@@ -54,3 +54,45 @@ def test_register_cfg4_maximum_size():
   # tracking from the registered pose on the same frame (one hypothesis, cfg-3 style call)
   pose2 = est.track_one(rgb=sc['rgb'], depth=sc['depth'], K=sc['K'], iteration=1)
   assert pose2.shape == (4, 4) and np.isfinite(pose2).all()
+
+
+def test_cfg4_render_and_refine_iteration_match_oracle():
+  """Parity AT cfg-4 size (500 k-face bent sheet, 1920x1200, the auto-selected lean + cull-then-rasterise kernels): for 4 of
+  the 1008 hypotheses the render is bit-exact against the oracle (colour, xyz, triangle ids) and one fp16 refine iteration
+  stays inside the north-star bounds (1e-3 rad, 0.1 mm) on the oracle's input poses."""
+  from foundationpose_b200 import nets, synthetic, utils as U
+  from foundationpose_b200.estimater import make_rotation_grid_host
+  from oracle import ops as oo
+  from oracle.pipeline import OracleEstimator
+  from tests.helpers import centered, mesh_np
+  sc = synthetic.make_scene(4, n_points=400000)
+  mesh, c = centered(sc)
+  grid = make_rotation_grid_host(min_n_views=40, inplane_step=15).astype(np.float32)
+  poses = grid[[3, 250, 611, 1000]].copy()
+  poses[:, :3, 3] = (sc['gt_pose'][:3, :3] @ c + sc['gt_pose'][:3, 3]).astype(np.float32)
+  S, H, W = 160, sc['H'], sc['W']
+  mnp = mesh_np(mesh)
+  cp = oo.crop_params(poses, sc['K'], sc['diameter'], 1.2, S, H, W)
+  color, xyz, tri = oo.render(poses, cp, mnp, S)
+  mt = U.make_mesh_tensors(mesh)
+  pt = torch.as_tensor(poses).cuda()
+  params = U.crop_params(pt, sc['K'], sc['diameter'], 1.2, S, H, W)
+  import os
+  os.environ.setdefault('FPB_RENDER_LEAN', '1')          # what N = 1008 selects automatically (read once per process)
+  _, ex = U.render_crops(mt, pt, params, S, sc['diameter'], 0.001, bf16=False, debug=True)
+  assert np.array_equal(ex['tri'].cpu().numpy(), tri) and (tri > 0).mean() > 0.05
+  assert np.array_equal(ex['color'].cpu().numpy(), color) and np.array_equal(ex['xyz'].cpu().numpy(), xyz)
+  sd_r, sd_s = nets.synthetic_state_dict(nets.REFINE), nets.synthetic_state_dict(nets.SCORE)
+  orc = OracleEstimator(mnp, sc['diameter'], sd_r, sd_s)
+  d = orc.preprocess(sc['depth'])
+  xyz_map = oo.depth2xyzmap(d, sc['K'])
+  ref = orc.refine_predict(sc['rgb'], xyz_map, poses, sc['K'], 1)
+  from foundationpose_b200.predict_pose_refine import PoseRefinePredictor
+  got, _ = PoseRefinePredictor(state_dict=sd_r, precision='fp16').predict(
+      rgb=sc['rgb'], depth=d, K=sc['K'], ob_in_cams=poses, xyz_map=xyz_map, mesh=mesh, mesh_tensors=mt, mesh_diameter=sc['diameter'],
+      iteration=1)
+  got = got.cpu().numpy()
+  rot = 2 * np.arcsin(np.clip(np.linalg.norm((got[:, :3, :3].astype(np.float64) - ref[:, :3, :3]).reshape(4, -1), axis=-1) / (2 * np.sqrt(2.0)), 0, 1))
+  trn = np.abs(got[:, :3, 3] - ref[:, :3, 3]).max()
+  print(f'cfg-4 size, 4 hypotheses: rot err {rot.max():.2e} rad, trans err {trn * 1e3:.4f} mm')
+  assert rot.max() < 1e-3 and trn < 1e-4

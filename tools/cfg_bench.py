@@ -27,6 +27,7 @@ def main():
   ap = argparse.ArgumentParser()
   ap.add_argument('--steps', type=int, default=5)
   ap.add_argument('--iters', type=int, default=5)
+  ap.add_argument('--precision', default='fp16', choices=['fp16', 'bf16'])
   args = ap.parse_args()
   world = int(os.environ.get('WORLD_SIZE', '1'))
   rank = int(os.environ.get('RANK', '0'))
@@ -35,7 +36,7 @@ def main():
   if world > 1:
     dist.init_process_group('nccl', device_id=torch.device('cuda', local))
   sc = synthetic.make_scene(4, n_points=400000)
-  est, _, _ = make_estimator(sc, 'bf16')
+  est, _, _ = make_estimator(sc, args.precision)
   grid = make_rotation_grid_host(min_n_views=40, inplane_step=15)
   est.rot_grid = torch.as_tensor(grid, device='cuda', dtype=torch.float)
   n = len(grid)
@@ -61,10 +62,18 @@ def main():
     t = torch.tensor([p50], device='cuda', dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     p50 = float(t[0])
+  match = None
+  if world > 1:                       # the sharded result against the unsharded register() on every rank
+    ps = step()
+    bs = int(est.best_id)
+    pu = est.register(K=sc['K'], rgb=rgb, depth=depth, ob_mask=mask, iteration=args.iters)
+    ok = torch.tensor([1.0 if (np.abs(ps - pu).max() <= 1e-4 and bs == int(est.best_id)) else 0.0], device='cuda')
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    match = bool(ok[0] > 0.5)
   if rank == 0:
     V, F = sc['mesh'].vertices.shape[0], sc['mesh'].faces.shape[0]
     print(json.dumps(dict(workload=f'cfg4: {V} vertices / {F} faces, {sc["W"]}x{sc["H"]}, {n} hypotheses, {args.iters} refine iterations',
-                          n_gpus=world, register_ms_p50=p50, hypotheses_per_s=n / (p50 / 1e3), steps=args.steps,
+                          n_gpus=world, precision=args.precision, matches_unsharded=match, register_ms_p50=p50, hypotheses_per_s=n / (p50 / 1e3), steps=args.steps,
                           sharding='hypotheses (dist.register_sharded, p2p exchange)' if world > 1 else 'none')))
   if world > 1:
     dist.destroy_process_group()
