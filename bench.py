@@ -40,9 +40,19 @@ WORKLOAD = ('cfg2: synthetic 20480-face mesh, 640x480 RGB-D, 252 hyps (42 views 
 _STDOUT = sys.stdout
 
 
+def claim_stdout():
+  """The ONE JSON line of the contract goes to the real stdout; everything else that libraries print while the estimator
+  is built goes to stderr -- including what C code writes to file descriptor 1 directly (cluster_poses' two printf lines,
+  mycpp/src/app/pybind_api.cpp:27,66; NCCL's "NCCL version ..." banner), hence the redirection at descriptor level."""
+  global _STDOUT
+  sys.stdout.flush()
+  real = os.dup(1)
+  os.dup2(2, 1)
+  _STDOUT = os.fdopen(real, 'w')
+  sys.stdout = sys.stderr
+
+
 def emit(line):
-  """The ONE JSON line of the contract goes to the real stdout; everything else the libraries print while the
-  estimator is built (e.g. cluster_poses' two printf lines, mycpp/src/app/pybind_api.cpp:27,66) goes to stderr."""
   _STDOUT.write(json.dumps(line) + '\n')
   _STDOUT.flush()
 
@@ -168,7 +178,7 @@ def time_dominant_kernel(torch, n_rep=20):
 
 
 def main():
-  sys.stdout = sys.stderr          # see emit()
+  claim_stdout()
   ap = argparse.ArgumentParser()
   ap.add_argument('--gpus', type=int, default=1)
   ap.add_argument('--exchange', default='auto', choices=['auto', 'p2p', 'nccl'], help='sharded register(): how features/poses are exchanged')

@@ -218,37 +218,49 @@ __global__ void __launch_bounds__(256) ln512_kernel(const act_t* __restrict__ x,
   }
 }
 
-// LayerNorm followed by the mean over a group's tokens (the normalised rows are never written): one block per group,
-// 8 warps stride over the tokens, fixed-order reduction over warps in shared memory (deterministic).
+// LayerNorm followed by the mean over a group's tokens (the normalised rows are never written): one block per group.
+// The summation order is EXACTLY that of the 8-CTA cluster kernel below (token t belongs to "rank" (t / 8) % 8 and warp
+// t % 8; per rank the 8 warp partials are added in warp order, the 8 rank rows in rank order), so that a hypothesis gets
+// bit-identical head outputs whether it is evaluated in a 252-hypothesis batch (this kernel) or in a 32-hypothesis
+// shard of it (cluster kernel): sharded and unsharded register() must agree exactly.
 __global__ void __launch_bounds__(256) ln512_token_mean_kernel(const act_t* __restrict__ x, const float* __restrict__ gamma,
                                                                const float* __restrict__ beta, float* __restrict__ out,
                                                                int tokens, float eps)
 {
   __shared__ float part[8][512];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float g[16], b[16], acc[16];
+  float g[16], b[16];
   ln512_params(gamma, beta, lane, g, b);
-#pragma unroll
-  for (int i = 0; i < 16; i++) acc[i] = 0.0f;
   const act_t* xg = x + (long long)blockIdx.x * tokens * 512;
-  for (int t = warp; t < tokens; t += 8) {
-    Ln512 r;
-    r.load(xg + (long long)t * 512, lane);
-    r.normalize(g, b, eps);
+  float total[2] = {0.0f, 0.0f};                    // columns threadIdx.x and threadIdx.x + 256
+  for (int rank = 0; rank < 8; rank++) {
+    float acc[16];
 #pragma unroll
-    for (int i = 0; i < 16; i++) acc[i] += r.v[i];
+    for (int i = 0; i < 16; i++) acc[i] = 0.0f;
+    for (int t = rank * 8 + warp; t < tokens; t += 64) {
+      Ln512 r;
+      r.load(xg + (long long)t * 512, lane);
+      r.normalize(g, b, eps);
+#pragma unroll
+      for (int i = 0; i < 16; i++) acc[i] += r.v[i];
+    }
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+#pragma unroll
+      for (int i = 0; i < 8; i++) part[warp][h * 256 + lane * 8 + i] = acc[h * 8 + i];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      const int c = threadIdx.x + k * 256;
+      float s = 0.0f;
+#pragma unroll
+      for (int w = 0; w < 8; w++) s += part[w][c];
+      total[k] += s;
+    }
+    __syncthreads();
   }
-#pragma unroll
-  for (int h = 0; h < 2; h++)
-#pragma unroll
-    for (int i = 0; i < 8; i++) part[warp][h * 256 + lane * 8 + i] = acc[h * 8 + i];
-  __syncthreads();
-  for (int c = threadIdx.x; c < 512; c += 256) {
-    float s = 0.0f;
-#pragma unroll
-    for (int w = 0; w < 8; w++) s += part[w][c];
-    out[(long long)blockIdx.x * 512 + c] = s / (float)tokens;
-  }
+  out[(long long)blockIdx.x * 512 + threadIdx.x] = total[0] / (float)tokens;
+  out[(long long)blockIdx.x * 512 + threadIdx.x + 256] = total[1] / (float)tokens;
 }
 
 // Small batches (track_one: one group; 8-GPU shards: 32 groups): a cluster of 8 CTAs per group, each CTA takes an

@@ -250,3 +250,27 @@ def test_head_gain_sweep_error_against_update_magnitude(scene2, gain, precision)
     assert er < ROT_BOUND and et < TRANS_BOUND, (gain, er, et)
   else:
     assert er < 1e-2 and et < 1e-3, (gain, er, et)      # reported; bf16 is not the default operand type
+
+
+def test_hypothesis_shards_reproduce_the_full_batch_bit_for_bit(scene2, trace, setup):
+  """What makes the hypothesis-sharded register() (dist.register_sharded, 8 ranks x 32 / 31 hypotheses) equal the unsharded
+  one EXACTLY, checked on one GPU: a hypothesis refined / encoded inside a 32-hypothesis shard gets bit-identical poses
+  and ScoreNet features to the same hypothesis inside the 252-hypothesis batch (no kernel's arithmetic depends on the
+  batch it runs in; the small-batch cluster kernels sum in the same order as the large-batch ones)."""
+  from foundationpose_b200.dist import shard_bounds
+  est, _, _, d, xyz = setup
+  sc = scene2
+  pin = trace['it2_poses_in']
+  kw = dict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=sc['rgb'], depth=d, K=sc['K'], mesh_diameter=est.diameter)
+  full, _ = est.refiner.predict(ob_in_cams=pin, xyz_map=xyz, iteration=2, **kw)
+  feats = est.scorer.extract_features(sc['rgb'], d, sc['K'], full, mesh=est.mesh, mesh_tensors=est.mesh_tensors,
+                                      mesh_diameter=est.diameter).clone()
+  full = full.clone()
+  for world in (8, 3):
+    for rank in range(world):
+      lo, hi = shard_bounds(252, rank, world)
+      part, _ = est.refiner.predict(ob_in_cams=pin[lo:hi], xyz_map=xyz, iteration=2, **kw)
+      assert torch.equal(part, full[lo:hi]), (est.precision, world, rank)
+      f = est.scorer.extract_features(sc['rgb'], d, sc['K'], part, mesh=est.mesh, mesh_tensors=est.mesh_tensors,
+                                      mesh_diameter=est.diameter)
+      assert torch.equal(f, feats[lo:hi]), (est.precision, world, rank)
