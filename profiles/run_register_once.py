@@ -10,7 +10,7 @@ from bench import make_estimator, ITERS  # noqa: E402
 from foundationpose_b200 import synthetic  # noqa: E402
 
 scene = synthetic.make_scene(2)
-est, _, _ = make_estimator(scene, os.environ.get('FPB_PRECISION', 'bf16'))
+est, _, _ = make_estimator(scene, os.environ.get('FPB_PRECISION', 'fp16'))
 d_rgb, d_depth, d_mask = (torch.as_tensor(scene[k]).cuda() for k in ('rgb', 'depth', 'mask'))
 for _ in range(2):
   est.register(K=scene['K'], rgb=d_rgb, depth=d_depth, ob_mask=d_mask, iteration=ITERS)

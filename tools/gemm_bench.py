@@ -17,6 +17,9 @@ LAYERS = {
 }
 
 
+DT = torch.float16
+
+
 def main():
   ap = argparse.ArgumentParser()
   ap.add_argument('--modes', default='2,3')
@@ -24,8 +27,12 @@ def main():
   ap.add_argument('--reps', type=int, default=10)
   ap.add_argument('--nhyp', type=int, default=252)
   ap.add_argument('--no-flush', action='store_true')
+  ap.add_argument('--dtype', default='fp16', choices=['fp16', 'bf16'], help='operand type of the tcgen05 kernels')
   ap.add_argument('--custom', default='', help='extra layer: name:ipn,H,Cin,Cout,k,stride,res,relu (repeat with ;)')
   a = ap.parse_args()
+  global DT
+  DT = torch.float16 if a.dtype == 'fp16' else torch.bfloat16
+  check(lib().fpb_debug_set_precision(2 if a.dtype == 'fp16' else 1))
   for spec in filter(None, a.custom.split(';')):
     nm, v = spec.split(':')
     LAYERS[nm] = tuple(int(t) for t in v.split(','))
@@ -39,10 +46,10 @@ def main():
     pad = (k - 1) // 2
     Ho = (H + 2 * pad - k) // stride + 1
     M, K = nimg * Ho * Ho, k * k * Cin
-    x = torch.randn(nimg, H, H, Cin, device='cuda').bfloat16()
-    w = (torch.randn(Cout, K, device='cuda') / K ** 0.5).bfloat16()
-    out = torch.empty(M, Cout, device='cuda', dtype=torch.bfloat16)
-    r = torch.randn(M, Cout, device='cuda').bfloat16() if res else None
+    x = torch.randn(nimg, H, H, Cin, device='cuda').to(DT)
+    w = (torch.randn(Cout, K, device='cuda') / K ** 0.5).to(DT)
+    out = torch.empty(M, Cout, device='cuda', dtype=DT)
+    r = torch.randn(M, Cout, device='cuda').to(DT) if res else None
     sc = torch.ones(Cout, device='cuda'); sh = torch.zeros(Cout, device='cuda')
     for mode in [int(m) for m in a.modes.split(',')]:
       if mode == 4 and Cout > 128 and not (k == 1 and K <= 512 and Cout % 128 == 0):
@@ -75,9 +82,9 @@ def stem(a):
   """7x7 stem as a 7x1 conv over wide pixels of the row-padded input (tests/test_nets_gpu.py::test_first_conv_7x7_padded_layout)"""
   flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
   n = 2 * a.nhyp
-  x = torch.randn(n, 160, 168, 8, device='cuda').bfloat16()
-  w = (torch.randn(64, 448, device='cuda') / 20).bfloat16()
-  out = torch.empty(n * 6400, 64, device='cuda', dtype=torch.bfloat16)
+  x = torch.randn(n, 160, 168, 8, device='cuda').to(DT)
+  w = (torch.randn(64, 448, device='cuda') / 20).to(DT)
+  out = torch.empty(n * 6400, 64, device='cuda', dtype=DT)
   sc = torch.ones(64, device='cuda'); sh = torch.zeros(64, device='cuda')
   for mode in [int(m) for m in a.modes.split(',')]:
     def launch():   # mode 5 (dedicated stem kernel) includes the debug entry's weight repack + cudaMalloc: use tools/stem_bench.py
