@@ -40,6 +40,7 @@ _SIGS = {
   'fpb_pose_update': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, vp, vp]),
   'fpb_pose_update_ex': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, ci, ci, vp, vp, ci, vp, vp]),
   'fpb_pose_update_deltas': (ci, [vp, vp, vp, ci, cf, cf, vp, ci, ci, ci, vp, vp, ci, vp, vp, vp, vp]),
+  'fpb_rank_poses': (ci, [vp, vp, vp, ci, vp, vp, vp, vp, vp]),
   'fpb_net_create': (ci, [vp, ci, ci, vp, sz, vp]),
   'fpb_net_destroy': (ci, [vp]),
   'fpb_net_ws_bytes': (sz, [ci, ci, ci]),

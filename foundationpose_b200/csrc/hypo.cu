@@ -282,6 +282,67 @@ FPB_EXPORT int fpb_hypotheses_from_stats(const int32_t* stats_i32, const float* 
   return FPB_OK;
 }
 
+// ---- ranking tail of register(): src/estimater.py:221-236 (argsort(descending) of the scores, gather of poses and
+//      scores, best pose @ tf_to_centered_mesh) in one block: bitonic sort of (score, index) keys in shared memory;
+//      equal scores keep their input order (index ascending) ----
+constexpr int RANK_MAX = 4096;
+__global__ void __launch_bounds__(1024) rank_poses_kernel(const float* __restrict__ scores, const float* __restrict__ poses,
+                                                           const float* __restrict__ tf, int N, int P, long long* __restrict__ out_ids,
+                                                           float* __restrict__ out_scores, float* __restrict__ out_poses,
+                                                           float* __restrict__ out_best)
+{
+  extern __shared__ unsigned long long keys[];      // P = next power of two >= N
+  for (int i = threadIdx.x; i < P; i += blockDim.x) {
+    unsigned long long k = ~0ull;                    // padding sorts last
+    if (i < N) {
+      uint32_t u = __float_as_uint(scores[i]);
+      u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);          // ascending unsigned order == ascending float order
+      k = ((unsigned long long)(~u) << 32) | (uint32_t)i;       // descending score, then ascending index (NaN-free scores)
+    }
+    keys[i] = k;
+  }
+  __syncthreads();
+  for (int size = 2; size <= P; size <<= 1)
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = threadIdx.x; i < P; i += blockDim.x) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const bool up = (i & size) == 0;
+          const unsigned long long a = keys[i], b = keys[j];
+          if ((a > b) == up) { keys[i] = b; keys[j] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  for (int r = threadIdx.x; r < N; r += blockDim.x) {
+    const int src = (int)(uint32_t)(keys[r] & 0xffffffffu);
+    out_ids[r] = src;
+    out_scores[r] = scores[src];
+    for (int e = 0; e < 16; e++) out_poses[(size_t)r * 16 + e] = poses[(size_t)src * 16 + e];
+  }
+  if (threadIdx.x < 16 && out_best) {                // best = poses[ids[0]] @ tf  (fp32, k ascending like a GEMM row)
+    const int src = (int)(uint32_t)(keys[0] & 0xffffffffu);
+    const int i = threadIdx.x >> 2, j = threadIdx.x & 3;
+    const float* Tp = poses + (size_t)src * 16;
+    float s = 0.0f;
+    for (int k = 0; k < 4; k++) s = fmaf(Tp[i * 4 + k], tf[k * 4 + j], s);
+    out_best[threadIdx.x] = s;
+  }
+}
+
+FPB_EXPORT int fpb_rank_poses(const float* scores, const float* poses, const float* tf16, int N, long long* out_ids,
+                              float* out_scores, float* out_poses, float* out_best16, void* stream)
+{
+  FPB_CHECK_ARG(scores && poses && tf16 && out_ids && out_scores && out_poses && N > 0);
+  if (N > RANK_MAX) { fpb_set_error("fpb_rank_poses: at most %d hypotheses per call", RANK_MAX); return FPB_ERR_UNSUPPORTED; }
+  int P = 1;
+  while (P < N) P <<= 1;
+  rank_poses_kernel<<<1, 1024, (size_t)P * sizeof(unsigned long long), (cudaStream_t)stream>>>(scores, poses, tf16, N, P, out_ids, out_scores,
+                                                                                            out_poses, out_best16);
+  FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
 // ---- small multi-destination store: the refined poses of this rank's hypotheses into every rank's pose table
 //      (peer-mapped symmetric memory), the pose half of the sharded register()'s exchange ----
 namespace {

@@ -157,8 +157,8 @@ def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, excha
     feats = all_gather_ragged(feats, n_total, world, group)
     poses = all_gather_ragged(poses.reshape(-1, 16), n_total, world, group).reshape(-1, 4, 4)
   scores = est.scorer.score_from_features(feats)
-  ids = scores.argsort(descending=True)
-  best = (poses[ids[0]] @ est.get_tf_to_centered_mesh()).data.cpu().numpy()          # the only synchronisation
+  ids, scores_sorted, poses_sorted, best_t = U.rank_poses(scores, poses, est.get_tf_to_centered_mesh(clone=False))
+  best = best_t.data.cpu().numpy()                                                    # the only synchronisation
   oi, of = est._stats_host[0].numpy(), est._stats_host[1].numpy()
   stats = (int(oi[0]), int(oi[1]), int(oi[2]), int(oi[3]), int(oi[4]), int(oi[5]), of[0], of[1])
   if stats[5] < 4:
@@ -167,7 +167,7 @@ def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, excha
     return pose
   est.H, est.W = depth_t.shape[:2]                   # the attributes register() leaves behind (src/estimater.py:192-240)
   est.K, est.ob_id, est.ob_mask = K, ob_id, ob_mask
-  est.poses, est.scores = poses[ids], scores[ids]
+  est.poses, est.scores = poses_sorted, scores_sorted
   est.pose_last, est.best_id = est.poses[0], ids[0]
   return best
 

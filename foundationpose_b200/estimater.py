@@ -124,14 +124,14 @@ class FoundationPose:
       self.symmetry_tfs = torch.as_tensor(symmetry_tfs, device=dev, dtype=torch.float)
     logging.info('reset done')
 
-  def get_tf_to_centered_mesh(self):
+  def get_tf_to_centered_mesh(self, clone=True):
     # cached per model_center: building it costs a pageable host-to-device copy, which would synchronise register()
     key = tuple(np.asarray(self.model_center, dtype=np.float64).reshape(-1).tolist())
     if getattr(self, '_tf_to_center', None) is None or self._tf_to_center[0] != key:
       tf_to_center = torch.eye(4, dtype=torch.float, device='cuda')
       tf_to_center[:3, 3] = -torch.as_tensor(self.model_center, device='cuda', dtype=torch.float)
       self._tf_to_center = (key, tf_to_center)
-    return self._tf_to_center[1].clone()
+    return self._tf_to_center[1].clone() if clone else self._tf_to_center[1]
 
   def to_device(self, s='cuda:0'):
     for k in self.__dict__:
@@ -191,10 +191,8 @@ class FoundationPose:
     scores, _ = self.scorer.predict(mesh=self.mesh, rgb=rgb_t, depth=depth_t, K=K, ob_in_cams=poses, normal_map=None,
                                     mesh_tensors=self.mesh_tensors, glctx=self.glctx, mesh_diameter=self.diameter,
                                     get_vis=False)
-    ids = torch.as_tensor(scores).argsort(descending=True)
-    scores = scores[ids]
-    poses = poses[ids]
-    best_pose = (poses[0] @ self.get_tf_to_centered_mesh()).data.cpu().numpy()        # the only synchronisation
+    ids, scores, poses, best = U.rank_poses(scores, poses, self.get_tf_to_centered_mesh(clone=False))
+    best_pose = best.data.cpu().numpy()                                                # the only synchronisation
     oi, of = self._stats_host[0].numpy(), self._stats_host[1].numpy()
     stats = (int(oi[0]), int(oi[1]), int(oi[2]), int(oi[3]), int(oi[4]), int(oi[5]), of[0], of[1])
     if stats[5] < 4:

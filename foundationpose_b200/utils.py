@@ -497,6 +497,24 @@ def pose_update(poses, trans, rot, mesh_diameter, rot_normalizer, trans_normaliz
   return out
 
 
+def rank_poses(scores, poses, tf_to_center):
+  """argsort(descending) + gathers + best pose of FoundationPose.register (src/estimater.py:221-236) in one launch.
+  Returns (ids int64 [N], scores sorted [N], poses sorted [N,4,4], best [4,4] = poses[ids[0]] @ tf_to_center)."""
+  scores = scores.contiguous()
+  poses = poses.reshape(-1, 4, 4).contiguous()
+  N = len(scores)
+  if N > 4096:                    # beyond the one-block kernel: library sort
+    ids = scores.argsort(descending=True, stable=True)
+    return ids, scores[ids], poses[ids], poses[ids[0]] @ tf_to_center
+  ids = torch.empty(N, dtype=torch.long, device=scores.device)
+  s_out = torch.empty_like(scores)
+  p_out = torch.empty_like(poses)
+  best = torch.empty((4, 4), dtype=torch.float, device=scores.device)
+  check(lib().fpb_rank_poses(ptr(scores), ptr(poses), ptr(tf_to_center.contiguous()), N, ptr(ids), ptr(s_out), ptr(p_out), ptr(best),
+                             stream()))
+  return ids, s_out, p_out, best
+
+
 def nvdiffrast_render(K=None, H=None, W=None, ob_in_cams=None, glctx=None, context='cuda', get_normal=False,
                       mesh_tensors=None, mesh=None, projection_mat=None, bbox2d=None, output_size=None, use_light=False,
                       light_color=None, light_dir=np.array([0, 0, 1]), light_pos=np.array([0, 0, 0]), w_ambient=0.8,

@@ -155,6 +155,12 @@ int fpb_pose_update_deltas(const float* poses, const float* trans, const float* 
                            const float* crop_params, const float* K9_h, int S, float* out_poses,
                            float* out_trans_delta, float* out_rot_delta, void* stream);
 
+/* ---- ranking tail of register(): src/estimater.py:221-236 -- ids = argsort(scores, descending) (equal scores keep
+ *      their input order), out_scores = scores[ids], out_poses = poses[ids], out_best16 = poses[ids[0]] @ tf16
+ *      (tf16 = get_tf_to_centered_mesh(), device; out_best16 may be NULL).  N <= 4096 (one block, bitonic sort). ---- */
+int fpb_rank_poses(const float* scores, const float* poses, const float* tf16, int N, long long* out_ids,
+                   float* out_scores, float* out_poses, float* out_best16, void* stream);
+
 /* ---- networks: learning/models/refine_network.py:26-93, score_network.py:27-90.
  *      Weights arrive as a flat host blob produced by foundationpose_b200.nets.pack_* (BN folded). ---- */
 typedef struct fpb_net fpb_net;

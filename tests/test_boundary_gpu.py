@@ -229,3 +229,19 @@ def test_render_and_warp_above_the_launch_limit(scene1):
   B7 = U.warp_crops(rgb_t, xyz_t, None, poses[:7], params[:7].contiguous(), sc['K'], S, sc['diameter'], 0, bf16=False)
   sel = torch.as_tensor(idx).cuda()
   assert torch.equal(A, A7[sel]) and torch.equal(B, B7[sel]) and float(A[-1].abs().sum()) > 0
+
+
+@pytest.mark.parametrize('N', [1, 7, 252, 1008, 4096])
+def test_rank_poses_matches_stable_descending_sort(N):
+  """src/estimater.py:221-236: argsort(descending) + gathers + best pose @ tf_to_center in one kernel; ties keep input order."""
+  from foundationpose_b200 import utils as U
+  g = torch.Generator(device='cuda').manual_seed(N)
+  scores = torch.randn(N, device='cuda', generator=g)
+  if N > 4:
+    scores[N // 2] = scores[1]; scores[N - 1] = scores[1]           # ties
+  poses = torch.randn(N, 4, 4, device='cuda', generator=g)
+  tf = torch.eye(4, device='cuda'); tf[:3, 3] = torch.tensor([0.1, -0.2, 0.3])
+  ids, s, p, best = U.rank_poses(scores, poses, tf)
+  want = torch.sort(scores, descending=True, stable=True).indices
+  assert torch.equal(ids, want) and torch.equal(s, scores[want]) and torch.equal(p, poses[want])
+  assert torch.allclose(best, poses[want[0]] @ tf, atol=1e-6)
