@@ -202,10 +202,7 @@ __global__ void __launch_bounds__(256) ln512_kernel(const act_t* __restrict__ x,
   float g[16], b[16];
   ln512_params(gamma, beta, lane, g, b);
   const long long nw = (long long)gridDim.x * 8;
-  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < rows; row += nw) {
-    Ln512 r;
-    r.load(x + row * 512, lane);
-    r.normalize(g, b, eps);
+  auto store = [&](const Ln512& r, long long row) {
     uint32_t w[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) {
@@ -215,6 +212,16 @@ __global__ void __launch_bounds__(256) ln512_kernel(const act_t* __restrict__ x,
     uint4* o = reinterpret_cast<uint4*>(out + row * 512);
     o[lane] = make_uint4(w[0], w[1], w[2], w[3]);
     o[32 + lane] = make_uint4(w[4], w[5], w[6], w[7]);
+  };
+  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < rows; row += 2 * nw) {   // two rows in flight per warp
+    Ln512 r0, r1;
+    const bool two = row + nw < rows;
+    r0.load(x + row * 512, lane);
+    if (two) r1.load(x + (row + nw) * 512, lane);
+    r0.normalize(g, b, eps);
+    if (two) r1.normalize(g, b, eps);
+    store(r0, row);
+    if (two) store(r1, row + nw);
   }
 }
 
@@ -237,12 +244,20 @@ __global__ void __launch_bounds__(256) ln512_token_mean_kernel(const act_t* __re
     float acc[16];
 #pragma unroll
     for (int i = 0; i < 16; i++) acc[i] = 0.0f;
-    for (int t = rank * 8 + warp; t < tokens; t += 64) {
-      Ln512 r;
-      r.load(xg + (long long)t * 512, lane);
-      r.normalize(g, b, eps);
+    // two rows in flight per warp (independent load -> reduce -> normalise chains); accumulated in token order
+    for (int t = rank * 8 + warp; t < tokens; t += 128) {
+      Ln512 r0, r1;
+      const bool two = t + 64 < tokens;
+      r0.load(xg + (long long)t * 512, lane);
+      if (two) r1.load(xg + (long long)(t + 64) * 512, lane);
+      r0.normalize(g, b, eps);
+      if (two) r1.normalize(g, b, eps);
 #pragma unroll
-      for (int i = 0; i < 16; i++) acc[i] += r.v[i];
+      for (int i = 0; i < 16; i++) acc[i] += r0.v[i];
+      if (two) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) acc[i] += r1.v[i];
+      }
     }
 #pragma unroll
     for (int h = 0; h < 2; h++)
@@ -282,12 +297,19 @@ ln512_token_mean_cluster_kernel(const act_t* __restrict__ x, const float* __rest
 #pragma unroll
   for (int i = 0; i < 16; i++) acc[i] = 0.0f;
   const act_t* xg = x + (long long)group * tokens * 512;
-  for (int t = (int)rank * 8 + warp; t < tokens; t += 8 * LNM_CLUSTER) {
-    Ln512 r;
-    r.load(xg + (long long)t * 512, lane);
-    r.normalize(g, b, eps);
+  for (int t = (int)rank * 8 + warp; t < tokens; t += 16 * LNM_CLUSTER) {      // two rows in flight, token order kept
+    Ln512 r0, r1;
+    const bool two = t + 8 * LNM_CLUSTER < tokens;
+    r0.load(xg + (long long)t * 512, lane);
+    if (two) r1.load(xg + (long long)(t + 8 * LNM_CLUSTER) * 512, lane);
+    r0.normalize(g, b, eps);
+    if (two) r1.normalize(g, b, eps);
 #pragma unroll
-    for (int i = 0; i < 16; i++) acc[i] += r.v[i];
+    for (int i = 0; i < 16; i++) acc[i] += r0.v[i];
+    if (two) {
+#pragma unroll
+      for (int i = 0; i < 16; i++) acc[i] += r1.v[i];
+    }
   }
 #pragma unroll
   for (int h = 0; h < 2; h++)
