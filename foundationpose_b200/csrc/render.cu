@@ -56,6 +56,30 @@ __device__ __forceinline__ void bary_zw(const float4 c0, const float4 c1, const 
   zw = fminf(fmaxf(z / w, -1.0f), 1.0f);
 }
 
+// Coverage + depth of a triangle that has a vertex behind the camera plane (w <= 0) or beyond the fixed-point range:
+// nvdiffrast clips such triangles against the frustum; the equivalent test without clipping is the 2-D homogeneous one
+// (Olano & Greer): with a_i the edge functions of the clip-space corners seen from the pixel, the pixel is inside iff
+// all a_i share the sign of their sum, the interpolated w is positive (in front of the camera) and z/w lies inside
+// the near / far planes.  Float arithmetic (no snapping, no top-left rule): exact ties on shared edges are not resolved.
+__device__ __forceinline__ bool homog_cover(const float4 c0, const float4 c1, const float4 c2, float fx, float fy, float& zw)
+{
+  float p0x = c0.x - fx * c0.w, p0y = c0.y - fy * c0.w;
+  float p1x = c1.x - fx * c1.w, p1y = c1.y - fy * c1.w;
+  float p2x = c2.x - fx * c2.w, p2y = c2.y - fy * c2.w;
+  float a0 = p1x * p2y - p1y * p2x;
+  float a1 = p2x * p0y - p2y * p0x;
+  float a2 = p0x * p1y - p0y * p1x;
+  float sum = (a0 + a1) + a2;
+  const bool pos = a0 >= 0.0f && a1 >= 0.0f && a2 >= 0.0f && sum > 0.0f;
+  const bool neg = a0 <= 0.0f && a1 <= 0.0f && a2 <= 0.0f && sum < 0.0f;
+  if (!(pos || neg)) return false;
+  float z = (c0.z * a0 + c1.z * a1) + c2.z * a2;
+  float w = (c0.w * a0 + c1.w * a1) + c2.w * a2;
+  if (!((w > 0.0f) == (sum > 0.0f)) || w == 0.0f) return false;      // interpolated w <= 0: behind the camera
+  zw = z / w;
+  return zw >= -1.0f && zw <= 1.0f;                                     // near / far clip
+}
+
 constexpr int SNAP_INVALID = INT32_MIN;   // vertex behind the camera (w <= 0) or beyond the fixed-point range
 
 // Clip-space position of one vertex (P * glcam * pose, then the crop zoom): the ONE instruction sequence used by the
@@ -256,6 +280,25 @@ __device__ __forceinline__ void raster_triangle(bool valid, int f, int i0, int i
   TriSetup t;
   t.ok = 0;
   if (valid) tri_setup(s0, s1, s2, S, t);
+  if (valid && (s0.x == SNAP_INVALID || s1.x == SNAP_INVALID || s2.x == SNAP_INVALID)) {
+    // a corner is behind the camera plane or outside the fixed-point range: if any corner is in front, the triangle may
+    // still cross the crop -> queue it for the homogeneous (clip-free) test over the whole crop (small = 2)
+    const float4 c0 = cl.get(i0), c1 = cl.get(i1), c2 = cl.get(i2);
+    if (c0.w > 0.0f || c1.w > 0.0f || c2.w > 0.0f) {
+      const uint32_t slot = atomicAdd(bigcnt, 1u) + 1u;
+      if (slot < (uint32_t)BIG_CAP) {                 // (a full queue drops it: it has no integer set-up for the sweep)
+        BigTri r;
+#pragma unroll
+        for (int e = 0; e < 3; e++) { r.X[e] = 0; r.Y[e] = 0; }
+        r.px0 = 0; r.px1 = S - 1; r.py0 = 0; r.py1 = S - 1; r.small = 2; r.face = (uint32_t)f;
+        r.c0 = c0; r.c1 = c1; r.c2 = c2;
+        const uint4* src = reinterpret_cast<const uint4*>(&r);
+        uint4* dst = reinterpret_cast<uint4*>(bigq + slot);
+#pragma unroll
+        for (int e = 0; e < 6; e++) dst[e] = src[e];
+      }
+    }
+  }
   int big = 0;
   if (t.ok) {
     int npx = (t.px1 - t.px0 + 1) * (t.py1 - t.py0 + 1);
@@ -391,12 +434,14 @@ __global__ void __launch_bounds__(256, 3) raster_cull_kernel(const int32_t* __re
     TriSetup t;
     t.ok = 0;
     if (f < F) tri_setup(sp[k][0], sp[k][1], sp[k][2], S, t);
-    const unsigned m = __ballot_sync(0xffffffffu, t.ok);
+    // survivors: a non-empty pixel box, or a corner behind the camera plane (handled by raster_triangle's clip-free path)
+    const bool keep = t.ok || (f < F && (sp[k][0].x == SNAP_INVALID || sp[k][1].x == SNAP_INVALID || sp[k][2].x == SNAP_INVALID));
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
     if (m) {
       int base = 0;
       if (lane == 0) base = atomicAdd(&q_count, __popc(m));
       base = __shfl_sync(0xffffffffu, base, 0);
-      if (t.ok) {
+      if (keep) {
         const int e = base + __popc(m & ((1u << lane) - 1u));
         q_f[e] = f;
 #pragma unroll
@@ -513,6 +558,14 @@ __device__ __noinline__ unsigned long long resolve_big_triangles(unsigned long l
         const BigTri& b = sh[k];
         if (b.px1 < rx0 || b.px0 > rx1 || b.py1 < ry0 || b.py0 > ry1) continue;     // misses this tile (block-uniform)
         if (px < b.px0 || px > b.px1 || py < b.py0 || py > b.py1) continue;
+        if (b.small == 2) {                              // clip-free homogeneous test (corner behind the camera plane)
+          float zh;
+          if (homog_cover(b.c0, b.c1, b.c2, fx, fy, zh)) {
+            const unsigned long long kk = ((unsigned long long)f2ord(zh) << 32) | b.face;
+            key = kk < key ? kk : key;
+          }
+          continue;
+        }
         bool in;
         if (b.small) {
           Tri32 q;

@@ -221,6 +221,27 @@ static inline void bary_zw(const float* c0, const float* c1, const float* c2, fl
   *zw = fminf(fmaxf(ZW, -1.0f), 1.0f);
 }
 
+/* coverage + z/w of a triangle with a corner behind the camera plane: all edge functions share the sign of their sum,
+ * interpolated w > 0, z/w inside the near / far planes (float arithmetic, no tie rule) */
+static inline int homog_cover(const float* c0, const float* c1, const float* c2, float fx, float fy, float* zw)
+{
+  float p0x = c0[0] - fx * c0[3], p0y = c0[1] - fy * c0[3];
+  float p1x = c1[0] - fx * c1[3], p1y = c1[1] - fy * c1[3];
+  float p2x = c2[0] - fx * c2[3], p2y = c2[1] - fy * c2[3];
+  float a0 = p1x * p2y - p1y * p2x;
+  float a1 = p2x * p0y - p2y * p0x;
+  float a2 = p0x * p1y - p0y * p1x;
+  float sum = (a0 + a1) + a2;
+  int pos = a0 >= 0.0f && a1 >= 0.0f && a2 >= 0.0f && sum > 0.0f;
+  int neg = a0 <= 0.0f && a1 <= 0.0f && a2 <= 0.0f && sum < 0.0f;
+  if (!(pos || neg)) return 0;
+  float z = (c0[2] * a0 + c1[2] * a1) + c2[2] * a2;
+  float w = (c0[3] * a0 + c1[3] * a1) + c2[3] * a2;
+  if (!((w > 0.0f) == (sum > 0.0f)) || w == 0.0f) return 0;
+  *zw = z / w;
+  return *zw >= -1.0f && *zw <= 1.0f;
+}
+
 /* ------------------------------------------------------------------------
  * Batched mesh render at crop resolution: restatement of nvdiffrast_render
  * (src/Utils.py:133-219) = dr.rasterize + dr.interpolate (+ dr.texture) +
@@ -275,19 +296,31 @@ ORC_API void orc_render(const float* poses, const float* mtx, const float* rtf, 
     for (int f = 0; f < F; f++) {
       const int i0 = faces[f * 3], i1 = faces[f * 3 + 1], i2 = faces[f * 3 + 2];
       const float *c0 = clip + i0 * 4, *c1 = clip + i1 * 4, *c2 = clip + i2 * 4;
-      if (!(c0[3] > 0.0f && c1[3] > 0.0f && c2[3] > 0.0f)) continue;
       float sxf[3], syf[3];
       const float* cc[3] = {c0, c1, c2};
-      int bad = 0;
+      int bad = !(c0[3] > 0.0f && c1[3] > 0.0f && c2[3] > 0.0f);
       int64_t X[3], Y[3];
-      for (int k = 0; k < 3; k++) {
+      for (int k = 0; k < 3 && !bad; k++) {
         sxf[k] = (cc[k][0] / cc[k][3]) * sub + sub;
         syf[k] = (cc[k][1] / cc[k][3]) * sub + sub;
         if (!(fabsf(sxf[k]) < 1073741824.0f) || !(fabsf(syf[k]) < 1073741824.0f)) bad = 1;
         X[k] = (int64_t)rintf(sxf[k]);
         Y[k] = (int64_t)rintf(syf[k]);
       }
-      if (bad) continue;
+      if (bad) {
+        /* a corner behind the camera plane (w <= 0) or beyond the fixed-point range: nvdiffrast clips the triangle
+         * against the frustum; the equivalent clip-free test is the 2-D homogeneous one over the whole crop */
+        if (!(c0[3] > 0.0f || c1[3] > 0.0f || c2[3] > 0.0f)) continue;
+        for (int py = 0; py < S; py++)
+          for (int px = 0; px < S; px++) {
+            float fx = (float)px * xs + xo, fy = (float)py * xs + xo;
+            float zw;
+            if (!homog_cover(c0, c1, c2, fx, fy, &zw)) continue;
+            uint64_t key = ((uint64_t)f2ord(zw) << 32) | (uint32_t)f;
+            if (key < zb[py * S + px]) zb[py * S + px] = key;
+          }
+        continue;
+      }
       int64_t area = (X[1] - X[0]) * (Y[2] - Y[0]) - (Y[1] - Y[0]) * (X[2] - X[0]);
       if (area == 0) continue;
       int a = 0, b = 1, c = 2;

@@ -239,3 +239,36 @@ def test_render_bit_exact_dense_mesh_paths(env):
                       '-k', 'test_render_bit_exact and not dense_mesh_paths'], capture_output=True, text=True,
                      env=dict(os.environ, **env), cwd=root, timeout=900)
   assert r.returncode == 0 and '2 passed' in r.stdout, r.stdout[-1500:] + r.stderr[-500:]
+
+
+@pytest.mark.parametrize('cfg', [1, 2])
+def test_render_triangles_crossing_the_camera_plane(cfg, scene1, scene2):
+  """Hypotheses so close that part of the mesh is behind the camera plane (w <= 0): nvdiffrast clips those triangles
+  against the frustum; here they take the clip-free homogeneous coverage test (render.cu homog_cover) instead of being
+  dropped.  Bit-exact against the oracle's restatement; the crossing triangles do contribute pixels."""
+  from foundationpose_b200 import utils as U
+  scene = scene1 if cfg == 1 else scene2
+  mesh, _ = centered(scene)
+  mnp = mesh_np(mesh)
+  poses, _ = hypo_poses(scene, n=6)
+  poses = poses.copy()
+  poses[:, :3, 3] = np.array([0.01, -0.005, 0.02], np.float32)           # camera inside the object's bounding sphere
+  poses[3, :3, 3] = np.array([0.0, 0.0, -0.2], np.float32)               # entirely behind the camera: nothing to draw
+  S = 160
+  cp = oo.crop_params(poses, scene['K'], scene['diameter'], 1.2, S, 480, 640)
+  color, xyz, tri = oo.render(poses, cp, mnp, S)
+  zc = (np.asarray(mnp['pos']) @ poses[0, :3, :3].T + poses[0, :3, 3])[:, 2]
+  assert (zc <= 0).any() and (zc > 0).any()                               # the mesh does straddle the camera plane
+  mt = {k: torch.as_tensor(v, device='cuda') for k, v in mnp.items()}
+  params = U.crop_params(torch.as_tensor(poses).cuda(), scene['K'], scene['diameter'], 1.2, S, 480, 640)
+  _, ex = U.render_crops(mt, torch.as_tensor(poses).cuda(), params, S, scene['diameter'], 0.001, bf16=False, debug=True)
+  assert np.array_equal(ex['tri'].cpu().numpy(), tri)
+  assert np.array_equal(ex['color'].cpu().numpy(), color) and np.array_equal(ex['xyz'].cpu().numpy(), xyz)
+  assert (tri[3] == 0).all() and (tri[0] > 0).mean() > 0.2
+  # faces that cross the plane are among the visible ones
+  faces = np.asarray(mnp['faces'])
+  crossing = ((zc[faces] <= 0).any(1)) & ((zc[faces] > 0).any(1))
+  vis = np.unique(tri[0][tri[0] > 0]) - 1
+  assert crossing.any()
+  if cfg == 1:                       # the cube's 5 cm faces reach far beyond the near plane; the blob's millimetre triangles that
+    assert crossing[vis].any()       # cross w = 0 lie entirely in front of the near plane (z < 1 mm) and are clipped away
