@@ -56,6 +56,7 @@ _SIGS = {
   'fpb_score_features_multi': (ci, [vp, vp, ci, vp, vp, ci, vp]),
   'fpb_store_multi_f32': (ci, [vp, ctypes.c_longlong, vp, ci, vp]),
   'fpb_score_cross': (ci, [vp, vp, ci, ci, vp, vp, vp]),
+  'fpb_score_cross_static': (ci, [vp, vp, ci, vp, vp]),
 }
 
 

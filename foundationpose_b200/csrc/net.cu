@@ -5,6 +5,7 @@
 // foundationpose_b200/nets.py); in bf16 mode a bf16 shadow of the blob feeds the tcgen05 kernel.
 #include "net_kernels.cuh"
 #include <stdlib.h>
+#include <mutex>
 #include <vector>
 
 namespace {
@@ -493,6 +494,48 @@ FPB_EXPORT size_t fpb_score_cross_ws_bytes(int L, int bs)
 {
   const size_t Lp = (L + 3) & ~3, R = (size_t)bs * L;
   return al(R * 3 * D * 4) + 2 * al((size_t)bs * HEADS * L * Lp * 4) + al((size_t)bs * HEADS * DH * Lp * 4) + 2 * al(R * D * 4) + 1024;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fpb_score_cross_static: fpb_score_cross for callers that cannot allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scratch of the cross-hypothesis attention (qkv, scores, probabilities, V^T, context, output rows: 5.0 MB at the
+// maximum L = 256, bs = 1) lives in a file-scope __device__ array that every GPU loading the library holds until exit.
+// In host code the array's NAME is only a host-side stand-in: the device address is resolved per device with
+// cudaGetSymbolAddress (with that device current) and that pointer is what the kernels get.
+// ---------------------------------------------------------------------------------------------
+constexpr int SCORE_CROSS_STATIC_MAX_L = 256;
+constexpr size_t SCORE_CROSS_STATIC_BYTES = 5243904;      // fpb_score_cross_ws_bytes(256, 1)
+static __device__ __align__(256) unsigned char g_score_cross_scratch[SCORE_CROSS_STATIC_BYTES];
+constexpr int SCORE_CROSS_MAX_DEVICES = 64;
+static void* g_score_cross_scratch_ptr[SCORE_CROSS_MAX_DEVICES];     // device address of the array, per device ordinal
+static std::mutex g_score_cross_mutex;
+
+FPB_EXPORT int fpb_score_cross_static(const fpb_net* net, const float* feat, int L, float* out_logits, void* stream)
+{
+  FPB_CHECK_ARG(net && net->kind == FPB_NET_SCORE && feat && out_logits && L > 0);
+  if (L > SCORE_CROSS_STATIC_MAX_L || fpb_score_cross_ws_bytes(L, 1) > SCORE_CROSS_STATIC_BYTES) {
+    fpb_set_error("fpb_score_cross_static: L = %d exceeds the static scratch (at most %d hypotheses per call); use fpb_score_cross "
+                  "with a caller-owned workspace", L, SCORE_CROSS_STATIC_MAX_L);
+    return FPB_ERR_UNSUPPORTED;
+  }
+  int dev = -1;
+  FPB_CUDA(cudaGetDevice(&dev));
+  FPB_CHECK_ARG(dev >= 0 && dev < SCORE_CROSS_MAX_DEVICES);
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_score_cross_mutex);
+    if (!g_score_cross_scratch_ptr[dev]) {           // set-up, once per device, with that device current
+      void* p = nullptr;
+      FPB_CUDA(cudaGetSymbolAddress(&p, g_score_cross_scratch));
+      g_score_cross_scratch_ptr[dev] = p;
+    }
+    scratch = g_score_cross_scratch_ptr[dev];
+  }
+  // the array keeps the previous call's contents: clear the part this call uses (nothing in the chain reads a scratch
+  // element before writing it, the memset keeps that true if the chain changes); stream-ordered, no allocation
+  FPB_CUDA(cudaMemsetAsync(scratch, 0, fpb_score_cross_ws_bytes(L, 1), (cudaStream_t)stream));
+  return fpb_score_cross(net, feat, L, 1, scratch, out_logits, stream);
 }
 
 // operand type the debug / unit-test entries below run in: FPB_PREC_BF16 (default) or FPB_PREC_FP16

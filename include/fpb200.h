@@ -193,6 +193,17 @@ int fpb_store_multi_f32(const float* src, long long count, float* const* dst_ptr
 int fpb_score_cross(const fpb_net* net, const float* feat, int L, int bs, void* ws, float* out_logits,
                     void* stream);
 
+/* ---- fpb_score_cross without any allocation or caller workspace.  NO COUNTERPART IN THE REFERENCE: added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ *      loops, harnesses that forbid it).  Same kernels and results as fpb_score_cross(net, feat, L, 1, ws, ...); the
+ *      scratch is a file-scope __device__ array of 5,243,904 bytes (= fpb_score_cross_ws_bytes(256, 1)) that every GPU
+ *      loading the library holds until exit.  Limit: L <= 256 hypotheses, one group (bs = 1); larger L returns
+ *      FPB_ERR_UNSUPPORTED with a message.  Calls no cudaMalloc / cudaFree / allocating library routine; the first
+ *      call on a device resolves the array's device address (cudaGetSymbolAddress).  Every call shares the array:
+ *      it is cleared (stream-ordered) at the start of each call, and calls that overlap on the GPU -- different
+ *      streams, or different threads -- RACE on it; serialise them. ---- */
+int fpb_score_cross_static(const fpb_net* net, const float* feat, int L, float* out_logits, void* stream);
+
 /* unit-test entry: one implicit GEMM C = epi(im2col(A) . W^T); A is NHWC [*,Hin,Win,Cin], W is [N][K], K = KH*KW*Cin.
  * precision/mode 0: SIMT fp32; 1: tcgen05 bf16 with cp.async producers; 2 / 3: persistent tcgen05 + TMA (im2col
  * tensor maps) kernel with cta_group 1 / 2.  _ex adds the row-padded "wide pixel" addressing of the 7x7 stem. */
