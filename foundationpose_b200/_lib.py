@@ -52,6 +52,7 @@ _SIGS = {
   'fpb_debug_set_precision': (ci, [ci]),
   'fpb_debug_attention': (ci, [vp, vp, ctypes.c_longlong, vp, vp, ci, vp]),
   'fpb_refine_forward': (ci, [vp, vp, ci, vp, vp, vp, vp]),
+  'fpb_refine_forward_shared_b': (ci, [vp, vp, ci, vp, vp, vp, vp]),
   'fpb_score_features': (ci, [vp, vp, ci, vp, vp, vp]),
   'fpb_score_features_multi': (ci, [vp, vp, ci, vp, vp, ci, vp]),
   'fpb_store_multi_f32': (ci, [vp, ctypes.c_longlong, vp, ci, vp]),

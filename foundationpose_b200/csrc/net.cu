@@ -208,23 +208,48 @@ int run_linear(const Ctx& c, const Lin& l, const void* in, long long rows, void*
   return c.gemm(p);
 }
 
-// both encoders: AB [2n,160,160,8] -> tokens (+pe) in w.d0 [n*400, 512]
-int run_encoders(const Ctx& c, const void* AB, int n, Ws& w)
+// shared-B mode: the observed-side features of hypothesis 0 (channels [128,256) of its 1600 rows, `seg` bytes per row at
+// byte offset `off` inside a row of `pitch` bytes) are copied to hypotheses 1..n-1
+__global__ void __launch_bounds__(256) broadcast_b_kernel(char* __restrict__ ab, int n, int rows, int pitch, int off, int seg)
 {
+  const int per_row = seg / 16;
+  const long long total = (long long)(n - 1) * rows * per_row;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int q = (int)(i % per_row);
+    const long long t = i / per_row;
+    const int r = (int)(t % rows);
+    const int h = (int)(t / rows) + 1;
+    const uint4 v = *reinterpret_cast<const uint4*>(ab + (size_t)r * pitch + off + q * 16);
+    *reinterpret_cast<uint4*>(ab + ((size_t)h * rows + r) * pitch + off + q * 16) = v;
+  }
+}
+
+// both encoders: AB [2n,160,160,8] -> tokens (+pe) in w.d0 [n*400, 512].
+// shared_b: AB is [n+1,...] = n rendered crops + ONE observed crop shared by all n hypotheses (first refine iteration of
+// register(): every hypothesis has the same translation, hence the same crop window, hence the same observed crop):
+// encodeA runs on n+1 images and the observed-side features are broadcast -- identical results, ~half of encodeA saved.
+int run_encoders(const Ctx& c, const void* AB, int n, Ws& w, bool shared_b = false)
+{
+  const int nA = shared_b ? n + 1 : 2 * n;
   int rc0 = FPB_ERR_UNSUPPORTED;
   if (c.bf && c.net->w_stem)      // dedicated stem kernel: input rows loaded once, two output rows stacked in the MMA M dimension
-    rc0 = c.k->stem_conv(AB, 2 * n, c.net->w_stem, c.F(c.net->conv[0].scale), c.F(c.net->conv[0].shift), 1, w.c0, c.st, 0);
-  if (rc0 == FPB_ERR_UNSUPPORTED) rc0 = run_conv(c, 0, AB, 2 * n, w.c0, nullptr, 1, false, 0, 0, 0);
+    rc0 = c.k->stem_conv(AB, nA, c.net->w_stem, c.F(c.net->conv[0].scale), c.F(c.net->conv[0].shift), 1, w.c0, c.st, 0);
+  if (rc0 == FPB_ERR_UNSUPPORTED) rc0 = run_conv(c, 0, AB, nA, w.c0, nullptr, 1, false, 0, 0, 0);
   RET(rc0);
   // optional (FPB_HALO=1): 3x3 stride-1 blocks in the zero-bordered position layout (one TMA box per 64 channels feeds all
   // 9 taps); kept for the record with its tests -- per-stage pipeline overhead makes it slower than the im2col path today
   const int hp = (c.bf && use_halo()) ? 1 : 0;
-  RET(run_conv(c, 1, w.c0, 2 * n, w.c1, nullptr, 1, false, 0, 0, 0, 0, hp));
-  RET(run_conv(c, 2, w.c1, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0, hp, hp));
-  RET(run_conv(c, 3, w.c2, 2 * n, w.c3, w.c1, 1, false, 0, 0, 0, hp, hp));
-  RET(run_conv(c, 4, w.c3, 2 * n, w.c2, nullptr, 1, false, 0, 0, 0, hp, hp));
+  RET(run_conv(c, 1, w.c0, nA, w.c1, nullptr, 1, false, 0, 0, 0, 0, hp));
+  RET(run_conv(c, 2, w.c1, nA, w.c2, nullptr, 1, false, 0, 0, 0, hp, hp));
+  RET(run_conv(c, 3, w.c2, nA, w.c3, w.c1, 1, false, 0, 0, 0, hp, hp));
+  RET(run_conv(c, 4, w.c3, nA, w.c2, nullptr, 1, false, 0, 0, 0, hp, hp));
   // last encodeA conv writes cat((a,b),1): rows of the first n images -> channels [0,128), last n -> [128,256)
-  RET(run_conv(c, 5, w.c2, 2 * n, w.ab0, w.c3, 1, false, n * 1600, 128, 256, hp, 0));
+  RET(run_conv(c, 5, w.c2, nA, w.ab0, w.c3, 1, false, n * 1600, 128, 256, hp, 0));
+  if (shared_b && n > 1) {      // the single B image landed in hypothesis 0's rows: copy to the others
+    const int pitch = 256 * (int)c.esz, seg = 128 * (int)c.esz;
+    broadcast_b_kernel<<<148 * 8, 256, 0, c.st>>>((char*)w.ab0, n, 1600, pitch, seg, seg);
+    FPB_LAUNCH_CHECK();
+  }
   RET(run_conv(c, 6, w.ab0, n, w.ab1, nullptr, 1, false, 0, 0, 0));
   RET(run_conv(c, 7, w.ab1, n, w.ab2, w.ab0, 1, false, 0, 0, 0));
   RET(run_conv(c, 8, w.ab2, n, w.ab1, nullptr, 1, false, 0, 0, 0));
@@ -380,8 +405,8 @@ static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* o
   return FPB_OK;
 }
 
-FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
-                                  void* stream)
+static int refine_forward_impl(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
+                               void* stream, bool shared_b)
 {
   FPB_CHECK_ARG(net && net->kind == FPB_NET_REFINE && AB && ws && out_trans && out_rot && N > 0);
   Ctx c{net, (cudaStream_t)stream, is16(net->precision), (size_t)(is16(net->precision) ? 2 : 4), kernels_of(net->precision)};
@@ -400,15 +425,30 @@ FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, voi
       char* stage = w.c1;
       static_assert(2 * 1600 * 128 >= 2 * IN_S * IN_PITCH * IN_C / 2, "staging fits");
       FPB_CUDA(cudaMemcpyAsync(stage, (const char*)AB + (size_t)b0 * img, (size_t)n * img, cudaMemcpyDeviceToDevice, c.st));
-      FPB_CUDA(cudaMemcpyAsync(stage + (size_t)n * img, (const char*)AB + (size_t)(N + b0) * img, (size_t)n * img,
-                               cudaMemcpyDeviceToDevice, c.st));
+      if (shared_b)      // the one observed crop sits behind the N rendered ones
+        FPB_CUDA(cudaMemcpyAsync(stage + (size_t)n * img, (const char*)AB + (size_t)N * img, img, cudaMemcpyDeviceToDevice, c.st));
+      else
+        FPB_CUDA(cudaMemcpyAsync(stage + (size_t)n * img, (const char*)AB + (size_t)(N + b0) * img, (size_t)n * img,
+                                 cudaMemcpyDeviceToDevice, c.st));
       in = stage;
     }
-    RET(run_encoders(c, in, n, w));
+    RET(run_encoders(c, in, n, w, shared_b));
     RET(encoder_layer(c, net->head[0], n, w, out_trans + (size_t)b0 * 3));
     RET(encoder_layer(c, net->head[1], n, w, out_rot + (size_t)b0 * net->rot_dim));
   }
   return FPB_OK;
+}
+
+FPB_EXPORT int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
+                                  void* stream)
+{
+  return refine_forward_impl(net, AB, N, ws, out_trans, out_rot, stream, false);
+}
+
+FPB_EXPORT int fpb_refine_forward_shared_b(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
+                                           void* stream)
+{
+  return refine_forward_impl(net, AB, N, ws, out_trans, out_rot, stream, true);
 }
 
 static int score_features_impl(const fpb_net* net, const void* AB, int N, void* ws, const MultiDst& dst, void* stream)

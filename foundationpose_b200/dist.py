@@ -140,7 +140,8 @@ def register_sharded(est, K, rgb, depth, ob_mask, iteration=5, group=None, excha
   poses = poses_all[lo:hi].contiguous()
   if hi > lo:
     poses, _ = est.refiner.predict(mesh=est.mesh, mesh_tensors=est.mesh_tensors, rgb=rgb_t, depth=depth_t, K=K,
-                                   ob_in_cams=poses, xyz_map=xyz_map, mesh_diameter=est.diameter, iteration=iteration)
+                                   ob_in_cams=poses, xyz_map=xyz_map, mesh_diameter=est.diameter, iteration=iteration,
+                                   same_translation=True)
     if px is not None:
       est.scorer.extract_features(rgb_t, depth_t, K, poses, mesh=est.mesh, mesh_tensors=est.mesh_tensors,
                                   mesh_diameter=est.diameter, dst_ptrs=px.feat_ptrs(lo))

@@ -187,7 +187,8 @@ class FoundationPose:
     self._stats_host[1].copy_(sf, non_blocking=True)
     poses, _ = self.refiner.predict(mesh=self.mesh, mesh_tensors=self.mesh_tensors, rgb=rgb_t, depth=depth_t, K=K,
                                     ob_in_cams=poses, normal_map=None, xyz_map=xyz_map, glctx=self.glctx,
-                                    mesh_diameter=self.diameter, iteration=iteration, get_vis=False)
+                                    mesh_diameter=self.diameter, iteration=iteration, get_vis=False,
+                                    same_translation=True)      # hypotheses = rot_grid x ONE guessed translation
     scores, _ = self.scorer.predict(mesh=self.mesh, rgb=rgb_t, depth=depth_t, K=K, ob_in_cams=poses, normal_map=None,
                                     mesh_tensors=self.mesh_tensors, glctx=self.glctx, mesh_diameter=self.diameter,
                                     get_vis=False)

@@ -244,13 +244,17 @@ class Net:
       self._ws = torch.empty(need, dtype=torch.uint8, device='cuda')
     return self._ws
 
-  def refine(self, AB, N):
-    """AB [2N,160,168,8] (utils.net_input_buffer layout) -> (trans [N,3], rot [N,3] or [N,6] for rot_rep='6d') fp32"""
+  def refine(self, AB, N, shared_b=False):
+    """AB [2N,160,168,8] (utils.net_input_buffer layout) -> (trans [N,3], rot [N,3] or [N,6] for rot_rep='6d') fp32.
+    shared_b: only AB[:N+1] is read -- N rendered crops and ONE observed crop shared by all hypotheses
+    (fpb_refine_forward_shared_b; bit-identical to the replicated input)."""
     AB = pad_input(AB)
-    assert AB.dtype == self.act_dtype and AB.shape == (2 * N, 160, 168, 8)
+    assert AB.dtype == self.act_dtype and AB.shape[1:] == (160, 168, 8) and AB.shape[0] >= (N + 1 if shared_b else 2 * N)
+    assert shared_b or AB.shape[0] == 2 * N
     trans = torch.empty((N, 3), dtype=torch.float, device='cuda')
     rot = torch.empty((N, self.rot_dim), dtype=torch.float, device='cuda')
-    check(lib().fpb_refine_forward(self.handle, ptr(AB), N, ptr(self.workspace(N)), ptr(trans), ptr(rot), stream()))
+    fn = lib().fpb_refine_forward_shared_b if shared_b else lib().fpb_refine_forward
+    check(fn(self.handle, ptr(AB), N, ptr(self.workspace(N)), ptr(trans), ptr(rot), stream()))
     return trans, rot
 
   def score_features(self, AB, N):

@@ -93,7 +93,7 @@ def resolve_weights(run_name, cfg_default, compat_defaults, cfg, state_dict, ckp
 
 def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_ratio, xyz_map, normal_map=None,
                          mesh_diameter=None, cfg=None, glctx=None, mesh_tensors=None, dataset=None, out_AB=None,
-                         bf16=True):
+                         bf16=True, shared_b=False):
   """reference :26-89 with the dataset transform fused in.  Returns a BatchPoseData (datasets.py) whose rgbAs /
   xyz_mapAs / rgbBs / xyz_mapBs are zero-copy [N,3,S,S] views of the network input `pose_data.AB`
   ([2N,S,S+8,8], rendered crops first), already normalised like PairH5Dataset.transform_batch would (rgb / 255,
@@ -108,13 +108,18 @@ def make_crop_data_batch(render_size, ob_in_cams, mesh, rgb, depth, K, crop_rati
   if out_AB is None:
     out_AB = U.net_input_buffer(N, S, torch.bfloat16 if bf16 else torch.float)
   U.render_crops(mesh_tensors, ob_in_cams, params, S, mesh_diameter, 0.001, out_A=out_AB[:N])
-  U.warp_crops(rgb, xyz_map, None, ob_in_cams, params, K, S, mesh_diameter, 0, out_B=out_AB[N:])
-  return batch_from_AB(out_AB, params, ob_in_cams, K, mesh_diameter, S)
+  if shared_b:      # every hypothesis has the same translation => the same crop window => ONE observed crop (see predict)
+    U.warp_crops(rgb, xyz_map, None, ob_in_cams[:1], params[:1], K, S, mesh_diameter, 0, out_B=out_AB[N:N + 1])
+  else:
+    U.warp_crops(rgb, xyz_map, None, ob_in_cams, params, K, S, mesh_diameter, 0, out_B=out_AB[N:])
+  return batch_from_AB(out_AB, params, ob_in_cams, K, mesh_diameter, S, shared_b)
 
 
-def batch_from_AB(AB, params, ob_in_cams, K, mesh_diameter, S):
+def batch_from_AB(AB, params, ob_in_cams, K, mesh_diameter, S, shared_b=False):
   N = len(ob_in_cams)
   rgbAs, xyzAs, rgbBs, xyzBs = views_of_AB(AB, N, S, U.IN_XOFF)
+  if shared_b:
+    rgbBs, xyzBs = rgbBs[:1].expand(N, -1, -1, -1), xyzBs[:1].expand(N, -1, -1, -1)
   poseA = torch.as_tensor(ob_in_cams, dtype=torch.float, device='cuda').reshape(-1, 4, 4)
   pd = BatchPoseData(rgbAs=rgbAs, rgbBs=rgbBs, xyz_mapAs=xyzAs, xyz_mapBs=xyzBs, poseA=poseA,
                      tf_to_crops=params[:, :9].reshape(N, 3, 3))
@@ -165,9 +170,18 @@ class PoseRefinePredictor:
 
   @torch.inference_mode()
   def predict(self, rgb, depth, K, ob_in_cams, xyz_map, normal_map=None, get_vis=False, mesh=None, mesh_tensors=None,
-              glctx=None, mesh_diameter=None, iteration=5):
+              glctx=None, mesh_diameter=None, iteration=5, same_translation=None):
     """reference :150-295.  Returns (B_in_cams [N,4,4] float32 cuda, None).  last_trans_update / last_rot_update hold
-    trans_delta [N,3] / rot_mat_delta [N,3,3] of the last iteration like the reference (:238-239)."""
+    trans_delta [N,3] / rot_mat_delta [N,3,3] of the last iteration like the reference (:238-239).
+    same_translation (not in the reference): all input poses share one translation, as the hypotheses of register() do
+    (src/estimater.py:127-134).  Then the first iteration's box_3d crop window and with it the observed crop B are the same
+    for every hypothesis: B is warped and encoded once instead of N times (bit-identical results).  None = detect it when
+    the poses arrive as host data (the reference passes numpy); device tensors are not inspected (no synchronisation)."""
+    if same_translation is None:
+      same_translation = False
+      if not (torch.is_tensor(ob_in_cams) and ob_in_cams.is_cuda):
+        t = np.asarray(ob_in_cams, dtype=np.float32).reshape(-1, 4, 4)[:, :3, 3]
+        same_translation = len(t) > 1 and bool((t == t[:1]).all())
     if get_vis:
       logging.info('get_vis is not supported headless; returning vis=None')
     if mesh_tensors is None:
@@ -184,10 +198,11 @@ class PoseRefinePredictor:
     tn = list(self.cfg['trans_normalizer']) if not isinstance(self.cfg['trans_normalizer'], float) else [self.cfg['trans_normalizer']] * 3
     trans = rot = td = rd = None
     for it in range(iteration):
+      shared_b = bool(same_translation) and it == 0 and N > 1
       pose_data = make_crop_data_batch(self.cfg['input_resize'], B_in_cams, mesh, rgb_t, None, K, self.cfg['crop_ratio'],
                                        xyz_t, mesh_diameter=mesh_diameter, cfg=self.cfg, mesh_tensors=mesh_tensors,
-                                       dataset=self.dataset, out_AB=AB)
-      trans, rot = self.model.refine(pose_data.AB, N)
+                                       dataset=self.dataset, out_AB=AB, shared_b=shared_b)
+      trans, rot = self.model.refine(pose_data.AB, N, shared_b=shared_b)
       last = it == iteration - 1
       res = U.pose_update(B_in_cams, trans, rot, mesh_diameter, self.cfg['rot_normalizer'], tn,
                           self.cfg['normalize_xyz'], trans_rep=self.cfg['trans_rep'], rot_rep=self.cfg['rot_rep'],

@@ -178,6 +178,13 @@ size_t fpb_score_cross_ws_bytes(int L, int bs);
 #define FPB_IN_XOFF 4
 int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
                        void* stream);
+/* same network, AB = [N+1,S,FPB_IN_PITCH,8]: N rendered crops + ONE observed crop shared by all N hypotheses.  In the
+ * first refine iteration of register() every hypothesis has the guessed translation (src/estimater.py:127-134), hence
+ * the same box_3d crop window (src/Utils.py:577-621), hence an identical observed crop B: the reference encodes it N
+ * times (refine_network.py:78-80), here encodeA runs on N+1 images and B's features are broadcast.  Results are
+ * bit-identical to fpb_refine_forward on the replicated input. */
+int fpb_refine_forward_shared_b(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
+                                void* stream);
 int fpb_score_features(const fpb_net* net, const void* AB, int N, void* ws, float* out_feat_n512, void* stream);
 /* ---- multi-GPU (new; the reference has no distributed code): hypotheses sharded over the GPUs of one box.
  *      ScoreNet's cross-hypothesis attention (score_network.py:86) needs all N feature rows on every rank, so the

@@ -245,3 +245,34 @@ def test_rank_poses_matches_stable_descending_sort(N):
   want = torch.sort(scores, descending=True, stable=True).indices
   assert torch.equal(ids, want) and torch.equal(s, scores[want]) and torch.equal(p, poses[want])
   assert torch.allclose(best, poses[want[0]] @ tf, atol=1e-6)
+
+
+@pytest.mark.parametrize('precision,N', [('fp32', 12), ('fp16', 252), ('bf16', 40), ('fp16', 300)])
+def test_first_iteration_shared_observed_crop_is_bit_identical(scene1, precision, N):
+  """register()'s hypotheses share one translation => one crop window => one observed crop B in the first refine iteration
+  (src/estimater.py:127-134, src/Utils.py:577-621).  fpb_refine_forward_shared_b warps / encodes B once and broadcasts its
+  features: poses and raw head outputs must equal the replicated path bit for bit (N = 300 crosses the 256-hypothesis chunk)."""
+  from foundationpose_b200 import nets, utils as U
+  from foundationpose_b200.predict_pose_refine import PoseRefinePredictor
+  from oracle import ops as oo
+  from tests.helpers import centered, hypo_poses
+  sc = scene1
+  mesh, _ = centered(sc)
+  base, d = hypo_poses(sc, n=None)
+  poses = base[np.arange(N) % len(base)].copy()
+  assert (poses[:, :3, 3] == poses[0, :3, 3]).all()
+  refiner = PoseRefinePredictor(state_dict=nets.synthetic_state_dict(nets.REFINE), precision=precision)
+  kw = dict(rgb=sc['rgb'], depth=d, K=sc['K'], xyz_map=oo.depth2xyzmap(d, sc['K']), mesh=mesh, mesh_tensors=U.make_mesh_tensors(mesh),
+            mesh_diameter=sc['diameter'], iteration=2)
+  a, _ = refiner.predict(ob_in_cams=poses, same_translation=False, **kw)
+  a, ta, ra = a.clone(), refiner.last_trans_raw.clone(), refiner.last_rot_raw.clone()
+  from foundationpose_b200._lib import lib
+  lib().fpb_launch_count(1)
+  b, _ = refiner.predict(ob_in_cams=poses, **kw)                      # host poses: detected automatically
+  assert torch.equal(a, b) and torch.equal(ta, refiner.last_trans_raw) and torch.equal(ra, refiner.last_rot_raw)
+  c, _ = refiner.predict(ob_in_cams=torch.as_tensor(poses).cuda(), same_translation=True, **kw)
+  assert torch.equal(a, c)
+  jit = poses.copy(); jit[1, 0, 3] += 1e-4                           # not shared: the detection must say no
+  e, _ = refiner.predict(ob_in_cams=jit, **kw)
+  f, _ = refiner.predict(ob_in_cams=jit, same_translation=False, **kw)
+  assert torch.equal(e, f) and not torch.equal(e[1], a[1])
