@@ -81,8 +81,8 @@ class FoundationPose:
     self.pose_last = None   # used for tracking; w.r.t. the centred mesh
 
   def reset_object(self, model_pts, model_normals, symmetry_tfs=None, mesh=None):
-    """src/estimater.py:44-78 (the open3d voxel down-sampling only feeds utilities off the hot path; kept as a
-    plain numpy grid-average)."""
+    """src/estimater.py:44-78 (open3d's voxel down-sampling, which only feeds utilities off the hot path, restated in
+    numpy)."""
     if isinstance(mesh, dict):                 # a ready mesh_tensors dict (SURVEY 8(b))
       mesh = U.mesh_from_tensors(mesh)
     elif not hasattr(mesh, 'copy'):            # duck-typed mesh without .copy()
@@ -103,7 +103,11 @@ class FoundationPose:
     logging.info(f'self.diameter:{self.diameter}, vox_size:{self.vox_size}')
     self.dist_bin = self.vox_size / 2
     self.angle_bin = 20
-    keys = np.floor(model_pts / self.vox_size).astype(np.int64)
+    # open3d 0.18 PointCloud::VoxelDownSample (src/estimater.py:59-60): voxel grid anchored half a voxel below the minimum
+    # bound, index = floor((p - (min_bound - voxel/2)) / voxel), points and normals averaged per occupied voxel.  open3d emits
+    # the voxels in hash-map order (unspecified); here they come in lexicographic voxel order.
+    vmin = model_pts.min(axis=0) - 0.5 * self.vox_size
+    keys = np.floor((model_pts - vmin) / self.vox_size).astype(np.int64)
     _, inv = np.unique(keys, axis=0, return_inverse=True)
     inv = inv.reshape(-1)
     cnt = np.bincount(inv).astype(np.float64)

@@ -276,3 +276,29 @@ def test_first_iteration_shared_observed_crop_is_bit_identical(scene1, precision
   e, _ = refiner.predict(ob_in_cams=jit, **kw)
   f, _ = refiner.predict(ob_in_cams=jit, same_translation=False, **kw)
   assert torch.equal(e, f) and not torch.equal(e[1], a[1])
+
+
+def test_reset_object_voxel_downsample_follows_open3d_rule(scene2):
+  """src/estimater.py:59-64: pcd.voxel_down_sample(vox_size) -- grid anchored at min_bound - vox/2, per-voxel averages of
+  points and normals; est.pts / est.normals / min_xyz / max_xyz derive from it (brute-force restatement of the rule)."""
+  from foundationpose_b200 import nets
+  from foundationpose_b200.estimater import FoundationPose
+  from foundationpose_b200.predict_pose_refine import PoseRefinePredictor
+  from foundationpose_b200.predict_score import ScorePredictor
+  sc = scene2
+  est = FoundationPose(model_pts=sc['mesh'].vertices, model_normals=sc['mesh'].vertex_normals, mesh=sc['mesh'],
+                       refiner=PoseRefinePredictor(state_dict=nets.synthetic_state_dict(nets.REFINE)),
+                       scorer=ScorePredictor(state_dict=nets.synthetic_state_dict(nets.SCORE)), mesh_diameter=sc['diameter'])
+  assert est.vox_size == max(sc['diameter'] / 20.0, 0.003) and est.dist_bin == est.vox_size / 2 and est.angle_bin == 20
+  V = np.asarray(sc['mesh'].vertices) - est.model_center.reshape(1, 3)
+  Nn = np.asarray(sc['mesh'].vertex_normals)
+  origin = V.min(0) - est.vox_size / 2
+  cells = {}
+  for p, n in zip(V, Nn):
+    cells.setdefault(tuple(np.floor((p - origin) / est.vox_size).astype(int)), []).append((p, n))
+  want_p = np.array([np.mean([q[0] for q in cells[k]], axis=0) for k in sorted(cells)])
+  want_n = np.array([np.mean([q[1] for q in cells[k]], axis=0) for k in sorted(cells)])
+  want_n /= np.linalg.norm(want_n, axis=1, keepdims=True)
+  assert est.pts.shape == (len(cells), 3) and 100 < len(cells) < len(V)
+  assert np.abs(est.pts.cpu().numpy() - want_p).max() < 1e-6 and np.abs(est.normals.cpu().numpy() - want_n).max() < 1e-5
+  assert np.allclose(est.max_xyz, want_p.max(0)) and np.allclose(est.min_xyz, want_p.min(0))
