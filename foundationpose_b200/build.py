@@ -18,7 +18,7 @@ ARCH = ['-gencode', 'arch=compute_100a,code=sm_100a']
 COMMON = ['-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC,-fvisibility=hidden', '--expt-relaxed-constexpr']
 # (source, extra flags, object suffix).  The network kernel units are compiled twice: bf16 operands (namespace bf16) and,
 # with -DFPB_ACT_FP16, IEEE fp16 operands (namespace f16) -- csrc/act_type.cuh.
-NET_UNITS = ['net_ref.cu', 'net_tc.cu', 'net_tc2.cu', 'net_tc3.cu', 'net_stem.cu', 'net_attn.cu']
+NET_UNITS = ['net_ref.cu', 'net_tc.cu', 'net_tc2.cu', 'net_tc3.cu', 'net_stem.cu', 'net_attn.cu', 'net_ffn.cu']
 UNITS = [
   ('api.cu', [], ''),
   ('depth.cu', ['-fmad=false'], ''),

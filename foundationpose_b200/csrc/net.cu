@@ -391,6 +391,18 @@ static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* o
 {
   const long long R = (long long)n * TOK;
   RET(run_self_attention(c, e.att, w.d0, n, w));
+  if (c.bf && D == 512) {
+    // row-tile kernels (net_ffn.cu): out_proj + residual + LayerNorm1 in one launch, then linear1 + ReLU + linear2 +
+    // residual + LayerNorm2 + token sums in one launch with the 512-wide intermediate kept in shared memory
+    // (w.scores is idle in the 16-bit modes: scratch for the per-16-token column sums)
+    int rc = c.k->proj_ln_512(w.ctx, c.W(e.att.out.w), c.F(e.att.out.b), w.d0, c.F(e.n1g), c.F(e.n1b), 1e-5f, w.y, R, c.st);
+    if (rc == FPB_OK) {
+      rc = c.k->ffn_ln_token_mean_512(w.y, c.W(e.l1.w), c.F(e.l1.b), c.W(e.l2.w), c.F(e.l2.b), c.F(e.n2g), c.F(e.n2b), 1e-5f,
+                                      w.scores, w.pooled, n, TOK, c.st);
+      if (rc == FPB_OK) return c.k->small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, e.fin.N, c.st);
+    }
+    if (rc != FPB_ERR_UNSUPPORTED) return rc;
+  }
   RET(run_linear(c, e.att.out, w.ctx, R, w.y1, w.d0, 0, c.bf));                       // x + SA(x)
   RET(c.k->layernorm_rows(w.y1, c.bf, c.F(e.n1g), c.F(e.n1b), w.y, c.bf, R, D, 1e-5f, c.st));
   RET(run_linear(c, e.l1, w.y, R, w.ff, nullptr, 1, c.bf));
@@ -657,6 +669,27 @@ FPB_EXPORT int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* 
   const int rc = DK->tc2_gemm(p, (cudaStream_t)stream);
   DK->tc2_force_cta_group(0);
   if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_conv3x3_halo: shape not supported");
+  return rc;
+}
+
+// unit-test entry of the row-tile encoder-layer kernels (net_ffn.cu).  mode 0: out = LN(A.W2^T + b2 + residual)*gamma+beta
+// ([M][512] 16-bit); mode 1: out = pooled [M/tokens][512] fp32 of the fused FFN + LayerNorm + token mean (residual = A),
+// scratch >= (M/16)*512 floats.
+FPB_EXPORT int fpb_debug_ffn(int mode, const void* A, const void* W1, const float* b1, const void* W2, const float* b2,
+                             const void* residual, const float* gamma, const float* beta, void* out, float* scratch,
+                             long long M, int tokens, void* stream)
+{
+  FPB_CHECK_ARG(A && W2 && b2 && gamma && beta && out && M > 0);
+  int rc;
+  if (mode == 0) {
+    FPB_CHECK_ARG(residual);
+    rc = DK->proj_ln_512(A, W2, b2, residual, gamma, beta, 1e-5f, out, M, (cudaStream_t)stream);
+  } else {
+    FPB_CHECK_ARG(W1 && b1 && scratch && tokens > 0 && M % tokens == 0);
+    rc = DK->ffn_ln_token_mean_512(A, W1, b1, W2, b2, gamma, beta, 1e-5f, scratch, (float*)out, (int)(M / tokens), tokens,
+                                   (cudaStream_t)stream);
+  }
+  if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_ffn: disabled (FPB_FFN=0) or unsupported alignment / shape");
   return rc;
 }
 

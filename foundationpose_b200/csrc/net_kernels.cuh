@@ -104,6 +104,13 @@ int small_linear(const float* x, const float* W, const float* b, float* out, int
 int transpose_v(const void* qkv, void* vt, int is_bf16, int groups, int tokens, int heads, int dh, int ld_qkv, int v_off, \
                 int ld_vt, cudaStream_t st); /* vt[(g*heads+h)][d][t] */ \
 int f32_to_act(const float* in, void* out, long long n, cudaStream_t st); /* fp32 -> act_t (bf16 / fp16) */ \
+/* row-tile kernels of the encoder-layer tail (net_ffn.cu); FPB_ERR_UNSUPPORTED (FPB_FFN=0, misaligned) -> unfused path */ \
+/* y = LayerNorm(A . W^T + b + residual) * gamma + beta on [M][512] 16-bit rows */ \
+int proj_ln_512(const void* A, const void* W, const float* b, const void* residual, const float* gamma, const float* beta, \
+                float eps, void* out, long long M, cudaStream_t st); \
+/* pooled[g] = mean_t LayerNorm(x + relu(x . W1^T + b1) . W2^T + b2) * gamma + beta; gs: (groups*tokens/16) x 512 floats scratch */ \
+int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const void* W2, const float* b2, const float* gamma, \
+                          const float* beta, float eps, float* gs, float* pooled, int groups, int tokens, cudaStream_t st); \
 
 namespace bf16 { FPB_NET_KERNEL_DECLS }
 namespace f16 { FPB_NET_KERNEL_DECLS }
@@ -126,8 +133,11 @@ struct NetKernels {
   decltype(&bf16::small_linear) small_linear;
   decltype(&bf16::transpose_v) transpose_v;
   decltype(&bf16::f32_to_act) f32_to_act;
+  decltype(&bf16::proj_ln_512) proj_ln_512;
+  decltype(&bf16::ffn_ln_token_mean_512) ffn_ln_token_mean_512;
 };
 #define FPB_NET_KERNEL_TABLE(ns)                                                                                        \
   {ns::ref_gemm, ns::tc_gemm, ns::tc2_gemm, ns::tc3_gemm, ns::stem_pack_weights, ns::stem_conv, ns::tc2_force_cta_group, \
    ns::tc_attention, ns::softmax_rows, ns::layernorm_rows, ns::token_mean, ns::token_mean_multi,                        \
-   ns::layernorm_token_mean_512, ns::small_linear, ns::transpose_v, ns::f32_to_act}
+   ns::layernorm_token_mean_512, ns::small_linear, ns::transpose_v, ns::f32_to_act, ns::proj_ln_512,              \
+   ns::ffn_ln_token_mean_512}

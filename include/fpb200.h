@@ -235,6 +235,16 @@ int fpb_debug_conv3x3_halo(int cta_group, const void* A, const void* W, void* C,
 int fpb_debug_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups,
                         void* stream);
 
+/* unit-test entry: row-tile kernels of the encoder-layer tail (512-wide rows, csrc/net_ffn.cu).
+ * mode 0: out[M][512] (16-bit) = LayerNorm(A . W2^T + b2 + residual) * gamma + beta   (out_proj + norm1,
+ *         refine_network.py:56-70 / nn.TransformerEncoderLayer);
+ * mode 1: out[M/tokens][512] (fp32) = mean over each group's tokens of LayerNorm(A + relu(A . W1^T + b1) . W2^T + b2)
+ *         * gamma + beta   (linear1 + ReLU + linear2 + norm2 + `.mean(dim=1)`, refine_network.py:88-93);
+ *         scratch: (M/16) x 512 floats, tokens % 16 == 0. */
+int fpb_debug_ffn(int mode, const void* A, const void* W1, const float* b1, const void* W2, const float* b2,
+                  const void* residual, const float* gamma, const float* beta, void* out, float* scratch, long long M,
+                  int tokens, void* stream);
+
 /* operand type (FPB_PREC_BF16 default, or FPB_PREC_FP16) the fpb_debug_* unit-test entries run in */
 int fpb_debug_set_precision(int precision);
 

@@ -399,3 +399,67 @@ def test_conv3x3_halo_layout(cg, shape):
   torch.cuda.synchronize()
   assert (_from_pos(out3, n, H, H).float() - ref).abs().max().item() < 3e-2
   assert out3.reshape(n, H + 1, H + 1, Cout)[:, 0].abs().max().item() == 0
+
+
+def _ffn_inputs(M, seed, dt):
+  g = torch.Generator(device='cuda').manual_seed(seed)
+  rn = lambda *s: torch.randn(*s, device='cuda', generator=g)
+  A = (rn(M, 512) * 1.2 + 0.3).to(dt)                       # rows with a non-zero mean (shifted-sum statistics)
+  res = rn(M, 512).to(dt)
+  W1, W2 = (rn(512, 512) / 512 ** 0.5).to(dt), (rn(512, 512) / 512 ** 0.5).to(dt)
+  b1, b2 = rn(512) * 0.2, rn(512) * 0.2
+  gamma, beta = 1.0 + 0.3 * rn(512), 0.2 * rn(512)
+  return A, res, W1, W2, b1, b2, gamma, beta
+
+
+def _ln(v, gamma, beta):
+  mu = v.mean(-1, keepdim=True)
+  var = ((v - mu) ** 2).mean(-1, keepdim=True)
+  return (v - mu) / torch.sqrt(var + 1e-5) * gamma.double() + beta.double()
+
+
+@pytest.mark.parametrize('prec', ['bf16', 'fp16'])
+@pytest.mark.parametrize('M', [400, 2000, 64 * 400, 252 * 400])
+def test_row_tile_proj_layernorm(prec, M):
+  """net_ffn.cu, proj+LN kernel: LayerNorm(A . W^T + b + residual) vs fp64 torch on the same 16-bit operands
+  (one ragged tile, several tiles, more tiles than CTA pairs so every pipeline phase wraps)."""
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  dt = torch.bfloat16 if prec == 'bf16' else torch.float16
+  check(lib().fpb_debug_set_precision(1 if prec == 'bf16' else 2))
+  try:
+    A, res, _, W2, _, b2, gamma, beta = _ffn_inputs(M, 5 + M % 97, dt)
+    out = torch.full((M + 8, 512), 7.0, device='cuda', dtype=dt)       # guard rows behind the tensor must stay untouched
+    check(lib().fpb_debug_ffn(0, ptr(A), None, None, ptr(W2), ptr(b2), ptr(res), ptr(gamma), ptr(beta), ptr(out), None, M, 400,
+                              stream()))
+    torch.cuda.synchronize()
+  finally:
+    check(lib().fpb_debug_set_precision(1))
+  ref = _ln(A.double() @ W2.double().t() + b2.double() + res.double(), gamma, beta)
+  err = (out[:M].double() - ref).abs().max().item()
+  assert (out[M:] == 7.0).all()
+  assert err < (4e-2 if prec == 'bf16' else 5e-3), err      # one 16-bit rounding of outputs of magnitude <= ~6
+
+
+@pytest.mark.parametrize('prec', ['bf16', 'fp16'])
+@pytest.mark.parametrize('M', [400, 2000, 64 * 400, 252 * 400])
+def test_row_tile_ffn_layernorm_token_mean(prec, M):
+  """net_ffn.cu, fused linear1 + ReLU + linear2 + residual + LayerNorm2 + token mean vs fp64 torch (h rounded to the
+  operand type like the kernel's shared-memory tile)."""
+  from foundationpose_b200._lib import lib, check, ptr, stream
+  dt = torch.bfloat16 if prec == 'bf16' else torch.float16
+  check(lib().fpb_debug_set_precision(1 if prec == 'bf16' else 2))
+  try:
+    A, _, W1, W2, b1, b2, gamma, beta = _ffn_inputs(M, 17 + M % 89, dt)
+    G = M // 400
+    out = torch.zeros(G, 512, device='cuda')
+    scratch = torch.zeros(M // 16, 512, device='cuda')
+    for _ in range(2):                                       # twice: scratch / pipeline state of a first call must not matter
+      check(lib().fpb_debug_ffn(1, ptr(A), ptr(W1), ptr(b1), ptr(W2), ptr(b2), None, ptr(gamma), ptr(beta), ptr(out),
+                                ptr(scratch), M, 400, stream()))
+    torch.cuda.synchronize()
+  finally:
+    check(lib().fpb_debug_set_precision(1))
+  h = torch.relu(A.double() @ W1.double().t() + b1.double()).to(dt).double()
+  ref = _ln(h @ W2.double().t() + b2.double() + A.double(), gamma, beta).reshape(G, 400, 512).mean(1)
+  err = (out.double() - ref).abs().max().item()
+  assert err < (2e-3 if prec == 'bf16' else 3e-4), err
