@@ -15,9 +15,13 @@
 //                      is evaluated in.  pool_groups_kernel adds a hypothesis' 25 group rows in order and applies
 //                      gamma / beta / (1 / tokens) (the affine map commutes with the mean).
 // Roles per CTA (10 warps): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (leader CTA), warps 2-9 =
-// epilogue (two warps per TMEM lane quarter, alternating 64-column groups).  TMEM holds ONE accumulator, so the MMA and
-// epilogue phases of a tile alternate; the weight stream (W1 / W2 through a 4-deep ring, half of every 256-row weight
-// block per CTA of the pair) keeps prefetching underneath.
+// epilogue (two warps per TMEM lane quarter; each owns two 64-column groups in either accumulator half).  TMEM holds ONE
+// 512-column accumulator, handled as two 256-column halves with their own full / free barriers: products with a streamed A
+// operand fill half 0, then half 1 (A passes through the ring twice), so the epilogue work on half 0 runs under the MMAs
+// of half 1 and the next tile's half 0 under the second pass of this tile's half 1.  Residual rows never go through
+// registers + staging: every epilogue warp TMA-loads its own [32 rows x 64 columns] boxes into the R/H region (proj+LN: a
+// whole tile ahead; FFN: chunk by chunk as the second product releases the h tile), reads them lane = row, writes the
+// output rows over them and TMA-stores the boxes.
 #include "net_kernels.cuh"
 #include "tc_ptx.cuh"
 #include <cuda.h>
@@ -32,44 +36,38 @@ constexpr int KC = 64;                     // K elements per stage (128 bytes: o
 constexpr int NKC = FD / KC;
 constexpr int TMR = 128;                   // rows per CTA
 constexpr int CHUNK = TMR * 128;           // one [128 rows x 64 K] operand block, 16 KB
+constexpr int BOX = 32 * 128;              // one warp's [32 rows x 64 columns] piece of a chunk, 4 KB
 constexpr int NTHREADS = 320;
+constexpr int NSTG = 3;                    // operand ring: stages of two 16 KB blocks
 
 struct FfnParams {
   int M, m_tiles;                          // rows, tiles of 256 rows
-  const act_t* residual;                   // [M][512]
   const float* b1;                         // FFN: bias of the first product
   const float* b2;                         // bias of the (last) product
   const float* gamma;                      // proj+LN only (the FFN kernel leaves gamma / beta to pool_groups_kernel)
   const float* beta;
   float eps;
-  act_t* out;                              // proj+LN: [M][512]
   float* gs;                               // FFN: [M/16][512] column sums of the normalised rows of each 16-row group
   int dbg;
 };
 
 struct FfnCtl {
-  uint64_t full_a[4], empty_a[4], full_b[4], empty_b[4];
-  uint64_t acc_full, acc_free, stg_free;
+  uint64_t full[NSTG], empty[NSTG];
+  uint64_t acc_full[2], acc_free[2];       // per accumulator half (TMEM columns 0-255 / 256-511)
+  uint64_t h_free[NKC];                    // FFN: K chunk kc of the h tile has been consumed by the second product
+  uint64_t r_full[8][2];                   // per epilogue warp and column half: its residual boxes have landed
   uint32_t tmem_base;
 };
 
-template <bool FFN>
-struct FCfg {
-  static constexpr int NA = FFN ? 2 : 4;                     // must divide NKC (slot of K chunk kc = kc % NA)
-  static constexpr int NB = 4;
-  static constexpr int OFF_H = 0;
-  static constexpr int OFF_B = FFN ? NKC * CHUNK : 0;
-  static constexpr int OFF_A = OFF_B + NB * CHUNK;
-  // 8 warp-private 4 KB staging tiles.  FFN: they overlay the A ring (32 KB), which is idle from the end of the first
-  // product until the next tile (the producer waits for stg_free before it refills the ring).
-  static constexpr int OFF_STG = FFN ? OFF_A : OFF_A + NA * CHUNK;
-  static constexpr int OFF_XCH = OFF_STG + 8 * 4096;         // proj+LN: 8 x 256 B row-statistics exchange
-  static constexpr int DATA = FFN ? OFF_A + NA * CHUNK : OFF_XCH + 8 * 256;
-  static constexpr int SMEM = DATA + 1024 + (int)sizeof(FfnCtl);
-  static_assert(NKC % NA == 0, "ring slot of a K chunk must not depend on the tile");
-  static_assert(!FFN || NA * CHUNK == 8 * 4096, "staging overlays the A ring exactly");
-  static_assert(SMEM <= 232448, "shared memory budget");
-};
+// Shared memory: [R/H region: 8 chunks x 16 KB][ring: NSTG x 32 KB][ctl].  The R/H region holds, per chunk g (columns
+// 64g .. 64g+63) and row r, 128 bytes at g*CHUNK + r*128 with the 16-byte pieces XOR-swizzled by (r & 7) -- the layout TMA
+// writes / reads with SWIZZLE_128B and tcgen05.mma reads as a K-major operand.  It is, in turn: the residual tile
+// (TMA-loaded in warp-private [32 rows x 64 columns] boxes), FFN: the h tile (A operand of the second product, written
+// by the epilogue threads), proj+LN: the output tile (written in place over the residual, TMA-stored box by box).
+constexpr int OFF_RING = NKC * CHUNK;
+constexpr int DATA_BYTES = OFF_RING + NSTG * 2 * CHUNK;
+constexpr int FFN_SMEM = DATA_BYTES + 1024 + (int)sizeof(FfnCtl);
+static_assert(FFN_SMEM <= 232448, "shared memory budget");
 
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity)
 {
@@ -101,10 +99,6 @@ __device__ __forceinline__ void mbar_arrive_cluster_release(uint64_t* bar, uint3
       "r"(cta)
       : "memory");
 }
-__device__ __forceinline__ void mbar_arrive_local(uint64_t* bar)
-{
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v)
 {
   asm volatile(
@@ -117,6 +111,12 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v)
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// TMA store of one [32 rows x 64 columns] box from shared memory (rows beyond the tensor are clipped)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int x, int y)
+{
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // v[i] += bias[n0 + i], 64 columns, warp-uniform 16-byte loads
 __device__ __forceinline__ void add_bias64(float (&v)[64], const float* __restrict__ bias, int n0)
@@ -129,29 +129,27 @@ __device__ __forceinline__ void add_bias64(float (&v)[64], const float* __restri
   }
 }
 
+// mapA: rows of the streamed A operand, box 64 x 128.  mapW1 / mapW2: weights [512][512], box 64 x 128.
+// mapR: residual rows, box 64 x 32.  mapO: output rows (proj+LN), box 64 x 32.
 template <bool FFN>
 __global__ void __launch_bounds__(NTHREADS, 1)
 ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapW1,
-           const __grid_constant__ CUtensorMap mapW2, const FfnParams q)
+           const __grid_constant__ CUtensorMap mapW2, const __grid_constant__ CUtensorMap mapR,
+           const __grid_constant__ CUtensorMap mapO, const FfnParams q)
 {
-  using C = FCfg<FFN>;
-  constexpr int NA = C::NA, NB = C::NB;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  FfnCtl* ctl = (FfnCtl*)(smem + C::DATA);
+  FfnCtl* ctl = (FfnCtl*)(smem + DATA_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   pdl_launch_dependents();
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 4; s++) {
-      mbar_init(&ctl->full_a[s], 1); mbar_init(&ctl->empty_a[s], 1);
-      mbar_init(&ctl->full_b[s], 1); mbar_init(&ctl->empty_b[s], 1);
-    }
-    mbar_init(&ctl->acc_full, 1);
-    mbar_init(&ctl->acc_free, 16);                 // 8 epilogue warps x 2 CTAs, on the leader's barrier
-    mbar_init(&ctl->stg_free, 8);                  // 8 epilogue warps of this CTA
+    for (int s = 0; s < NSTG; s++) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+    for (int b = 0; b < 2; b++) { mbar_init(&ctl->acc_full[b], 1); mbar_init(&ctl->acc_free[b], 16); }   // 8 warps x 2 CTAs
+    for (int k = 0; k < NKC; k++) mbar_init(&ctl->h_free[k], 1);
+    for (int w = 0; w < 8; w++) { mbar_init(&ctl->r_full[w][0], 1); mbar_init(&ctl->r_full[w][1], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -162,6 +160,8 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW1) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW2) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapR) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapO) : "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -170,92 +170,92 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   const uint32_t tmem_base = ctl->tmem_base;
   pdl_wait();
 
-  const uint32_t sH = smem_u32(smem + C::OFF_H), sB = smem_u32(smem + C::OFF_B), sA = smem_u32(smem + C::OFF_A);
+  const uint32_t sH = smem_u32(smem), sRing = smem_u32(smem + OFF_RING);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (one lane, both CTAs)
     if (lane == 0) {
-      const uint32_t full_a0 = mapa_u32(smem_u32(&ctl->full_a[0]), 0), full_b0 = mapa_u32(smem_u32(&ctl->full_b[0]), 0);
-      int sa = 0, sb = 0;
-      uint32_t pa = 1, pb = 1;                               // producer waits with inverted parity
-      uint32_t it = 0;
-      for (int t = cluster_id; t < q.m_tiles; t += n_clusters, it++) {
+      const uint32_t full0 = mapa_u32(smem_u32(&ctl->full[0]), 0);     // the leader's barriers collect both CTAs' bytes
+      int st = 0;
+      uint32_t ph = 1;                                       // producer waits with inverted parity
+      // one ring stage = two 16 KB blocks per CTA
+      auto stage = [&](const CUtensorMap* m0, int x0, int y0, const CUtensorMap* m1, int x1, int y1) {
+        mbar_wait(&ctl->empty[st], ph);
+        if (rank == 0) mbar_arrive_expect_tx(&ctl->full[st], 4u * CHUNK);
+        const uint32_t dst = sRing + st * (2 * CHUNK);
+        tma_load_2d<2>(dst, m0, full0 + 8u * st, x0, y0);
+        tma_load_2d<2>(dst + CHUNK, m1, full0 + 8u * st, x1, y1);
+        if (++st == NSTG) { st = 0; ph ^= 1u; }
+      };
+      for (int t = cluster_id; t < q.m_tiles; t += n_clusters) {
         const int m0 = (t * 2 + (int)rank) * TMR;
-        if (FFN && it > 0) mbar_wait(&ctl->stg_free, (it - 1) & 1u);   // the staging tiles that overlay the A ring are idle again
-        for (int kc = 0; kc < NKC; kc++) {
-          mbar_wait(&ctl->empty_a[sa], pa);
-          if (rank == 0) mbar_arrive_expect_tx(&ctl->full_a[sa], 2u * CHUNK);
-          tma_load_2d<2>(sA + sa * CHUNK, &mapA, full_a0 + 8u * sa, kc * KC, m0);
-          if (++sa == NA) { sa = 0; pa ^= 1u; }
-#pragma unroll 1
-          for (int nh = 0; nh < 2; nh++) {
-            mbar_wait(&ctl->empty_b[sb], pb);
-            if (rank == 0) mbar_arrive_expect_tx(&ctl->full_b[sb], 2u * CHUNK);
-            tma_load_2d<2>(sB + sb * CHUNK, FFN ? &mapW1 : &mapW2, full_b0 + 8u * sb, kc * KC, nh * 256 + (int)rank * TMR);
-            if (++sb == NB) { sb = 0; pb ^= 1u; }
-          }
-        }
-        if (FFN) {
-          for (int kc = 0; kc < NKC; kc++) {
-#pragma unroll 1
-            for (int nh = 0; nh < 2; nh++) {
-              mbar_wait(&ctl->empty_b[sb], pb);
-              if (rank == 0) mbar_arrive_expect_tx(&ctl->full_b[sb], 2u * CHUNK);
-              tma_load_2d<2>(sB + sb * CHUNK, &mapW2, full_b0 + 8u * sb, kc * KC, nh * 256 + (int)rank * TMR);
-              if (++sb == NB) { sb = 0; pb ^= 1u; }
-            }
-          }
-        }
+        // product with a streamed A operand, one accumulator half after the other (A passes twice)
+        for (int nh = 0; nh < 2; nh++)
+          for (int kc = 0; kc < NKC; kc++)
+            stage(&mapA, kc * KC, m0, FFN ? &mapW1 : &mapW2, kc * KC, nh * 256 + (int)rank * TMR);
+        if (FFN)
+          for (int kc = 0; kc < NKC; kc++)
+            stage(&mapW2, kc * KC, (int)rank * TMR, &mapW2, kc * KC, 256 + (int)rank * TMR);
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA, one lane)
     if (rank == 0 && lane == 0) {
       constexpr uint32_t idesc = make_idesc(256, 256);
-      int sa = 0, sb = 0;
-      uint32_t pa = 0, pb = 0, fph = 0;
-      bool first = true;
-      // one 256 x 512 x 512 product into the pair's accumulators: A from the ring (streamed) or from the resident h tile
-      auto product = [&](bool a_ring) {
-        if (!first) {                                        // accumulator drained (and, before the second product, h written)
-          mbar_wait_cluster(&ctl->acc_free, fph);
-          fph ^= 1u;
+      int st = 0;
+      uint32_t ph = 0, fph[2] = {0u, 0u};
+      bool used[2] = {false, false};
+      // accumulator half b drained by the epilogue (and, before the second product, the h columns of that half written)
+      auto wait_free = [&](int b) {
+        if (used[b]) {
+          mbar_wait_cluster(&ctl->acc_free[b], fph[b]);
+          fph[b] ^= 1u;
           tc_fence_after();
         }
-        first = false;
-        for (int kc = 0; kc < NKC; kc++) {
-          uint64_t da;
-          if (a_ring) {
-            mbar_wait(&ctl->full_a[sa], pa);
+        used[b] = true;
+      };
+      for (int t = cluster_id; t < q.m_tiles; t += n_clusters) {
+        for (int nh = 0; nh < 2; nh++) {
+          wait_free(nh);
+          const uint32_t d_tmem = tmem_base + (uint32_t)(nh * 256);
+          for (int kc = 0; kc < NKC; kc++) {
+            mbar_wait(&ctl->full[st], ph);
             tc_fence_after();
-            da = make_desc(sA + sa * CHUNK);
-          } else {
-            da = make_desc(sH + kc * CHUNK);
-          }
-#pragma unroll 1
-          for (int nh = 0; nh < 2; nh++) {
-            mbar_wait(&ctl->full_b[sb], pb);
-            tc_fence_after();
-            const uint64_t db = make_desc(sB + sb * CHUNK);
-            const uint32_t d_tmem = tmem_base + (uint32_t)(nh * 256);
+            const uint32_t sa = sRing + st * (2 * CHUNK);
+            const uint64_t da = make_desc(sa), db = make_desc(sa + CHUNK);
             if (!(q.dbg & 8)) {
 #pragma unroll
               for (int k = 0; k < KC / 16; k++)
                 umma_bf16<2>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
             }
-            umma_commit<2>(&ctl->empty_b[sb]);
-            if (++sb == NB) { sb = 0; pb ^= 1u; }
+            umma_commit<2>(&ctl->empty[st]);
+            if (++st == NSTG) { st = 0; ph ^= 1u; }
           }
-          if (a_ring) {
-            umma_commit<2>(&ctl->empty_a[sa]);
-            if (++sa == NA) { sa = 0; pa ^= 1u; }
-          }
+          umma_commit<2>(&ctl->acc_full[nh]);
         }
-        umma_commit<2>(&ctl->acc_full);
-      };
-      for (int t = cluster_id; t < q.m_tiles; t += n_clusters) {
-        product(true);
-        if (FFN) product(false);
+        if (FFN) {
+          wait_free(0);
+          wait_free(1);
+          for (int kc = 0; kc < NKC; kc++) {
+            mbar_wait(&ctl->full[st], ph);
+            tc_fence_after();
+            const uint32_t sb = sRing + st * (2 * CHUNK);
+            const uint64_t da = make_desc(sH + kc * CHUNK), db0 = make_desc(sb), db1 = make_desc(sb + CHUNK);
+            if (!(q.dbg & 8)) {
+#pragma unroll
+              for (int k = 0; k < KC / 16; k++)
+                umma_bf16<2>(tmem_base, da + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
+#pragma unroll
+              for (int k = 0; k < KC / 16; k++)
+                umma_bf16<2>(tmem_base + 256u, da + (uint64_t)(k * 2), db1 + (uint64_t)(k * 2), idesc, (kc | k) ? 1u : 0u);
+            }
+            umma_commit<2>(&ctl->empty[st]);
+            umma_commit<2>(&ctl->h_free[kc]);               // this K chunk of h may be overwritten (residual boxes)
+            if (++st == NSTG) { st = 0; ph ^= 1u; }
+          }
+          umma_commit<2>(&ctl->acc_full[0]);
+          umma_commit<2>(&ctl->acc_full[1]);
+        }
       }
     }
   } else {
@@ -264,172 +264,194 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     const int ehalf = (warp - 2) >> 2;            // which of the two warps sharing this lane quarter
     const int widx = warp - 2;
     const int row = quarter * 32 + lane;          // row inside the CTA's 128-row tile
-    const int sub = lane >> 3, cj = lane & 7;     // coalesced role: row 4i + sub, 16-byte chunk cj
     const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t s_stg = smem_u32(smem + C::OFF_STG + widx * 4096);
-    // row-statistics exchange between the two warps of a lane quarter: 256 B per warp
-    float2* xch_mine = reinterpret_cast<float2*>(FFN ? smem + C::OFF_STG + widx * 4096 : smem + C::OFF_XCH + widx * 256);
-    float2* xch_peer = reinterpret_cast<float2*>(FFN ? smem + C::OFF_STG + (widx ^ 4) * 4096 : smem + C::OFF_XCH + (widx ^ 4) * 256);
-    uint32_t full_ph = 0;
-    uint4 rr[8];
-    auto load_res = [&](int mw_, int nb_) {       // residual rows mw_ + 4i + sub, columns nb_ + 8 cj .. + 7
+    // this warp's four 64-column groups: two in each accumulator half
+    auto group_of = [&](int i) { return (i >> 1) * 4 + 2 * ehalf + (i & 1); };
+    // shared-memory address of 16-byte piece j of this thread's row in group g
+    auto piece = [&](int g, int j) { return sH + (uint32_t)(g * CHUNK) + stg_off(row, j); };
+    const uint32_t xch_mine = piece(5 + 2 * ehalf, 0), xch_peer = piece(5 + 2 * (ehalf ^ 1), 0);
+    uint32_t full_ph[2] = {0u, 0u};
+    uint32_t it = 0;
+    auto wait_acc = [&](int b) {
+      mbar_wait(&ctl->acc_full[b], full_ph[b]);
+      full_ph[b] ^= 1u;
+      tc_fence_after();
+    };
+    // residual boxes of column half hb for the tile whose first row (of this warp) is mw
+    auto load_boxes = [&](int hb, int mw) {
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&ctl->r_full[widx][hb], 2u * BOX);
 #pragma unroll
-      for (int i = 0; i < 8; i++) {
-        const int mr = mw_ + 4 * i + sub;
-        rr[i] = mr < q.M ? __ldg(reinterpret_cast<const uint4*>(q.residual + (long long)mr * FD + nb_) + cj) : make_uint4(0u, 0u, 0u, 0u);
+        for (int i = 0; i < 2; i++) {
+          const int g = hb * 4 + 2 * ehalf + i;
+          tma_load_2d<1>(sH + (uint32_t)(g * CHUNK + quarter * BOX), &mapR, smem_u32(&ctl->r_full[widx][hb]), g * 64, mw);
+        }
       }
     };
-    for (int t = cluster_id; t < q.m_tiles; t += n_clusters) {
+    if (!FFN && cluster_id < q.m_tiles) {          // proj+LN: the residual tile is prefetched a whole tile ahead
+      const int mw0 = (cluster_id * 2 + (int)rank) * TMR + quarter * 32;
+      load_boxes(0, mw0);
+      load_boxes(1, mw0);
+    }
+    for (int t = cluster_id; t < q.m_tiles; t += n_clusters, it++) {
       const int m_w = (t * 2 + (int)rank) * TMR + quarter * 32;      // first row of this warp
       if (FFN) {
-        // ---- first product done: h = relu(acc + b1) -> shared memory, K-major with the 128B swizzle (chunk g = K columns
-        //      64g .. 64g+63: row r at r * 128, 16-byte piece j at (j ^ (r & 7)) * 16), i.e. exactly what TMA writes
-        mbar_wait(&ctl->acc_full, full_ph);
-        full_ph ^= 1u;
-        tc_fence_after();
+        // ---- first product: h = relu(acc + b1) -> shared memory (A operand of the second product), half by half
+        for (int hb = 0; hb < 2; hb++) {
+          wait_acc(hb);
 #pragma unroll 1
-        for (int g = ehalf; g < NKC; g += 2) {
+          for (int i = 0; i < 2; i++) {
+            const int g = hb * 4 + 2 * ehalf + i;
+            uint32_t r0[32], r1[32];
+            tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
+            tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
+            tmem_ld_wait();
+            float v[64];
+#pragma unroll
+            for (int k = 0; k < 32; k++) { v[k] = __uint_as_float(r0[k]); v[32 + k] = __uint_as_float(r1[k]); }
+            add_bias64(v, q.b1, g * 64);
+            const act2_t zero2 = f2act2(0.0f, 0.0f);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+              act2_t h0 = __hmax2(f2act2(v[j * 8 + 0], v[j * 8 + 1]), zero2), h1 = __hmax2(f2act2(v[j * 8 + 2], v[j * 8 + 3]), zero2);
+              act2_t h2 = __hmax2(f2act2(v[j * 8 + 4], v[j * 8 + 5]), zero2), h3 = __hmax2(f2act2(v[j * 8 + 6], v[j * 8 + 7]), zero2);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(piece(g, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
+                           "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
+            }
+          }
+          // generic-proxy writes of h -> visible to the tensor core's async-proxy reads; accumulator half drained
+          fence_async_smem();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster_release(&ctl->acc_free[hb], 0);
+        }
+        // ---- while the second product runs: as soon as it has consumed K chunk g of h, this warp's box of that chunk
+        //      is refilled with the residual rows (TMA, warp-private)
+        for (int hb = 0; hb < 2; hb++) {
+          mbar_wait(&ctl->h_free[hb * 4 + 2 * ehalf], it & 1u);
+          mbar_wait(&ctl->h_free[hb * 4 + 2 * ehalf + 1], it & 1u);
+          load_boxes(hb, m_w);
+        }
+      }
+      // ---- last product: v = acc + b2 + residual; LayerNorm statistics per row; v parked in TMEM
+      float shift = 0.0f, s1 = 0.0f, s2 = 0.0f;
+      for (int hb = 0; hb < 2; hb++) {
+        wait_acc(hb);
+        mbar_wait(&ctl->r_full[widx][hb], it & 1u);
+#pragma unroll 1
+        for (int i = 0; i < 2; i++) {
+          const int g = hb * 4 + 2 * ehalf + i;
           uint32_t r0[32], r1[32];
           tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
           tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
           tmem_ld_wait();
           float v[64];
 #pragma unroll
-          for (int i = 0; i < 32; i++) { v[i] = __uint_as_float(r0[i]); v[32 + i] = __uint_as_float(r1[i]); }
-          add_bias64(v, q.b1, g * 64);
-          const act2_t zero2 = f2act2(0.0f, 0.0f);
-          const uint32_t hb = sH + (uint32_t)(g * CHUNK);
+          for (int k = 0; k < 32; k++) { v[k] = __uint_as_float(r0[k]); v[32 + k] = __uint_as_float(r1[k]); }
+          add_bias64(v, q.b2, g * 64);
 #pragma unroll
-          for (int j = 0; j < 8; j++) {
-            act2_t h0 = __hmax2(f2act2(v[j * 8 + 0], v[j * 8 + 1]), zero2), h1 = __hmax2(f2act2(v[j * 8 + 2], v[j * 8 + 3]), zero2);
-            act2_t h2 = __hmax2(f2act2(v[j * 8 + 4], v[j * 8 + 5]), zero2), h3 = __hmax2(f2act2(v[j * 8 + 6], v[j * 8 + 7]), zero2);
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(hb + stg_off(row, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
-                         "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
+          for (int j = 0; j < 8; j++) {           // residual: lane = row reads of the swizzled box, conflict-free
+            uint4 rv;
+            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(rv.x), "=r"(rv.y), "=r"(rv.z), "=r"(rv.w) : "r"(piece(g, j)) : "memory");
+            const act2_t* h = reinterpret_cast<const act2_t*>(&rv);
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              const float2 f = act22f2(h[e]);
+              v[j * 8 + e * 2] += f.x; v[j * 8 + e * 2 + 1] += f.y;
+            }
           }
+          if (hb == 0 && i == 0) shift = v[0];    // shifted sums: no cancellation for rows with a large mean
+#pragma unroll
+          for (int k = 0; k < 64; k++) { const float d = v[k] - shift; s1 += d; s2 = fmaf(d, d, s2); }
+          tmem_st32(t_row + (uint32_t)(g * 64), v);
+          tmem_st32(t_row + (uint32_t)(g * 64 + 32), v + 32);
         }
-        // generic-proxy writes of h -> visible to the tensor core's async-proxy reads; accumulator reads done
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster_release(&ctl->acc_free, 0);
-      }
-      // ---- last product done: v = acc + b2 + residual; LayerNorm statistics per row; v parked in TMEM
-      load_res(m_w, ehalf * 64);
-      mbar_wait(&ctl->acc_full, full_ph);
-      full_ph ^= 1u;
-      tc_fence_after();
-      float shift = 0.0f, s1 = 0.0f, s2 = 0.0f;
-#pragma unroll 1
-      for (int g = ehalf; g < NKC; g += 2) {
-        uint32_t r0[32], r1[32];
-        tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
-        tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
-        tmem_ld_wait();
-        float v[64];
-#pragma unroll
-        for (int i = 0; i < 32; i++) { v[i] = __uint_as_float(r0[i]); v[32 + i] = __uint_as_float(r1[i]); }
-        add_bias64(v, q.b2, g * 64);
-        // residual: coalesced registers -> warp-private swizzled tile -> lane = row
-#pragma unroll
-        for (int i = 0; i < 8; i++)
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(s_stg + stg_off(4 * i + sub, cj)), "r"(rr[i].x), "r"(rr[i].y), "r"(rr[i].z), "r"(rr[i].w) : "memory");
-        __syncwarp();
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-          uint4 rv;
-          asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(rv.x), "=r"(rv.y), "=r"(rv.z), "=r"(rv.w) : "r"(s_stg + stg_off(lane, j)) : "memory");
-          const act2_t* h = reinterpret_cast<const act2_t*>(&rv);
-#pragma unroll
-          for (int e = 0; e < 4; e++) {
-            const float2 f = act22f2(h[e]);
-            v[j * 8 + e * 2] += f.x; v[j * 8 + e * 2 + 1] += f.y;
-          }
-        }
-        __syncwarp();
-        if (g + 2 < NKC) load_res(m_w, (g + 2) * 64);
-        if (g == ehalf) shift = v[0];             // shifted sums: no cancellation for rows with a large mean
-#pragma unroll
-        for (int i = 0; i < 64; i++) { const float d = v[i] - shift; s1 += d; s2 = fmaf(d, d, s2); }
-        tmem_st32(t_row + (uint32_t)(g * 64), v);
-        tmem_st32(t_row + (uint32_t)(g * 64 + 32), v + 32);
       }
       tmem_st_wait();
-      // combine the two half rows (256 columns each): mean_w = shift + s1/256, M2_w = s2 - s1^2/256
+      // combine the two warps' 256 columns each: mean_w = shift + s1/256, M2_w = s2 - s1^2/256.  The exchange slot is the
+      // first piece of this thread's row in its last box (the residual there has been consumed).
       const float mean_w = shift + s1 * (1.0f / 256.0f), m2_w = s2 - s1 * s1 * (1.0f / 256.0f);
-      xch_mine[lane] = make_float2(mean_w, m2_w);
+      asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(xch_mine), "f"(mean_w), "f"(m2_w) : "memory");
       asm volatile("bar.sync %0, 64;" ::"r"(2 + quarter) : "memory");
-      const float2 o = xch_peer[lane];
+      float2 o;
+      asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(o.x), "=f"(o.y) : "r"(xch_peer) : "memory");
+      asm volatile("bar.sync %0, 64;" ::"r"(2 + quarter) : "memory");      // both have read before either overwrites its slot
       const float mean = 0.5f * (mean_w + o.x);
       const float dm = mean_w - o.x;
       const float var = (m2_w + o.y + dm * dm * 128.0f) * (1.0f / 512.0f);
       const float rstd = rsqrtf(var + q.eps);
-      if (FFN) {
-        // staging (and the statistics in it) no longer needed: the producer may refill the A ring underneath it.  The
-        // proxy fence orders this warp's generic-proxy accesses before the TMA (async-proxy) writes that follow.
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) mbar_arrive_local(&ctl->stg_free);
-      }
-      // ---- second pass over TMEM
+      const float nmr = -mean * rstd;
+      // ---- second pass over TMEM, half by half (the MMA issuer refills a half as soon as all warps have read it)
+      for (int hb = 0; hb < 2; hb++) {
 #pragma unroll 1
-      for (int g = ehalf; g < NKC; g += 2) {
-        uint32_t r0[32], r1[32];
-        tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
-        tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
-        tmem_ld_wait();
-        if (g + 2 >= NKC) {                        // last TMEM read of this warp: hand the accumulator back
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(&ctl->acc_free, 0);
+        for (int i = 0; i < 2; i++) {
+          const int g = hb * 4 + 2 * ehalf + i;
+          uint32_t r0[32], r1[32];
+          tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
+          tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
+          tmem_ld_wait();
+          if (i == 1) {                            // last TMEM read of this half: hand it back
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(&ctl->acc_free[hb], 0);
+          }
+          float v[64];
+#pragma unroll
+          for (int k = 0; k < 32; k++) { v[k] = fmaf(__uint_as_float(r0[k]), rstd, nmr); v[32 + k] = fmaf(__uint_as_float(r1[k]), rstd, nmr); }
+          if (FFN) {
+            // column sums over the 16 rows of each half warp: halving exchange, lane l (mod 16) ends with columns 4l .. 4l+3
+            const unsigned FULL = 0xffffffffu;
+            float a[32], b[16], c[8], d[4];
+            const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
+#pragma unroll
+            for (int k = 0; k < 32; k++) { const float keep = b3 ? v[32 + k] : v[k], send = b3 ? v[k] : v[32 + k]; a[k] = keep + __shfl_xor_sync(FULL, send, 8); }
+#pragma unroll
+            for (int k = 0; k < 16; k++) { const float keep = b2 ? a[16 + k] : a[k], send = b2 ? a[k] : a[16 + k]; b[k] = keep + __shfl_xor_sync(FULL, send, 4); }
+#pragma unroll
+            for (int k = 0; k < 8; k++) { const float keep = b1 ? b[8 + k] : b[k], send = b1 ? b[k] : b[8 + k]; c[k] = keep + __shfl_xor_sync(FULL, send, 2); }
+#pragma unroll
+            for (int k = 0; k < 4; k++) { const float keep = b0 ? c[4 + k] : c[k], send = b0 ? c[k] : c[4 + k]; d[k] = keep + __shfl_xor_sync(FULL, send, 1); }
+            const int mg = m_w + (lane >> 4) * 16;   // first row of this half warp's group
+            if (mg < q.M && !(q.dbg & 1))
+              *reinterpret_cast<float4*>(q.gs + (long long)(mg >> 4) * FD + g * 64 + (lane & 15) * 4) = make_float4(d[0], d[1], d[2], d[3]);
+          } else {
+            const float4* g4 = reinterpret_cast<const float4*>(q.gamma + g * 64);
+            const float4* b4 = reinterpret_cast<const float4*>(q.beta + g * 64);
+#pragma unroll
+            for (int c4 = 0; c4 < 16; c4++) {
+              const float4 gm = __ldg(g4 + c4), bt = __ldg(b4 + c4);
+              v[c4 * 4 + 0] = fmaf(v[c4 * 4 + 0], gm.x, bt.x); v[c4 * 4 + 1] = fmaf(v[c4 * 4 + 1], gm.y, bt.y);
+              v[c4 * 4 + 2] = fmaf(v[c4 * 4 + 2], gm.z, bt.z); v[c4 * 4 + 3] = fmaf(v[c4 * 4 + 3], gm.w, bt.w);
+            }
+            // the output rows replace the residual rows in this warp's box; one TMA store per box
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+              act2_t h0 = f2act2(v[j * 8 + 0], v[j * 8 + 1]), h1 = f2act2(v[j * 8 + 2], v[j * 8 + 3]);
+              act2_t h2 = f2act2(v[j * 8 + 4], v[j * 8 + 5]), h3 = f2act2(v[j * 8 + 6], v[j * 8 + 7]);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(piece(g, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
+                           "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0 && !(q.dbg & 1)) {
+              tma_store_2d(&mapO, sH + (uint32_t)(g * CHUNK + quarter * BOX), g * 64, m_w);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+          }
         }
-        float v[64];
-#pragma unroll
-        for (int i = 0; i < 32; i++) { v[i] = (__uint_as_float(r0[i]) - mean) * rstd; v[32 + i] = (__uint_as_float(r1[i]) - mean) * rstd; }
-        if (FFN) {
-          // column sums over the 16 rows of each half warp: halving exchange, lane l (mod 16) ends with columns 4l .. 4l+3
-          const unsigned FULL = 0xffffffffu;
-          float a[32], b[16], c[8], d[4];
-          const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
-#pragma unroll
-          for (int i = 0; i < 32; i++) { const float keep = b3 ? v[32 + i] : v[i], send = b3 ? v[i] : v[32 + i]; a[i] = keep + __shfl_xor_sync(FULL, send, 8); }
-#pragma unroll
-          for (int i = 0; i < 16; i++) { const float keep = b2 ? a[16 + i] : a[i], send = b2 ? a[i] : a[16 + i]; b[i] = keep + __shfl_xor_sync(FULL, send, 4); }
-#pragma unroll
-          for (int i = 0; i < 8; i++) { const float keep = b1 ? b[8 + i] : b[i], send = b1 ? b[i] : b[8 + i]; c[i] = keep + __shfl_xor_sync(FULL, send, 2); }
-#pragma unroll
-          for (int i = 0; i < 4; i++) { const float keep = b0 ? c[4 + i] : c[i], send = b0 ? c[i] : c[4 + i]; d[i] = keep + __shfl_xor_sync(FULL, send, 1); }
-          const int mg = m_w + (lane >> 4) * 16;   // first row of this half warp's group
-          if (mg < q.M && !(q.dbg & 1))
-            *reinterpret_cast<float4*>(q.gs + (long long)(mg >> 4) * FD + g * 64 + (lane & 15) * 4) = make_float4(d[0], d[1], d[2], d[3]);
-        } else {
-          const float4* g4 = reinterpret_cast<const float4*>(q.gamma + g * 64);
-          const float4* b4 = reinterpret_cast<const float4*>(q.beta + g * 64);
-#pragma unroll
-          for (int c4 = 0; c4 < 16; c4++) {
-            const float4 gm = __ldg(g4 + c4), bt = __ldg(b4 + c4);
-            v[c4 * 4 + 0] = fmaf(v[c4 * 4 + 0], gm.x, bt.x); v[c4 * 4 + 1] = fmaf(v[c4 * 4 + 1], gm.y, bt.y);
-            v[c4 * 4 + 2] = fmaf(v[c4 * 4 + 2], gm.z, bt.z); v[c4 * 4 + 3] = fmaf(v[c4 * 4 + 3], gm.w, bt.w);
-          }
-#pragma unroll
-          for (int j = 0; j < 8; j++) {
-            act2_t h0 = f2act2(v[j * 8 + 0], v[j * 8 + 1]), h1 = f2act2(v[j * 8 + 2], v[j * 8 + 3]);
-            act2_t h2 = f2act2(v[j * 8 + 4], v[j * 8 + 5]), h3 = f2act2(v[j * 8 + 6], v[j * 8 + 7]);
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(s_stg + stg_off(lane, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
-                         "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
-          }
-          __syncwarp();
-          char* ob = (char*)(q.out + (long long)(m_w + sub) * FD + g * 64 + cj * 8);
-          const int rows_left = q.M - m_w - sub;   // row 4i + sub is stored iff 4i < rows_left
-#pragma unroll
-          for (int i = 0; i < 8; i++) {
-            uint4 ov;
-            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(ov.x), "=r"(ov.y), "=r"(ov.z), "=r"(ov.w) : "r"(s_stg + stg_off(4 * i + sub, cj)) : "memory");
-            if (4 * i < rows_left && !(q.dbg & 1)) *reinterpret_cast<uint4*>(ob + (size_t)i * (4 * FD * sizeof(act_t))) = ov;
-          }
-          __syncwarp();
+      }
+      if (!FFN) {
+        // boxes free again once the stores have read them: prefetch the next tile's residual rows
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+        if (t + n_clusters < q.m_tiles) {
+          const int mw_next = ((t + n_clusters) * 2 + (int)rank) * TMR + quarter * 32;
+          load_boxes(0, mw_next);
+          load_boxes(1, mw_next);
         }
       }
     }
+    if (!FFN && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -466,12 +488,12 @@ int ffn_enabled()
 }
 
 template <bool FFN>
-int launch_ffn(const CUtensorMap& mA, const CUtensorMap& mW1, const CUtensorMap& mW2, const FfnParams& q, int num_sms, cudaStream_t st)
+int launch_ffn(const CUtensorMap& mA, const CUtensorMap& mW1, const CUtensorMap& mW2, const CUtensorMap& mR, const CUtensorMap& mO,
+               const FfnParams& q, int num_sms, cudaStream_t st)
 {
-  using C = FCfg<FFN>;
   static bool configured = false;
   if (!configured) {
-    FPB_CUDA(cudaFuncSetAttribute(ffn_kernel<FFN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    FPB_CUDA(cudaFuncSetAttribute(ffn_kernel<FFN>, cudaFuncAttributeMaxDynamicSharedMemorySize, FFN_SMEM));
     configured = true;
   }
   int clusters = num_sms / 2;
@@ -480,7 +502,7 @@ int launch_ffn(const CUtensorMap& mA, const CUtensorMap& mW1, const CUtensorMap&
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(clusters * 2, 1, 1);
   cfg.blockDim = dim3(NTHREADS, 1, 1);
-  cfg.dynamicSmemBytes = C::SMEM;
+  cfg.dynamicSmemBytes = FFN_SMEM;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -489,7 +511,7 @@ int launch_ffn(const CUtensorMap& mA, const CUtensorMap& mW1, const CUtensorMap&
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = fpb_pdl_enabled() ? 2 : 1;
-  FPB_CUDA(cudaLaunchKernelEx(&cfg, ffn_kernel<FFN>, mA, mW1, mW2, q));
+  FPB_CUDA(cudaLaunchKernelEx(&cfg, ffn_kernel<FFN>, mA, mW1, mW2, mR, mO, q));
   fpb_count_launch();
   return FPB_OK;
 }
@@ -505,18 +527,22 @@ int proj_ln_512(const void* A, const void* W, const float* b, const void* residu
   if (!ffn_enabled() || M <= 0 || M > 0x7fffff00LL || !aligned16(A) || !aligned16(W) || !aligned16(residual) || !aligned16(out) ||
       !aligned16(b) || !aligned16(gamma) || !aligned16(beta))
     return FPB_ERR_UNSUPPORTED;
-  CUtensorMap mA, mW;
+  CUtensorMap mA, mW, mR, mO;
   int num_sms = 0;
   int rc = fpb_tiled_map_act(A, M, FD, FD, TMR, &mA, &num_sms);
   if (rc) return rc;
   rc = fpb_tiled_map_act(W, FD, FD, FD, TMR, &mW, nullptr);
   if (rc) return rc;
+  rc = fpb_tiled_map_act(residual, M, FD, FD, 32, &mR, nullptr);
+  if (rc) return rc;
+  rc = fpb_tiled_map_act(out, M, FD, FD, 32, &mO, nullptr);
+  if (rc) return rc;
   FfnParams q;
   memset(&q, 0, sizeof(q));
   q.M = (int)M; q.m_tiles = fpb_cdiv(M, 2 * TMR);
-  q.residual = (const act_t*)residual; q.b2 = b; q.gamma = gamma; q.beta = beta; q.eps = eps; q.out = (act_t*)out;
+  q.b2 = b; q.gamma = gamma; q.beta = beta; q.eps = eps;
   { const char* e = getenv("FPB_FFN_DBG"); q.dbg = e ? atoi(e) : 0; }
-  return launch_ffn<false>(mA, mW, mW, q, num_sms, st);
+  return launch_ffn<false>(mA, mW, mW, mR, mO, q, num_sms, st);
 }
 
 // pooled[g] = mean over the `tokens` rows of group g of LayerNorm(x + relu(x . W1^T + b1) . W2^T + b2) * gamma + beta
@@ -528,7 +554,7 @@ int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const 
   if (!ffn_enabled() || groups <= 0 || tokens <= 0 || tokens % 16 != 0 || M > 0x7fffff00LL || !aligned16(x) || !aligned16(W1) ||
       !aligned16(W2) || !aligned16(b1) || !aligned16(b2) || !aligned16(gamma) || !aligned16(beta) || !aligned16(gs) || !aligned16(pooled))
     return FPB_ERR_UNSUPPORTED;
-  CUtensorMap mA, mW1, mW2;
+  CUtensorMap mA, mW1, mW2, mR;
   int num_sms = 0;
   int rc = fpb_tiled_map_act(x, M, FD, FD, TMR, &mA, &num_sms);
   if (rc) return rc;
@@ -536,12 +562,14 @@ int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const 
   if (rc) return rc;
   rc = fpb_tiled_map_act(W2, FD, FD, FD, TMR, &mW2, nullptr);
   if (rc) return rc;
+  rc = fpb_tiled_map_act(x, M, FD, FD, 32, &mR, nullptr);
+  if (rc) return rc;
   FfnParams q;
   memset(&q, 0, sizeof(q));
   q.M = (int)M; q.m_tiles = fpb_cdiv(M, 2 * TMR);
-  q.residual = (const act_t*)x; q.b1 = b1; q.b2 = b2; q.eps = eps; q.gs = gs;
+  q.b1 = b1; q.b2 = b2; q.eps = eps; q.gs = gs;
   { const char* e = getenv("FPB_FFN_DBG"); q.dbg = e ? atoi(e) : 0; }
-  rc = launch_ffn<true>(mA, mW1, mW2, q, num_sms, st);
+  rc = launch_ffn<true>(mA, mW1, mW2, mR, mR, q, num_sms, st);
   if (rc) return rc;
   pool_groups_kernel<<<groups, 128, 0, st>>>(gs, gamma, beta, pooled, tokens / 16, 1.0f / (float)tokens);
   FPB_LAUNCH_CHECK();

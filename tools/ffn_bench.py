@@ -16,6 +16,7 @@ def main():
   ap.add_argument('--reps', type=int, default=10)
   ap.add_argument('--dtype', default='fp16', choices=['fp16', 'bf16'])
   ap.add_argument('--no-flush', action='store_true')
+  ap.add_argument('--only', default='', help='proj | ffn | lin')
   a = ap.parse_args()
   dt = torch.float16 if a.dtype == 'fp16' else torch.bfloat16
   check(lib().fpb_debug_set_precision(2 if a.dtype == 'fp16' else 1))
@@ -39,7 +40,9 @@ def main():
   def lin_old():
     check(lib().fpb_debug_igemm(4, ptr(A), ptr(W2), ptr(out), M, 512, 512, 1, 1, 512, 1, 1, 1, 1, 1, 0, ptr(ones), ptr(b2), ptr(res), 0, 1, stream()))
 
-  for name, fn in (('proj+LN (ffn_kernel<0>)', proj_ln), ('FFN+LN+sum (ffn_kernel<1> + pool)', ffn), ('one K=512 linear, old kernel', lin_old)):
+  for name, fn in (('proj+LN (ffn_kernel<0>)', proj_ln), ('FFN+LN+sum (ffn_kernel<1> + pool)', ffn), ('lin: one K=512 linear, old kernel', lin_old)):
+    if a.only and not name.lower().startswith(a.only):
+      continue
     for _ in range(2):
       fn()
     torch.cuda.synchronize()
