@@ -52,6 +52,7 @@ _SIGS = {
   'fpb_debug_set_precision': (ci, [ci]),
   'fpb_debug_attention': (ci, [vp, vp, ctypes.c_longlong, vp, vp, ci, vp]),
   'fpb_debug_ffn': (ci, [ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, ctypes.c_longlong, ci, vp]),
+  'fpb_debug_ffn_stamps': (ci, [vp, ci]),
   'fpb_refine_forward': (ci, [vp, vp, ci, vp, vp, vp, vp]),
   'fpb_refine_forward_shared_b': (ci, [vp, vp, ci, vp, vp, vp, vp]),
   'fpb_score_features': (ci, [vp, vp, ci, vp, vp, vp]),

@@ -693,6 +693,13 @@ FPB_EXPORT int fpb_debug_ffn(int mode, const void* A, const void* W1, const floa
   return rc;
 }
 
+// dev tool: clock64 stamps recorded by the last row-tile kernel launched with FPB_FFN_DBG=2048 (tools/ffn_bench.py --stamps)
+FPB_EXPORT int fpb_debug_ffn_stamps(long long* out_host, int n)
+{
+  FPB_CHECK_ARG(out_host && n > 0);
+  return DK->ffn_debug_stamps(out_host, n);
+}
+
 // unit-test entry of the fused self-attention kernel (net_attn.cu)
 FPB_EXPORT int fpb_debug_attention(const void* qk, const void* vt, long long vt_pitch, const float* bv, void* ctx, int groups,
                                    void* stream)

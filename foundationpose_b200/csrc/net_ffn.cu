@@ -51,6 +51,10 @@ struct FfnParams {
   int dbg;
 };
 
+// FPB_FFN_DBG & 2048: the first epilogue warp of CTA 0 records clock64 stamps of its phases here (dev tool:
+// fpb_debug_ffn_stamps copies them out; tools/ffn_bench.py --stamps)
+__device__ long long g_ffn_stamps[512];
+
 struct FfnCtl {
   uint64_t full[NSTG], empty[NSTG];
   uint64_t acc_full[2], acc_free[2];       // per accumulator half (TMEM columns 0-255 / 256-511)
@@ -69,36 +73,6 @@ constexpr int DATA_BYTES = OFF_RING + NSTG * 2 * CHUNK;
 constexpr int FFN_SMEM = DATA_BYTES + 1024 + (int)sizeof(FfnCtl);
 static_assert(FFN_SMEM <= 232448, "shared memory budget");
 
-__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity)
-{
-  const uint32_t addr = smem_u32(bar);
-  uint32_t ok = 0;
-  long long t0 = 0;
-  for (uint32_t spin = 0; !ok; spin++) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.b32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (!ok && (spin & 1023u) == 1023u) {
-      const long long now = clock64();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 8000000000LL) __trap();
-    }
-  }
-}
-// release at cluster scope: orders this thread's earlier shared-memory writes (the h tile) before the arrival
-__device__ __forceinline__ void mbar_arrive_cluster_release(uint64_t* bar, uint32_t cta)
-{
-  asm volatile(
-      "{\n\t.reg .b32 ra;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
-      "r"(cta)
-      : "memory");
-}
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v)
 {
   asm volatile(
@@ -118,29 +92,19 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// v[i] += bias[n0 + i], 64 columns, warp-uniform 16-byte loads
-__device__ __forceinline__ void add_bias64(float (&v)[64], const float* __restrict__ bias, int n0)
-{
-  const float4* b4 = reinterpret_cast<const float4*>(bias + n0);
-#pragma unroll
-  for (int c = 0; c < 16; c++) {
-    const float4 b = __ldg(b4 + c);
-    v[c * 4 + 0] += b.x; v[c * 4 + 1] += b.y; v[c * 4 + 2] += b.z; v[c * 4 + 3] += b.w;
-  }
-}
-
 // mapA: rows of the streamed A operand, box 64 x 128.  mapW1 / mapW2: weights [512][512], box 64 x 128.
 // mapR: residual rows, box 64 x 32.  mapO: output rows (proj+LN), box 64 x 32.
 template <bool FFN>
 __global__ void __launch_bounds__(NTHREADS, 1)
 ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapW1,
            const __grid_constant__ CUtensorMap mapW2, const __grid_constant__ CUtensorMap mapR,
-           const __grid_constant__ CUtensorMap mapO, const FfnParams q)
+           const __grid_constant__ CUtensorMap mapO, const __grid_constant__ FfnParams q)
 {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   FfnCtl* ctl = (FfnCtl*)(smem + DATA_BYTES);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);     // provably warp-uniform: constant-bank indexing
+  const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   pdl_launch_dependents();
@@ -208,7 +172,7 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       // accumulator half b drained by the epilogue (and, before the second product, the h columns of that half written)
       auto wait_free = [&](int b) {
         if (used[b]) {
-          mbar_wait_cluster(&ctl->acc_free[b], fph[b]);
+          mbar_wait(&ctl->acc_free[b], fph[b]);
           fph[b] ^= 1u;
           tc_fence_after();
         }
@@ -265,8 +229,6 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     const int widx = warp - 2;
     const int row = quarter * 32 + lane;          // row inside the CTA's 128-row tile
     const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    // this warp's four 64-column groups: two in each accumulator half
-    auto group_of = [&](int i) { return (i >> 1) * 4 + 2 * ehalf + (i & 1); };
     // shared-memory address of 16-byte piece j of this thread's row in group g
     auto piece = [&](int g, int j) { return sH + (uint32_t)(g * CHUNK) + stg_off(row, j); };
     const uint32_t xch_mine = piece(5 + 2 * ehalf, 0), xch_peer = piece(5 + 2 * (ehalf ^ 1), 0);
@@ -293,37 +255,58 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       load_boxes(0, mw0);
       load_boxes(1, mw0);
     }
+    // The epilogue works in slabs of 32 columns (one tcgen05.ld.x32): slab j = 0..3 of half hb is columns
+    // 64 * g + 32 * (j & 1) of group g = 4 hb + 2 ehalf + (j >> 1).  The TMEM load of slab j+1 is issued before slab j is
+    // processed, and the per-column parameters (bias / gamma / beta: warp-uniform 16-byte loads) and the residual pieces
+    // are requested BEFORE the wait for slab j, so that none of these latencies is exposed per slab.
+    uint32_t rb[2][32];
+    int n_st = 0;
+    auto stamp = [&]() {
+      if ((q.dbg & 2048) && blockIdx.x == 0 && warp == 2 && lane == 0 && n_st < 512) g_ffn_stamps[n_st++] = clock64();
+    };
     for (int t = cluster_id; t < q.m_tiles; t += n_clusters, it++) {
       const int m_w = (t * 2 + (int)rank) * TMR + quarter * 32;      // first row of this warp
       if (FFN) {
         // ---- first product: h = relu(acc + b1) -> shared memory (A operand of the second product), half by half
-        for (int hb = 0; hb < 2; hb++) {
-          wait_acc(hb);
 #pragma unroll 1
-          for (int i = 0; i < 2; i++) {
-            const int g = hb * 4 + 2 * ehalf + i;
-            uint32_t r0[32], r1[32];
-            tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
-            tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
-            tmem_ld_wait();
-            float v[64];
+        for (int hb = 0; hb < 2; hb++) {
+          const int g0 = hb * 4 + 2 * ehalf;
+          stamp();
+          wait_acc(hb);
+          stamp();
+          tmem_ld32_nowait(t_row + (uint32_t)(g0 * 64), rb[0]);
 #pragma unroll
-            for (int k = 0; k < 32; k++) { v[k] = __uint_as_float(r0[k]); v[32 + k] = __uint_as_float(r1[k]); }
-            add_bias64(v, q.b1, g * 64);
+          for (int j = 0; j < 4; j++) {
+            const int g = g0 + (j >> 1), c0 = g * 64 + (j & 1) * 32;
+            float4 bb[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) bb[k] = __ldg(reinterpret_cast<const float4*>(q.b1 + c0) + k);
+            tmem_ld_wait();
+            if (j < 3) tmem_ld32_nowait(t_row + (uint32_t)((g0 + ((j + 1) >> 1)) * 64 + ((j + 1) & 1) * 32), rb[(j + 1) & 1]);
+            const uint32_t(&r)[32] = rb[j & 1];
             const act2_t zero2 = f2act2(0.0f, 0.0f);
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-              act2_t h0 = __hmax2(f2act2(v[j * 8 + 0], v[j * 8 + 1]), zero2), h1 = __hmax2(f2act2(v[j * 8 + 2], v[j * 8 + 3]), zero2);
-              act2_t h2 = __hmax2(f2act2(v[j * 8 + 4], v[j * 8 + 5]), zero2), h3 = __hmax2(f2act2(v[j * 8 + 6], v[j * 8 + 7]), zero2);
-              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(piece(g, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
+            for (int p = 0; p < 4; p++) {
+              const float4 ba = bb[2 * p], bc = bb[2 * p + 1];
+              act2_t h0 = __hmax2(f2act2(__uint_as_float(r[p * 8 + 0]) + ba.x, __uint_as_float(r[p * 8 + 1]) + ba.y), zero2);
+              act2_t h1 = __hmax2(f2act2(__uint_as_float(r[p * 8 + 2]) + ba.z, __uint_as_float(r[p * 8 + 3]) + ba.w), zero2);
+              act2_t h2 = __hmax2(f2act2(__uint_as_float(r[p * 8 + 4]) + bc.x, __uint_as_float(r[p * 8 + 5]) + bc.y), zero2);
+              act2_t h3 = __hmax2(f2act2(__uint_as_float(r[p * 8 + 6]) + bc.z, __uint_as_float(r[p * 8 + 7]) + bc.w), zero2);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(piece(g, (j & 1) * 4 + p)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
                            "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
             }
           }
-          // generic-proxy writes of h -> visible to the tensor core's async-proxy reads; accumulator half drained
+          // generic-proxy writes of h -> visible to the tensor core's async-proxy reads; accumulator half drained.  The
+          // hand-over to the MMA issuer (possibly in the other CTA of the pair) is: these st.shared -> fence.proxy.async
+          // (completes only when they are performed) -> remote mbarrier arrive -> the issuer's wait -> tcgen05.mma, whose
+          // operand reads happen in the SM that owns the shared memory.  A cluster-scope release / acquire pair on the
+          // barrier is not needed for that chain and was measured to be expensive: the acquire compiles to CCTL.IVALL,
+          // which wipes this SM's L1 twice per tile (every per-column parameter load of the epilogue then misses), the
+          // release to MEMBAR.ALL.GPU on the critical path between the two products.
           fence_async_smem();
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster_release(&ctl->acc_free[hb], 0);
+          if (lane == 0) mbar_arrive_cluster(&ctl->acc_free[hb], 0);
         }
         // ---- while the second product runs: as soon as it has consumed K chunk g of h, this warp's box of that chunk
         //      is refilled with the residual rows (TMA, warp-private)
@@ -335,39 +318,53 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       }
       // ---- last product: v = acc + b2 + residual; LayerNorm statistics per row; v parked in TMEM
       float shift = 0.0f, s1 = 0.0f, s2 = 0.0f;
-      for (int hb = 0; hb < 2; hb++) {
-        wait_acc(hb);
-        mbar_wait(&ctl->r_full[widx][hb], it & 1u);
 #pragma unroll 1
-        for (int i = 0; i < 2; i++) {
-          const int g = hb * 4 + 2 * ehalf + i;
-          uint32_t r0[32], r1[32];
-          tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
-          tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
+      for (int hb = 0; hb < 2; hb++) {
+        const int g0 = hb * 4 + 2 * ehalf;
+        stamp();
+        wait_acc(hb);
+        stamp();
+        mbar_wait(&ctl->r_full[widx][hb], it & 1u);
+        stamp();
+        tmem_ld32_nowait(t_row + (uint32_t)(g0 * 64), rb[0]);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const int g = g0 + (j >> 1), c0 = g * 64 + (j & 1) * 32;
+          float4 bb[8];
+          uint4 rv[4];
+#pragma unroll
+          for (int k = 0; k < 8; k++) bb[k] = __ldg(reinterpret_cast<const float4*>(q.b2 + c0) + k);
+#pragma unroll
+          for (int p = 0; p < 4; p++)           // residual: lane = row reads of the swizzled box, conflict-free
+            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(rv[p].x), "=r"(rv[p].y), "=r"(rv[p].z), "=r"(rv[p].w) : "r"(piece(g, (j & 1) * 4 + p)) : "memory");
           tmem_ld_wait();
-          float v[64];
+          if (j < 3) tmem_ld32_nowait(t_row + (uint32_t)((g0 + ((j + 1) >> 1)) * 64 + ((j + 1) & 1) * 32), rb[(j + 1) & 1]);
+          const uint32_t(&r)[32] = rb[j & 1];
+          float v[32];
 #pragma unroll
-          for (int k = 0; k < 32; k++) { v[k] = __uint_as_float(r0[k]); v[32 + k] = __uint_as_float(r1[k]); }
-          add_bias64(v, q.b2, g * 64);
-#pragma unroll
-          for (int j = 0; j < 8; j++) {           // residual: lane = row reads of the swizzled box, conflict-free
-            uint4 rv;
-            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(rv.x), "=r"(rv.y), "=r"(rv.z), "=r"(rv.w) : "r"(piece(g, j)) : "memory");
-            const act2_t* h = reinterpret_cast<const act2_t*>(&rv);
-#pragma unroll
-            for (int e = 0; e < 4; e++) {
-              const float2 f = act22f2(h[e]);
-              v[j * 8 + e * 2] += f.x; v[j * 8 + e * 2 + 1] += f.y;
-            }
+          for (int p = 0; p < 4; p++) {
+            const float4 ba = bb[2 * p], bc = bb[2 * p + 1];
+            const act2_t* h = reinterpret_cast<const act2_t*>(&rv[p]);
+            const float2 f0 = act22f2(h[0]), f1 = act22f2(h[1]), f2 = act22f2(h[2]), f3 = act22f2(h[3]);
+            v[p * 8 + 0] = (__uint_as_float(r[p * 8 + 0]) + ba.x) + f0.x; v[p * 8 + 1] = (__uint_as_float(r[p * 8 + 1]) + ba.y) + f0.y;
+            v[p * 8 + 2] = (__uint_as_float(r[p * 8 + 2]) + ba.z) + f1.x; v[p * 8 + 3] = (__uint_as_float(r[p * 8 + 3]) + ba.w) + f1.y;
+            v[p * 8 + 4] = (__uint_as_float(r[p * 8 + 4]) + bc.x) + f2.x; v[p * 8 + 5] = (__uint_as_float(r[p * 8 + 5]) + bc.y) + f2.y;
+            v[p * 8 + 6] = (__uint_as_float(r[p * 8 + 6]) + bc.z) + f3.x; v[p * 8 + 7] = (__uint_as_float(r[p * 8 + 7]) + bc.w) + f3.y;
           }
-          if (hb == 0 && i == 0) shift = v[0];    // shifted sums: no cancellation for rows with a large mean
+          if (hb == 0 && j == 0) shift = v[0];    // shifted sums: no cancellation for rows with a large mean
+          float t1 = 0.0f, t2 = 0.0f;            // two accumulator pairs shorten the dependent chains
 #pragma unroll
-          for (int k = 0; k < 64; k++) { const float d = v[k] - shift; s1 += d; s2 = fmaf(d, d, s2); }
-          tmem_st32(t_row + (uint32_t)(g * 64), v);
-          tmem_st32(t_row + (uint32_t)(g * 64 + 32), v + 32);
+          for (int k = 0; k < 32; k += 2) {
+            const float d0 = v[k] - shift, d1 = v[k + 1] - shift;
+            s1 += d0; s2 = fmaf(d0, d0, s2);
+            t1 += d1; t2 = fmaf(d1, d1, t2);
+          }
+          s1 += t1; s2 += t2;
+          tmem_st32(t_row + (uint32_t)c0, v);
         }
       }
       tmem_st_wait();
+      stamp();
       // combine the two warps' 256 columns each: mean_w = shift + s1/256, M2_w = s2 - s1^2/256.  The exchange slot is the
       // first piece of this thread's row in its last box (the residual there has been consumed).
       const float mean_w = shift + s1 * (1.0f / 256.0f), m2_w = s2 - s1 * s1 * (1.0f / 256.0f);
@@ -381,65 +378,73 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
       const float var = (m2_w + o.y + dm * dm * 128.0f) * (1.0f / 512.0f);
       const float rstd = rsqrtf(var + q.eps);
       const float nmr = -mean * rstd;
+      stamp();
       // ---- second pass over TMEM, half by half (the MMA issuer refills a half as soon as all warps have read it)
-      for (int hb = 0; hb < 2; hb++) {
 #pragma unroll 1
-        for (int i = 0; i < 2; i++) {
-          const int g = hb * 4 + 2 * ehalf + i;
-          uint32_t r0[32], r1[32];
-          tmem_ld32_nowait(t_row + (uint32_t)(g * 64), r0);
-          tmem_ld32_nowait(t_row + (uint32_t)(g * 64 + 32), r1);
+      for (int hb = 0; hb < 2; hb++) {
+        const int g0 = hb * 4 + 2 * ehalf;
+        if (hb) stamp();
+        tmem_ld32_nowait(t_row + (uint32_t)(g0 * 64), rb[0]);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const int g = g0 + (j >> 1), c0 = g * 64 + (j & 1) * 32;
+          float4 gm[8], bt[8];
+          if (!FFN) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) { gm[k] = __ldg(reinterpret_cast<const float4*>(q.gamma + c0) + k); bt[k] = __ldg(reinterpret_cast<const float4*>(q.beta + c0) + k); }
+          }
           tmem_ld_wait();
-          if (i == 1) {                            // last TMEM read of this half: hand it back
+          if (j < 3) {
+            tmem_ld32_nowait(t_row + (uint32_t)((g0 + ((j + 1) >> 1)) * 64 + ((j + 1) & 1) * 32), rb[(j + 1) & 1]);
+          } else {                                 // last TMEM read of this half: hand it back
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(&ctl->acc_free[hb], 0);
           }
-          float v[64];
+          const uint32_t(&r)[32] = rb[j & 1];
+          float v[32];
 #pragma unroll
-          for (int k = 0; k < 32; k++) { v[k] = fmaf(__uint_as_float(r0[k]), rstd, nmr); v[32 + k] = fmaf(__uint_as_float(r1[k]), rstd, nmr); }
+          for (int k = 0; k < 32; k++) v[k] = fmaf(__uint_as_float(r[k]), rstd, nmr);
           if (FFN) {
-            // column sums over the 16 rows of each half warp: halving exchange, lane l (mod 16) ends with columns 4l .. 4l+3
+            // column sums over the 16 rows of each half warp: halving exchange, lane l (mod 16) ends with columns 2l, 2l+1
             const unsigned FULL = 0xffffffffu;
-            float a[32], b[16], c[8], d[4];
+            float a[16], b[8], c[4], d[2];
             const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
 #pragma unroll
-            for (int k = 0; k < 32; k++) { const float keep = b3 ? v[32 + k] : v[k], send = b3 ? v[k] : v[32 + k]; a[k] = keep + __shfl_xor_sync(FULL, send, 8); }
+            for (int k = 0; k < 16; k++) { const float keep = b3 ? v[16 + k] : v[k], send = b3 ? v[k] : v[16 + k]; a[k] = keep + __shfl_xor_sync(FULL, send, 8); }
 #pragma unroll
-            for (int k = 0; k < 16; k++) { const float keep = b2 ? a[16 + k] : a[k], send = b2 ? a[k] : a[16 + k]; b[k] = keep + __shfl_xor_sync(FULL, send, 4); }
+            for (int k = 0; k < 8; k++) { const float keep = b2 ? a[8 + k] : a[k], send = b2 ? a[k] : a[8 + k]; b[k] = keep + __shfl_xor_sync(FULL, send, 4); }
 #pragma unroll
-            for (int k = 0; k < 8; k++) { const float keep = b1 ? b[8 + k] : b[k], send = b1 ? b[k] : b[8 + k]; c[k] = keep + __shfl_xor_sync(FULL, send, 2); }
+            for (int k = 0; k < 4; k++) { const float keep = b1 ? b[4 + k] : b[k], send = b1 ? b[k] : b[4 + k]; c[k] = keep + __shfl_xor_sync(FULL, send, 2); }
 #pragma unroll
-            for (int k = 0; k < 4; k++) { const float keep = b0 ? c[4 + k] : c[k], send = b0 ? c[k] : c[4 + k]; d[k] = keep + __shfl_xor_sync(FULL, send, 1); }
+            for (int k = 0; k < 2; k++) { const float keep = b0 ? c[2 + k] : c[k], send = b0 ? c[k] : c[2 + k]; d[k] = keep + __shfl_xor_sync(FULL, send, 1); }
             const int mg = m_w + (lane >> 4) * 16;   // first row of this half warp's group
             if (mg < q.M && !(q.dbg & 1))
-              *reinterpret_cast<float4*>(q.gs + (long long)(mg >> 4) * FD + g * 64 + (lane & 15) * 4) = make_float4(d[0], d[1], d[2], d[3]);
+              *reinterpret_cast<float2*>(q.gs + (long long)(mg >> 4) * FD + c0 + (lane & 15) * 2) = make_float2(d[0], d[1]);
           } else {
-            const float4* g4 = reinterpret_cast<const float4*>(q.gamma + g * 64);
-            const float4* b4 = reinterpret_cast<const float4*>(q.beta + g * 64);
-#pragma unroll
-            for (int c4 = 0; c4 < 16; c4++) {
-              const float4 gm = __ldg(g4 + c4), bt = __ldg(b4 + c4);
-              v[c4 * 4 + 0] = fmaf(v[c4 * 4 + 0], gm.x, bt.x); v[c4 * 4 + 1] = fmaf(v[c4 * 4 + 1], gm.y, bt.y);
-              v[c4 * 4 + 2] = fmaf(v[c4 * 4 + 2], gm.z, bt.z); v[c4 * 4 + 3] = fmaf(v[c4 * 4 + 3], gm.w, bt.w);
-            }
             // the output rows replace the residual rows in this warp's box; one TMA store per box
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-              act2_t h0 = f2act2(v[j * 8 + 0], v[j * 8 + 1]), h1 = f2act2(v[j * 8 + 2], v[j * 8 + 3]);
-              act2_t h2 = f2act2(v[j * 8 + 4], v[j * 8 + 5]), h3 = f2act2(v[j * 8 + 6], v[j * 8 + 7]);
-              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(piece(g, j)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
+            for (int p = 0; p < 4; p++) {
+              const float4 ga = gm[2 * p], gc = gm[2 * p + 1], ba = bt[2 * p], bc = bt[2 * p + 1];
+              act2_t h0 = f2act2(fmaf(v[p * 8 + 0], ga.x, ba.x), fmaf(v[p * 8 + 1], ga.y, ba.y));
+              act2_t h1 = f2act2(fmaf(v[p * 8 + 2], ga.z, ba.z), fmaf(v[p * 8 + 3], ga.w, ba.w));
+              act2_t h2 = f2act2(fmaf(v[p * 8 + 4], gc.x, bc.x), fmaf(v[p * 8 + 5], gc.y, bc.y));
+              act2_t h3 = f2act2(fmaf(v[p * 8 + 6], gc.z, bc.z), fmaf(v[p * 8 + 7], gc.w, bc.w));
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(piece(g, (j & 1) * 4 + p)), "r"(*reinterpret_cast<uint32_t*>(&h0)),
                            "r"(*reinterpret_cast<uint32_t*>(&h1)), "r"(*reinterpret_cast<uint32_t*>(&h2)), "r"(*reinterpret_cast<uint32_t*>(&h3)) : "memory");
             }
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0 && !(q.dbg & 1)) {
-              tma_store_2d(&mapO, sH + (uint32_t)(g * CHUNK + quarter * BOX), g * 64, m_w);
-              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            if (j & 1) {                           // box of group g complete
+              fence_async_smem();
+              __syncwarp();
+              if (lane == 0 && !(q.dbg & 1)) {
+                tma_store_2d(&mapO, sH + (uint32_t)(g * CHUNK + quarter * BOX), g * 64, m_w);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+              }
             }
           }
         }
       }
+      stamp();
       if (!FFN) {
         // boxes free again once the stores have read them: prefetch the next tile's residual rows
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -573,6 +578,13 @@ int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const 
   if (rc) return rc;
   pool_groups_kernel<<<groups, 128, 0, st>>>(gs, gamma, beta, pooled, tokens / 16, 1.0f / (float)tokens);
   FPB_LAUNCH_CHECK();
+  return FPB_OK;
+}
+
+int ffn_debug_stamps(long long* out_host, int n)
+{
+  if (n > 512) n = 512;
+  FPB_CUDA(cudaMemcpyFromSymbol(out_host, g_ffn_stamps, (size_t)n * sizeof(long long)));
   return FPB_OK;
 }
 

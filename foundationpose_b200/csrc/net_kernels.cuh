@@ -111,6 +111,7 @@ int proj_ln_512(const void* A, const void* W, const float* b, const void* residu
 /* pooled[g] = mean_t LayerNorm(x + relu(x . W1^T + b1) . W2^T + b2) * gamma + beta; gs: (groups*tokens/16) x 512 floats scratch */ \
 int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const void* W2, const float* b2, const float* gamma, \
                           const float* beta, float eps, float* gs, float* pooled, int groups, int tokens, cudaStream_t st); \
+int ffn_debug_stamps(long long* out_host, int n); /* dev tool: clock64 stamps of the last FPB_FFN_DBG=2048 launch */ \
 
 namespace bf16 { FPB_NET_KERNEL_DECLS }
 namespace f16 { FPB_NET_KERNEL_DECLS }
@@ -135,9 +136,10 @@ struct NetKernels {
   decltype(&bf16::f32_to_act) f32_to_act;
   decltype(&bf16::proj_ln_512) proj_ln_512;
   decltype(&bf16::ffn_ln_token_mean_512) ffn_ln_token_mean_512;
+  decltype(&bf16::ffn_debug_stamps) ffn_debug_stamps;
 };
 #define FPB_NET_KERNEL_TABLE(ns)                                                                                        \
   {ns::ref_gemm, ns::tc_gemm, ns::tc2_gemm, ns::tc3_gemm, ns::stem_pack_weights, ns::stem_conv, ns::tc2_force_cta_group, \
    ns::tc_attention, ns::softmax_rows, ns::layernorm_rows, ns::token_mean, ns::token_mean_multi,                        \
    ns::layernorm_token_mean_512, ns::small_linear, ns::transpose_v, ns::f32_to_act, ns::proj_ln_512,              \
-   ns::ffn_ln_token_mean_512}
+   ns::ffn_ln_token_mean_512, ns::ffn_debug_stamps}

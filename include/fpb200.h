@@ -245,6 +245,9 @@ int fpb_debug_ffn(int mode, const void* A, const void* W1, const float* b1, cons
                   const void* residual, const float* gamma, const float* beta, void* out, float* scratch, long long M,
                   int tokens, void* stream);
 
+/* dev tool: clock64 stamps of the epilogue phases recorded by the last row-tile kernel launched with FPB_FFN_DBG=2048 */
+int fpb_debug_ffn_stamps(long long* out_host, int n);
+
 /* operand type (FPB_PREC_BF16 default, or FPB_PREC_FP16) the fpb_debug_* unit-test entries run in */
 int fpb_debug_set_precision(int precision);
 

@@ -17,6 +17,7 @@ def main():
   ap.add_argument('--dtype', default='fp16', choices=['fp16', 'bf16'])
   ap.add_argument('--no-flush', action='store_true')
   ap.add_argument('--only', default='', help='proj | ffn | lin')
+  ap.add_argument('--stamps', action='store_true', help='run with FPB_FFN_DBG=2048 in the environment: print the phase stamps of CTA 0')
   a = ap.parse_args()
   dt = torch.float16 if a.dtype == 'fp16' else torch.bfloat16
   check(lib().fpb_debug_set_precision(2 if a.dtype == 'fp16' else 1))
@@ -55,6 +56,18 @@ def main():
       torch.cuda.synchronize()
       ts.append(e0.elapsed_time(e1) * 1e3)
     ts.sort()
+    if a.stamps and 'lin' not in name:
+      import ctypes
+      import numpy as np
+      buf = np.zeros(512, dtype=np.int64)
+      check(lib().fpb_debug_ffn_stamps(buf.ctypes.data_as(ctypes.c_void_p), 512))
+      per = 14 if 'FFN' in name else 10
+      st = buf[:per * 6].reshape(-1, per)
+      print('stamps (cycles, deltas within a tile; last column = gap to the next tile):')
+      for i in range(len(st)):
+        d = np.diff(st[i]).tolist()
+        nxt = int(st[i + 1][0] - st[i][-1]) if i + 1 < len(st) and st[i + 1][0] > 0 else -1
+        print('  tile', i, d, nxt)
     gf = 2.0 * M * 512 * 512 * (2 if 'FFN' in name else 1)
     print(f'{name}: median {ts[len(ts)//2]:.1f} us, min {ts[0]:.1f} us, {gf / ts[len(ts)//2] / 1e6:.0f} TFLOP/s (M={M})')
 
