@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_PATH = os.path.join(_HERE, 'libfpb200.so')
+_PATH = os.environ.get('FPB_LIB_PATH') or os.path.join(_HERE, 'libfpb200.so')   # FPB_LIB_PATH: dev A/B of two builds
 _lib = None
 
 vp = ctypes.c_void_p

@@ -16,6 +16,11 @@ OBJ = os.path.join(HERE, 'build')
 
 ARCH = ['-gencode', 'arch=compute_100a,code=sm_100a']
 COMMON = ['-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC,-fvisibility=hidden', '--expt-relaxed-constexpr']
+# dev only (same-box A/B of compile-time variants): FPB_EXTRA_NVCC_FLAGS='-DFOO' FPB_LIB_OUT=/path/lib.so python -m foundationpose_b200.build
+COMMON += os.environ.get('FPB_EXTRA_NVCC_FLAGS', '').split()
+if os.environ.get('FPB_LIB_OUT'):
+  OUT = os.environ['FPB_LIB_OUT']
+  OBJ = OUT + '.build'
 # (source, extra flags, object suffix).  The network kernel units are compiled twice: bf16 operands (namespace bf16) and,
 # with -DFPB_ACT_FP16, IEEE fp16 operands (namespace f16) -- csrc/act_type.cuh.
 NET_UNITS = ['net_ref.cu', 'net_tc.cu', 'net_tc2.cu', 'net_tc3.cu', 'net_stem.cu', 'net_attn.cu', 'net_ffn.cu']

@@ -61,11 +61,19 @@ struct Cfg {
   static constexpr int B_STAGE_BYTES = B_ROWS * 128;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   // per epilogue warp: 4 KB output staging + 4 KB residual staging + 4 KB positional-embedding staging + scale/shift
-  static constexpr int EPI_WARPS = BN >= 128 ? 8 : 4;         // 2 warps per TMEM lane quarter split the 64-column groups
+  // 2 warps per TMEM lane quarter split the 64-column groups -- except for the CTA-pair kernel of the long-K layers
+  // (BN = 256, CG = 2, K >= 2304): its main loop (>= 18 k cycles per tile) hides a 4-warp epilogue, and the 16 KB of
+  // staging this frees buys a 6th pipeline stage.  The operand stream of these layers is latency x bandwidth bound
+  // (bytes in flight / ~2.5 k cycles of loaded TMA latency), so ring depth is throughput (FPB_TC2_EPI8 = old layout).
+#ifdef FPB_TC2_EPI8
+  static constexpr int EPI_WARPS = BN >= 128 ? 8 : 4;
+#else
+  static constexpr int EPI_WARPS = (BN >= 128 && !(BN == 256 && CG == 2)) ? 8 : 4;
+#endif
   // one 4 KB staging tile per epilogue warp (residual in, positional embedding in, result out share it) plus a
   // double-buffered scale/shift table shared by the CTA
   static constexpr int EPI_WARP_BYTES = 4096;
-  static constexpr int EPI_BYTES = 8 * EPI_WARP_BYTES + 2 * (2 * BN * 4);
+  static constexpr int EPI_BYTES = EPI_WARPS * EPI_WARP_BYTES + 2 * (2 * BN * 4);
   static constexpr int STAGES_RAW = (224 * 1024 - EPI_BYTES) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
@@ -323,7 +331,7 @@ tc2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         //      travel the same way in the opposite direction.
         uint8_t* ew = epi_smem + (warp - 2) * C::EPI_WARP_BYTES;
         const uint32_t s_out = smem_u32(ew), s_res = s_out, s_pe = s_out;   // one tile, used in turn (guarded by __syncwarp)
-        float* ss = (float*)(epi_smem + 8 * C::EPI_WARP_BYTES) + (tc & 1u) * (2 * BN);   // scale[BN], shift[BN] of this n-tile
+        float* ss = (float*)(epi_smem + C::EPI_WARPS * C::EPI_WARP_BYTES) + (tc & 1u) * (2 * BN);   // scale[BN], shift[BN] of this n-tile
         const int m_w = (mt * CG + (int)rank) * TM + quarter * 32;   // first row of this warp
         const int sub = lane >> 3, cj = lane & 7;               // coalesced role: row 4i+sub, 16-byte chunk cj
         int mw_next = 0, n0_next = 0;

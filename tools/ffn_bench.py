@@ -41,7 +41,14 @@ def main():
   def lin_old():
     check(lib().fpb_debug_igemm(4, ptr(A), ptr(W2), ptr(out), M, 512, 512, 1, 1, 512, 1, 1, 1, 1, 1, 0, ptr(ones), ptr(b2), ptr(res), 0, 1, stream()))
 
-  for name, fn in (('proj+LN (ffn_kernel<0>)', proj_ln), ('FFN+LN+sum (ffn_kernel<1> + pool)', ffn), ('lin: one K=512 linear, old kernel', lin_old)):
+  vt = torch.empty(512, M, device='cuda', dtype=dt)
+
+  def vt_proj():     # V^T = Wv . X^T + bv, stored channel-major (the attention kernel's K-major B operand)
+    check(lib().fpb_debug_igemm_ex(4, ptr(A), ptr(W2), ptr(vt), M, 512, 512, 1, 1, 512, 1, 1, 1, 1, 1, 0, 0, 0, 0, None, ptr(b2), None, 0, 2,
+                                   stream()))
+
+  for name, fn in (('proj+LN (ffn_kernel<0>)', proj_ln), ('FFN+LN+sum (ffn_kernel<1> + pool)', ffn), ('lin: one K=512 linear, old kernel', lin_old),
+                   ('vt: V^T projection (transposed output)', vt_proj)):
     if a.only and not name.lower().startswith(a.only):
       continue
     for _ in range(2):
