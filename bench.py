@@ -362,7 +362,7 @@ def main():
   dom = time_dominant_kernel(torch)
   step_flops = n_hyp * (ITERS * FLOP_REFINE + FLOP_SCORE)
   traffic = traffic_from = None
-  for name in ('ncu_conv6_r02.json', 'ncu_conv6_r01.json'):      # dram__bytes_read+write of this kernel, one ncu --set full capture
+  for name in ('ncu_conv6_r02g.json', 'ncu_conv6_r02.json', 'ncu_conv6_r01.json'):      # dram__bytes_read+write of this kernel, one ncu --set full capture
     prof = os.path.join(ROOT, 'profiles', name)
     if os.path.exists(prof):
       pj = json.load(open(prof))
