@@ -10,7 +10,7 @@ from bench import make_estimator, ITERS  # noqa: E402
 from foundationpose_b200 import synthetic  # noqa: E402
 
 scene = synthetic.make_scene(2)
-est, _, _ = make_estimator(scene, 'bf16')
+est, _, _ = make_estimator(scene, os.environ.get('FPB_PRECISION', 'fp16'))
 n = int(os.environ.get('FPB_SHARD', '32'))
 est.rot_grid = est.rot_grid[:n].contiguous()
 d_rgb, d_depth, d_mask = (torch.as_tensor(scene[k]).cuda() for k in ('rgb', 'depth', 'mask'))

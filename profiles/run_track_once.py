@@ -10,7 +10,7 @@ from bench import make_estimator  # noqa: E402
 from foundationpose_b200 import synthetic  # noqa: E402
 
 scene = synthetic.make_scene(2)
-est, _, _ = make_estimator(scene, 'bf16')
+est, _, _ = make_estimator(scene, os.environ.get('FPB_PRECISION', 'fp16'))
 d_rgb, d_depth = (torch.as_tensor(scene[k]).cuda() for k in ('rgb', 'depth'))
 est.register(K=scene['K'], rgb=scene['rgb'], depth=scene['depth'], ob_mask=scene['mask'], iteration=5)
 for _ in range(3):
