@@ -38,6 +38,8 @@ struct fpb_net {
   float* w32;
   uint16_t* w16;           // 16-bit shadow of the blob in the operand type of `precision` (bf16 or fp16)
   uint16_t* w_stem;        // stem weights stacked for net_stem.cu ([9][128][64], 16-bit modes only)
+  cudaStream_t st2;        // refine, 16-bit modes: the rot head runs on this stream beside the trans head (fork / join by events)
+  cudaEvent_t ev_fork, ev_join;
   Conv conv[15];
   size_t pe;
   EncLayer head[2];   // refine: trans, rot
@@ -100,6 +102,7 @@ struct Ws {
   char *c0, *c1, *c2, *c3, *ab0, *ab1, *ab2, *d0, *d1, *d2, *qkv, *P, *vt, *ctx, *y1, *y, *ff;
   float *scores, *pooled;
   char* splitk;       // split-K scratch of the persistent GEMM kernel (small batches only)
+  char* splitk2;      // the same for the head that runs on the second stream
   size_t total;
 };
 constexpr size_t SPLITK_BYTES = 16u << 20;
@@ -129,6 +132,7 @@ Ws carve(char* base, int n, size_t esz)
   w.scores = (float*)take((size_t)n * HEADS * TOK * TOKP * sizeof(float));
   w.pooled = (float*)take((size_t)n * D * sizeof(float));
   w.splitk = take(SPLITK_BYTES);
+  w.splitk2 = take(SPLITK_BYTES);
   w.total = o;
   return w;
 }
@@ -159,6 +163,13 @@ struct Ctx {
 };
 
 #define RET(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+
+bool head_streams()
+{
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("FPB_HEAD_STREAMS"); v = e ? atoi(e) : 1; }
+  return v != 0;
+}
 
 bool use_halo()
 {
@@ -356,6 +367,11 @@ FPB_EXPORT int fpb_net_create(fpb_net** out, int kind, int precision, const void
     rc = k->stem_pack_weights(n->w32 + n->conv[0].w, 0, n->w_stem, st);
     if (rc) return rc;
   }
+  if (n->kind == FPB_NET_REFINE && is16(precision)) {
+    FPB_CUDA(cudaStreamCreateWithFlags(&n->st2, cudaStreamNonBlocking));
+    FPB_CUDA(cudaEventCreateWithFlags(&n->ev_fork, cudaEventDisableTiming));
+    FPB_CUDA(cudaEventCreateWithFlags(&n->ev_join, cudaEventDisableTiming));
+  }
   FPB_CUDA(cudaStreamSynchronize(st));
   *out = n;
   return FPB_OK;
@@ -367,6 +383,7 @@ FPB_EXPORT int fpb_net_destroy(fpb_net* n)
   cudaFree(n->w32);
   cudaFree(n->w16);
   cudaFree(n->w_stem);
+  if (n->st2) { cudaStreamDestroy(n->st2); cudaEventDestroy(n->ev_fork); cudaEventDestroy(n->ev_join); }
   delete n;
   return FPB_OK;
 }
@@ -445,8 +462,28 @@ static int refine_forward_impl(const fpb_net* net, const void* AB, int N, void* 
       in = stage;
     }
     RET(run_encoders(c, in, n, w, shared_b));
-    RET(encoder_layer(c, net->head[0], n, w, out_trans + (size_t)b0 * 3));
-    RET(encoder_layer(c, net->head[1], n, w, out_rot + (size_t)b0 * net->rot_dim));
+    if (c.bf && net->st2 && head_streams()) {
+      // The two pose heads are independent chains over the same tokens: the rot head runs on a second stream (fork / join
+      // by events, also under stream capture), so that its kernels fill the SMs the trans head's partial last waves leave
+      // idle -- and, for a single hypothesis (track_one: 4-16 CTAs per kernel), the two chains simply run side by side.
+      // Its buffers alias encoder buffers that are dead once the tokens (w.d0) exist; results do not depend on the overlap.
+      Ws w2 = w;
+      w2.qkv = w.c0; w2.ctx = w.d1; w2.y = w.d2; w2.y1 = w.ab1; w2.ff = w.ab2;
+      w2.scores = (float*)w.c1; w2.pooled = (float*)w.c2;
+      Ctx c2 = c;
+      c2.st = net->st2;
+      c2.splitk = c.splitk ? w.splitk2 : nullptr;
+      FPB_CUDA(cudaEventRecord(net->ev_fork, c.st));
+      FPB_CUDA(cudaStreamWaitEvent(net->st2, net->ev_fork, 0));
+      const int rc0 = encoder_layer(c, net->head[0], n, w, out_trans + (size_t)b0 * 3);
+      const int rc1 = rc0 ? rc0 : encoder_layer(c2, net->head[1], n, w2, out_rot + (size_t)b0 * net->rot_dim);
+      FPB_CUDA(cudaEventRecord(net->ev_join, net->st2));          // always join, also on an error: the fork is pending
+      FPB_CUDA(cudaStreamWaitEvent(c.st, net->ev_join, 0));
+      RET(rc1);
+    } else {
+      RET(encoder_layer(c, net->head[0], n, w, out_trans + (size_t)b0 * 3));
+      RET(encoder_layer(c, net->head[1], n, w, out_rot + (size_t)b0 * net->rot_dim));
+    }
   }
   return FPB_OK;
 }
