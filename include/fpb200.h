@@ -176,6 +176,9 @@ size_t fpb_score_cross_ws_bytes(int L, int bs);
  * FPB_IN_PITCH pixels, image pixels at columns [FPB_IN_XOFF, FPB_IN_XOFF+S), pad pixels must be zero. */
 #define FPB_IN_PITCH 168
 #define FPB_IN_XOFF 4
+/* fpb_refine_forward is stream-ordered on `stream` for the caller; internally the rot head runs on a private stream of
+ * the net beside the trans head (forked from / joined to `stream` by events, legal under stream capture).  One net (and
+ * workspace) per concurrently used stream / host thread. */
 int fpb_refine_forward(const fpb_net* net, const void* AB, int N, void* ws, float* out_trans, float* out_rot,
                        void* stream);
 /* same network, AB = [N+1,S,FPB_IN_PITCH,8]: N rendered crops + ONE observed crop shared by all N hypotheses.  In the
