@@ -415,8 +415,8 @@ static int encoder_layer(const Ctx& c, const EncLayer& e, int n, Ws& w, float* o
     int rc = c.k->proj_ln_512(w.ctx, c.W(e.att.out.w), c.F(e.att.out.b), w.d0, c.F(e.n1g), c.F(e.n1b), 1e-5f, w.y, R, c.st);
     if (rc == FPB_OK) {
       rc = c.k->ffn_ln_token_mean_512(w.y, c.W(e.l1.w), c.F(e.l1.b), c.W(e.l2.w), c.F(e.l2.b), c.F(e.n2g), c.F(e.n2b), 1e-5f,
-                                      w.scores, w.pooled, n, TOK, c.st);
-      if (rc == FPB_OK) return c.k->small_linear(w.pooled, c.F(e.fin.w), c.F(e.fin.b), out3, n, D, e.fin.N, c.st);
+                                      w.scores, w.pooled, n, TOK, c.F(e.fin.w), c.F(e.fin.b), out3, e.fin.N, c.st);
+      if (rc == FPB_OK) return FPB_OK;
     }
     if (rc != FPB_ERR_UNSUPPORTED) return rc;
   }
@@ -724,7 +724,7 @@ FPB_EXPORT int fpb_debug_ffn(int mode, const void* A, const void* W1, const floa
   } else {
     FPB_CHECK_ARG(W1 && b1 && scratch && tokens > 0 && M % tokens == 0);
     rc = DK->ffn_ln_token_mean_512(A, W1, b1, W2, b2, gamma, beta, 1e-5f, scratch, (float*)out, (int)(M / tokens), tokens,
-                                   (cudaStream_t)stream);
+                                   nullptr, nullptr, nullptr, 0, (cudaStream_t)stream);
   }
   if (rc == FPB_ERR_UNSUPPORTED) fpb_set_error("fpb_debug_ffn: disabled (FPB_FFN=0) or unsupported alignment / shape");
   return rc;

@@ -467,11 +467,16 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   }
 }
 
-// pooled[h][c] = gamma[c] * (sum of the `per` group rows of hypothesis h, in order) / tokens + beta[c]
+// pooled[h][c] = gamma[c] * (sum of the `per` group rows of hypothesis h, in order) / tokens + beta[c], then the output
+// Linear(512, n_out) of the head on the pooled row (mean over tokens commutes with it): out[h][n] = pooled[h] . Wf[n] + bf[n].
+// One block per hypothesis: 128 threads x 4 columns for the pooling, then one warp per output (same lane-strided fmaf order
+// + butterfly sum as small_linear_kernel, which this replaces together with the separate pooling launch).
 __global__ void __launch_bounds__(128) pool_groups_kernel(const float* __restrict__ gs, const float* __restrict__ gamma,
-                                                          const float* __restrict__ beta, float* __restrict__ out, int per,
-                                                          float inv_tokens)
+                                                          const float* __restrict__ beta, float* __restrict__ pooled, int per,
+                                                          float inv_tokens, const float* __restrict__ Wf,
+                                                          const float* __restrict__ bf, float* __restrict__ out, int n_out)
 {
+  __shared__ float row[FD];
   const int c = threadIdx.x * 4;
   const float4* src = reinterpret_cast<const float4*>(gs + (long long)blockIdx.x * per * FD + c);
   float4 s = src[0];
@@ -480,9 +485,20 @@ __global__ void __launch_bounds__(128) pool_groups_kernel(const float* __restric
     s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
   }
   const float4 gm = *reinterpret_cast<const float4*>(gamma + c), bt = *reinterpret_cast<const float4*>(beta + c);
-  *reinterpret_cast<float4*>(out + (long long)blockIdx.x * FD + c) =
-      make_float4(fmaf(s.x * inv_tokens, gm.x, bt.x), fmaf(s.y * inv_tokens, gm.y, bt.y), fmaf(s.z * inv_tokens, gm.z, bt.z),
-                  fmaf(s.w * inv_tokens, gm.w, bt.w));
+  const float4 p = make_float4(fmaf(s.x * inv_tokens, gm.x, bt.x), fmaf(s.y * inv_tokens, gm.y, bt.y), fmaf(s.z * inv_tokens, gm.z, bt.z),
+                               fmaf(s.w * inv_tokens, gm.w, bt.w));
+  *reinterpret_cast<float4*>(pooled + (long long)blockIdx.x * FD + c) = p;
+  if (!Wf) return;
+  *reinterpret_cast<float4*>(row + c) = p;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int n = warp; n < n_out; n += 4) {
+    float a = 0.0f;
+    for (int k = lane; k < FD; k += 32) a = fmaf(row[k], Wf[(long long)n * FD + k], a);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if (lane == 0) out[(long long)blockIdx.x * n_out + n] = a + (bf ? bf[n] : 0.0f);
+  }
 }
 
 int ffn_enabled()
@@ -551,9 +567,11 @@ int proj_ln_512(const void* A, const void* W, const float* b, const void* residu
 }
 
 // pooled[g] = mean over the `tokens` rows of group g of LayerNorm(x + relu(x . W1^T + b1) . W2^T + b2) * gamma + beta
-// x: [groups * tokens][512] 16-bit rows; gs: scratch of (groups * tokens / 16) x 512 floats; tokens % 16 == 0
+// x: [groups * tokens][512] 16-bit rows; gs: scratch of (groups * tokens / 16) x 512 floats; tokens % 16 == 0.
+// Wf != null: also out[g][n] = pooled[g] . Wf[n] + bf[n] for n < n_out (the head's output Linear) in the pooling launch.
 int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const void* W2, const float* b2, const float* gamma,
-                          const float* beta, float eps, float* gs, float* pooled, int groups, int tokens, cudaStream_t st)
+                          const float* beta, float eps, float* gs, float* pooled, int groups, int tokens, const float* Wf,
+                          const float* bf, float* out, int n_out, cudaStream_t st)
 {
   const long long M = (long long)groups * tokens;
   if (!ffn_enabled() || groups <= 0 || tokens <= 0 || tokens % 16 != 0 || M > 0x7fffff00LL || !aligned16(x) || !aligned16(W1) ||
@@ -576,7 +594,7 @@ int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const 
   { const char* e = getenv("FPB_FFN_DBG"); q.dbg = e ? atoi(e) : 0; }
   rc = launch_ffn<true>(mA, mW1, mW2, mR, mR, q, num_sms, st);
   if (rc) return rc;
-  pool_groups_kernel<<<groups, 128, 0, st>>>(gs, gamma, beta, pooled, tokens / 16, 1.0f / (float)tokens);
+  pool_groups_kernel<<<groups, 128, 0, st>>>(gs, gamma, beta, pooled, tokens / 16, 1.0f / (float)tokens, Wf, bf, out, n_out);
   FPB_LAUNCH_CHECK();
   return FPB_OK;
 }

@@ -109,8 +109,10 @@ int f32_to_act(const float* in, void* out, long long n, cudaStream_t st); /* fp3
 int proj_ln_512(const void* A, const void* W, const float* b, const void* residual, const float* gamma, const float* beta, \
                 float eps, void* out, long long M, cudaStream_t st); \
 /* pooled[g] = mean_t LayerNorm(x + relu(x . W1^T + b1) . W2^T + b2) * gamma + beta; gs: (groups*tokens/16) x 512 floats scratch */ \
+/* Wf != null: the head's output Linear on the pooled row in the same pooling launch: out[g][n] = pooled[g] . Wf[n] + bf[n] */ \
 int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const void* W2, const float* b2, const float* gamma, \
-                          const float* beta, float eps, float* gs, float* pooled, int groups, int tokens, cudaStream_t st); \
+                          const float* beta, float eps, float* gs, float* pooled, int groups, int tokens, const float* Wf, \
+                          const float* bf, float* out, int n_out, cudaStream_t st); \
 int ffn_debug_stamps(long long* out_host, int n); /* dev tool: clock64 stamps of the last FPB_FFN_DBG=2048 launch */ \
 
 namespace bf16 { FPB_NET_KERNEL_DECLS }
