@@ -501,6 +501,13 @@ __global__ void __launch_bounds__(128) pool_groups_kernel(const float* __restric
   }
 }
 
+int ffn_dbg()
+{
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("FPB_FFN_DBG"); v = e ? atoi(e) : 0; }
+  return v;
+}
+
 int ffn_enabled()
 {
   static int v = -1;
@@ -562,7 +569,7 @@ int proj_ln_512(const void* A, const void* W, const float* b, const void* residu
   memset(&q, 0, sizeof(q));
   q.M = (int)M; q.m_tiles = fpb_cdiv(M, 2 * TMR);
   q.b2 = b; q.gamma = gamma; q.beta = beta; q.eps = eps;
-  { const char* e = getenv("FPB_FFN_DBG"); q.dbg = e ? atoi(e) : 0; }
+  q.dbg = ffn_dbg();
   return launch_ffn<false>(mA, mW, mW, mR, mO, q, num_sms, st);
 }
 
@@ -591,7 +598,7 @@ int ffn_ln_token_mean_512(const void* x, const void* W1, const float* b1, const 
   memset(&q, 0, sizeof(q));
   q.M = (int)M; q.m_tiles = fpb_cdiv(M, 2 * TMR);
   q.b1 = b1; q.b2 = b2; q.eps = eps; q.gs = gs;
-  { const char* e = getenv("FPB_FFN_DBG"); q.dbg = e ? atoi(e) : 0; }
+  q.dbg = ffn_dbg();
   rc = launch_ffn<true>(mA, mW1, mW2, mR, mR, q, num_sms, st);
   if (rc) return rc;
   pool_groups_kernel<<<groups, 128, 0, st>>>(gs, gamma, beta, pooled, tokens / 16, 1.0f / (float)tokens, Wf, bf, out, n_out);
