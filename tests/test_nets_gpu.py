@@ -451,14 +451,16 @@ def test_row_tile_ffn_layernorm_token_mean(prec, M):
   try:
     A, _, W1, W2, b1, b2, gamma, beta = _ffn_inputs(M, 17 + M % 89, dt)
     G = M // 400
-    out = torch.zeros(G, 512, device='cuda')
-    scratch = torch.zeros(M // 16, 512, device='cuda')
+    out = torch.full((G + 1, 512), 7.0, device='cuda')     # one guard row behind each output: must stay untouched
+    scratch = torch.full((M // 16 + 16, 512), 7.0, device='cuda')
     for _ in range(2):                                       # twice: scratch / pipeline state of a first call must not matter
       check(lib().fpb_debug_ffn(1, ptr(A), ptr(W1), ptr(b1), ptr(W2), ptr(b2), None, ptr(gamma), ptr(beta), ptr(out),
                                 ptr(scratch), M, 400, stream()))
     torch.cuda.synchronize()
   finally:
     check(lib().fpb_debug_set_precision(1))
+  assert (out[G:] == 7.0).all() and (scratch[M // 16:] == 7.0).all()
+  out = out[:G]
   h = torch.relu(A.double() @ W1.double().t() + b1.double()).to(dt).double()
   ref = _ln(h @ W2.double().t() + b2.double() + A.double(), gamma, beta).reshape(G, 400, 512).mean(1)
   err = (out.double() - ref).abs().max().item()
