@@ -38,7 +38,7 @@ constexpr int TMR = 128;                   // rows per CTA
 constexpr int CHUNK = TMR * 128;           // one [128 rows x 64 K] operand block, 16 KB
 constexpr int BOX = 32 * 128;              // one warp's [32 rows x 64 columns] piece of a chunk, 4 KB
 constexpr int NTHREADS = 320;
-constexpr int NSTG = 3;                    // operand ring: stages of two 16 KB blocks
+constexpr int NSTG_MAX = 5;                // operand ring: stages of two 16 KB blocks (3 beside the h tile, 5 in proj+LN)
 
 struct FfnParams {
   int M, m_tiles;                          // rows, tiles of 256 rows
@@ -56,22 +56,31 @@ struct FfnParams {
 __device__ long long g_ffn_stamps[512];
 
 struct FfnCtl {
-  uint64_t full[NSTG], empty[NSTG];
+  uint64_t full[NSTG_MAX], empty[NSTG_MAX];
   uint64_t acc_full[2], acc_free[2];       // per accumulator half (TMEM columns 0-255 / 256-511)
   uint64_t h_free[NKC];                    // FFN: K chunk kc of the h tile has been consumed by the second product
   uint64_t r_full[8][2];                   // per epilogue warp and column half: its residual boxes have landed
   uint32_t tmem_base;
 };
 
-// Shared memory: [R/H region: 8 chunks x 16 KB][ring: NSTG x 32 KB][ctl].  The R/H region holds, per chunk g (columns
-// 64g .. 64g+63) and row r, 128 bytes at g*CHUNK + r*128 with the 16-byte pieces XOR-swizzled by (r & 7) -- the layout TMA
-// writes / reads with SWIZZLE_128B and tcgen05.mma reads as a K-major operand.  It is, in turn: the residual tile
-// (TMA-loaded in warp-private [32 rows x 64 columns] boxes), FFN: the h tile (A operand of the second product, written
-// by the epilogue threads), proj+LN: the output tile (written in place over the residual, TMA-stored box by box).
-constexpr int OFF_RING = NKC * CHUNK;
-constexpr int DATA_BYTES = OFF_RING + NSTG * 2 * CHUNK;
-constexpr int FFN_SMEM = DATA_BYTES + 1024 + (int)sizeof(FfnCtl);
-static_assert(FFN_SMEM <= 232448, "shared memory budget");
+// Shared memory: [R/H region][ring: NSTG x 32 KB][ctl].  The R/H region holds, per chunk (64 columns) and row r, 128 bytes
+// at chunk*CHUNK + r*128 with the 16-byte pieces XOR-swizzled by (r & 7) -- the layout TMA writes / reads with SWIZZLE_128B
+// and tcgen05.mma reads as a K-major operand.
+//   FFN:     8 chunks (128 KB): the h tile (A operand of the second product, written by the epilogue threads), then,
+//            chunk by chunk as the second product releases it, the residual boxes.  3 ring stages fit beside it.
+//   proj+LN: 4 chunks (64 KB) used in turn for the residual boxes of accumulator half 0, those of half 1 (loaded when the
+//            first pass over half 0 has consumed the former), the output boxes of half 0 and the output boxes of half 1
+//            (group g lives in chunk g & 3).  The 64 KB this saves make the ring 5 stages deep: the kernel is bound by
+//            bytes in flight, so ring depth is throughput.
+template <bool FFN>
+struct FLayout {
+  static constexpr int R_CHUNKS = FFN ? NKC : NKC / 2;
+  static constexpr int NSTG = FFN ? 3 : 5;
+  static constexpr int OFF_RING = R_CHUNKS * CHUNK;
+  static constexpr int DATA_BYTES = OFF_RING + NSTG * 2 * CHUNK;
+  static constexpr int SMEM = DATA_BYTES + 1024 + (int)sizeof(FfnCtl);
+  static_assert(NSTG <= NSTG_MAX && SMEM <= 232448, "shared memory budget");
+};
 
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v)
 {
@@ -100,9 +109,12 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
            const __grid_constant__ CUtensorMap mapW2, const __grid_constant__ CUtensorMap mapR,
            const __grid_constant__ CUtensorMap mapO, const __grid_constant__ FfnParams q)
 {
+  using L = FLayout<FFN>;
+  constexpr int NSTG = L::NSTG;
+  constexpr int CMASK = L::R_CHUNKS - 1;        // chunk of group g in the R/H region: g & CMASK
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  FfnCtl* ctl = (FfnCtl*)(smem + DATA_BYTES);
+  FfnCtl* ctl = (FfnCtl*)(smem + L::DATA_BYTES);
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);     // provably warp-uniform: constant-bank indexing
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -134,7 +146,7 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
   const uint32_t tmem_base = ctl->tmem_base;
   pdl_wait();
 
-  const uint32_t sH = smem_u32(smem), sRing = smem_u32(smem + OFF_RING);
+  const uint32_t sH = smem_u32(smem), sRing = smem_u32(smem + L::OFF_RING);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (one lane, both CTAs)
@@ -230,7 +242,7 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     const int row = quarter * 32 + lane;          // row inside the CTA's 128-row tile
     const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16);
     // shared-memory address of 16-byte piece j of this thread's row in group g
-    auto piece = [&](int g, int j) { return sH + (uint32_t)(g * CHUNK) + stg_off(row, j); };
+    auto piece = [&](int g, int j) { return sH + (uint32_t)((g & CMASK) * CHUNK) + stg_off(row, j); };
     const uint32_t xch_mine = piece(5 + 2 * ehalf, 0), xch_peer = piece(5 + 2 * (ehalf ^ 1), 0);
     uint32_t full_ph[2] = {0u, 0u};
     uint32_t it = 0;
@@ -246,15 +258,12 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
         for (int i = 0; i < 2; i++) {
           const int g = hb * 4 + 2 * ehalf + i;
-          tma_load_2d<1>(sH + (uint32_t)(g * CHUNK + quarter * BOX), &mapR, smem_u32(&ctl->r_full[widx][hb]), g * 64, mw);
+          tma_load_2d<1>(sH + (uint32_t)((g & CMASK) * CHUNK + quarter * BOX), &mapR, smem_u32(&ctl->r_full[widx][hb]), g * 64, mw);
         }
       }
     };
-    if (!FFN && cluster_id < q.m_tiles) {          // proj+LN: the residual tile is prefetched a whole tile ahead
-      const int mw0 = (cluster_id * 2 + (int)rank) * TMR + quarter * 32;
-      load_boxes(0, mw0);
-      load_boxes(1, mw0);
-    }
+    if (!FFN && cluster_id < q.m_tiles)            // proj+LN: the residual boxes of half 0 are prefetched a tile ahead
+      load_boxes(0, (cluster_id * 2 + (int)rank) * TMR + quarter * 32);
     // The epilogue works in slabs of 32 columns (one tcgen05.ld.x32): slab j = 0..3 of half hb is columns
     // 64 * g + 32 * (j & 1) of group g = 4 hb + 2 ehalf + (j >> 1).  The TMEM load of slab j+1 is issued before slab j is
     // processed, and the per-column parameters (bias / gamma / beta: warp-uniform 16-byte loads) and the residual pieces
@@ -362,7 +371,10 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
           s1 += t1; s2 += t2;
           tmem_st32(t_row + (uint32_t)c0, v);
         }
-        if (!FFN && hb == 0 && it > 0) load_boxes(1, m_w);     // see the prefetch at the end of the tile loop
+        if (!FFN && hb == 0) {                   // proj+LN: the boxes of half 0 are consumed, those of half 1 take their place
+          __syncwarp();                          // (a whole accumulator half of MMAs before they are needed)
+          load_boxes(1, m_w);
+        }
       }
       tmem_st_wait();
       stamp();
@@ -389,6 +401,12 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
 #pragma unroll
         for (int j = 0; j < 4; j++) {
           const int g = g0 + (j >> 1), c0 = g * 64 + (j & 1) * 32;
+          if (!FFN && hb == 1 && !(j & 1)) {
+            // proj+LN: this box still holds an output box of half 0 until its TMA store has read it (stores complete in
+            // order: at most the most recent one may still be pending)
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncwarp();
+          }
           float4 gm[8], bt[8];
           if (!FFN) {
 #pragma unroll
@@ -438,7 +456,7 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
               fence_async_smem();
               __syncwarp();
               if (lane == 0 && !(q.dbg & 1)) {
-                tma_store_2d(&mapO, sH + (uint32_t)(g * CHUNK + quarter * BOX), g * 64, m_w);
+                tma_store_2d(&mapO, sH + (uint32_t)((g & CMASK) * CHUNK + quarter * BOX), g * 64, m_w);
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
               }
             }
@@ -450,9 +468,6 @@ ffn_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         // boxes free again once the stores have read them: prefetch the next tile's residual rows
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
-        // (only the boxes of half 0 now: all 128 KB at once queue in front of the operand loads of the next tile's first
-        //  accumulator half -- measured 12.5 k cycles for that half against 6 k for the second; the boxes of half 1 follow
-        //  when this warp has finished the first pass over half 0, a whole accumulator half before they are needed)
         if (t + n_clusters < q.m_tiles) load_boxes(0, ((t + n_clusters) * 2 + (int)rank) * TMR + quarter * 32);
       }
     }
@@ -521,7 +536,7 @@ int launch_ffn(const CUtensorMap& mA, const CUtensorMap& mW1, const CUtensorMap&
 {
   static bool configured = false;
   if (!configured) {
-    FPB_CUDA(cudaFuncSetAttribute(ffn_kernel<FFN>, cudaFuncAttributeMaxDynamicSharedMemorySize, FFN_SMEM));
+    FPB_CUDA(cudaFuncSetAttribute(ffn_kernel<FFN>, cudaFuncAttributeMaxDynamicSharedMemorySize, FLayout<FFN>::SMEM));
     configured = true;
   }
   int clusters = num_sms / 2;
@@ -530,7 +545,7 @@ int launch_ffn(const CUtensorMap& mA, const CUtensorMap& mW1, const CUtensorMap&
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(clusters * 2, 1, 1);
   cfg.blockDim = dim3(NTHREADS, 1, 1);
-  cfg.dynamicSmemBytes = FFN_SMEM;
+  cfg.dynamicSmemBytes = FLayout<FFN>::SMEM;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
