@@ -19,9 +19,9 @@
 // 512-column accumulator, handled as two 256-column halves with their own full / free barriers: products with a streamed A
 // operand fill half 0, then half 1 (A passes through the ring twice), so the epilogue work on half 0 runs under the MMAs
 // of half 1 and the next tile's half 0 under the second pass of this tile's half 1.  Residual rows never go through
-// registers + staging: every epilogue warp TMA-loads its own [32 rows x 64 columns] boxes into the R/H region (proj+LN: a
-// whole tile ahead; FFN: chunk by chunk as the second product releases the h tile), reads them lane = row, writes the
-// output rows over them and TMA-stores the boxes.
+// registers + staging: every epilogue warp TMA-loads its own [32 rows x 64 columns] boxes into the R/H region (proj+LN:
+// half 0 a tile ahead, half 1 when the first pass over half 0 is done; FFN: chunk by chunk as the second product releases
+// the h tile), reads them lane = row, writes the output rows over them and TMA-stores the boxes.
 #include "net_kernels.cuh"
 #include "tc_ptx.cuh"
 #include <cuda.h>
