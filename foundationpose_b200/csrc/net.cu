@@ -40,6 +40,10 @@ struct fpb_net {
   uint16_t* w_stem;        // stem weights stacked for net_stem.cu ([9][128][64], 16-bit modes only)
   cudaStream_t st2;        // refine, 16-bit modes: the rot head runs on this stream beside the trans head (fork / join by events)
   cudaEvent_t ev_fork, ev_join;
+  // 16-bit modes: the V^T projection of a self-attention block runs beside its Q|K projection (both only read the tokens);
+  // chain 0 = caller's stream (+ the ScoreNet head), chain 1 = st2
+  cudaStream_t st_v[2];
+  cudaEvent_t ev_vf[2], ev_vj[2];
   Conv conv[15];
   size_t pe;
   EncLayer head[2];   // refine: trans, rot
@@ -148,6 +152,7 @@ struct Ctx {
   size_t esz;
   const NetKernels* k;        // kernels of the operand type (fp32 mode: either table, the SIMT kernels are the same)
   void* splitk = nullptr;     // set per chunk from the workspace (Ws::splitk)
+  int chain = 0;              // which of the net's V^T side streams this context may fork onto
   const void* W(size_t off) const { return bf ? (const void*)(net->w16 + off) : (const void*)(net->w32 + off); }
   const float* F(size_t off) const { return net->w32 + off; }
   int gemm(const GemmProblem& p_in) const
@@ -314,6 +319,12 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
   uint16_t* qk = (uint16_t*)w.qkv;
   uint16_t* vt = qk + R * 2 * D;
   Lin lqk = m.in; lqk.N = 2 * D;
+  // V^T on a side stream beside Q|K (FPB_HEAD_STREAMS): for one hypothesis the two projections are two 15 us latencies
+  cudaStream_t sv = (c.net->st_v[c.chain] && head_streams()) ? c.net->st_v[c.chain] : nullptr;
+  if (sv) {
+    FPB_CUDA(cudaEventRecord(c.net->ev_vf[c.chain], c.st));
+    FPB_CUDA(cudaStreamWaitEvent(sv, c.net->ev_vf[c.chain], 0));
+  }
   RET(run_linear(c, lqk, x, R, qk, nullptr, 0, 1));
   {
     // preferred: V = X . Wv^T + bv through the operand-swapped kernel, which stores its (channel-major) accumulator
@@ -322,7 +333,11 @@ int run_self_attention(const Ctx& c, const Mha& m, const void* x, int n, Ws& w)
     t.A = x; t.W = c.W(m.in.w + (size_t)2 * D * D); t.C = vt;
     t.M = (int)R; t.N = D; t.K = D; t.Cin = D; t.pix_pitch = D; t.ldw = D; t.ldc = (int)R; t.out_bf16 = 1;
     t.shift = c.F(m.in.b + 2 * D); t.c_transposed = 1;
-    const int rc3 = c.k->tc3_gemm(t, c.st, 0);
+    const int rc3 = c.k->tc3_gemm(t, sv ? sv : c.st, 0);
+    if (sv) {                                  // join (also when the kernel did not take the shape: nothing was enqueued then)
+      FPB_CUDA(cudaEventRecord(c.net->ev_vj[c.chain], sv));
+      FPB_CUDA(cudaStreamWaitEvent(c.st, c.net->ev_vj[c.chain], 0));
+    }
     if (rc3 != FPB_ERR_UNSUPPORTED) {
       RET(rc3);
       return c.k->tc_attention(qk, vt, R, nullptr, w.ctx, n, c.st);
@@ -372,6 +387,13 @@ FPB_EXPORT int fpb_net_create(fpb_net** out, int kind, int precision, const void
     FPB_CUDA(cudaEventCreateWithFlags(&n->ev_fork, cudaEventDisableTiming));
     FPB_CUDA(cudaEventCreateWithFlags(&n->ev_join, cudaEventDisableTiming));
   }
+  if (is16(precision)) {
+    for (int i = 0; i < (n->kind == FPB_NET_REFINE ? 2 : 1); i++) {
+      FPB_CUDA(cudaStreamCreateWithFlags(&n->st_v[i], cudaStreamNonBlocking));
+      FPB_CUDA(cudaEventCreateWithFlags(&n->ev_vf[i], cudaEventDisableTiming));
+      FPB_CUDA(cudaEventCreateWithFlags(&n->ev_vj[i], cudaEventDisableTiming));
+    }
+  }
   FPB_CUDA(cudaStreamSynchronize(st));
   *out = n;
   return FPB_OK;
@@ -384,6 +406,8 @@ FPB_EXPORT int fpb_net_destroy(fpb_net* n)
   cudaFree(n->w16);
   cudaFree(n->w_stem);
   if (n->st2) { cudaStreamDestroy(n->st2); cudaEventDestroy(n->ev_fork); cudaEventDestroy(n->ev_join); }
+  for (int i = 0; i < 2; i++)
+    if (n->st_v[i]) { cudaStreamDestroy(n->st_v[i]); cudaEventDestroy(n->ev_vf[i]); cudaEventDestroy(n->ev_vj[i]); }
   delete n;
   return FPB_OK;
 }
@@ -472,6 +496,7 @@ static int refine_forward_impl(const fpb_net* net, const void* AB, int N, void* 
       w2.scores = (float*)w.c1; w2.pooled = (float*)w.c2;
       Ctx c2 = c;
       c2.st = net->st2;
+      c2.chain = 1;
       c2.splitk = c.splitk ? w.splitk2 : nullptr;
       FPB_CUDA(cudaEventRecord(net->ev_fork, c.st));
       FPB_CUDA(cudaStreamWaitEvent(net->st2, net->ev_fork, 0));
